@@ -1,0 +1,111 @@
+"""ctypes binding of libcoslam_b200.so (include/coslam_b200.h).
+
+PyTorch is plumbing here: it owns device memory and streams; every call below passes raw device pointers and the
+current CUDA stream handle across the C ABI.  There is NO fallback: if the library is missing or a call fails, a
+RuntimeError is raised.
+"""
+import ctypes
+import os
+
+import torch
+
+from . import build as _build
+
+MAX_LEVELS = 16
+ABI_VERSION = 3
+
+c_f32p = ctypes.c_void_p
+c_stream = ctypes.c_void_p
+
+
+class GridCfg(ctypes.Structure):
+    _fields_ = [('n_levels', ctypes.c_uint32), ('n_features_per_level', ctypes.c_uint32),
+                ('log2_hashmap_size', ctypes.c_uint32), ('base_resolution', ctypes.c_uint32),
+                ('per_level_scale', ctypes.c_float)]
+
+
+class Grid(ctypes.Structure):
+    _fields_ = [('n_levels', ctypes.c_uint32), ('n_features', ctypes.c_uint32),
+                ('offset', ctypes.c_uint32 * (MAX_LEVELS + 1)), ('res', ctypes.c_uint32 * MAX_LEVELS),
+                ('hashed', ctypes.c_uint32 * MAX_LEVELS), ('scale', ctypes.c_float * MAX_LEVELS)]
+
+
+class Scene(ctypes.Structure):
+    _fields_ = [('grid', Grid), ('bb_lo', ctypes.c_float * 3), ('bb_ext', ctypes.c_float * 3),
+                ('normalise', ctypes.c_uint32), ('n_bins', ctypes.c_uint32)]
+
+
+class RenderCfg(ctypes.Structure):
+    _fields_ = [('n_uniform', ctypes.c_uint32), ('n_guided', ctypes.c_uint32), ('perturb', ctypes.c_uint32),
+                ('rgb_missing_nz', ctypes.c_uint32), ('trunc', ctypes.c_float), ('trunc_sc', ctypes.c_float),
+                ('depth_trunc', ctypes.c_float), ('white_bkgd', ctypes.c_uint32)]
+
+
+class Mlp(ctypes.Structure):
+    _fields_ = [('w_sdf0', ctypes.c_void_p), ('w_sdf1', ctypes.c_void_p), ('w_col0', ctypes.c_void_p),
+                ('w_col1', ctypes.c_void_p)]
+
+
+EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
+           'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays',
+           'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd',
+           'cb200_debug_positions']
+
+_lib = None
+
+
+def library_path():
+    return _build.LIB_PATH
+
+
+def load():
+    """Loads (building first if the in-tree .so is stale and nvcc is present) and returns the CDLL."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if _build.needs_build():
+        if os.path.isfile(_build.NVCC):
+            _build.build()
+        elif not os.path.isfile(path):
+            raise RuntimeError('coslam_b200: %s is missing and nvcc is not available to build it; '
+                               'there is no fallback path' % path)
+    lib = ctypes.CDLL(path)
+    lib.cb200_last_error.restype = ctypes.c_char_p
+    for name in EXPORTS:
+        if not hasattr(lib, name):
+            raise RuntimeError('coslam_b200: %s does not export %s' % (path, name))
+    if lib.cb200_abi_version() != ABI_VERSION:
+        raise RuntimeError('coslam_b200: ABI version mismatch (library %d, binding %d); rebuild with '
+                           '`python -m coslam_b200.build --force`' % (lib.cb200_abi_version(), ABI_VERSION))
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().cb200_last_error().decode('utf-8', 'replace')
+        raise RuntimeError('coslam_b200 %s failed (%d): %s' % (what, rc, msg))
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL).  The tensor must be contiguous CUDA memory."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError('coslam_b200: expected a CUDA tensor (there is no CPU path)')
+    if not t.is_contiguous():
+        raise RuntimeError('coslam_b200: internal error, non-contiguous tensor reached the C ABI')
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def grid_meta(n_levels, n_features, log2_hashmap_size, base_resolution, per_level_scale):
+    """Host-side geometry; works without a GPU."""
+    cfg = GridCfg(n_levels, n_features, log2_hashmap_size, base_resolution, float(per_level_scale))
+    g = Grid()
+    check(load().cb200_grid_meta(ctypes.byref(cfg), ctypes.byref(g)), 'grid_meta')
+    return g

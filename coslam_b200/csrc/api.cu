@@ -1,0 +1,255 @@
+// extern "C" surface of libcoslam_b200.so (include/coslam_b200.h): argument validation, host-side grid geometry and
+// kernel launches.  No allocation, no synchronisation, no default-stream work.
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "args.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_result(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    return fail((int)e, "%s: %s", what, cudaGetErrorString(e));
+}
+
+#define CB_REQUIRE(cond, ...)                  \
+    do {                                       \
+        if (!(cond)) return fail(-1, __VA_ARGS__); \
+    } while (0)
+
+int check_grid(const cb200_grid* g) {
+    CB_REQUIRE(g != nullptr, "grid is NULL");
+    CB_REQUIRE(g->n_levels >= 1 && g->n_levels <= CB200_MAX_LEVELS, "n_levels %u not in [1,%d]", g->n_levels, CB200_MAX_LEVELS);
+    CB_REQUIRE(g->n_features == 2, "n_features_per_level %u unsupported (kernels are written for 2)", g->n_features);
+    return 0;
+}
+
+int check_fused_scene(const cb200_scene* s) {
+    CB_REQUIRE(s != nullptr, "scene is NULL");
+    if (int rc = check_grid(&s->grid)) return rc;
+    CB_REQUIRE(s->grid.n_levels == CB200_MAX_LEVELS, "fused decoder expects %d grid levels (got %u)", CB200_MAX_LEVELS, s->grid.n_levels);
+    CB_REQUIRE(s->n_bins == 16, "fused decoder expects OneBlob n_bins == 16 (got %u)", s->n_bins);
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cb200_abi_version(void) { return CB200_ABI_VERSION; }
+
+const char* cb200_last_error(void) { return g_err; }
+
+int cb200_device_sm_count(void) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+    return sms;
+}
+
+// tiny-cuda-nn grid.h: grid_scale / grid_resolution and the offset table of the GridEncodingTemplated constructor
+// (SURVEY.md section 9.1-9.2).  exp2f/log2f are taken correctly rounded (double evaluation rounded once).
+int cb200_grid_meta(const cb200_grid_cfg* cfg, cb200_grid* grid) {
+    CB_REQUIRE(cfg && grid, "cfg/grid is NULL");
+    CB_REQUIRE(cfg->n_levels >= 1 && cfg->n_levels <= CB200_MAX_LEVELS, "n_levels %u not in [1,%d]", cfg->n_levels, CB200_MAX_LEVELS);
+    CB_REQUIRE(cfg->n_features_per_level == 2, "n_features_per_level %u unsupported", cfg->n_features_per_level);
+    CB_REQUIRE(cfg->log2_hashmap_size >= 3 && cfg->log2_hashmap_size <= 28, "log2_hashmap_size %u out of range", cfg->log2_hashmap_size);
+    CB_REQUIRE(cfg->per_level_scale > 0.f && cfg->base_resolution >= 1, "bad base_resolution / per_level_scale");
+    grid->n_levels = cfg->n_levels;
+    grid->n_features = cfg->n_features_per_level;
+    const float log2_pls = (float)log2((double)cfg->per_level_scale);
+    const uint32_t cap = 1u << cfg->log2_hashmap_size;
+    uint64_t offset = 0;
+    for (uint32_t l = 0; l < CB200_MAX_LEVELS; ++l) {
+        if (l >= cfg->n_levels) {
+            grid->scale[l] = 0.f; grid->res[l] = 1; grid->hashed[l] = 0; grid->offset[l + 1] = (uint32_t)offset;
+            continue;
+        }
+        const float arg = (float)l * log2_pls;
+        const float e = (float)exp2((double)arg);
+        const float scale = e * (float)cfg->base_resolution - 1.0f;
+        const uint32_t res = (uint32_t)ceilf(scale) + 1u;
+        const uint32_t max_params = UINT32_MAX / 2;
+        uint32_t n = powf((float)res, 3.0f) > (float)max_params ? max_params : res * res * res;
+        n = (n + 7u) / 8u * 8u;
+        if (n > cap) n = cap;
+        // grid_index: the dense stride walk stops as soon as stride > size; a level is hashed iff it stopped early
+        uint32_t stride = 1;
+        for (int d = 0; d < 3 && stride <= n; ++d) stride *= res;
+        grid->scale[l] = scale;
+        grid->res[l] = res;
+        grid->hashed[l] = n < stride ? 1u : 0u;
+        grid->offset[l] = (uint32_t)offset;
+        offset += n;
+        CB_REQUIRE(offset < (1ull << 31), "grid too large");
+        grid->offset[l + 1] = (uint32_t)offset;
+    }
+    return 0;
+}
+
+int cb200_hash_fwd(const cb200_grid* grid, const float* x, const float* table, int64_t n_points, float* out, void* stream) {
+    if (int rc = check_grid(grid)) return rc;
+    CB_REQUIRE(n_points >= 0 && (n_points == 0 || (x && table && out)), "hash_fwd: NULL buffer");
+    return cuda_result(cb200::launch_hash_fwd(cb200::make_scene_dev(*grid), x, table, n_points, out, (cudaStream_t)stream), "hash_fwd");
+}
+
+int cb200_hash_bwd(const cb200_grid* grid, const float* x, const float* table, const float* dy, int64_t n_points, float* dtable, float* dx,
+                   void* stream) {
+    if (int rc = check_grid(grid)) return rc;
+    CB_REQUIRE(n_points >= 0 && (n_points == 0 || (x && dy)), "hash_bwd: NULL buffer");
+    CB_REQUIRE(dx == nullptr || table != nullptr, "hash_bwd: dx needs the table");
+    return cuda_result(cb200::launch_hash_bwd(cb200::make_scene_dev(*grid), x, table, dy, n_points, dtable, dx, (cudaStream_t)stream), "hash_bwd");
+}
+
+int cb200_hash_indices(const cb200_grid* grid, const float* x, int64_t n_points, uint32_t* idx, void* stream) {
+    if (int rc = check_grid(grid)) return rc;
+    CB_REQUIRE(n_points >= 0 && (n_points == 0 || (x && idx)), "hash_indices: NULL buffer");
+    return cuda_result(cb200::launch_hash_indices(cb200::make_scene_dev(*grid), x, n_points, idx, (cudaStream_t)stream), "hash_indices");
+}
+
+int cb200_oneblob_fwd(const float* x, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* out, void* stream) {
+    CB_REQUIRE(n_points >= 0 && n_dims >= 1 && n_bins >= 1, "oneblob_fwd: bad sizes");
+    CB_REQUIRE(n_points == 0 || (x && out), "oneblob_fwd: NULL buffer");
+    return cuda_result(cb200::launch_oneblob_fwd(x, n_points * n_dims, (int)n_bins, out, (cudaStream_t)stream), "oneblob_fwd");
+}
+
+int cb200_oneblob_bwd(const float* x, const float* dy, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* dx, void* stream) {
+    CB_REQUIRE(n_points >= 0 && n_dims >= 1 && n_bins >= 1, "oneblob_bwd: bad sizes");
+    CB_REQUIRE(n_points == 0 || (x && dy && dx), "oneblob_bwd: NULL buffer");
+    return cuda_result(cb200::launch_oneblob_bwd(x, dy, n_points * n_dims, (int)n_bins, dx, (cudaStream_t)stream), "oneblob_bwd");
+}
+
+int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform, const float* lin_guided,
+                      const float* lin_nodepth, const float* noise, uint64_t seed, int64_t n_rays, float* z_vals, int64_t* counts,
+                      void* stream) {
+    CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
+    const int S = (int)(cfg->n_uniform + cfg->n_guided);
+    CB_REQUIRE(cfg->n_guided >= 1 && S <= 256, "n_samples_d + n_range_d = %d must be in [1,256] with n_range_d >= 1", S);
+    CB_REQUIRE(n_rays >= 0, "negative ray count");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(target_d && lin_guided && lin_nodepth && z_vals && (cfg->n_uniform == 0 || lin_uniform), "sample_rays: NULL buffer");
+    cb200::SampleArgs a{};
+    a.target_d = target_d; a.lin_uniform = lin_uniform; a.lin_guided = lin_guided; a.lin_nodepth = lin_nodepth;
+    a.noise = noise; a.seed = seed; a.n_rays = n_rays; a.z_vals = z_vals;
+    a.counts = reinterpret_cast<unsigned long long*>(counts);
+    a.n_uniform = (int)cfg->n_uniform; a.n_guided = (int)cfg->n_guided; a.perturb = (int)cfg->perturb;
+    a.trunc_sc = cfg->trunc_sc; a.depth_trunc = cfg->depth_trunc;
+    return cuda_result(cb200::launch_sample_rays(a, (cudaStream_t)stream), "sample_rays");
+}
+
+static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
+                            const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples) {
+    if (int rc = check_fused_scene(scene)) return rc;
+    CB_REQUIRE(table && mlp && mlp->w_sdf0 && mlp->w_sdf1 && mlp->w_col0 && mlp->w_col1, "points: NULL table / weights");
+    CB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples < (1 << 30), "points: bad sizes");
+    CB_REQUIRE((pts != nullptr) != (rays_o != nullptr), "points: pass either pts or (rays_o, rays_d, z_vals)");
+    CB_REQUIRE(rays_o == nullptr || (rays_d && z_vals), "points: ray mode needs rays_d and z_vals");
+    a.scene = cb200::make_scene_dev(*scene);
+    a.table = reinterpret_cast<const float2*>(table);
+    a.w1 = mlp->w_sdf0; a.w2 = mlp->w_sdf1; a.w3 = mlp->w_col0; a.w4 = mlp->w_col1;
+    a.pts = pts; a.rays_o = rays_o; a.rays_d = rays_d; a.z = z_vals;
+    a.n_points = n_rays * n_samples;
+    a.n_samples = (int)n_samples;
+    return 0;
+}
+
+int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                     const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
+                     uint32_t* act_mask, int sdf_only, void* stream) {
+    cb200::PointsArgs a{};
+    if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
+    if (a.n_points == 0) return 0;
+    a.raw = raw; a.geo = geo; a.act_mask = act_mask; a.sdf_only = sdf_only;
+    return cuda_result(cb200::launch_points_fwd(a, (cudaStream_t)stream), "points_fwd");
+}
+
+int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                     const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
+                     const float* d_geo, const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
+                     float* d_rays_o, float* d_rays_d, int sdf_only, void* stream) {
+    cb200::PointsArgs a{};
+    if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
+    if (a.n_points == 0) return 0;
+    CB_REQUIRE(d_raw && act_mask, "points_bwd: d_raw / act_mask is NULL");
+    CB_REQUIRE((d_rays_o == nullptr) == (d_rays_d == nullptr), "points_bwd: d_rays_o and d_rays_d go together");
+    CB_REQUIRE(d_rays_o == nullptr || rays_o != nullptr, "points_bwd: ray gradients need ray mode");
+    a.d_raw = d_raw; a.d_geo = d_geo; a.act_mask = const_cast<uint32_t*>(act_mask); a.sdf_only = sdf_only;
+    a.dtable = reinterpret_cast<float2*>(dtable);
+    if (d_mlp) {
+        CB_REQUIRE(d_mlp->w_sdf0 && d_mlp->w_sdf1 && d_mlp->w_col0 && d_mlp->w_col1, "points_bwd: partial weight-gradient set");
+        a.dw1 = d_mlp->w_sdf0; a.dw2 = d_mlp->w_sdf1; a.dw3 = d_mlp->w_col0; a.dw4 = d_mlp->w_col1;
+    }
+    a.d_pts = d_pts; a.d_rays_o = d_rays_o; a.d_rays_d = d_rays_d;
+    return cuda_result(cb200::launch_points_bwd(a, (cudaStream_t)stream), "points_bwd");
+}
+
+static int fill_render_args(cb200::RenderArgs& a, const cb200_render_cfg* cfg, const float* raw, const float* z_vals,
+                            const float* target_rgb, const float* target_d, int64_t n_rays, int64_t n_samples) {
+    CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
+    CB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples <= 256, "render: n_samples %lld must be in [1,256]", (long long)n_samples);
+    CB_REQUIRE(n_rays == 0 || (raw && z_vals), "render: NULL raw / z_vals");
+    a.raw = raw; a.z_vals = z_vals; a.target_rgb = target_rgb; a.target_d = target_d;
+    a.n_rays = n_rays; a.n_samples = (int)n_samples;
+    a.trunc = cfg->trunc; a.trunc_sc = cfg->trunc_sc; a.depth_trunc = cfg->depth_trunc;
+    a.rgb_missing_nz = (int)cfg->rgb_missing_nz; a.white_bkgd = (int)cfg->white_bkgd;
+    return 0;
+}
+
+int cb200_render_fwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb, const float* target_d,
+                     int64_t n_rays, int64_t n_samples, float* rgb, float* depth, float* depth_var, float* disp, float* acc,
+                     float* weights, double* loss_sums, void* stream) {
+    cb200::RenderArgs a{};
+    if (int rc = fill_render_args(a, cfg, raw, z_vals, target_rgb, target_d, n_rays, n_samples)) return rc;
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(loss_sums == nullptr || (target_rgb && target_d), "render_fwd: the loss head needs target_rgb and target_d");
+    a.rgb = rgb; a.depth = depth; a.depth_var = depth_var; a.disp = disp; a.acc = acc; a.weights = weights; a.loss_sums = loss_sums;
+    return cuda_result(cb200::launch_render_fwd(a, (cudaStream_t)stream), "render_fwd");
+}
+
+int cb200_loss_finish(const double* loss_sums, const int64_t* counts, int64_t n_rays_total, int64_t n_samples, float* losses, float* coef,
+                      void* stream) {
+    CB_REQUIRE(loss_sums && counts && losses && coef, "loss_finish: NULL buffer");
+    return cuda_result(cb200::launch_loss_finish(loss_sums, reinterpret_cast<const long long*>(counts), n_rays_total, n_samples, losses, coef,
+                                                 (cudaStream_t)stream),
+                       "loss_finish");
+}
+
+int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb, const float* target_d,
+                     int64_t n_rays, int64_t n_samples, const cb200_loss_grads* g_loss, const float* coef, const float* g_rgb, const float* g_depth,
+                     float* d_raw, void* stream) {
+    cb200::RenderArgs a{};
+    if (int rc = fill_render_args(a, cfg, raw, z_vals, target_rgb, target_d, n_rays, n_samples)) return rc;
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(d_raw != nullptr, "render_bwd: d_raw is NULL");
+    CB_REQUIRE(g_loss == nullptr || (coef && target_rgb && target_d), "render_bwd: loss gradients need coef and the targets");
+    if (g_loss) {
+        a.g_loss[0] = g_loss->rgb; a.g_loss[1] = g_loss->depth; a.g_loss[2] = g_loss->sdf; a.g_loss[3] = g_loss->fs;
+        a.has_loss = (g_loss->rgb || g_loss->depth || g_loss->sdf || g_loss->fs) ? 1 : 0;
+    }
+    a.coef = coef; a.g_rgb = g_rgb; a.g_depth = g_depth; a.d_raw = d_raw;
+    return cuda_result(cb200::launch_render_bwd(a, (cudaStream_t)stream), "render_bwd");
+}
+
+int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
+                          int64_t n_samples, float* pts, float* x, void* stream) {
+    CB_REQUIRE(scene && rays_o && rays_d && z_vals && pts && x, "debug_positions: NULL buffer");
+    cb200::PointsArgs a{};
+    a.scene = cb200::make_scene_dev(*scene);
+    a.rays_o = rays_o; a.rays_d = rays_d; a.z = z_vals;
+    a.n_points = n_rays * n_samples; a.n_samples = (int)n_samples;
+    if (a.n_points == 0) return 0;
+    return cuda_result(cb200::launch_debug_positions(a, pts, x, (cudaStream_t)stream), "debug_positions");
+}
+
+}  // extern "C"

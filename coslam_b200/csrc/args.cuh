@@ -1,0 +1,83 @@
+// Kernel argument blocks and host launchers shared between the kernels (*.cu) and the C ABI (api.cu).
+#pragma once
+#include "common.cuh"
+
+namespace cb200 {
+
+struct PointsArgs {
+    SceneDev scene;
+    const float2* table;
+    const float *w1, *w2, *w3, *w4;
+    const float* pts;
+    const float* rays_o;
+    const float* rays_d;
+    const float* z;
+    int64_t n_points;
+    int n_samples;
+    int sdf_only;
+    // forward outputs
+    float* raw;
+    float* geo;
+    uint32_t* act_mask;
+    // backward
+    const float* d_raw;
+    const float* d_geo;
+    float2* dtable;
+    float *dw1, *dw2, *dw3, *dw4;
+    float* d_pts;
+    float* d_rays_o;
+    float* d_rays_d;
+};
+
+struct SampleArgs {
+    const float* target_d;
+    const float* lin_uniform;
+    const float* lin_guided;
+    const float* lin_nodepth;
+    const float* noise;
+    uint64_t seed;
+    int64_t n_rays;
+    float* z_vals;
+    unsigned long long* counts;
+    int n_uniform, n_guided;
+    int perturb;
+    float trunc_sc, depth_trunc;
+};
+
+struct RenderArgs {
+    const float* raw;          // [N,S,4]
+    const float* z_vals;       // [N,S]
+    const float* target_rgb;   // [N,3]  (loss head only)
+    const float* target_d;     // [N]
+    int64_t n_rays;
+    int n_samples;
+    float trunc, trunc_sc, depth_trunc;
+    int rgb_missing_nz, white_bkgd;
+    // forward outputs
+    float *rgb, *depth, *depth_var, *disp, *acc, *weights;
+    double* loss_sums;
+    // backward inputs / outputs
+    const float* g_loss[4];    // upstream gradients of rgb/depth/sdf/fs losses (each nullable)
+    int has_loss;              // loss head participates in the backward
+    const float* coef;         // [4] d loss_k / d sum_k
+    const float* g_rgb;        // [N,3]
+    const float* g_depth;      // [N]
+    float* d_raw;              // [N,S,4]
+};
+
+cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st);
+cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st);
+cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st);
+cudaError_t launch_loss_finish(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
+                               float* losses, float* coef, cudaStream_t st);
+cudaError_t launch_points_fwd(const PointsArgs& a, cudaStream_t st);
+cudaError_t launch_points_bwd(const PointsArgs& a, cudaStream_t st);
+cudaError_t launch_debug_positions(const PointsArgs& a, float* pts_out, float* x_out, cudaStream_t st);
+cudaError_t launch_hash_fwd(const SceneDev& sc, const float* x, const float* table, int64_t n, float* out, cudaStream_t st);
+cudaError_t launch_hash_indices(const SceneDev& sc, const float* x, int64_t n, uint32_t* idx, cudaStream_t st);
+cudaError_t launch_hash_bwd(const SceneDev& sc, const float* x, const float* table, const float* dy, int64_t n, float* dtable, float* dx,
+                            cudaStream_t st);
+cudaError_t launch_oneblob_fwd(const float* x, int64_t n_flat, int n_bins, float* out, cudaStream_t st);
+cudaError_t launch_oneblob_bwd(const float* x, const float* dy, int64_t n_flat, int n_bins, float* dx, cudaStream_t st);
+
+}  // namespace cb200

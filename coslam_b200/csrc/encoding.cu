@@ -1,0 +1,162 @@
+// Stand-alone encodings behind the tinycudann-compatible lower boundary (model/encodings.py:31-46, 61-71) and the
+// feature-grid smoothness term (coslam.py:251-274 -> model/scene_rep.py:126-139 query_sdf(embed=True)).
+// The fused per-point kernels in points.cu share the index / interpolation helpers of common.cuh with these.
+#include "args.cuh"
+
+namespace cb200 {
+
+// thread (p, l): one level of one point, like tiny-cuda-nn's kernel_grid -- 8 independent gathers per thread and
+// blockIdx.y = level keeps each CTA inside one level's slice of the table (L1/L2 locality on the coarse levels).
+__global__ void __launch_bounds__(256) hash_fwd_kernel(SceneDev sc, const float* __restrict__ x, const float2* __restrict__ table,
+                                                       int64_t n_points, float* __restrict__ out) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int l = blockIdx.y;
+    if (p >= n_points) return;
+    const float xp[3] = {x[p * 3], x[p * 3 + 1], x[p * 3 + 2]};
+    const uint32_t size = sc.offset[l + 1] - sc.offset[l];
+    uint32_t cell[3];
+    float w[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) grid_pos(sc.scale[l], xp[d], cell[d], w[d]);
+    float2 v[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const uint32_t idx = grid_index(sc.hashed[l] != 0, size, sc.res[l], cell[0] + (c & 1), cell[1] + ((c >> 1) & 1), cell[2] + (c >> 2));
+        v[c] = ldg_f2(table + sc.offset[l] + idx);
+    }
+    float f0 = 0.f, f1 = 0.f;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const float wc = ((c & 1) ? w[0] : 1.f - w[0]) * ((c & 2) ? w[1] : 1.f - w[1]) * ((c & 4) ? w[2] : 1.f - w[2]);
+        f0 = fmaf(wc, v[c].x, f0);
+        f1 = fmaf(wc, v[c].y, f1);
+    }
+    reinterpret_cast<float2*>(out)[p * sc.n_levels + l] = make_float2(f0, f1);
+}
+
+__global__ void __launch_bounds__(256) hash_indices_kernel(SceneDev sc, const float* __restrict__ x, int64_t n_points, uint32_t* __restrict__ idx_out) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int l = blockIdx.y;
+    if (p >= n_points) return;
+    const uint32_t size = sc.offset[l + 1] - sc.offset[l];
+    uint32_t cell[3];
+    float w[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) grid_pos(sc.scale[l], x[p * 3 + d], cell[d], w[d]);
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+        idx_out[(p * sc.n_levels + l) * 8 + c] =
+            grid_index(sc.hashed[l] != 0, size, sc.res[l], cell[0] + (c & 1), cell[1] + ((c >> 1) & 1), cell[2] + (c >> 2));
+}
+
+// backward: thread per point, loop over levels (dx needs the sum over levels; the scatter is one v2 reduction/corner)
+__global__ void __launch_bounds__(256) hash_bwd_kernel(SceneDev sc, const float* __restrict__ x, const float2* __restrict__ table,
+                                                       const float* __restrict__ dy, int64_t n_points, float2* dtable, float* __restrict__ dx_out) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_points) return;
+    const float xp[3] = {x[p * 3], x[p * 3 + 1], x[p * 3 + 2]};
+    float dx[3] = {0.f, 0.f, 0.f};
+    const int L = sc.n_levels;
+    for (int l = 0; l < L; ++l) {
+        const uint32_t size = sc.offset[l + 1] - sc.offset[l];
+        uint32_t cell[3];
+        float w[3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) grid_pos(sc.scale[l], xp[d], cell[d], w[d]);
+        const float2 g = reinterpret_cast<const float2*>(dy)[p * L + l];
+        uint32_t idx[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            idx[c] = sc.offset[l] + grid_index(sc.hashed[l] != 0, size, sc.res[l], cell[0] + (c & 1), cell[1] + ((c >> 1) & 1), cell[2] + (c >> 2));
+        if (dx_out) {
+            float s[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const float2 v = ldg_f2(table + idx[c]);
+                s[c] = v.x * g.x + v.y * g.y;
+            }
+            const float w0 = w[0], w1 = w[1], w2 = w[2];
+            dx[0] += sc.scale[l] * ((1.f - w1) * (1.f - w2) * (s[1] - s[0]) + w1 * (1.f - w2) * (s[3] - s[2]) +
+                                    (1.f - w1) * w2 * (s[5] - s[4]) + w1 * w2 * (s[7] - s[6]));
+            dx[1] += sc.scale[l] * ((1.f - w0) * (1.f - w2) * (s[2] - s[0]) + w0 * (1.f - w2) * (s[3] - s[1]) +
+                                    (1.f - w0) * w2 * (s[6] - s[4]) + w0 * w2 * (s[7] - s[5]));
+            dx[2] += sc.scale[l] * ((1.f - w0) * (1.f - w1) * (s[4] - s[0]) + w0 * (1.f - w1) * (s[5] - s[1]) +
+                                    (1.f - w0) * w1 * (s[6] - s[2]) + w0 * w1 * (s[7] - s[3]));
+        }
+        if (dtable) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const float wc = ((c & 1) ? w[0] : 1.f - w[0]) * ((c & 2) ? w[1] : 1.f - w[1]) * ((c & 4) ? w[2] : 1.f - w[2]);
+                red_add_f2(dtable + idx[c], wc * g.x, wc * g.y);
+            }
+        }
+    }
+    if (dx_out) {
+        dx_out[p * 3 + 0] = dx[0];
+        dx_out[p * 3 + 1] = dx[1];
+        dx_out[p * 3 + 2] = dx[2];
+    }
+}
+
+// OneBlob: thread per (point, dim)
+__global__ void __launch_bounds__(256) oneblob_fwd_kernel(const float* __restrict__ x, int64_t n, int n_bins, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // flat (point, dim)
+    if (i >= n) return;
+    const float xv = x[i];
+    const float nb = (float)n_bins;
+    const float f_first = blob_edge_cdf(0.f, xv, nb);
+    float f_prev = f_first;
+    for (int b = 0; b < n_bins; ++b) {
+        const float f_next = (b == n_bins - 1) ? f_first + 1.0f : blob_edge_cdf((float)(b + 1) / nb, xv, nb);
+        out[i * n_bins + b] = f_next - f_prev;
+        f_prev = f_next;
+    }
+}
+
+__global__ void __launch_bounds__(256) oneblob_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, int64_t n, int n_bins,
+                                                          float* __restrict__ dx) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float xv = x[i];
+    const float nb = (float)n_bins;
+    const float k_first = blob_edge_pdf(0.f, xv, nb);
+    float k_prev = k_first, acc = 0.f;
+    for (int b = 0; b < n_bins; ++b) {
+        const float k_next = (b == n_bins - 1) ? k_first : blob_edge_pdf((float)(b + 1) / nb, xv, nb);
+        acc += dy[i * n_bins + b] * (k_prev - k_next);
+        k_prev = k_next;
+    }
+    dx[i] = acc;
+}
+
+cudaError_t launch_hash_fwd(const SceneDev& sc, const float* x, const float* table, int64_t n, float* out, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    dim3 grid((unsigned)((n + 255) / 256), sc.n_levels);
+    hash_fwd_kernel<<<grid, 256, 0, st>>>(sc, x, reinterpret_cast<const float2*>(table), n, out);
+    return cudaGetLastError();
+}
+cudaError_t launch_hash_indices(const SceneDev& sc, const float* x, int64_t n, uint32_t* idx, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    dim3 grid((unsigned)((n + 255) / 256), sc.n_levels);
+    hash_indices_kernel<<<grid, 256, 0, st>>>(sc, x, n, idx);
+    return cudaGetLastError();
+}
+cudaError_t launch_hash_bwd(const SceneDev& sc, const float* x, const float* table, const float* dy, int64_t n, float* dtable, float* dx,
+                            cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    hash_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sc, x, reinterpret_cast<const float2*>(table), dy, n,
+                                                                reinterpret_cast<float2*>(dtable), dx);
+    return cudaGetLastError();
+}
+cudaError_t launch_oneblob_fwd(const float* x, int64_t n_flat, int n_bins, float* out, cudaStream_t st) {
+    if (n_flat == 0) return cudaSuccess;
+    oneblob_fwd_kernel<<<(unsigned)((n_flat + 255) / 256), 256, 0, st>>>(x, n_flat, n_bins, out);
+    return cudaGetLastError();
+}
+cudaError_t launch_oneblob_bwd(const float* x, const float* dy, int64_t n_flat, int n_bins, float* dx, cudaStream_t st) {
+    if (n_flat == 0) return cudaSuccess;
+    oneblob_bwd_kernel<<<(unsigned)((n_flat + 255) / 256), 256, 0, st>>>(x, dy, n_flat, n_bins, dx);
+    return cudaGetLastError();
+}
+
+}  // namespace cb200

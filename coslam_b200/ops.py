@@ -1,0 +1,390 @@
+"""Host side of the fused path: scene/render parameter blocks, thin wrappers over the C ABI and the autograd glue.
+
+Every compute call goes through libcoslam_b200.so (coslam_b200/_lib.py); torch only allocates buffers and records
+the autograd graph.  Reference lines each piece stands in for are cited at the wrappers.
+"""
+import ctypes
+import math
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream
+
+N_GEO = 15
+
+
+def _f32c(t):
+    """fp32 + contiguous view of a CUDA tensor (copy only when needed)."""
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+class LossGrads(ctypes.Structure):
+    _fields_ = [('rgb', ctypes.c_void_p), ('depth', ctypes.c_void_p), ('sdf', ctypes.c_void_p), ('fs', ctypes.c_void_p)]
+
+
+class SceneSpec(object):
+    """Plain-python description of the scene + sampling/loss parameters the kernels need.
+
+    Holds no device pointers and no ctypes objects in its pickled state, so the owning nn.Module survives
+    share_memory(), copy.deepcopy and spawn-pickling (coslam_mp.py:52, mp_slam/tracker.py:27); the ctypes blocks and
+    the per-device linspace constants are rebuilt lazily in each process.
+    """
+
+    def __init__(self, config, bound_box, grid_cfg, n_bins):
+        t, cam = config['training'], config['cam']
+        bb = torch.as_tensor(bound_box, dtype=torch.float32).detach().cpu()
+        self.bb_lo = [float(v) for v in bb[:, 0]]
+        self.bb_ext = [float(v) for v in (bb[:, 1] - bb[:, 0])]          # fp32 subtraction, model/scene_rep.py:186
+        self.normalise = bool(config['grid']['tcnn_encoding'])
+        self.grid_cfg = dict(grid_cfg)
+        self.n_bins = int(n_bins)
+        self.n_uniform = int(t['n_samples_d'])
+        self.n_guided = int(t['n_range_d'])
+        self.range_d = t['range_d']
+        self.near, self.far = cam['near'], cam['far']
+        self.perturb = float(t['perturb']) > 0.
+        self.rgb_missing_nz = bool(t['rgb_missing'])
+        self.trunc = float(t['trunc'])
+        self.trunc_sc = float(t['trunc']) * float(config['data']['sc_factor'])   # python double product, like the reference
+        self.depth_trunc = float(cam['depth_trunc'])
+        self.white_bkgd = bool(t['white_bkgd'])
+        self.n_importance = int(t.get('n_importance', 0))
+        self._cache = {}
+
+    def __getstate__(self):
+        d = dict(self.__dict__)
+        d['_cache'] = {}
+        return d
+
+    @property
+    def n_samples(self):
+        return self.n_uniform + self.n_guided
+
+    def grid(self):
+        g = self._cache.get('grid')
+        if g is None:
+            c = self.grid_cfg
+            g = _lib.grid_meta(c['n_levels'], c['n_features_per_level'], c['log2_hashmap_size'], c['base_resolution'],
+                               c['per_level_scale'])
+            self._cache['grid'] = g
+        return g
+
+    def n_table_params(self):
+        g = self.grid()
+        return int(g.offset[g.n_levels]) * int(g.n_features)
+
+    def scene(self):
+        s = self._cache.get('scene')
+        if s is None:
+            s = _lib.Scene()
+            s.grid = self.grid()
+            for i in range(3):
+                s.bb_lo[i] = self.bb_lo[i]
+                s.bb_ext[i] = self.bb_ext[i]
+            s.normalise = 1 if self.normalise else 0
+            s.n_bins = self.n_bins
+            self._cache['scene'] = s
+        return s
+
+    def scene_unnormalised(self):
+        """Same grid, inputs already in the unit cube (query_sdf / query_color_sdf take normalised points)."""
+        s = self._cache.get('scene_raw')
+        if s is None:
+            s = _lib.Scene()
+            s.grid = self.grid()
+            for i in range(3):
+                s.bb_lo[i] = 0.0
+                s.bb_ext[i] = 1.0
+            s.normalise = 0
+            s.n_bins = self.n_bins
+            self._cache['scene_raw'] = s
+        return s
+
+    def render_cfg(self, perturb=None):
+        key = ('rcfg', perturb)
+        r = self._cache.get(key)
+        if r is None:
+            r = _lib.RenderCfg()
+            r.n_uniform, r.n_guided = self.n_uniform, self.n_guided
+            r.perturb = 1 if (self.perturb if perturb is None else perturb) else 0
+            r.rgb_missing_nz = 1 if self.rgb_missing_nz else 0
+            r.trunc = self.trunc
+            r.trunc_sc = self.trunc_sc
+            r.depth_trunc = self.depth_trunc
+            r.white_bkgd = 1 if self.white_bkgd else 0
+            self._cache[key] = r
+        return r
+
+    def linspaces(self, device):
+        """The three torch.linspace constants of model/scene_rep.py:227, :239, :242 -- created on the CPU by
+        torch itself (bit-identical to the reference) and uploaded once per device."""
+        key = ('lin', str(device))
+        v = self._cache.get(key)
+        if v is None:
+            lin_g = torch.linspace(-self.range_d, self.range_d, steps=self.n_guided)
+            lin_n = torch.linspace(self.near, self.far, steps=self.n_guided)
+            lin_u = torch.linspace(self.near, self.far, self.n_uniform) if self.n_uniform > 0 else torch.zeros(1)
+            v = tuple(t.float().to(device) for t in (lin_u, lin_g, lin_n))
+            self._cache[key] = v
+        return v
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# raw wrappers (no autograd)
+# --------------------------------------------------------------------------------------------------------------------
+
+def sample_rays(spec, target_d, noise=None, seed=0, counts=None, perturb=None):
+    """model/scene_rep.py:227-255.  target_d [N] or [N,1]; noise [N,S] CPU-drawn uniforms or None (device Philox).
+    Returns z_vals [N,S]; accumulates (n_front, n_sdf, n_valid_depth) into counts (int64 [3]) when given."""
+    d = _f32c(target_d.reshape(-1))
+    n = d.shape[0]
+    z = torch.empty((n, spec.n_samples), dtype=torch.float32, device=d.device)
+    lin_u, lin_g, lin_n = spec.linspaces(d.device)
+    if noise is not None:
+        noise = _f32c(noise)
+        if tuple(noise.shape) != (n, spec.n_samples):
+            raise ValueError('noise must have shape [N, S]')
+    check(_lib.load().cb200_sample_rays(ctypes.byref(spec.render_cfg(perturb)), ptr(d), ptr(lin_u), ptr(lin_g), ptr(lin_n),
+                                        ptr(noise), ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ctypes.c_int64(n), ptr(z),
+                                        ptr(counts), stream()), 'sample_rays')
+    return z
+
+
+def _mlp_block(w1, w2, w3, w4):
+    m = _lib.Mlp()
+    m.w_sdf0, m.w_sdf1, m.w_col0, m.w_col1 = w1.data_ptr(), w2.data_ptr(), w3.data_ptr(), w4.data_ptr()
+    return m
+
+
+def _check_weights(w1, w2, w3, w4):
+    if tuple(w1.shape) != (32, 80) or tuple(w2.shape) != (16, 32) or tuple(w3.shape) != (32, 63) or tuple(w4.shape) != (3, 32):
+        raise RuntimeError('coslam_b200: the fused decoder kernels serve hidden_dim 32, geo_feat_dim 15, 2+2 layers and '
+                           'a 32+48 wide input (every shipped YAML); got weight shapes %s' %
+                           [tuple(w.shape) for w in (w1, w2, w3, w4)])
+
+
+def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo=False, want_mask=True, sdf_only=False):
+    """query_color_sdf / run_network forward through the fused kernel.  rays = (rays_o [N,3], rays_d [N,3], z [N,S])."""
+    _check_weights(*w)
+    if rays is not None:
+        o, d, z = rays
+        n, s = z.shape
+        dev = z.device
+    else:
+        n, s = pts.shape[0], 1
+        dev = pts.device
+        o = d = z = None
+    P = n * s
+    raw = torch.empty((P, 4), dtype=torch.float32, device=dev) if want_raw else None
+    geo = torch.empty((P, N_GEO), dtype=torch.float32, device=dev) if want_geo else None
+    mask = torch.empty((P, 2), dtype=torch.int32, device=dev) if want_mask else None
+    mlp = _mlp_block(*w)
+    check(_lib.load().cb200_points_fwd(ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z),
+                                       ctypes.c_int64(n), ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask),
+                                       1 if sdf_only else 0, stream()), 'points_fwd')
+    return raw, geo, mask
+
+
+def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=None, need_table=True, need_mlp=True,
+                    need_pos=True, sdf_only=False):
+    """Backward of points_forward.  Returns (d_table, (dW1..dW4), d_pts | (d_rays_o, d_rays_d))."""
+    if rays is not None:
+        o, d, z = rays
+        n, s = z.shape
+        dev = z.device
+    else:
+        n, s = pts.shape[0], 1
+        dev = pts.device
+        o = d = z = None
+    d_table = torch.zeros_like(table) if need_table else None
+    d_w = None
+    gblock = None
+    if need_mlp:
+        flat = torch.zeros(sum(x.numel() for x in w), dtype=torch.float32, device=dev)
+        d_w, off = [], 0
+        for x in w:
+            d_w.append(flat[off:off + x.numel()].view_as(x))
+            off += x.numel()
+        gblock = _mlp_block(*d_w)
+    d_pts = d_o = d_d = None
+    if need_pos:
+        if rays is not None:
+            d_od = torch.zeros((2, n, 3), dtype=torch.float32, device=dev)
+            d_o, d_d = d_od[0], d_od[1]
+        else:
+            d_pts = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    mlp = _mlp_block(*w)
+    check(_lib.load().cb200_points_bwd(ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z),
+                                       ctypes.c_int64(n), ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(d_table),
+                                       ctypes.byref(gblock) if gblock is not None else None, ptr(d_pts), ptr(d_o), ptr(d_d),
+                                       1 if sdf_only else 0, stream()), 'points_bwd')
+    return d_table, d_w, (d_pts if rays is None else (d_o, d_d))
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# autograd
+# --------------------------------------------------------------------------------------------------------------------
+
+class RayPointsFunction(torch.autograd.Function):
+    """raw[N,S,4] = decoder(encodings(normalise(rays_o + rays_d * z)))   (model/scene_rep.py:258 + run_network)."""
+
+    @staticmethod
+    def forward(ctx, rays_o, rays_d, z_vals, table, w1, w2, w3, w4, spec):
+        o, d, z = _f32c(rays_o), _f32c(rays_d), _f32c(z_vals)
+        tb, w = _f32c(table), tuple(_f32c(x) for x in (w1, w2, w3, w4))
+        need_grad = any(ctx.needs_input_grad)
+        ctx.set_materialize_grads(False)
+        raw, _, mask = points_forward(spec.scene(), tb, w, rays=(o, d, z), want_mask=need_grad)
+        ctx.spec = spec
+        ctx.save_for_backward(o, d, z, tb, *w, mask if mask is not None else torch.empty(0))
+        return raw.view(z.shape[0], z.shape[1], 4)
+
+    @staticmethod
+    def backward(ctx, g_raw):
+        if g_raw is None:
+            return (None,) * 9
+        o, d, z, tb, w1, w2, w3, w4, mask = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        d_table, d_w, d_ray = points_backward(ctx.spec.scene(), tb, (w1, w2, w3, w4), mask, _f32c(g_raw), rays=(o, d, z),
+                                              need_table=need[3], need_mlp=any(need[4:8]), need_pos=need[0] or need[1])
+        d_o, d_d = d_ray if d_ray is not None else (None, None)
+        d_w = d_w or (None, None, None, None)
+        return d_o, d_d, None, d_table, d_w[0], d_w[1], d_w[2], d_w[3], None
+
+
+class PointsFunction(torch.autograd.Function):
+    """raw[P,4] (and optionally geo[P,15]) for explicit points; `normalised` = points already in the unit cube
+    (query_color_sdf / query_sdf, model/scene_rep.py:126-171) or world points (run_network, :173-191)."""
+
+    @staticmethod
+    def forward(ctx, pts, table, w1, w2, w3, w4, spec, normalised, sdf_only):
+        p = _f32c(pts)
+        tb, w = _f32c(table), tuple(_f32c(x) for x in (w1, w2, w3, w4))
+        scene = spec.scene_unnormalised() if (normalised or not spec.normalise) else spec.scene()
+        need_grad = any(ctx.needs_input_grad)
+        ctx.set_materialize_grads(False)
+        raw, geo, mask = points_forward(scene, tb, w, pts=p, want_geo=sdf_only, want_mask=need_grad, sdf_only=sdf_only)
+        ctx.scene, ctx.sdf_only = scene, sdf_only
+        ctx.save_for_backward(p, tb, *w, mask if mask is not None else torch.empty(0))
+        if sdf_only:
+            return raw, geo
+        return raw, torch.empty(0, device=p.device)
+
+    @staticmethod
+    def backward(ctx, g_raw, g_geo):
+        if g_raw is None and (g_geo is None or g_geo.numel() == 0):
+            return (None,) * 9
+        p, tb, w1, w2, w3, w4, mask = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        if g_raw is None:
+            g_raw = torch.zeros((p.shape[0], 4), dtype=torch.float32, device=p.device)
+        d_geo = _f32c(g_geo) if (ctx.sdf_only and g_geo is not None and g_geo.numel() > 0) else None
+        d_table, d_w, d_pts = points_backward(ctx.scene, tb, (w1, w2, w3, w4), mask, _f32c(g_raw), d_geo=d_geo, pts=p,
+                                              need_table=need[1], need_mlp=any(need[2:6]), need_pos=need[0],
+                                              sdf_only=ctx.sdf_only)
+        d_w = d_w or (None, None, None, None)
+        return d_pts, d_table, d_w[0], d_w[1], d_w[2], d_w[3], None, None, None
+
+
+def _render_forward(spec, raw, z, target_rgb=None, target_d=None, loss_sums=None, want_aux=False, want_weights=False):
+    n, s = z.shape
+    dev = z.device
+    rgb = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    depth = torch.empty((n,), dtype=torch.float32, device=dev)
+    aux = torch.empty((3, n), dtype=torch.float32, device=dev) if want_aux else None
+    weights = torch.empty((n, s), dtype=torch.float32, device=dev) if want_weights else None
+    check(_lib.load().cb200_render_fwd(ctypes.byref(spec.render_cfg()), ptr(raw), ptr(z), ptr(target_rgb), ptr(target_d),
+                                       ctypes.c_int64(n), ctypes.c_int64(s), ptr(rgb), ptr(depth),
+                                       ptr(aux[0]) if want_aux else None, ptr(aux[1]) if want_aux else None,
+                                       ptr(aux[2]) if want_aux else None, ptr(weights), ptr(loss_sums), stream()),
+          'render_fwd')
+    return rgb, depth, aux, weights
+
+
+def _render_backward(spec, raw, z, target_rgb, target_d, g_losses, coef, g_rgb, g_depth):
+    n, s = z.shape
+    d_raw = torch.empty((n, s, 4), dtype=torch.float32, device=z.device)
+    lg = None
+    keep = []
+    if g_losses is not None and any(g is not None for g in g_losses):
+        lg = LossGrads()
+        for name, g in zip(('rgb', 'depth', 'sdf', 'fs'), g_losses):
+            if g is not None:
+                g = _f32c(g)
+                keep.append(g)
+                setattr(lg, name, g.data_ptr())
+    check(_lib.load().cb200_render_bwd(ctypes.byref(spec.render_cfg()), ptr(raw), ptr(z), ptr(target_rgb), ptr(target_d),
+                                       ctypes.c_int64(n), ctypes.c_int64(s), ctypes.byref(lg) if lg is not None else None,
+                                       ptr(coef), ptr(g_rgb), ptr(g_depth), ptr(d_raw), stream()), 'render_bwd')
+    return d_raw
+
+
+class RenderFunction(torch.autograd.Function):
+    """raw2outputs + sdf2weights (model/scene_rep.py:77-124): (raw, z) -> rgb, depth, depth_var, disp, acc, weights.
+    Gradients flow back from rgb and depth; the diagnostic maps are not differentiable here."""
+
+    @staticmethod
+    def forward(ctx, raw, z_vals, spec):
+        r, z = _f32c(raw), _f32c(z_vals)
+        rgb, depth, aux, weights = _render_forward(spec, r, z, want_aux=True, want_weights=True)
+        ctx.spec = spec
+        ctx.set_materialize_grads(False)
+        ctx.save_for_backward(r, z)
+        ctx.mark_non_differentiable(aux, weights)
+        return rgb, depth, aux, weights
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_depth, g_aux, g_weights):
+        if g_rgb is None and g_depth is None:
+            return None, None, None
+        r, z = ctx.saved_tensors
+        d_raw = _render_backward(ctx.spec, r, z, None, None, None, None,
+                                 _f32c(g_rgb) if g_rgb is not None else None, _f32c(g_depth) if g_depth is not None else None)
+        return d_raw, None, None
+
+
+class RenderLossFunction(torch.autograd.Function):
+    """Rendering + the loss head of JointEncoding.forward (model/scene_rep.py:319-338, model/utils.py:138-161).
+
+    `ws` is the zero-initialised step workspace: 8 x 8 bytes = [n_front, n_sdf, n_valid (int64) | pad | 4 double sums];
+    the sampling kernel has already accumulated the counts.  With a process group the sums and counts are all-reduced
+    before the losses are finished, so every rank sees the global losses.
+    """
+
+    @staticmethod
+    def forward(ctx, raw, z_vals, target_rgb, target_d, ws, spec, n_rays_total, group):
+        r, z = _f32c(raw), _f32c(z_vals)
+        t_rgb, t_d = _f32c(target_rgb), _f32c(target_d.reshape(-1))
+        counts, sums = ws[:4].view(torch.int64), ws[4:8]
+        rgb, depth, _, _ = _render_forward(spec, r, z, t_rgb, t_d, loss_sums=sums)
+        if group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(counts, group=group)
+            dist.all_reduce(sums, group=group)
+        out = torch.empty(8, dtype=torch.float32, device=z.device)
+        losses, coef = out[:4], out[4:]
+        check(_lib.load().cb200_loss_finish(ptr(sums), ptr(counts), ctypes.c_int64(int(n_rays_total)),
+                                            ctypes.c_int64(z.shape[1]), ptr(losses), ptr(coef), stream()), 'loss_finish')
+        ctx.spec = spec
+        ctx.set_materialize_grads(False)
+        ctx.save_for_backward(r, z, t_rgb, t_d, coef)
+        l = losses.unbind(0)
+        return rgb, depth, l[0], l[1], l[2], l[3]
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_depth, g0, g1, g2, g3):
+        if all(g is None for g in (g_rgb, g_depth, g0, g1, g2, g3)):
+            return (None,) * 8
+        r, z, t_rgb, t_d, coef = ctx.saved_tensors
+        d_raw = _render_backward(ctx.spec, r, z, t_rgb, t_d, (g0, g1, g2, g3), coef,
+                                 _f32c(g_rgb) if g_rgb is not None else None, _f32c(g_depth) if g_depth is not None else None)
+        return d_raw, None, None, None, None, None, None, None
+
+
+def new_step_workspace(device):
+    """8 x float64 zeroed: int64 counts in the first 4 slots, double loss sums in the last 4."""
+    return torch.zeros(8, dtype=torch.float64, device=device)

@@ -1,0 +1,190 @@
+/* coslam_b200 -- C ABI of the B200-native (sm_100a) Co-SLAM render-and-optimise hot path.
+ *
+ * This is the drop-in boundary.  The reference has no FFI of its own: its hot path is
+ * Python that calls the tinycudann torch bindings (model/encodings.py:34-46, 63-71) and ATen ops
+ * (model/scene_rep.py:77-351, model/decoder.py:165-180, model/utils.py:89-161).  Each entry point below names
+ * the reference lines it replaces.  The reference-side binding is a ctypes stub.
+ *
+ * Conventions
+ *   - every pointer argument is a DEVICE pointer, except the small config structs (cb200_grid_cfg, cb200_grid,
+ *     cb200_scene, cb200_render_cfg, cb200_mlp, cb200_mlp_grad) which are HOST structs passed by address;
+ *     buffers are owned by the caller (PyTorch): the library never allocates, frees or synchronises;
+ *   - `stream` is a cudaStream_t passed as void*;
+ *   - return value: 0 = ok, negative = argument error, positive = cudaError_t of the launch;
+ *     cb200_last_error() returns a thread-local message for the last non-zero return;
+ *   - all tensors are dense row-major fp32 unless stated; counts are int64.
+ */
+#ifndef COSLAM_B200_H_
+#define COSLAM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CB200_ABI_VERSION 3
+#define CB200_MAX_LEVELS 16
+
+/* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
+ * hidden_dim 32, geo_feat_dim 15, num_layers 2, hidden_dim_color 32, num_layers_color 2, bias-free) */
+#define CB200_GRID_FEATS 32 /* 16 levels x 2 features          */
+#define CB200_BLOB_FEATS 48 /* 3 dims x 16 bins                */
+#define CB200_SDF_IN 80     /* [embed | embed_pos]             */
+#define CB200_HIDDEN 32
+#define CB200_SDF_OUT 16 /* 1 sdf + 15 geometric features   */
+#define CB200_COL_IN 63  /* [embed_pos | geo_feat]          */
+
+/* tinycudann HashGrid hyper-parameters as the reference passes them (model/encodings.py:34-43) */
+typedef struct cb200_grid_cfg {
+    uint32_t n_levels;
+    uint32_t n_features_per_level;
+    uint32_t log2_hashmap_size;
+    uint32_t base_resolution;
+    float per_level_scale;
+} cb200_grid_cfg;
+
+/* derived per-level geometry (host side, filled by cb200_grid_meta) */
+typedef struct cb200_grid {
+    uint32_t n_levels;
+    uint32_t n_features;
+    uint32_t offset[CB200_MAX_LEVELS + 1]; /* first entry of each level, in entries (not floats) */
+    uint32_t res[CB200_MAX_LEVELS];
+    uint32_t hashed[CB200_MAX_LEVELS]; /* 1: coherent-prime XOR hash, 0: dense stride index */
+    float scale[CB200_MAX_LEVELS];
+} cb200_grid;
+
+/* scene = grid geometry + bounding box normalisation (model/scene_rep.py:182-186) + OneBlob bins */
+typedef struct cb200_scene {
+    cb200_grid grid;
+    float bb_lo[3];
+    float bb_ext[3];    /* bound[:,1] - bound[:,0], subtracted in fp32 by the caller */
+    uint32_t normalise; /* config['grid']['tcnn_encoding']: 1 = apply (p - lo) / ext */
+    uint32_t n_bins;    /* OneBlob bins per dimension; the fused kernels require 16 */
+} cb200_scene;
+
+/* ray sampling + loss head parameters (model/scene_rep.py:220-255, 311-338; model/utils.py:89-161) */
+typedef struct cb200_render_cfg {
+    uint32_t n_uniform;       /* training.n_samples_d */
+    uint32_t n_guided;        /* training.n_range_d   */
+    uint32_t perturb;         /* training.perturb > 0 */
+    uint32_t rgb_missing_nz;  /* bool(training.rgb_missing): weight of rays without valid depth */
+    float trunc;              /* (float) training.trunc */
+    float trunc_sc;           /* (float)(training.trunc * data.sc_factor), product taken in double like Python does */
+    float depth_trunc;        /* cam.depth_trunc */
+    uint32_t white_bkgd;      /* training.white_bkgd */
+} cb200_render_cfg;
+
+/* the four decoder matrices, PyTorch nn.Linear layout [out, in], fp32 */
+typedef struct cb200_mlp {
+    const float* w_sdf0;   /* [32, 80]  decoder.sdf_net.model.0.weight   */
+    const float* w_sdf1;   /* [16, 32]  decoder.sdf_net.model.2.weight   */
+    const float* w_col0;   /* [32, 63]  decoder.color_net.model.0.weight */
+    const float* w_col1;   /* [3, 32]   decoder.color_net.model.2.weight */
+} cb200_mlp;
+
+typedef struct cb200_mlp_grad {
+    float* w_sdf0;
+    float* w_sdf1;
+    float* w_col0;
+    float* w_col1;
+} cb200_mlp_grad;
+
+int cb200_abi_version(void);
+const char* cb200_last_error(void);
+/* number of SMs of the current device (host query), used by callers to size persistent grids/workspaces */
+int cb200_device_sm_count(void);
+
+/* replaces tinycudann's GridEncoding constructor geometry (called via model/encodings.py:34-46);
+ * `grid` is HOST memory */
+int cb200_grid_meta(const cb200_grid_cfg* cfg, cb200_grid* grid);
+
+/* ---- lower boundary: the two tinycudann encodings as stand-alone operators ------------------------------ */
+
+/* tcnn.Encoding(HashGrid).forward  (model/scene_rep.py:137,166):  x [P,3] in [0,1] -> out [P, 2*n_levels] */
+int cb200_hash_fwd(const cb200_grid* grid, const float* x, const float* table, int64_t n_points, float* out,
+                   void* stream);
+/* its backward: dy [P, 2L] -> dtable (+=, may be NULL) and dx [P,3] (=, may be NULL) */
+int cb200_hash_bwd(const cb200_grid* grid, const float* x, const float* table, const float* dy, int64_t n_points,
+                   float* dtable, float* dx, void* stream);
+/* test hook for the bit-exact index gate: idx [P, L, 8] uint32 level-local entry indices */
+int cb200_hash_indices(const cb200_grid* grid, const float* x, int64_t n_points, uint32_t* idx, void* stream);
+/* tcnn.Encoding(OneBlob)  (model/scene_rep.py:141,167):  x [P,D] -> out [P, D*n_bins];  backward dy -> dx */
+int cb200_oneblob_fwd(const float* x, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* out, void* stream);
+int cb200_oneblob_bwd(const float* x, const float* dy, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* dx,
+                      void* stream);
+
+/* ---- upper boundary: the fused JointEncoding path -------------------------------------------------------- */
+
+/* render_rays sampling (model/scene_rep.py:227-255) + the mask counts of get_masks (model/utils.py:103-115)
+ * and of valid_depth_mask (model/scene_rep.py:319).
+ *   target_d [N]; lin_uniform [n_uniform], lin_guided [n_guided], lin_nodepth [n_guided] are the three
+ *   torch.linspace constants of :227,:239,:242 (device copies);
+ *   noise [N,S] = the torch.rand of :255, or NULL to draw Philox noise in-kernel from (seed, ray, sample);
+ *   z_vals [N,S] out;  counts [3] int64, ACCUMULATED (+=): n_front, n_sdf, n_valid_depth  (may be NULL). */
+int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform,
+                      const float* lin_guided, const float* lin_nodepth, const float* noise, uint64_t seed,
+                      int64_t n_rays, float* z_vals, int64_t* counts, void* stream);
+
+/* run_network / query_color_sdf / query_sdf forward (model/scene_rep.py:126-191 + model/decoder.py:165-180):
+ * positions are either explicit (pts [P,3], rays_o == NULL) or pts = rays_o + rays_d * z (scene_rep.py:258,
+ * separate multiply and add) with P = n_rays * n_samples.
+ *   raw   [P,4]  (rgb logits, sdf)            -- may be NULL
+ *   geo   [P,15] geometric feature            -- may be NULL
+ *   act_mask [P,2] uint32: ReLU sign bits of the two hidden layers, saved for the backward -- may be NULL
+ *   sdf_only != 0 skips the colour network (query_sdf). */
+int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
+                     const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
+                     int64_t n_samples, float* raw, float* geo, uint32_t* act_mask, int sdf_only, void* stream);
+
+/* its backward.  d_raw [P,4] (d_geo [P,15] optional, NULL = zero).  Outputs, each optional (NULL = skip):
+ *   dtable (+=)  [n_params]     d_mlp (+=) four matrices
+ *   d_pts [P,3] (=)             d_rays_o, d_rays_d [N,3] (+=, ray mode only)
+ * act_mask is the array written by cb200_points_fwd on the same inputs. */
+int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
+                     const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
+                     int64_t n_samples, const float* d_raw, const float* d_geo, const uint32_t* act_mask,
+                     float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts, float* d_rays_o, float* d_rays_d,
+                     int sdf_only, void* stream);
+
+/* raw2outputs + sdf2weights (model/scene_rep.py:77-124) and, when loss_sums != NULL, the loss head
+ * (model/scene_rep.py:319-338, model/utils.py:138-161).
+ *   raw [N,S,4], z_vals [N,S], target_rgb [N,3] / target_d [N] (only for the loss head)
+ *   outputs (each may be NULL): rgb [N,3], depth [N], depth_var [N], disp [N], acc [N], weights [N,S]
+ *   loss_sums [4] double, ACCUMULATED: sum of squared residuals of rgb, depth, sdf, free-space terms. */
+int cb200_render_fwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb,
+                     const float* target_d, int64_t n_rays, int64_t n_samples, float* rgb, float* depth,
+                     float* depth_var, float* disp, float* acc, float* weights, double* loss_sums, void* stream);
+
+/* finishes the four losses from the (possibly all-reduced) sums and counts:
+ *   losses [4] = rgb_loss, depth_loss, sdf_loss, fs_loss;  coef [4] = d loss_k / d (sum of squares)_k, saved for
+ *   the backward.  totals [2] int64 = global number of rays and of samples per ray (host-known but kept on the
+ *   device so that a sharded run can pass global values without a sync). */
+int cb200_loss_finish(const double* loss_sums, const int64_t* counts, int64_t n_rays_total, int64_t n_samples,
+                      float* losses, float* coef, void* stream);
+
+/* upstream gradients of the four losses: DEVICE pointers to 0-d fp32 tensors, each may be NULL (= no gradient) */
+typedef struct cb200_loss_grads {
+    const float* rgb;
+    const float* depth;
+    const float* sdf;
+    const float* fs;
+} cb200_loss_grads;
+
+/* backward of cb200_render_fwd (+ loss head).  g_loss: upstream gradients of the four losses (host struct of device
+ * pointers, may be NULL), coef [4] from cb200_loss_finish, g_rgb [N,3] / g_depth [N] upstream gradients of the
+ * rendered maps (may be NULL).  d_raw [N,S,4] out (=). */
+int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb,
+                     const float* target_d, int64_t n_rays, int64_t n_samples, const cb200_loss_grads* g_loss,
+                     const float* coef, const float* g_rgb, const float* g_depth, float* d_raw, void* stream);
+
+/* test hook for the bit-exact sample-position gate: pts [P,3] and normalised x [P,3] exactly as the fused
+ * kernels compute them (model/scene_rep.py:258 and :186) */
+int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals,
+                          int64_t n_rays, int64_t n_samples, float* pts, float* x, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COSLAM_B200_H_ */

@@ -1,0 +1,168 @@
+"""ORACLE tooling (test infrastructure) -- golden-vector generator.
+
+Runs the reference's OWN, UNMODIFIED model/scene_rep.py:JointEncoding (imported from /root/reference, with
+oracle/tcnn_shim.py standing in for the un-vendored tinycudann) on the seeded synthetic batches of
+coslam_b200/synth.py, checks that the restatement oracle/coslam_oracle.py reproduces it, and writes the fixtures under
+tests/golden/.  Works only where /root/reference exists (the build container); the fixtures travel with the repo.
+
+    python -m oracle.gen_golden
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from coslam_b200 import synth                      # noqa: E402
+from oracle import coslam_oracle, ref_loader, tcnn_shim   # noqa: E402
+
+GOLDEN_DIR = os.path.join(ROOT, 'tests', 'golden')
+NOISE_SEED = 4321
+
+CASES = [
+    # name, config factory, kwargs, n_rays, table kind, batch seed, extra batch kwargs
+    ('room0_small', 'room0', {}, 128, 'small', 0, {}),
+    ('room0_trained', 'room0', {}, 128, 'trained', 1, {}),
+    ('scannet0000_trained', 'scannet0000', {}, 64, 'trained', 2, {}),
+    ('tum_desk_trained', 'tum_desk', {'n_importance': 0}, 64, 'trained', 3, {'over_trunc_frac': 0.05}),
+]
+
+
+def checksum(t):
+    return hashlib.sha256(np.ascontiguousarray(t.detach().cpu().numpy()).tobytes()).hexdigest()[:16]
+
+
+def build_reference_model(cfg, table, weights):
+    JointEncoding = ref_loader.load_reference_model_class()
+    model = JointEncoding(cfg, synth.bound_tensor(cfg))
+    with torch.no_grad():
+        model.embed_fn.params.copy_(table)
+        model.decoder.sdf_net.model[0].weight.copy_(weights[0])
+        model.decoder.sdf_net.model[2].weight.copy_(weights[1])
+        model.decoder.color_net.model[0].weight.copy_(weights[2])
+        model.decoder.color_net.model[2].weight.copy_(weights[3])
+    return model
+
+
+def table_grad_summary(g, meta, n_pick=4096, seed=0):
+    g = g.detach()
+    F = 2
+    level_sum = np.array([float(g[meta['offset'][l] * F:meta['offset'][l + 1] * F].double().sum()) for l in range(len(meta['res']))])
+    level_abs = np.array([float(g[meta['offset'][l] * F:meta['offset'][l + 1] * F].double().abs().sum()) for l in range(len(meta['res']))])
+    nz = torch.nonzero(g).reshape(-1)
+    rng = np.random.RandomState(seed)
+    pick = nz[torch.as_tensor(rng.choice(nz.numel(), size=min(n_pick, nz.numel()), replace=False))]
+    pick, _ = torch.sort(pick)
+    return {'tg_level_sum': level_sum, 'tg_level_abs': level_abs, 'tg_norm': float(g.double().norm()),
+            'tg_nnz': int(nz.numel()), 'tg_pick_idx': pick.numpy().astype(np.int64), 'tg_pick_val': g[pick].numpy()}
+
+
+def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
+    cfg = synth.CONFIGS[cfg_name](**cfg_kw)
+    rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n_rays, seed=seed, **batch_kw)
+    weights = synth.decoder_init(seed=seed)
+    # table size comes from the reference model itself
+    JointEncoding = ref_loader.load_reference_model_class()
+    model = JointEncoding(cfg, synth.bound_tensor(cfg))
+    n_params = model.embed_fn.params.numel()
+    table = synth.table_init(n_params, table_kind)
+    model = build_reference_model(cfg, table, weights)
+    model.train()
+
+    S = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
+    torch.manual_seed(NOISE_SEED)
+    noise = torch.rand((n_rays, S))
+
+    # ---- the reference, training mode: forward + backward of the weighted loss (coslam.py:140-160) -------------
+    ro = rays_o.clone().requires_grad_(True)
+    rd = rays_d.clone().requires_grad_(True)
+    torch.manual_seed(NOISE_SEED)
+    ret = model.forward(ro, rd, rgb, depth)
+    t = cfg['training']
+    loss = t['rgb_weight'] * ret['rgb_loss'] + t['depth_weight'] * ret['depth_loss'] + t['sdf_weight'] * ret['sdf_loss'] \
+        + t['fs_weight'] * ret['fs_loss']
+    loss.backward()
+    # ---- the reference, eval mode: the full render dictionary ---------------------------------------------------
+    model.eval()
+    with torch.no_grad():
+        torch.manual_seed(NOISE_SEED)
+        ev = model.forward(rays_o, rays_d, rgb, depth)
+    model.train()
+
+    # ---- cross-check the restatement against the reference ----------------------------------------------------
+    orc = coslam_oracle.OracleScene(cfg, synth.bound_tensor(cfg))
+    orc.load_weights(table, *weights)
+    o2 = rays_o.clone().requires_grad_(True)
+    d2 = rays_d.clone().requires_grad_(True)
+    r2 = orc.forward(o2, d2, rgb, depth, noise=noise)
+    orc.total_loss(r2).backward()
+
+    def close(a, b, what, rtol=1e-5, atol=1e-7):
+        a, b = a.detach().double(), b.detach().double()
+        err = (a - b).abs().max().item() if a.numel() else 0.0
+        scale = b.abs().max().item() if b.numel() else 1.0
+        assert err <= atol + rtol * scale, '%s: restatement deviates from the reference: %g (scale %g)' % (what, err, scale)
+
+    assert torch.equal(ev['z_vals'], r2['z_vals']), 'z_vals not bit-identical'
+    close(r2['raw'], ev['raw'], 'raw')
+    close(r2['rgb'], ret['rgb'], 'rgb')
+    close(r2['depth'], ret['depth'], 'depth')
+    for k in ('rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):
+        close(r2[k], ret[k], k)
+    close(o2.grad, ro.grad, 'd rays_o', rtol=1e-4)
+    close(d2.grad, rd.grad, 'd rays_d', rtol=1e-4)
+    close(orc.table.grad, model.embed_fn.params.grad, 'd table', rtol=1e-4)
+    close(orc.W1.grad, model.decoder.sdf_net.model[0].weight.grad, 'dW1', rtol=1e-4)
+    close(orc.W2.grad, model.decoder.sdf_net.model[2].weight.grad, 'dW2', rtol=1e-4)
+    close(orc.W3.grad, model.decoder.color_net.model[0].weight.grad, 'dW3', rtol=1e-4)
+    close(orc.W4.grad, model.decoder.color_net.model[2].weight.grad, 'dW4', rtol=1e-4)
+
+    # ---- bit-exact gates: positions and hash indices from the reference's arithmetic --------------------------
+    z = ev['z_vals']
+    pts = rays_o[..., None, :] + rays_d[..., None, :] * z[..., :, None]
+    bb = synth.bound_tensor(cfg)
+    x = (pts.reshape(-1, 3) - bb[:, 0]) / (bb[:, 1] - bb[:, 0])
+    meta = model.embed_fn.impl.meta
+    n_idx = min(2048, x.shape[0])
+    idx = torch.stack([tcnn_shim.hash_corner_indices(x[:n_idx], meta, l)[0] for l in range(16)], 1)   # [n,16,8]
+
+    out = {
+        'cfg_name': cfg_name, 'cfg_kw': repr(cfg_kw), 'n_rays': n_rays, 'table_kind': table_kind, 'seed': seed,
+        'batch_kw': repr(batch_kw), 'noise_seed': NOISE_SEED,
+        'chk_rays_o': checksum(rays_o), 'chk_rays_d': checksum(rays_d), 'chk_rgb': checksum(rgb), 'chk_depth': checksum(depth),
+        'chk_table': checksum(table), 'chk_w': checksum(torch.cat([w.reshape(-1) for w in weights])),
+        'noise': noise.numpy(), 'z_vals': z.numpy(), 'pts': pts.reshape(-1, 3).numpy(), 'x': x.numpy(),
+        'hash_idx': idx.numpy().astype(np.uint32),
+        'grid_scale': np.asarray(meta['scale'], dtype=np.float32), 'grid_res': np.asarray(meta['res'], dtype=np.uint32),
+        'grid_offset': np.asarray(meta['offset'], dtype=np.uint32),
+        'raw': ev['raw'].numpy(), 'rgb': ev['rgb'].numpy(), 'depth': ev['depth'].numpy(), 'depth_var': ev['depth_var'].numpy(),
+        'disp_map': ev['disp_map'].numpy(), 'acc_map': ev['acc_map'].numpy(),
+        'rgb_loss': ret['rgb_loss'].item(), 'depth_loss': ret['depth_loss'].item(), 'sdf_loss': ret['sdf_loss'].item(),
+        'fs_loss': ret['fs_loss'].item(), 'psnr': ret['psnr'].detach().numpy(), 'loss': loss.item(),
+        'd_rays_o': ro.grad.numpy(), 'd_rays_d': rd.grad.numpy(),
+        'dW1': model.decoder.sdf_net.model[0].weight.grad.numpy(), 'dW2': model.decoder.sdf_net.model[2].weight.grad.numpy(),
+        'dW3': model.decoder.color_net.model[0].weight.grad.numpy(), 'dW4': model.decoder.color_net.model[2].weight.grad.numpy(),
+        'state_dict_keys': np.array(sorted(model.state_dict().keys())),
+    }
+    out.update(table_grad_summary(model.embed_fn.params.grad, meta))
+    path = os.path.join(GOLDEN_DIR, name + '.npz')
+    np.savez_compressed(path, **out)
+    print('%-22s N=%d S=%d loss=%.6f  -> %s (%.0f KB)' % (name, n_rays, S, loss.item(), os.path.relpath(path, ROOT),
+                                                          os.path.getsize(path) / 1024))
+
+
+def main():
+    if not ref_loader.available():
+        raise SystemExit('reference tree not present; fixtures can only be regenerated in the build container')
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    for case in CASES:
+        run_case(*case)
+
+
+if __name__ == '__main__':
+    main()

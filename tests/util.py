@@ -1,0 +1,74 @@
+"""Shared helpers of the parity tests: rebuild a golden case's inputs from its seeds, build the oracle and the
+CUDA model with identical weights, and the tolerance helper for the 1e-3 relative gate of BASELINE.md section 5."""
+import ast
+import hashlib
+import os
+
+import numpy as np
+import torch
+
+from coslam_b200 import synth
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+GOLDEN_CASES = ['room0_small', 'room0_trained', 'scannet0000_trained', 'tum_desk_trained']
+
+REL_TOL = 1e-3          # north_star: rendered depth/colour, SDF and gradients within 1e-3 relative (fp32 tables)
+
+
+def checksum(t):
+    return hashlib.sha256(np.ascontiguousarray(t.detach().cpu().numpy()).tobytes()).hexdigest()[:16]
+
+
+def load_golden(name):
+    return np.load(os.path.join(GOLDEN_DIR, name + '.npz'), allow_pickle=False)
+
+
+def case_inputs(g):
+    """Regenerates the seeded inputs of a golden case and verifies them against the stored checksums."""
+    cfg = synth.CONFIGS[str(g['cfg_name'])](**ast.literal_eval(str(g['cfg_kw'])))
+    n = int(g['n_rays'])
+    rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n, seed=int(g['seed']), **ast.literal_eval(str(g['batch_kw'])))
+    weights = synth.decoder_init(seed=int(g['seed']))
+    from oracle import tcnn_shim
+    from oracle.coslam_oracle import hashgrid_encoding_config
+    enc = hashgrid_encoding_config(cfg, synth.bound_tensor(cfg))
+    meta = tcnn_shim.grid_meta(enc['n_levels'], enc['log2_hashmap_size'], enc['base_resolution'], enc['per_level_scale'])
+    table = synth.table_init(meta['offset'][-1] * 2, str(g['table_kind']))
+    assert checksum(rays_o) == str(g['chk_rays_o']) and checksum(rays_d) == str(g['chk_rays_d'])
+    assert checksum(rgb) == str(g['chk_rgb']) and checksum(depth) == str(g['chk_depth'])
+    assert checksum(table) == str(g['chk_table'])
+    assert checksum(torch.cat([w.reshape(-1) for w in weights])) == str(g['chk_w'])
+    return cfg, (rays_o, rays_d, rgb, depth), table, weights, torch.from_numpy(g['noise'])
+
+
+def make_oracle(cfg, table, weights):
+    from oracle.coslam_oracle import OracleScene
+    orc = OracleScene(cfg, synth.bound_tensor(cfg))
+    orc.load_weights(table, *weights)
+    return orc
+
+
+def make_cuda_model(cfg, table, weights, device='cuda:0', noise_mode='host'):
+    from coslam_b200.scene_rep import JointEncoding
+    model = JointEncoding(cfg, synth.bound_tensor(cfg).to(device)).to(device)
+    model.noise_mode = noise_mode
+    with torch.no_grad():
+        model.embed_fn.params.copy_(table.to(device))
+        for dst, src in zip(model.decoder.fused_weights(), weights):
+            dst.copy_(src.to(device))
+    model.train()
+    return model
+
+
+def rel_err(a, b):
+    """max |a - b| relative to the scale (max |b|) of the reference tensor."""
+    a = torch.as_tensor(a).detach().double().cpu()
+    b = torch.as_tensor(b).detach().double().cpu()
+    scale = max(b.abs().max().item(), 1e-30)
+    return (a - b).abs().max().item() / scale
+
+
+def assert_close(a, b, what, tol=REL_TOL):
+    e = rel_err(a, b)
+    assert e <= tol, '%s: relative error %.3e exceeds %.1e' % (what, e, tol)
+    return e
