@@ -49,7 +49,7 @@ class Mlp(ctypes.Structure):
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
            'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays',
            'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd',
-           'cb200_debug_positions']
+           'cb200_debug_positions', 'cb200_selftest_mma']
 
 _lib = None
 
@@ -82,7 +82,12 @@ def load():
     return lib
 
 
+KERNEL_LAUNCHES = 0        # every successful device call below launches exactly one kernel of this library
+
+
 def check(rc, what):
+    global KERNEL_LAUNCHES
+    KERNEL_LAUNCHES += 1
     if rc != 0:
         msg = load().cb200_last_error().decode('utf-8', 'replace')
         raise RuntimeError('coslam_b200 %s failed (%d): %s' % (what, rc, msg))
@@ -107,5 +112,7 @@ def grid_meta(n_levels, n_features, log2_hashmap_size, base_resolution, per_leve
     """Host-side geometry; works without a GPU."""
     cfg = GridCfg(n_levels, n_features, log2_hashmap_size, base_resolution, float(per_level_scale))
     g = Grid()
+    global KERNEL_LAUNCHES
     check(load().cb200_grid_meta(ctypes.byref(cfg), ctypes.byref(g)), 'grid_meta')
+    KERNEL_LAUNCHES -= 1       # host-only call
     return g

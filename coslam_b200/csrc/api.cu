@@ -151,6 +151,9 @@ int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const 
 static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
                             const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples) {
     if (int rc = check_fused_scene(scene)) return rc;
+    CB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples < (1 << 30), "points: bad sizes");
+    a.n_points = n_rays * n_samples;
+    if (a.n_points == 0) return 0;
     CB_REQUIRE(table && mlp && mlp->w_sdf0 && mlp->w_sdf1 && mlp->w_col0 && mlp->w_col1, "points: NULL table / weights");
     CB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples < (1 << 30), "points: bad sizes");
     CB_REQUIRE((pts != nullptr) != (rays_o != nullptr), "points: pass either pts or (rays_o, rays_d, z_vals)");
@@ -250,6 +253,14 @@ int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const f
     a.n_points = n_rays * n_samples; a.n_samples = (int)n_samples;
     if (a.n_points == 0) return 0;
     return cuda_result(cb200::launch_debug_positions(a, pts, x, (cudaStream_t)stream), "debug_positions");
+}
+
+int cb200_selftest_mma(const float* a, const float* b, int k, int n, int mode, float* c, void* stream) {
+    CB_REQUIRE(a && b && c, "selftest_mma: NULL buffer");
+    CB_REQUIRE(mode == 0 || mode == 1, "selftest_mma: mode must be 0 (K-major) or 1 (MN-major)");
+    CB_REQUIRE(n >= 16 && n <= 128 && n % 16 == 0, "selftest_mma: N must be a multiple of 16 in [16,128]");
+    CB_REQUIRE(mode == 1 || (k >= 16 && k <= 128 && k % 16 == 0), "selftest_mma: K must be a multiple of 16 in [16,128]");
+    return cuda_result(cb200::launch_tc_selftest(a, b, k, n, mode, c, (cudaStream_t)stream), "selftest_mma");
 }
 
 }  // extern "C"

@@ -78,6 +78,7 @@ cudaError_t launch_hash_indices(const SceneDev& sc, const float* x, int64_t n, u
 cudaError_t launch_hash_bwd(const SceneDev& sc, const float* x, const float* table, const float* dy, int64_t n, float* dtable, float* dx,
                             cudaStream_t st);
 cudaError_t launch_oneblob_fwd(const float* x, int64_t n_flat, int n_bins, float* out, cudaStream_t st);
+cudaError_t launch_tc_selftest(const float* A, const float* B, int K, int N, int mode, float* C, cudaStream_t st);
 cudaError_t launch_oneblob_bwd(const float* x, const float* dy, int64_t n_flat, int n_bins, float* dx, cudaStream_t st);
 
 }  // namespace cb200

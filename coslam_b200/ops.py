@@ -14,6 +14,19 @@ from ._lib import check, ptr, stream
 
 N_GEO = 15
 
+# bench.py sets this to a list to collect (name, start_event, end_event) around the two per-point kernels
+KERNEL_EVENTS = None
+
+
+def _timed(name, fn):
+    if KERNEL_EVENTS is None:
+        return fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn()
+    e1.record()
+    KERNEL_EVENTS.append((name, e0, e1))
+
 
 def _f32c(t):
     """fp32 + contiguous view of a CUDA tensor (copy only when needed)."""
@@ -183,9 +196,9 @@ def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo
     geo = torch.empty((P, N_GEO), dtype=torch.float32, device=dev) if want_geo else None
     mask = torch.empty((P, 2), dtype=torch.int32, device=dev) if want_mask else None
     mlp = _mlp_block(*w)
-    check(_lib.load().cb200_points_fwd(ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z),
-                                       ctypes.c_int64(n), ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask),
-                                       1 if sdf_only else 0, stream()), 'points_fwd')
+    _timed('points_fwd', lambda: check(_lib.load().cb200_points_fwd(
+        ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
+        ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask), 1 if sdf_only else 0, stream()), 'points_fwd'))
     return raw, geo, mask
 
 
@@ -218,10 +231,11 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
         else:
             d_pts = torch.empty((n, 3), dtype=torch.float32, device=dev)
     mlp = _mlp_block(*w)
-    check(_lib.load().cb200_points_bwd(ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z),
-                                       ctypes.c_int64(n), ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(d_table),
-                                       ctypes.byref(gblock) if gblock is not None else None, ptr(d_pts), ptr(d_o), ptr(d_d),
-                                       1 if sdf_only else 0, stream()), 'points_bwd')
+    _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd(
+        ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
+        ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(d_table),
+        ctypes.byref(gblock) if gblock is not None else None, ptr(d_pts), ptr(d_o), ptr(d_d), 1 if sdf_only else 0,
+        stream()), 'points_bwd'))
     return d_table, d_w, (d_pts if rays is None else (d_o, d_d))
 
 

@@ -126,3 +126,26 @@ def decoder_init(seed=0):
         return (torch.rand(o, i, generator=g) * 2 - 1) * k
 
     return lin(32, 80), lin(16, 32), lin(32, 63), lin(3, 32)
+
+
+def keyframe_ray_batch(cfg, n_rays, n_kf=64, seed=0, invalid_frac=0.05):
+    """Mapping-BA style batch (coslam.py:336-355): rays drawn from `n_kf` keyframe cameras scattered in the bound.
+    Returns CPU fp32 rays_o [N,3], rays_d [N,3], target_rgb [N,3], target_d [N,1] and the keyframe id of each ray."""
+    rng = np.random.RandomState(seed)
+    cam = cfg['cam']
+    bound = np.asarray(cfg['mapping']['bound'], dtype=np.float64)
+    centre, half = bound.mean(1), 0.25 * (bound[:, 1] - bound[:, 0])
+    t = centre + rng.uniform(-1, 1, size=(n_kf, 3)) * half
+    R = np.stack([_rodrigues(a / np.linalg.norm(a) * rng.uniform(0.1, 3.0)) for a in rng.normal(size=(n_kf, 3))])
+    ids = torch.as_tensor(rng.randint(0, n_kf, size=n_rays), dtype=torch.long)
+    H, W = cam['H'], cam['W']
+    px = torch.as_tensor(rng.uniform(0, W, size=n_rays), dtype=torch.float32).floor()
+    py = torch.as_tensor(rng.uniform(0, H, size=n_rays), dtype=torch.float32).floor()
+    d_cam = torch.stack([(px - cam['cx']) / cam['fx'], -(py - cam['cy']) / cam['fy'], -torch.ones_like(px)], -1)
+    Rt = torch.as_tensor(R, dtype=torch.float32)[ids]                      # [N,3,3]
+    rays_d = torch.sum(d_cam[:, None, :] * Rt, -1)
+    rays_o = torch.as_tensor(t, dtype=torch.float32)[ids]
+    depth = torch.as_tensor(rng.uniform(0.5, min(4.5, cam['far'] - 0.5), size=(n_rays, 1)), dtype=torch.float32)
+    depth[torch.as_tensor(rng.uniform(size=n_rays) < invalid_frac)] = 0.0
+    rgb = torch.as_tensor(rng.uniform(size=(n_rays, 3)), dtype=torch.float32)
+    return rays_o, rays_d, rgb, depth, ids

@@ -184,6 +184,10 @@ int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float*
 int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals,
                           int64_t n_rays, int64_t n_samples, float* pts, float* x, void* stream);
 
+/* test hook for the tcgen05 decoder plumbing (one 128-row tile, bf16 hi/lo split, three MMAs per reduction step):
+ *   mode 0: c[128,n] = a[128,k] * b[n,k]^T     mode 1: c[128,n] = a[128,128]^T * b[128,n]     (fp32 row-major) */
+int cb200_selftest_mma(const float* a, const float* b, int k, int n, int mode, float* c, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

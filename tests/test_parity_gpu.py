@@ -1,0 +1,259 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the oracle on the same seeded inputs
+and against the committed golden vectors (which came from the reference's own code).
+
+Gates: z_vals, sample positions and hash indices bit-exact; raw / rendered maps / losses /
+gradients within 1e-3 relative (relative to the largest magnitude of the reference tensor)."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from coslam_b200 import _lib, ops, synth
+from tests import util
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+
+def _weighted_loss(cfg, ret):
+    t = cfg['training']
+    return t['rgb_weight'] * ret['rgb_loss'] + t['depth_weight'] * ret['depth_loss'] + t['sdf_weight'] * ret['sdf_loss'] \
+        + t['fs_weight'] * ret['fs_loss']
+
+
+@pytest.mark.parametrize('name', util.GOLDEN_CASES)
+def test_bit_exact_samples_positions_indices(name):
+    g = util.load_golden(name)
+    cfg, (rays_o, rays_d, rgb, depth), table, weights, noise = util.case_inputs(g)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    z = ops.sample_rays(model.spec, depth.to(DEV), noise=noise.to(DEV))
+    assert np.array_equal(z.cpu().numpy(), g['z_vals'])
+    n, s = z.shape
+    pts = torch.empty((n * s, 3), device=DEV)
+    x = torch.empty((n * s, 3), device=DEV)
+    o, d = rays_o.to(DEV).contiguous(), rays_d.to(DEV).contiguous()
+    _lib.check(_lib.load().cb200_debug_positions(ctypes.byref(model.spec.scene()), _lib.ptr(o), _lib.ptr(d), _lib.ptr(z),
+                                                 ctypes.c_int64(n), ctypes.c_int64(s), _lib.ptr(pts), _lib.ptr(x),
+                                                 _lib.stream()), 'debug_positions')
+    assert np.array_equal(pts.cpu().numpy(), g['pts'])
+    assert np.array_equal(x.cpu().numpy(), g['x'])
+    m = g['hash_idx'].shape[0]
+    idx = torch.empty((m, 16, 8), dtype=torch.int32, device=DEV)
+    xs = x[:m].contiguous()
+    _lib.check(_lib.load().cb200_hash_indices(ctypes.byref(model.spec.grid()), _lib.ptr(xs), ctypes.c_int64(m), _lib.ptr(idx),
+                                              _lib.stream()), 'hash_indices')
+    assert np.array_equal(idx.cpu().numpy().view(np.uint32), g['hash_idx'])
+
+
+@pytest.mark.parametrize('name', util.GOLDEN_CASES)
+def test_forward_backward_matches_reference_golden(name):
+    g = util.load_golden(name)
+    cfg, (rays_o, rays_d, rgb, depth), table, weights, noise = util.case_inputs(g)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    o = rays_o.to(DEV).requires_grad_(True)
+    d = rays_d.to(DEV).requires_grad_(True)
+    torch.manual_seed(int(g['noise_seed']))               # host noise mode consumes the same CPU stream as the reference
+    ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
+    loss = _weighted_loss(cfg, ret)
+    loss.backward()
+    util.assert_close(ret['rgb'], g['rgb'], 'rgb')
+    util.assert_close(ret['depth'], g['depth'], 'depth')
+    for k in ('rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):
+        util.assert_close(ret[k], float(g[k]), k)
+    util.assert_close(ret['psnr'], g['psnr'], 'psnr')
+    assert tuple(ret['psnr'].shape) == (1,) and ret['rgb_loss'].dim() == 0
+    util.assert_close(loss, float(g['loss']), 'loss')
+    util.assert_close(o.grad, g['d_rays_o'], 'd_rays_o')
+    util.assert_close(d.grad, g['d_rays_d'], 'd_rays_d')
+    for k, w in zip(('dW1', 'dW2', 'dW3', 'dW4'), model.decoder.fused_weights()):
+        util.assert_close(w.grad, g[k], k)
+    tg = model.embed_fn.params.grad
+    util.assert_close(tg[torch.from_numpy(g['tg_pick_idx']).to(DEV)], g['tg_pick_val'], 'table grad (sampled)')
+    assert int(torch.count_nonzero(tg)) == int(g['tg_nnz'])
+    lvl = np.array([float(tg[int(g['grid_offset'][l]) * 2:int(g['grid_offset'][l + 1]) * 2].double().sum()) for l in range(16)])
+    assert np.abs(lvl - g['tg_level_sum']).max() <= 1e-3 * np.abs(g['tg_level_abs']).max()
+    # eval mode: full render dictionary
+    model.eval()
+    with torch.no_grad():
+        torch.manual_seed(int(g['noise_seed']))
+        ev = model.forward(rays_o.to(DEV), rays_d.to(DEV), rgb.to(DEV), depth.to(DEV))
+    assert set(ev.keys()) == {'rgb', 'depth', 'disp_map', 'acc_map', 'depth_var', 'z_vals', 'raw'}
+    assert np.array_equal(ev['z_vals'].cpu().numpy(), g['z_vals'])
+    for k in ('raw', 'rgb', 'depth', 'depth_var', 'acc_map'):
+        util.assert_close(ev[k], g[k], 'eval ' + k)
+    util.assert_close(1.0 / ev['disp_map'], 1.0 / torch.from_numpy(g['disp_map']), 'eval 1/disp')
+
+
+@pytest.mark.parametrize('cfg_name,n_rays,kind', [('room0', 4096, 'small'), ('room0', 4096, 'trained'),
+                                                  ('scannet0000', 1024, 'trained'), ('tum_desk', 1024, 'trained'),
+                                                  ('room0', 1, 'trained'), ('room0', 33, 'trained')])
+def test_forward_backward_matches_oracle(cfg_name, n_rays, kind):
+    """BASELINE.json configs[0]: fixed 4096-ray batch with room0 hyper-parameters (plus the other shapes, and ragged
+    sizes that leave partial tiles / warps)."""
+    cfg = synth.CONFIGS[cfg_name]()
+    rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n_rays, seed=11, over_trunc_frac=0.02 if cfg_name == 'tum_desk' else 0.0)
+    weights = synth.decoder_init(seed=5)
+    from coslam_b200.scene_rep import JointEncoding
+    model = JointEncoding(cfg, synth.bound_tensor(cfg).to(DEV)).to(DEV)
+    table = synth.table_init(model.embed_fn.params.numel(), kind, seed=77)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    orc = util.make_oracle(cfg, table, weights)
+    S = model.spec.n_samples
+    torch.manual_seed(3)
+    noise = torch.rand(n_rays, S)
+    oo = rays_o.clone().requires_grad_(True)
+    od = rays_d.clone().requires_grad_(True)
+    r_ref = orc.forward(oo, od, rgb, depth, noise=noise)
+    orc.total_loss(r_ref).backward()
+
+    o = rays_o.to(DEV).requires_grad_(True)
+    d = rays_d.to(DEV).requires_grad_(True)
+    torch.manual_seed(3)
+    ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
+    _weighted_loss(cfg, ret).backward()
+    util.assert_close(ret['rgb'], r_ref['rgb'], 'rgb')
+    util.assert_close(ret['depth'], r_ref['depth'], 'depth')
+    for k in ('rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):
+        if torch.isnan(r_ref[k]):
+            assert torch.isnan(ret[k]), k
+        else:
+            util.assert_close(ret[k], r_ref[k], k)
+    if not torch.isnan(r_ref['depth_loss']):
+        util.assert_close(o.grad, oo.grad, 'd_rays_o')
+        util.assert_close(d.grad, od.grad, 'd_rays_d')
+        util.assert_close(model.embed_fn.params.grad, orc.table.grad, 'd_table')
+        for k, w, wr in zip(('dW1', 'dW2', 'dW3', 'dW4'), model.decoder.fused_weights(), (orc.W1, orc.W2, orc.W3, orc.W4)):
+            util.assert_close(w.grad, wr.grad, k)
+
+
+def test_tracking_mode_input_gradients_only():
+    """Tracking (coslam.py:502-594) needs dL/d rays only: map parameters frozen -> no table scatter / weight gradients."""
+    cfg = synth.room0_config()
+    g = util.load_golden('room0_trained')
+    cfg, (rays_o, rays_d, rgb, depth), table, weights, noise = util.case_inputs(g)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    for p in model.parameters():
+        p.requires_grad_(False)
+    o = rays_o.to(DEV).requires_grad_(True)
+    d = rays_d.to(DEV).requires_grad_(True)
+    torch.manual_seed(int(g['noise_seed']))
+    ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
+    _weighted_loss(cfg, ret).backward()
+    util.assert_close(o.grad, g['d_rays_o'], 'd_rays_o')
+    util.assert_close(d.grad, g['d_rays_d'], 'd_rays_d')
+    assert model.embed_fn.params.grad is None
+
+
+def test_retain_graph_double_backward_call():
+    """global_BA calls loss.backward(retain_graph=True) (coslam.py:361): a second backward must give the same result."""
+    g = util.load_golden('room0_trained')
+    cfg, (rays_o, rays_d, rgb, depth), table, weights, noise = util.case_inputs(g)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    o = rays_o.to(DEV).requires_grad_(True)
+    torch.manual_seed(int(g['noise_seed']))
+    ret = model.forward(o, rays_d.to(DEV), rgb.to(DEV), depth.to(DEV))
+    loss = _weighted_loss(cfg, ret)
+    loss.backward(retain_graph=True)
+    g1 = o.grad.clone()
+    t1 = model.embed_fn.params.grad.clone()
+    loss.backward()
+    util.assert_close(o.grad, 2 * g1, 'accumulated d_rays_o', 1e-6)
+    util.assert_close(model.embed_fn.params.grad, 2 * t1, 'accumulated d_table', 1e-5)
+
+
+def test_lower_boundary_encodings_match_shim():
+    from oracle import tcnn_shim
+    from oracle.coslam_oracle import hashgrid_encoding_config
+    from coslam_b200 import tcnn
+    cfg = synth.room0_config()
+    enc_cfg = hashgrid_encoding_config(cfg, synth.bound_tensor(cfg))
+    shim = tcnn_shim.Encoding(3, enc_cfg)
+    ours = tcnn.Encoding(3, enc_cfg, dtype=torch.float).to(DEV)
+    assert torch.equal(ours.params.detach().cpu(), shim.params.detach())           # same U(-1e-4,1e-4) seed-1337 init
+    table = synth.table_init(shim.params.numel(), 'trained')
+    with torch.no_grad():
+        shim.params.copy_(table)
+        ours.params.copy_(table.to(DEV))
+    torch.manual_seed(1)
+    x = torch.rand(3000, 3)
+    x[:16] = torch.tensor([[0.0, 1.0, 0.5]]) + torch.linspace(-0.3, 0.3, 16)[:, None]      # boundary and out-of-box points
+    xs = x.clone().requires_grad_(True)
+    xo = x.to(DEV).requires_grad_(True)
+    ys, yo = shim(xs), ours(xo)
+    util.assert_close(yo, ys, 'hash fwd', 1e-5)
+    gy = torch.randn(3000, 32)
+    ys.backward(gy)
+    yo.backward(gy.to(DEV))
+    util.assert_close(xo.grad, xs.grad, 'hash dx')
+    util.assert_close(ours.params.grad, shim.params.grad, 'hash dtable')
+    blob_s = tcnn_shim.Encoding(3, {'otype': 'OneBlob', 'n_bins': 16})
+    blob_o = tcnn.Encoding(3, {'otype': 'OneBlob', 'n_bins': 16}).to(DEV)
+    xs2 = x.clone().requires_grad_(True)
+    xo2 = x.to(DEV).requires_grad_(True)
+    bs, bo = blob_s(xs2), blob_o(xo2)
+    util.assert_close(bo, bs, 'oneblob fwd', 1e-5)
+    gb = torch.randn(3000, 48)
+    bs.backward(gb)
+    bo.backward(gb.to(DEV))
+    util.assert_close(xo2.grad, xs2.grad, 'oneblob dx')
+
+
+def test_query_api_matches_oracle():
+    g = util.load_golden('room0_trained')
+    cfg, _, table, weights, _ = util.case_inputs(g)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    orc = util.make_oracle(cfg, table, weights)
+    torch.manual_seed(2)
+    x = torch.rand(7, 50, 3)
+    xd = x.to(DEV)
+    with torch.no_grad():
+        util.assert_close(model.query_sdf(xd), orc.query_sdf(x), 'query_sdf')
+        s, geo = model.query_sdf(xd, return_geo=True)
+        s2, geo2 = orc.query_sdf(x, return_geo=True)
+        assert tuple(geo.shape) == (7, 50, 15)
+        util.assert_close(geo, geo2, 'geo_feat')
+        util.assert_close(model.query_sdf(xd, embed=True), orc.query_sdf(x, embed=True), 'embed', 1e-5)
+        util.assert_close(model.query_color_sdf(xd), orc.query_color_sdf(x), 'query_color_sdf')
+        util.assert_close(model.query_color(xd), orc.query_color(x), 'query_color')
+        pts = x * (synth.bound_tensor(cfg)[:, 1] - synth.bound_tensor(cfg)[:, 0]) + synth.bound_tensor(cfg)[:, 0]
+        util.assert_close(model.run_network(pts.to(DEV)), orc.run_network(pts), 'run_network')
+    # gradients of the explicit-point path (mesh colour / smoothness style use): d sdf / d x and d embed / d table
+    xg = x.reshape(-1, 3).clone().requires_grad_(True)
+    xgd = x.reshape(-1, 3).to(DEV).requires_grad_(True)
+    orc.query_sdf(xg).sum().backward()
+    model.query_sdf(xgd).sum().backward()
+    util.assert_close(xgd.grad, xg.grad, 'd query_sdf / d x')
+    util.assert_close(model.embed_fn.params.grad, orc.table.grad, 'd query_sdf / d table')
+
+
+def test_device_noise_mode_statistics():
+    """Philox mode is a different random stream: check that it is a valid stratified jitter (ordering, bounds, mean)."""
+    cfg = synth.room0_config()
+    rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, 2048, seed=4)
+    g = util.load_golden('room0_small')
+    _, _, table, weights, _ = util.case_inputs(g)
+    model = util.make_cuda_model(cfg, table, weights, DEV, noise_mode='device')
+    z0 = ops.sample_rays(model.spec, depth.to(DEV), perturb=False)
+    z1 = ops.sample_rays(model.spec, depth.to(DEV), noise=None, seed=123)
+    z2 = ops.sample_rays(model.spec, depth.to(DEV), noise=None, seed=124)
+    assert not torch.equal(z1, z2)
+    assert bool((z1[:, 1:] >= z1[:, :-1]).all())
+    mids = 0.5 * (z0[:, 1:] + z0[:, :-1])
+    lower = torch.cat([z0[:, :1], mids], -1)
+    upper = torch.cat([mids, z0[:, -1:]], -1)
+    assert bool((z1 >= lower - 1e-6).all()) and bool((z1 <= upper + 1e-6).all())
+    u = ((z1 - lower) / (upper - lower).clamp_min(1e-12))[(upper - lower) > 1e-6]
+    assert abs(float(u.mean()) - 0.5) < 0.01 and abs(float(u.var()) - 1.0 / 12.0) < 0.005
+
+
+def test_empty_batch():
+    cfg = synth.room0_config()
+    g = util.load_golden('room0_small')
+    _, _, table, weights, _ = util.case_inputs(g)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    model.eval()
+    e = torch.zeros((0, 3), device=DEV)
+    with torch.no_grad():
+        ev = model.forward(e, e, e, torch.zeros((0, 1), device=DEV))
+    assert tuple(ev['raw'].shape) == (0, 43, 4) and tuple(ev['rgb'].shape) == (0, 3)
