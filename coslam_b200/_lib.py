@@ -49,7 +49,8 @@ class Mlp(ctypes.Structure):
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
            'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays',
            'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd',
-           'cb200_debug_positions', 'cb200_selftest_mma']
+           'cb200_debug_positions', 'cb200_selftest_mma', 'cb200_set_decoder',
+           'cb200_get_decoder']
 
 _lib = None
 
@@ -79,10 +80,19 @@ def load():
         raise RuntimeError('coslam_b200: ABI version mismatch (library %d, binding %d); rebuild with '
                            '`python -m coslam_b200.build --force`' % (lib.cb200_abi_version(), ABI_VERSION))
     _lib = lib
+    if os.environ.get('COSLAM_B200_DECODER'):
+        lib.cb200_set_decoder({'simt': 0, 'tc': 1}[os.environ['COSLAM_B200_DECODER']])
     return lib
 
 
 KERNEL_LAUNCHES = 0        # every successful device call below launches exactly one kernel of this library
+
+
+def set_decoder(kind):
+    """'tc' (tcgen05 tensor-core decoder, default) or 'simt' (fp32 FMA decoder)."""
+    rc = load().cb200_set_decoder({'simt': 0, 'tc': 1}[kind])
+    if rc != 0:
+        raise RuntimeError('cb200_set_decoder failed')
 
 
 def check(rc, what):

@@ -28,6 +28,8 @@ int cuda_result(cudaError_t e, const char* what) {
         if (!(cond)) return fail(-1, __VA_ARGS__); \
     } while (0)
 
+int g_decoder = 1;      // 0 = SIMT decoder (points.cu), 1 = tcgen05 decoder (points_tc.cu)
+
 int check_grid(const cb200_grid* g) {
     CB_REQUIRE(g != nullptr, "grid is NULL");
     CB_REQUIRE(g->n_levels >= 1 && g->n_levels <= CB200_MAX_LEVELS, "n_levels %u not in [1,%d]", g->n_levels, CB200_MAX_LEVELS);
@@ -50,6 +52,14 @@ extern "C" {
 int cb200_abi_version(void) { return CB200_ABI_VERSION; }
 
 const char* cb200_last_error(void) { return g_err; }
+
+int cb200_set_decoder(int kind) {
+    CB_REQUIRE(kind == 0 || kind == 1, "decoder kind must be 0 (simt) or 1 (tcgen05)");
+    g_decoder = kind;
+    return 0;
+}
+
+int cb200_get_decoder(void) { return g_decoder; }
 
 int cb200_device_sm_count(void) {
     int dev = 0, sms = 0;
@@ -174,6 +184,7 @@ int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_m
     if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
     if (a.n_points == 0) return 0;
     a.raw = raw; a.geo = geo; a.act_mask = act_mask; a.sdf_only = sdf_only;
+    if (g_decoder == 1) return cuda_result(cb200::launch_points_fwd_tc(a, (cudaStream_t)stream), "points_fwd_tc");
     return cuda_result(cb200::launch_points_fwd(a, (cudaStream_t)stream), "points_fwd");
 }
 

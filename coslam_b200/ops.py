@@ -14,6 +14,10 @@ from ._lib import check, ptr, stream
 
 N_GEO = 15
 
+# tests set KEEP_LAST_MASK to read back the ReLU sign bits the last ray forward saved for its backward
+KEEP_LAST_MASK = False
+LAST_MASK = None
+
 # bench.py sets this to a list to collect (name, start_event, end_event) around the two per-point kernels
 KERNEL_EVENTS = None
 
@@ -253,6 +257,9 @@ class RayPointsFunction(torch.autograd.Function):
         need_grad = any(ctx.needs_input_grad)
         ctx.set_materialize_grads(False)
         raw, _, mask = points_forward(spec.scene(), tb, w, rays=(o, d, z), want_mask=need_grad)
+        if KEEP_LAST_MASK:
+            global LAST_MASK
+            LAST_MASK = mask
         ctx.spec = spec
         ctx.save_for_backward(o, d, z, tb, *w, mask if mask is not None else torch.empty(0))
         return raw.view(z.shape[0], z.shape[1], 4)

@@ -93,6 +93,10 @@ typedef struct cb200_mlp_grad {
 
 int cb200_abi_version(void);
 const char* cb200_last_error(void);
+/* decoder implementation used by cb200_points_fwd / cb200_points_bwd: 1 = tcgen05 tensor-core decoder (default),
+ * 0 = SIMT fp32 decoder (kept as the A/B reference of the tensor-core path).  Process-wide, not thread-safe. */
+int cb200_set_decoder(int kind);
+int cb200_get_decoder(void);
 /* number of SMs of the current device (host query), used by callers to size persistent grids/workspaces */
 int cb200_device_sm_count(void);
 

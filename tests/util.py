@@ -72,3 +72,25 @@ def assert_close(a, b, what, tol=REL_TOL):
     e = rel_err(a, b)
     assert e <= tol, '%s: relative error %.3e exceeds %.1e' % (what, e, tol)
     return e
+
+
+def unpack_masks(mask):
+    """[P,2] int32 ReLU sign words (hidden layer of the SDF net, hidden layer of the colour net) -> two bool [P,32]."""
+    m = mask.detach().cpu().to(torch.int64) & 0xFFFFFFFF
+    bits = torch.arange(32, dtype=torch.int64)
+    return ((m[:, 0:1] >> bits) & 1).bool(), ((m[:, 1:2] >> bits) & 1).bool()
+
+
+def audit_activation_flips(cuda_masks, oracle_pre, max_frac=2e-5, band=1e-4):
+    """The CUDA forward and the oracle may disagree on the sign of a pre-activation only where it is ~0 (within `band` of
+    the layer's largest magnitude), and only on a vanishing fraction of units."""
+    n_flip = 0
+    for m, h in zip(cuda_masks, oracle_pre):
+        diff = m != (h > 0)
+        n_flip += int(diff.sum())
+        if diff.any():
+            worst = float(h[diff].abs().max() / h.abs().max())
+            assert worst <= band, 'activation sign differs at a pre-activation of relative size %.2e' % worst
+    total = sum(m.numel() for m in cuda_masks)
+    assert n_flip <= max(2, max_frac * total), '%d of %d activation signs differ' % (n_flip, total)
+    return n_flip
