@@ -205,6 +205,7 @@ int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_m
         a.dw1 = d_mlp->w_sdf0; a.dw2 = d_mlp->w_sdf1; a.dw3 = d_mlp->w_col0; a.dw4 = d_mlp->w_col1;
     }
     a.d_pts = d_pts; a.d_rays_o = d_rays_o; a.d_rays_d = d_rays_d;
+    if (g_decoder == 1) return cuda_result(cb200::launch_points_bwd_tc(a, (cudaStream_t)stream), "points_bwd_tc");
     return cuda_result(cb200::launch_points_bwd(a, (cudaStream_t)stream), "points_bwd");
 }
 

@@ -71,6 +71,7 @@ cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st);
 cudaError_t launch_loss_finish(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
                                float* losses, float* coef, cudaStream_t st);
 cudaError_t launch_points_fwd(const PointsArgs& a, cudaStream_t st);
+cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_points_bwd(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_debug_positions(const PointsArgs& a, float* pts_out, float* x_out, cudaStream_t st);

@@ -272,6 +272,385 @@ __global__ void __launch_bounds__(tc::kTile) points_fwd_tc_kernel(PointsArgs a) 
     if (warp == 0) tmem_dealloc<tc::kTmemCols>(tmem);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------------------------------
+// Per 128-point tile:
+//   (1) input-gradient chain on the tensor core, from d_raw and the saved ReLU masks only (no features needed):
+//         d_h3 = relu'(h3) . (d_rgb W4)                      SIMT (K = 3)
+//         d_in2 [128,64] = d_h3 W3        -> d_geo            round "b"
+//         d_h1 = relu'(h1) . (d_h2 W2)                        round "c"
+//         d_in1 [128,80] = d_h1 W1  (+= d_h3 W3[:, :48] on the OneBlob columns)   round "d"
+//   (2) ONE gather pass per point: dL/dx from the corner values and d_embed (read back from TMEM 8 columns at a time),
+//       the table scatter (red.global.add.v2.f32 per corner) and -- for the weight gradients -- the features, written
+//       into the A tile;
+//   (3) kWgrad: forward recompute on the tensor core (h1, h2, h3) and the four weight-gradient products, which read the
+//       SAME activation / gradient tiles through MN-major descriptors (reduction over the 128 points) and accumulate in
+//       TMEM for the whole persistent loop; one atomicAdd per weight per CTA at the end.
+// Shared memory (kWgrad): A 48 K | HG (d_h1 tile, then relu(h1), then relu(h3)) 16 K | G3 (d_h3) 16 K | G2 (d_h2, then d_rgb) 8 K
+//                         | weights 24 K  = 112 K  -> 2 CTAs/SM.
+// TMEM (256 columns): dW1^T 0 | dW3^T 32 | dW2^T 64 | dW4^T 80 | d_in1 96..175 | d_in2 176..239 | d_h1 224..255 (after d_in2 died)
+//                     forward recompute reuses 176.. : h1 176 | h2 208 | h3 224
+namespace tc {
+
+constexpr uint32_t kG2GS = 2 * 128, kG2Bytes = 16 * kG2GS;    // [128 x 16] tile: 4096 per half
+
+constexpr uint32_t kBOffHG = kOffHHi;                          // reuse the forward layout: A | H(=HG) | weights ...
+constexpr uint32_t kBOffG3Hi = kFwdSmem, kBOffG3Lo = kBOffG3Hi + kHBytes;
+constexpr uint32_t kBOffG2Hi = kBOffG3Lo + kHBytes, kBOffG2Lo = kBOffG2Hi + kG2Bytes;
+constexpr uint32_t kBOffW4f = kBOffG2Lo + kG2Bytes;            // fp32 copy of W4 [3][32]
+constexpr uint32_t kBwdSmem = kBOffW4f + 3 * 32 * 4;           // 90112 + 16384 + 8192 + 384 = 115072
+
+constexpr uint32_t kColDW1 = 0, kColDW3 = 32, kColDW2 = 64, kColDW4 = 80;
+constexpr uint32_t kColDin1 = 96, kColDin2 = 176, kColDh1 = 224;
+constexpr uint32_t kColRH1 = 176, kColRH2 = 208, kColRH3 = 224;
+constexpr int kBwdTmemCols = 256;
+
+}  // namespace tc
+
+template <bool kWgrad>
+__global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t sbase = smem_u32(smem);
+    const uint32_t a_hi = sbase + kOffAHi, a_lo = sbase + kOffALo;
+    const uint32_t hg_hi = sbase + kOffHHi, hg_lo = sbase + kOffHLo;
+    const uint32_t g3_hi = sbase + kBOffG3Hi, g3_lo = sbase + kBOffG3Lo;
+    const uint32_t g2_hi = sbase + kBOffG2Hi, g2_lo = sbase + kBOffG2Lo;
+    float* sW4f = reinterpret_cast<float*>(smem + kBOffW4f);
+
+    if (warp == 0) tmem_alloc<kBwdTmemCols>(&tmem_slot);
+    if (tid == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    stage_all_weights(sbase, a);
+    if (tid < 96) sW4f[tid] = a.w4[tid];
+    publish_tiles();
+    const uint32_t tmem = tmem_slot;
+    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+    uint32_t parity = 0;
+    bool first_tile = true;
+
+#define TC_WAIT()                 \
+    do {                          \
+        mbar_wait(&bar, parity);  \
+        parity ^= 1u;             \
+        tc_fence_after();         \
+    } while (0)
+
+    const int64_t n_tiles = (a.n_points + kTile - 1) / kTile;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t p_raw = tile * kTile + tid;
+        const bool valid = p_raw < a.n_points;
+        const int64_t p = valid ? p_raw : a.n_points - 1;
+        float x[3], zray;
+        point_position(a, p, x, zray);
+
+        // ---- (1) input-gradient chain ---------------------------------------------------------------------------------
+        float4 g = reinterpret_cast<const float4*>(a.d_raw)[p];
+        uint2 m = reinterpret_cast<const uint2*>(a.act_mask)[p];
+        if (!valid) g = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.sdf_only) { g.x = g.y = g.z = 0.f; m.y = 0u; }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int j = c * 8 + e;
+                const float t = sW4f[j] * g.x + sW4f[32 + j] * g.y + sW4f[64 + j] * g.z;
+                v[e] = ((m.y >> j) & 1u) ? t : 0.f;
+            }
+            tile_store8(g3_hi, g3_lo, kHGS, tid, c, v);
+        }
+        publish_tiles();
+        if (tid == 0) {      // round b: d_in2 = d_h3 W3   (B = W3 tile read MN-major: reduce over its rows)
+            umma_split3(tmem + kColDin2, g3_hi, g3_lo, 128u, kHGS, 256u, sbase + kOffW3Hi, sbase + kOffW3Lo, kW3GS, 128u, 2 * kW3GS, 2,
+                        umma_idesc_bf16(128, 64, false, true), false);
+            umma_commit(&bar);
+        }
+        TC_WAIT();
+        {
+            uint32_t r[16];
+            tmem_ld_x16(trow + kColDin2 + 48, r);      // columns 48..62 = d geo
+            tmem_ld_wait();
+            float v[8];
+            v[0] = g.w;
+#pragma unroll
+            for (int e = 1; e < 8; ++e) {
+                float t = __uint_as_float(r[e - 1]);
+                if (a.d_geo && valid) t += a.d_geo[p * kGeo + (e - 1)];
+                v[e] = t;
+            }
+            tile_store8(g2_hi, g2_lo, kG2GS, tid, 0, v);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                float t = __uint_as_float(r[7 + e]);
+                if (a.d_geo && valid) t += a.d_geo[p * kGeo + 7 + e];
+                v[e] = t;
+            }
+            tile_store8(g2_hi, g2_lo, kG2GS, tid, 1, v);
+        }
+        publish_tiles();
+        if (tid == 0) {      // round c: d_h1 (pre-mask) = d_h2 W2
+            umma_split3(tmem + kColDh1, g2_hi, g2_lo, 128u, kG2GS, 256u, sbase + kOffW2Hi, sbase + kOffW2Lo, kW2GS, 128u, 2 * kW2GS, 1,
+                        umma_idesc_bf16(128, 32, false, true), false);
+            umma_commit(&bar);
+        }
+        TC_WAIT();
+        {
+            uint32_t r[32];
+            tmem_ld_x32(trow + kColDh1, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = ((m.x >> (c * 8 + e)) & 1u) ? __uint_as_float(r[c * 8 + e]) : 0.f;
+                tile_store8(hg_hi, hg_lo, kHGS, tid, c, v);
+            }
+        }
+        publish_tiles();
+        if (tid == 0) {      // round d: d_in1 = d_h1 W1, then the OneBlob columns += d_h3 W3[:, :48]
+            umma_split3(tmem + kColDin1, hg_hi, hg_lo, 128u, kHGS, 256u, sbase + kOffW1Hi, sbase + kOffW1Lo, kW1GS, 128u, 2 * kW1GS, 2,
+                        umma_idesc_bf16(128, 80, false, true), false);
+            umma_split3(tmem + kColDin1 + 32, g3_hi, g3_lo, 128u, kHGS, 256u, sbase + kOffW3Hi, sbase + kOffW3Lo, kW3GS, 128u, 2 * kW3GS, 2,
+                        umma_idesc_bf16(128, 48, false, true), true);
+            umma_commit(&bar);
+        }
+        TC_WAIT();
+
+        // ---- (2) one gather pass: dL/dx, table scatter, features -----------------------------------------------------------
+        float dx[3] = {0.f, 0.f, 0.f};
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t de[8];
+            tmem_ld_x8(trow + kColDin1 + 8 * c, de);            // d embed of levels 4c .. 4c+3
+            float2 v[4][8];
+            uint32_t idx[4][8];
+            float w[4][3];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                LevelCorners lc;
+                level_corners(a.scene, 4 * c + q, x, lc);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    idx[q][k] = lc.idx[k];
+                    v[q][k] = ldg_f2(a.table + lc.idx[k]);
+                }
+                w[q][0] = lc.w[0]; w[q][1] = lc.w[1]; w[q][2] = lc.w[2];
+            }
+            tmem_ld_wait();
+            float feat[8];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float de0 = __uint_as_float(de[2 * q]), de1 = __uint_as_float(de[2 * q + 1]);
+                float s[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] = v[q][k].x * de0 + v[q][k].y * de1;
+                const float w0 = w[q][0], w1 = w[q][1], w2 = w[q][2];
+                const float scale = a.scene.scale[4 * c + q];
+                const float gx = (1.f - w1) * (1.f - w2) * (s[1] - s[0]) + w1 * (1.f - w2) * (s[3] - s[2]) +
+                                 (1.f - w1) * w2 * (s[5] - s[4]) + w1 * w2 * (s[7] - s[6]);
+                const float gy = (1.f - w0) * (1.f - w2) * (s[2] - s[0]) + w0 * (1.f - w2) * (s[3] - s[1]) +
+                                 (1.f - w0) * w2 * (s[6] - s[4]) + w0 * w2 * (s[7] - s[5]);
+                const float gz = (1.f - w0) * (1.f - w1) * (s[4] - s[0]) + w0 * (1.f - w1) * (s[5] - s[1]) +
+                                 (1.f - w0) * w1 * (s[6] - s[2]) + w0 * w1 * (s[7] - s[3]);
+                dx[0] = fmaf(scale, gx, dx[0]);
+                dx[1] = fmaf(scale, gy, dx[1]);
+                dx[2] = fmaf(scale, gz, dx[2]);
+                float f0 = 0.f, f1 = 0.f;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float wc = corner_weight(w[q], k);
+                    if (a.dtable && valid) red_add_f2(a.dtable + idx[q][k], wc * de0, wc * de1);
+                    if (kWgrad) {
+                        f0 = fmaf(wc, v[q][k].x, f0);
+                        f1 = fmaf(wc, v[q][k].y, f1);
+                    }
+                }
+                feat[2 * q] = f0;
+                feat[2 * q + 1] = f1;
+            }
+            if (kWgrad) tile_store8(a_hi, a_lo, kAGS, tid, c, feat);
+        }
+        // OneBlob: backward into dx (gradient columns 32..79 of d_in1), forward values into the A tile
+#pragma unroll 1
+        for (int d = 0; d < 3; ++d) {
+            uint32_t gb[16];
+            tmem_ld_x16(trow + kColDin1 + 32 + 16 * d, gb);
+            const float f_first = blob_edge_cdf(0.f, x[d], (float)kBins);
+            const float k_first = blob_edge_pdf(0.f, x[d], (float)kBins);
+            float f_prev = f_first, k_prev = k_first, acc = 0.f;
+            tmem_ld_wait();
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int b = half * 8 + e;
+                    const float edge = (float)(b + 1) / (float)kBins;
+                    const float f_next = (b == kBins - 1) ? f_first + 1.0f : blob_edge_cdf(edge, x[d], (float)kBins);
+                    const float k_next = (b == kBins - 1) ? k_first : blob_edge_pdf(edge, x[d], (float)kBins);
+                    acc += __uint_as_float(gb[b]) * (k_prev - k_next);
+                    v[e] = f_next - f_prev;
+                    f_prev = f_next;
+                    k_prev = k_next;
+                }
+                if (kWgrad) tile_store8(a_hi, a_lo, kAGS, tid, 4 + d * 2 + half, v);
+            }
+            dx[d] += acc;
+        }
+
+        // ---- (3) forward recompute + weight gradients -------------------------------------------------------------------------
+        if (kWgrad) {
+            publish_tiles();
+            if (tid == 0) {      // h1 = in1 W1^T ;  dW1^T += in1^T d_h1   (A tile and HG tile read MN-major, reduce over the points)
+                umma_split3(tmem + kColRH1, a_hi, a_lo, 128u, kAGS, 256u, sbase + kOffW1Hi, sbase + kOffW1Lo, 128u, kW1GS, 256u, 5,
+                            umma_idesc_bf16(128, 32, false, false), false);
+                umma_split3(tmem + kColDW1, a_hi, a_lo, kAGS, 128u, 2 * kAGS, hg_hi, hg_lo, kHGS, 128u, 2 * kHGS, 8,
+                            umma_idesc_bf16(128, 32, true, true), !first_tile);
+                umma_commit(&bar);
+            }
+            TC_WAIT();
+            {
+                uint32_t r[32];
+                tmem_ld_x32(trow + kColRH1, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    float v[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) v[e] = ((m.x >> (c * 8 + e)) & 1u) ? __uint_as_float(r[c * 8 + e]) : 0.f;
+                    tile_store8(hg_hi, hg_lo, kHGS, tid, c, v);       // HG now holds relu(h1)
+                }
+            }
+            publish_tiles();
+            if (tid == 0) {      // h2 = relu(h1) W2^T ;  dW2^T += relu(h1)^T d_h2
+                umma_split3(tmem + kColRH2, hg_hi, hg_lo, 128u, kHGS, 256u, sbase + kOffW2Hi, sbase + kOffW2Lo, 128u, kW2GS, 256u, 2,
+                            umma_idesc_bf16(128, 16, false, false), false);
+                umma_split3(tmem + kColDW2, hg_hi, hg_lo, kHGS, 128u, 2 * kHGS, g2_hi, g2_lo, kG2GS, 128u, 2 * kG2GS, 8,
+                            umma_idesc_bf16(128, 16, true, true), !first_tile);
+                umma_commit(&bar);
+            }
+            TC_WAIT();
+            {
+                uint32_t r[16];
+                tmem_ld_x16(trow + kColRH2, r);
+                tmem_ld_wait();
+                float v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[1 + e]);
+                tile_store8(a_hi, a_lo, kAGS, tid, 10, v);
+#pragma unroll
+                for (int e = 0; e < 7; ++e) v[e] = __uint_as_float(r[9 + e]);
+                v[7] = 0.f;
+                tile_store8(a_hi, a_lo, kAGS, tid, 11, v);
+                // the d_h2 tile is dead now (dW2 completed): reuse it for d_rgb, the B operand of dW4
+                float u[8] = {g.x, g.y, g.z, 0.f, 0.f, 0.f, 0.f, 0.f};
+                tile_store8(g2_hi, g2_lo, kG2GS, tid, 0, u);
+                u[0] = u[1] = u[2] = 0.f;
+                tile_store8(g2_hi, g2_lo, kG2GS, tid, 1, u);
+            }
+            publish_tiles();
+            if (tid == 0) {      // h3 = [blob | geo] W3^T ;  dW3^T += [blob | geo]^T d_h3
+                umma_split3(tmem + kColRH3, a_hi + 4 * 128, a_lo + 4 * 128, 128u, kAGS, 256u, sbase + kOffW3Hi, sbase + kOffW3Lo, 128u, kW3GS,
+                            256u, 4, umma_idesc_bf16(128, 32, false, false), false);
+                umma_split3(tmem + kColDW3, a_hi + 4 * 128, a_lo + 4 * 128, kAGS, 128u, 2 * kAGS, g3_hi, g3_lo, kHGS, 128u, 2 * kHGS, 8,
+                            umma_idesc_bf16(128, 32, true, true), !first_tile);
+                umma_commit(&bar);
+            }
+            TC_WAIT();
+            {
+                uint32_t r[32];
+                tmem_ld_x32(trow + kColRH3, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    float v[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) v[e] = ((m.y >> (c * 8 + e)) & 1u) ? __uint_as_float(r[c * 8 + e]) : 0.f;
+                    tile_store8(hg_hi, hg_lo, kHGS, tid, c, v);       // HG now holds relu(h3)
+                }
+            }
+            publish_tiles();
+            if (tid == 0) {      // dW4^T += relu(h3)^T d_rgb
+                umma_split3(tmem + kColDW4, hg_hi, hg_lo, kHGS, 128u, 2 * kHGS, g2_hi, g2_lo, kG2GS, 128u, 2 * kG2GS, 8,
+                            umma_idesc_bf16(128, 16, true, true), !first_tile);
+                umma_commit(&bar);
+            }
+            TC_WAIT();           // the tiles are rewritten by the next iteration
+            first_tile = false;
+        }
+
+        // ---- position gradient ------------------------------------------------------------------------------------------------
+        float dp[3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) dp[d] = valid ? (a.scene.normalise ? dx[d] / a.scene.bb_ext[d] : dx[d]) : 0.f;
+        if (a.d_pts && valid) {
+#pragma unroll
+            for (int d = 0; d < 3; ++d) a.d_pts[p * 3 + d] = dp[d];
+        }
+        if (a.d_rays_o) {
+            const int64_t ray = valid ? p / a.n_samples : -1;
+            float v6[6] = {dp[0], dp[1], dp[2], dp[0] * zray, dp[1] * zray, dp[2] * zray};
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int64_t r2 = __shfl_down_sync(0xffffffffu, ray, o);
+                const bool take = (lane + o < 32) && (r2 == ray);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    const float t = __shfl_down_sync(0xffffffffu, v6[i], o);
+                    if (take) v6[i] += t;
+                }
+            }
+            const int64_t rprev = __shfl_up_sync(0xffffffffu, ray, 1);
+            if (valid && (lane == 0 || rprev != ray)) {
+#pragma unroll
+                for (int d = 0; d < 3; ++d) {
+                    atomicAdd(a.d_rays_o + ray * 3 + d, v6[d]);
+                    atomicAdd(a.d_rays_d + ray * 3 + d, v6[3 + d]);
+                }
+            }
+        }
+        tc_fence_before();
+        __syncthreads();         // every lane has read its d_in1 columns before the next tile's MMAs overwrite TMEM
+    }
+#undef TC_WAIT
+
+    if (kWgrad && !first_tile) {
+        // lane = row of the transposed weight gradients: dW1^T [80 x 32], dW3^T [63 x 32], dW2^T [32 x 16], dW4^T [32 x 3]
+        tc_fence_after();
+        uint32_t r[32];
+        tmem_ld_x32(trow + kColDW1, r);
+        tmem_ld_wait();
+        if (tid < kSdfIn) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) atomicAdd(a.dw1 + j * kSdfIn + tid, __uint_as_float(r[j]));
+        }
+        tmem_ld_x32(trow + kColDW3, r);
+        tmem_ld_wait();
+        if (tid < kColIn) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) atomicAdd(a.dw3 + j * kColIn + tid, __uint_as_float(r[j]));
+        }
+        tmem_ld_x32(trow + kColDW2, r);      // columns 64..79 = dW2^T, 80..95 = dW4^T
+        tmem_ld_wait();
+        if (tid < kHidden) {
+#pragma unroll
+            for (int i = 0; i < kSdfOut; ++i) atomicAdd(a.dw2 + i * kHidden + tid, __uint_as_float(r[i]));
+#pragma unroll
+            for (int c = 0; c < 3; ++c) atomicAdd(a.dw4 + c * kHidden + tid, __uint_as_float(r[16 + c]));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<tc::kBwdTmemCols>(tmem);
+}
+
 static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -280,6 +659,22 @@ static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
     if (g > n_tiles) g = n_tiles;
     if (g < 1) g = 1;
     return (int)g;
+}
+
+cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st) {
+    const bool wgrad = a.dw1 != nullptr;
+    const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
+    const size_t smem = tc::kBwdSmem;
+    if (wgrad) {
+        cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        points_bwd_tc_kernel<true><<<tc_persistent_grid(n_tiles, 2), tc::kTile, smem, st>>>(a);
+    } else {
+        cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        points_bwd_tc_kernel<false><<<tc_persistent_grid(n_tiles, 2), tc::kTile, smem, st>>>(a);
+    }
+    return cudaGetLastError();
 }
 
 cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st) {
