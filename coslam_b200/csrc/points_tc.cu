@@ -61,54 +61,108 @@ __device__ __forceinline__ void stage_all_weights(uint32_t sbase, const PointsAr
     stage_weight(sbase + kOffW4Hi, sbase + kOffW4Lo, kW4GS, a.w4, 16, 4, 3, kHidden);
 }
 
-// hash-grid features of one point -> chunks 0..3 of the A tile.  Four levels (32 gathers) are in flight per thread.
-__device__ __forceinline__ void encode_grid_to_tile(const PointsArgs& a, const float x[3], uint32_t a_hi, uint32_t a_lo, int row) {
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-        float2 v[4][8];
-        float w[4][3];
+// Thread roles (256 threads per 128-point tile, warp w = (quadrant q = w & 3, hsel = w >> 2), lane l):
+//   * epilogue role: row_e = 32 q + l -- the TMEM lane this thread reads with tcgen05.ld (warps q and q + 4 address the same 32
+//     lanes) -- and 16 of each 32-column accumulator row, selected by half = hsel;
+//   * gather role: row_g = 32 q + 16 hsel + (l >> 1), xb = l & 1: a LANE PAIR shares one point and thread xb owns the four
+//     corners at x = cell.x + xb of every level.  The two x-neighbours of a corner are adjacent table entries on the dense
+//     levels and, on the hashed levels, share a 128-byte line 15 times out of 16 (the hash leaves x un-multiplied), so one
+//     warp-wide LDG / RED touches ~16 lines instead of 32.  profiles/r1/NOTES.md: the L1TEX data pipe replays a scattered
+//     request once per line and was the saturated unit (~2 cycles per wavefront) -- halving the lines per request is what
+//     this layout is for.  Pair partial sums are combined with shfl.xor 1; TMEM values (lane = row_e) reach the pair that owns
+//     the row with one shfl from lane 16 hsel + (l >> 1) of the same warp.
+constexpr int kThreads = 256;
+
+struct HalfCorners {
+    uint32_t idx[4];      // (y, z) = (j & 1, j >> 1) corners at this thread's x
+    float wx, w1, w2;
+};
+
+__device__ __forceinline__ void level_corners_x(const SceneDev& sc, int l, const float x[3], int xb, HalfCorners& hc) {
+    const float scale = sc.scale[l];
+    const uint32_t res = sc.res[l];
+    const uint32_t size = sc.offset[l + 1] - sc.offset[l];
+    const bool hashed = sc.hashed[l] != 0;
+    uint32_t cell[3];
+    float w0;
+    grid_pos(scale, x[0], cell[0], w0);
+    grid_pos(scale, x[1], cell[1], hc.w1);
+    grid_pos(scale, x[2], cell[2], hc.w2);
+    hc.wx = xb ? w0 : 1.f - w0;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            LevelCorners lc;
-            level_corners(a.scene, 4 * c + q, x, lc);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[q][k] = ldg_f2(a.table + lc.idx[k]);
-            w[q][0] = lc.w[0]; w[q][1] = lc.w[1]; w[q][2] = lc.w[2];
-        }
-        float feat[8];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            float f0 = 0.f, f1 = 0.f;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const float wc = corner_weight(w[q], k);
-                f0 = fmaf(wc, v[q][k].x, f0);
-                f1 = fmaf(wc, v[q][k].y, f1);
-            }
-            feat[2 * q] = f0;
-            feat[2 * q + 1] = f1;
-        }
-        tile_store8(a_hi, a_lo, kAGS, row, c, feat);
-    }
+    for (int j = 0; j < 4; ++j) hc.idx[j] = sc.offset[l] + grid_index(hashed, size, res, cell[0] + xb, cell[1] + (j & 1), cell[2] + (j >> 1));
 }
 
-// OneBlob features -> chunks 4..9 of the A tile
-__device__ __forceinline__ void encode_blob_to_tile(const float x[3], uint32_t a_hi, uint32_t a_lo, int row) {
-#pragma unroll 1
-    for (int d = 0; d < 3; ++d) {
-        const float f_first = blob_edge_cdf(0.f, x[d], (float)kBins);
-        float f_prev = f_first;
+__device__ __forceinline__ float yz_weight(float w1, float w2, int j) { return ((j & 1) ? w1 : 1.f - w1) * ((j & 2) ? w2 : 1.f - w2); }
+
+// 4 consecutive columns (sub = 0 / 1: first / second half of a chunk) of row r into the hi and lo tiles
+__device__ __forceinline__ void tile_store4(uint32_t hi_base, uint32_t lo_base, uint32_t group_stride, int r, int chunk, int sub, const float (&v)[4]) {
+    uint32_t h[2], l[2];
+    split_bf16x2(v[0], v[1], h[0], l[0]);
+    split_bf16x2(v[2], v[3], h[1], l[1]);
+    const uint32_t off = (uint32_t)(r >> 3) * group_stride + (uint32_t)chunk * 128u + (uint32_t)(r & 7) * 16u + (uint32_t)sub * 8u;
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(hi_base + off), "r"(h[0]), "r"(h[1]) : "memory");
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(lo_base + off), "r"(l[0]), "r"(l[1]) : "memory");
+}
+
+// the pair's per-corner partial features of one chunk (4 levels x 2) -> complete features; thread xb keeps columns 4 xb .. 4 xb + 3
+__device__ __forceinline__ void pair_combine_store(const float (&part)[8], int xb, uint32_t a_hi, uint32_t a_lo, int row, int c) {
+    float mine[4];
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            float v[8];
+    for (int i = 0; i < 4; ++i) {
+        const float send = xb ? part[i] : part[4 + i];
+        const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+        mine[i] = (xb ? part[4 + i] : part[i]) + recv;
+    }
+    tile_store4(a_hi, a_lo, kAGS, row, c, xb, mine);
+}
+
+// one chunk (4 levels, 8 features) of hash-grid features -> A tile; 16 gathers in flight per thread
+__device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row) {
+    float2 v[4][4];
+    float wx[4], w1[4], w2[4];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const int b = half * 8 + e;
-                const float f_next = (b == kBins - 1) ? f_first + 1.0f : blob_edge_cdf((float)(b + 1) / (float)kBins, x[d], (float)kBins);
-                v[e] = f_next - f_prev;
-                f_prev = f_next;
-            }
-            tile_store8(a_hi, a_lo, kAGS, row, 4 + d * 2 + half, v);
+    for (int q = 0; q < 4; ++q) {
+        HalfCorners hc;
+        level_corners_x(a.scene, 4 * c + q, x, xb, hc);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[q][j] = ldg_f2(a.table + hc.idx[j]);
+        wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
+    }
+    float part[8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        float f0 = 0.f, f1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
+            f0 = fmaf(wc, v[q][j].x, f0);
+            f1 = fmaf(wc, v[q][j].y, f1);
+        }
+        part[2 * q] = f0;
+        part[2 * q + 1] = f1;
+    }
+    pair_combine_store(part, xb, a_hi, a_lo, row, c);
+}
+
+// OneBlob bins 8*hb .. 8*hb+7 of one coordinate: values (and optionally d value / d x) from the 9 bin-edge CDFs
+template <bool kDeriv>
+__device__ __forceinline__ void blob_half(float xd, int hb, float (&val)[8], float (&dval)[8]) {
+    const float nb = (float)kBins;
+    float f_prev = blob_edge_cdf((float)(8 * hb) / nb, xd, nb);
+    float k_prev = kDeriv ? blob_edge_pdf((float)(8 * hb) / nb, xd, nb) : 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        const int b = 8 * hb + e + 1;                    // right edge index
+        // the last right edge wraps: F(1 - x) = F(0 - x) + 1, identical kernel value
+        const float edge = (b == kBins) ? 0.f : (float)b / nb;
+        const float f_next = blob_edge_cdf(edge, xd, nb) + ((b == kBins) ? 1.0f : 0.f);
+        val[e] = f_next - f_prev;
+        f_prev = f_next;
+        if (kDeriv) {
+            const float k_next = blob_edge_pdf(edge, xd, nb);
+            dval[e] = k_prev - k_next;
+            k_prev = k_next;
         }
     }
 }
@@ -121,17 +175,48 @@ __device__ __forceinline__ void publish_tiles() {
     tc_fence_after();
 }
 
+// relu + sign bits of 16 accumulator columns -> two chunks of a [128 x 32] tile
+__device__ __forceinline__ uint32_t relu16_to_tile(const uint32_t (&r)[16], uint32_t hi, uint32_t lo, int row, int half) {
+    uint32_t bits = 0;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const float h = __uint_as_float(r[c * 8 + e]);
+            const bool on = h > 0.f;
+            bits |= on ? (1u << (c * 8 + e)) : 0u;
+            v[e] = on ? h : 0.f;
+        }
+        tile_store8(hi, lo, kHGS, row, 2 * half + c, v);
+    }
+    return bits;
+}
+
+// masked copy (given sign bits) of 16 accumulator columns -> two chunks of a [128 x 32] tile
+__device__ __forceinline__ void mask16_to_tile(const uint32_t (&r)[16], uint32_t bits, uint32_t hi, uint32_t lo, int row, int half) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = ((bits >> (c * 8 + e)) & 1u) ? __uint_as_float(r[c * 8 + e]) : 0.f;
+        tile_store8(hi, lo, kHGS, row, 2 * half + c, v);
+    }
+}
+
 }  // namespace tc
 
 // ------------------------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(tc::kTile) points_fwd_tc_kernel(PointsArgs a) {
+__global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsArgs a) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint64_t bar;
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int row = tid & (kTile - 1), half = tid >> 7;                                  // epilogue role
+    const int row_g = (warp & 3) * 32 + (warp >> 2) * 16 + ((tid & 31) >> 1), xb = tid & 1;  // gather role
     const uint32_t sbase = smem_u32(smem);
     const uint32_t a_hi = sbase + kOffAHi, a_lo = sbase + kOffALo, h_hi = sbase + kOffHHi, h_lo = sbase + kOffHLo;
 
@@ -143,19 +228,36 @@ __global__ void __launch_bounds__(tc::kTile) points_fwd_tc_kernel(PointsArgs a) 
     stage_all_weights(sbase, a);
     publish_tiles();
     const uint32_t tmem = tmem_slot;
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);      // this warp's 32 TMEM lanes
+    const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);      // this warp's 32 TMEM lanes
     uint32_t parity = 0;
+    uint16_t* mask16 = reinterpret_cast<uint16_t*>(a.act_mask);
+
+#define TC_WAIT()                 \
+    do {                          \
+        mbar_wait(&bar, parity);  \
+        parity ^= 1u;             \
+        tc_fence_after();         \
+    } while (0)
 
     const int64_t n_tiles = (a.n_points + kTile - 1) / kTile;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int64_t p_raw = tile * kTile + tid;
+        const int64_t p_raw = tile * kTile + row;
         const bool valid = p_raw < a.n_points;
         const int64_t p = valid ? p_raw : a.n_points - 1;
-        float x[3], zdummy;
-        point_position(a, p, x, zdummy);
-        encode_grid_to_tile(a, x, a_hi, a_lo, tid);
-        encode_blob_to_tile(x, a_hi, a_lo, tid);
-
+        {
+            const int64_t pg_raw = tile * kTile + row_g;
+            const int64_t pg = pg_raw < a.n_points ? pg_raw : a.n_points - 1;
+            float x[3], zdummy;
+            point_position(a, pg, x, zdummy);
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) encode_grid_chunk(a, x, xb, c, a_hi, a_lo, row_g);
+#pragma unroll 1
+            for (int d = 0; d < 3; ++d) {             // OneBlob: thread xb does bins 8 xb .. 8 xb + 7 of every coordinate
+                float v[8], unused[8];
+                blob_half<false>(x[d], xb, v, unused);
+                tile_store8(a_hi, a_lo, kAGS, row_g, 4 + 2 * d + xb, v);
+            }
+        }
         // ---- SDF net layer 1: h1[128,32] = in1[128,80] W1^T ----------------------------------------------------------
         publish_tiles();
         if (tid == 0) {
@@ -163,26 +265,13 @@ __global__ void __launch_bounds__(tc::kTile) points_fwd_tc_kernel(PointsArgs a) 
                         umma_idesc_bf16(128, 32, false, false), false);
             umma_commit(&bar);
         }
-        mbar_wait(&bar, parity);
-        parity ^= 1u;
-        tc_fence_after();
-        uint32_t m1 = 0;
+        TC_WAIT();
+        uint32_t m1;
         {
-            uint32_t r[32];
-            tmem_ld_x32(trow + kColH1, r);
+            uint32_t r[16];
+            tmem_ld_x16(trow + kColH1 + 16 * half, r);
             tmem_ld_wait();
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                float v[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const float h = __uint_as_float(r[c * 8 + e]);
-                    const bool on = h > 0.f;
-                    m1 |= on ? (1u << (c * 8 + e)) : 0u;
-                    v[e] = on ? h : 0.f;
-                }
-                tile_store8(h_hi, h_lo, kHGS, tid, c, v);
-            }
+            m1 = relu16_to_tile(r, h_hi, h_lo, row, half);
         }
         // ---- layer 2: h2[128,16] = relu(h1) W2^T ------------------------------------------------------------------------
         publish_tiles();
@@ -191,28 +280,28 @@ __global__ void __launch_bounds__(tc::kTile) points_fwd_tc_kernel(PointsArgs a) 
                         umma_idesc_bf16(128, 16, false, false), false);
             umma_commit(&bar);
         }
-        mbar_wait(&bar, parity);
-        parity ^= 1u;
-        tc_fence_after();
+        TC_WAIT();
         float sdf;
         {
             uint32_t r[16];
             tmem_ld_x16(trow + kColH2, r);
             tmem_ld_wait();
             sdf = __uint_as_float(r[0]);
-            if (a.geo && valid) {
+            if (a.geo && valid && half == 0) {
 #pragma unroll
                 for (int g = 0; g < kGeo; ++g) a.geo[p * kGeo + g] = __uint_as_float(r[1 + g]);
             }
             if (!a.sdf_only) {
                 float v[8];
+                if (half == 0) {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[1 + e]);
-                tile_store8(a_hi, a_lo, kAGS, tid, 10, v);
+                    for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[1 + e]);
+                } else {
 #pragma unroll
-                for (int e = 0; e < 7; ++e) v[e] = __uint_as_float(r[9 + e]);
-                v[7] = 0.f;
-                tile_store8(a_hi, a_lo, kAGS, tid, 11, v);
+                    for (int e = 0; e < 7; ++e) v[e] = __uint_as_float(r[9 + e]);
+                    v[7] = 0.f;
+                }
+                tile_store8(a_hi, a_lo, kAGS, row, 10 + half, v);
             }
         }
         float rgb[3] = {0.f, 0.f, 0.f};
@@ -225,25 +314,12 @@ __global__ void __launch_bounds__(tc::kTile) points_fwd_tc_kernel(PointsArgs a) 
                             256u, 4, umma_idesc_bf16(128, 32, false, false), false);
                 umma_commit(&bar);
             }
-            mbar_wait(&bar, parity);
-            parity ^= 1u;
-            tc_fence_after();
+            TC_WAIT();
             {
-                uint32_t r[32];
-                tmem_ld_x32(trow + kColH3, r);
+                uint32_t r[16];
+                tmem_ld_x16(trow + kColH3 + 16 * half, r);
                 tmem_ld_wait();
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    float v[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const float h = __uint_as_float(r[c * 8 + e]);
-                        const bool on = h > 0.f;
-                        m3 |= on ? (1u << (c * 8 + e)) : 0u;
-                        v[e] = on ? h : 0.f;
-                    }
-                    tile_store8(h_hi, h_lo, kHGS, tid, c, v);
-                }
+                m3 = relu16_to_tile(r, h_hi, h_lo, row, half);
             }
             // ---- colour net layer 2: rgb[128,16(3)] = relu(h3) W4^T --------------------------------------------------------
             publish_tiles();
@@ -252,23 +328,27 @@ __global__ void __launch_bounds__(tc::kTile) points_fwd_tc_kernel(PointsArgs a) 
                             umma_idesc_bf16(128, 16, false, false), false);
                 umma_commit(&bar);
             }
-            mbar_wait(&bar, parity);
-            parity ^= 1u;
-            tc_fence_after();
-            uint32_t r[4];
-            tmem_ld_x4(trow + kColRgb, r);
-            tmem_ld_wait();
-            rgb[0] = __uint_as_float(r[0]);
-            rgb[1] = __uint_as_float(r[1]);
-            rgb[2] = __uint_as_float(r[2]);
+            TC_WAIT();
+            if (half == 0) {
+                uint32_t r[4];
+                tmem_ld_x4(trow + kColRgb, r);
+                tmem_ld_wait();
+                rgb[0] = __uint_as_float(r[0]);
+                rgb[1] = __uint_as_float(r[1]);
+                rgb[2] = __uint_as_float(r[2]);
+            }
         }
         if (valid) {
-            if (a.raw) reinterpret_cast<float4*>(a.raw)[p] = make_float4(rgb[0], rgb[1], rgb[2], sdf);
-            if (a.act_mask) reinterpret_cast<uint2*>(a.act_mask)[p] = make_uint2(m1, m3);
+            if (a.raw && half == 0) reinterpret_cast<float4*>(a.raw)[p] = make_float4(rgb[0], rgb[1], rgb[2], sdf);
+            if (a.act_mask) {                     // [P,2] uint32 seen as [P,4] uint16: m1 low, m1 high, m3 low, m3 high
+                mask16[p * 4 + half] = (uint16_t)m1;
+                mask16[p * 4 + 2 + half] = (uint16_t)m3;
+            }
         }
+        tc_fence_before();
+        __syncthreads();
     }
-    tc_fence_before();
-    __syncthreads();
+#undef TC_WAIT
     if (warp == 0) tmem_dealloc<tc::kTmemCols>(tmem);
 }
 
@@ -682,7 +762,7 @@ cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(points_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
-    points_fwd_tc_kernel<<<tc_persistent_grid(n_tiles, 2), tc::kTile, smem, st>>>(a);
+    points_fwd_tc_kernel<<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
