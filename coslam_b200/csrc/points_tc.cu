@@ -389,18 +389,22 @@ constexpr int kBwdTmemCols = 256;
 }  // namespace tc
 
 template <bool kWgrad>
-__global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) {
+__global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsArgs a) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint64_t bar;
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int row = tid & (kTile - 1), half = tid >> 7;                                // epilogue role
+    const int row_g = (warp & 3) * 32 + half * 16 + (lane >> 1), xb = lane & 1;          // gather role
+    const int src_lane = half * 16 + (lane >> 1);                                      // lane of this warp that reads row_g from TMEM
     const uint32_t sbase = smem_u32(smem);
     const uint32_t a_hi = sbase + kOffAHi, a_lo = sbase + kOffALo;
     const uint32_t hg_hi = sbase + kOffHHi, hg_lo = sbase + kOffHLo;
     const uint32_t g3_hi = sbase + kBOffG3Hi, g3_lo = sbase + kBOffG3Lo;
     const uint32_t g2_hi = sbase + kBOffG2Hi, g2_lo = sbase + kBOffG2Lo;
     float* sW4f = reinterpret_cast<float*>(smem + kBOffW4f);
+    const uint16_t* mask16 = reinterpret_cast<const uint16_t*>(a.act_mask);
 
     if (warp == 0) tmem_alloc<kBwdTmemCols>(&tmem_slot);
     if (tid == 0) {
@@ -411,7 +415,7 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
     if (tid < 96) sW4f[tid] = a.w4[tid];
     publish_tiles();
     const uint32_t tmem = tmem_slot;
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+    const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     uint32_t parity = 0;
     bool first_tile = true;
 
@@ -424,27 +428,26 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
 
     const int64_t n_tiles = (a.n_points + kTile - 1) / kTile;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const int64_t p_raw = tile * kTile + tid;
+        const int64_t p_raw = tile * kTile + row;
         const bool valid = p_raw < a.n_points;
         const int64_t p = valid ? p_raw : a.n_points - 1;
-        float x[3], zray;
-        point_position(a, p, x, zray);
 
-        // ---- (1) input-gradient chain ---------------------------------------------------------------------------------
+        // ---- (1) input-gradient chain (epilogue role: 16 columns per thread) --------------------------------------------
         float4 g = reinterpret_cast<const float4*>(a.d_raw)[p];
-        uint2 m = reinterpret_cast<const uint2*>(a.act_mask)[p];
+        const uint32_t m1 = mask16[p * 4 + half];
+        uint32_t m3 = mask16[p * 4 + 2 + half];
         if (!valid) g = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (a.sdf_only) { g.x = g.y = g.z = 0.f; m.y = 0u; }
+        if (a.sdf_only) { g.x = g.y = g.z = 0.f; m3 = 0u; }
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
             float v[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-                const int j = c * 8 + e;
+                const int j = half * 16 + c * 8 + e;
                 const float t = sW4f[j] * g.x + sW4f[32 + j] * g.y + sW4f[64 + j] * g.z;
-                v[e] = ((m.y >> j) & 1u) ? t : 0.f;
+                v[e] = ((m3 >> (c * 8 + e)) & 1u) ? t : 0.f;
             }
-            tile_store8(g3_hi, g3_lo, kHGS, tid, c, v);
+            tile_store8(g3_hi, g3_lo, kHGS, row, 2 * half + c, v);
         }
         publish_tiles();
         if (tid == 0) {      // round b: d_in2 = d_h3 W3   (B = W3 tile read MN-major: reduce over its rows)
@@ -458,21 +461,23 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
             tmem_ld_x16(trow + kColDin2 + 48, r);      // columns 48..62 = d geo
             tmem_ld_wait();
             float v[8];
-            v[0] = g.w;
+            if (half == 0) {                           // d_h2 columns 0..7 = [d sdf, d geo 0..6]
+                v[0] = g.w;
 #pragma unroll
-            for (int e = 1; e < 8; ++e) {
-                float t = __uint_as_float(r[e - 1]);
-                if (a.d_geo && valid) t += a.d_geo[p * kGeo + (e - 1)];
-                v[e] = t;
-            }
-            tile_store8(g2_hi, g2_lo, kG2GS, tid, 0, v);
+                for (int e = 1; e < 8; ++e) {
+                    float t = __uint_as_float(r[e - 1]);
+                    if (a.d_geo && valid) t += a.d_geo[p * kGeo + (e - 1)];
+                    v[e] = t;
+                }
+            } else {                                   // columns 8..15 = d geo 7..14
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                float t = __uint_as_float(r[7 + e]);
-                if (a.d_geo && valid) t += a.d_geo[p * kGeo + 7 + e];
-                v[e] = t;
+                for (int e = 0; e < 8; ++e) {
+                    float t = __uint_as_float(r[7 + e]);
+                    if (a.d_geo && valid) t += a.d_geo[p * kGeo + 7 + e];
+                    v[e] = t;
+                }
             }
-            tile_store8(g2_hi, g2_lo, kG2GS, tid, 1, v);
+            tile_store8(g2_hi, g2_lo, kG2GS, row, half, v);
         }
         publish_tiles();
         if (tid == 0) {      // round c: d_h1 (pre-mask) = d_h2 W2
@@ -482,16 +487,10 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
         }
         TC_WAIT();
         {
-            uint32_t r[32];
-            tmem_ld_x32(trow + kColDh1, r);
+            uint32_t r[16];
+            tmem_ld_x16(trow + kColDh1 + 16 * half, r);
             tmem_ld_wait();
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                float v[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) v[e] = ((m.x >> (c * 8 + e)) & 1u) ? __uint_as_float(r[c * 8 + e]) : 0.f;
-                tile_store8(hg_hi, hg_lo, kHGS, tid, c, v);
-            }
+            mask16_to_tile(r, m1, hg_hi, hg_lo, row, half);
         }
         publish_tiles();
         if (tid == 0) {      // round d: d_in1 = d_h1 W1, then the OneBlob columns += d_h3 W3[:, :48]
@@ -503,89 +502,122 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
         }
         TC_WAIT();
 
-        // ---- (2) one gather pass: dL/dx, table scatter, features -----------------------------------------------------------
+        // ---- (2) one gather pass (gather role: lane pair per point): dL/dx, table scatter, features ---------------------
+        const int64_t pg_raw = tile * kTile + row_g;
+        const bool valid_g = pg_raw < a.n_points;
+        const int64_t pg = valid_g ? pg_raw : a.n_points - 1;
+        float x[3], zray;
+        point_position(a, pg, x, zray);
         float dx[3] = {0.f, 0.f, 0.f};
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
-            uint32_t de[8];
-            tmem_ld_x8(trow + kColDin1 + 8 * c, de);            // d embed of levels 4c .. 4c+3
-            float2 v[4][8];
-            uint32_t idx[4][8];
-            float w[4][3];
+            uint32_t de_raw[8];
+            tmem_ld_x8(trow + kColDin1 + 8 * c, de_raw);        // d embed of levels 4c .. 4c+3, row = this lane's TMEM lane
+            float2 v[4][4];
+            uint32_t idx[4][4];
+            float wx[4], w1[4], w2[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                LevelCorners lc;
-                level_corners(a.scene, 4 * c + q, x, lc);
+                HalfCorners hc;
+                level_corners_x(a.scene, 4 * c + q, x, xb, hc);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    idx[q][k] = lc.idx[k];
-                    v[q][k] = ldg_f2(a.table + lc.idx[k]);
+                for (int j = 0; j < 4; ++j) {
+                    idx[q][j] = hc.idx[j];
+                    v[q][j] = ldg_f2(a.table + hc.idx[j]);
                 }
-                w[q][0] = lc.w[0]; w[q][1] = lc.w[1]; w[q][2] = lc.w[2];
+                wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
             }
             tmem_ld_wait();
-            float feat[8];
+            float part[8];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const float de0 = __uint_as_float(de[2 * q]), de1 = __uint_as_float(de[2 * q + 1]);
-                float s[8];
+                const float de0 = __uint_as_float(__shfl_sync(0xffffffffu, de_raw[2 * q], src_lane));
+                const float de1 = __uint_as_float(__shfl_sync(0xffffffffu, de_raw[2 * q + 1], src_lane));
+                float s[4];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) s[k] = v[q][k].x * de0 + v[q][k].y * de1;
-                const float w0 = w[q][0], w1 = w[q][1], w2 = w[q][2];
+                for (int j = 0; j < 4; ++j) s[j] = v[q][j].x * de0 + v[q][j].y * de1;
                 const float scale = a.scene.scale[4 * c + q];
-                const float gx = (1.f - w1) * (1.f - w2) * (s[1] - s[0]) + w1 * (1.f - w2) * (s[3] - s[2]) +
-                                 (1.f - w1) * w2 * (s[5] - s[4]) + w1 * w2 * (s[7] - s[6]);
-                const float gy = (1.f - w0) * (1.f - w2) * (s[2] - s[0]) + w0 * (1.f - w2) * (s[3] - s[1]) +
-                                 (1.f - w0) * w2 * (s[6] - s[4]) + w0 * w2 * (s[7] - s[5]);
-                const float gz = (1.f - w0) * (1.f - w1) * (s[4] - s[0]) + w0 * (1.f - w1) * (s[5] - s[1]) +
-                                 (1.f - w0) * w1 * (s[6] - s[2]) + w0 * w1 * (s[7] - s[3]);
+                // d/dx: (value at x+1) - (value at x), bilinear in (y, z): this thread contributes its side with its sign
+                float t = 0.f;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) t = fmaf(yz_weight(w1[q], w2[q], j), s[j], t);
+                const float gx = xb ? t : -t;
+                const float gy = wx[q] * ((1.f - w2[q]) * (s[1] - s[0]) + w2[q] * (s[3] - s[2]));
+                const float gz = wx[q] * ((1.f - w1[q]) * (s[2] - s[0]) + w1[q] * (s[3] - s[1]));
                 dx[0] = fmaf(scale, gx, dx[0]);
                 dx[1] = fmaf(scale, gy, dx[1]);
                 dx[2] = fmaf(scale, gz, dx[2]);
                 float f0 = 0.f, f1 = 0.f;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const float wc = corner_weight(w[q], k);
-                    if (a.dtable && valid) red_add_f2(a.dtable + idx[q][k], wc * de0, wc * de1);
+                for (int j = 0; j < 4; ++j) {
+                    const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
+                    if (a.dtable && valid_g) red_add_f2(a.dtable + idx[q][j], wc * de0, wc * de1);
                     if (kWgrad) {
-                        f0 = fmaf(wc, v[q][k].x, f0);
-                        f1 = fmaf(wc, v[q][k].y, f1);
+                        f0 = fmaf(wc, v[q][j].x, f0);
+                        f1 = fmaf(wc, v[q][j].y, f1);
                     }
                 }
-                feat[2 * q] = f0;
-                feat[2 * q + 1] = f1;
+                part[2 * q] = f0;
+                part[2 * q + 1] = f1;
             }
-            if (kWgrad) tile_store8(a_hi, a_lo, kAGS, tid, c, feat);
+            if (kWgrad) pair_combine_store(part, xb, a_hi, a_lo, row_g, c);
         }
-        // OneBlob: backward into dx (gradient columns 32..79 of d_in1), forward values into the A tile
+        // OneBlob: thread xb owns bins 8 xb .. 8 xb + 7 of every coordinate (gradient columns 32 + 16 d + 8 xb .. of d_in1)
 #pragma unroll 1
         for (int d = 0; d < 3; ++d) {
             uint32_t gb[16];
             tmem_ld_x16(trow + kColDin1 + 32 + 16 * d, gb);
-            const float f_first = blob_edge_cdf(0.f, x[d], (float)kBins);
-            const float k_first = blob_edge_pdf(0.f, x[d], (float)kBins);
-            float f_prev = f_first, k_prev = k_first, acc = 0.f;
+            float val[8], dval[8];
+            blob_half<true>(x[d], xb, val, dval);
             tmem_ld_wait();
+            float acc = 0.f;
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                float v[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int b = half * 8 + e;
-                    const float edge = (float)(b + 1) / (float)kBins;
-                    const float f_next = (b == kBins - 1) ? f_first + 1.0f : blob_edge_cdf(edge, x[d], (float)kBins);
-                    const float k_next = (b == kBins - 1) ? k_first : blob_edge_pdf(edge, x[d], (float)kBins);
-                    acc += __uint_as_float(gb[b]) * (k_prev - k_next);
-                    v[e] = f_next - f_prev;
-                    f_prev = f_next;
-                    k_prev = k_next;
-                }
-                if (kWgrad) tile_store8(a_hi, a_lo, kAGS, tid, 4 + d * 2 + half, v);
+            for (int e = 0; e < 8; ++e) {
+                const uint32_t lo8 = __shfl_sync(0xffffffffu, gb[e], src_lane);
+                const uint32_t hi8 = __shfl_sync(0xffffffffu, gb[8 + e], src_lane);
+                acc = fmaf(__uint_as_float(xb ? hi8 : lo8), dval[e], acc);
             }
             dx[d] += acc;
+            if (kWgrad) tile_store8(a_hi, a_lo, kAGS, row_g, 4 + 2 * d + xb, val);
+        }
+#pragma unroll
+        for (int d = 0; d < 3; ++d) dx[d] += __shfl_xor_sync(0xffffffffu, dx[d], 1);      // both threads of the pair: full dL/dx
+
+        // ---- position gradient (pair leader) ----------------------------------------------------------------------------------
+        {
+            float dp[3];
+#pragma unroll
+            for (int d = 0; d < 3; ++d) dp[d] = valid_g ? (a.scene.normalise ? dx[d] / a.scene.bb_ext[d] : dx[d]) : 0.f;
+            if (a.d_pts && valid_g && xb == 0) {
+#pragma unroll
+                for (int d = 0; d < 3; ++d) a.d_pts[pg * 3 + d] = dp[d];
+            }
+            if (a.d_rays_o) {
+                // segmented sum over the 16 consecutive points of this warp (even lanes; odd lanes mirror them)
+                const int64_t ray = valid_g ? pg / a.n_samples : -1;
+                float v6[6] = {dp[0], dp[1], dp[2], dp[0] * zray, dp[1] * zray, dp[2] * zray};
+#pragma unroll
+                for (int o = 2; o < 32; o <<= 1) {
+                    const int64_t r2 = __shfl_down_sync(0xffffffffu, ray, o);
+                    const bool take = (lane + o < 32) && (r2 == ray);
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) {
+                        const float t = __shfl_down_sync(0xffffffffu, v6[i], o);
+                        if (take) v6[i] += t;
+                    }
+                }
+                const int64_t rprev = __shfl_up_sync(0xffffffffu, ray, 2);
+                if (valid_g && xb == 0 && (lane < 2 || rprev != ray)) {
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) {
+                        atomicAdd(a.d_rays_o + ray * 3 + d, v6[d]);
+                        atomicAdd(a.d_rays_d + ray * 3 + d, v6[3 + d]);
+                    }
+                }
+            }
         }
 
-        // ---- (3) forward recompute + weight gradients -------------------------------------------------------------------------
+        // ---- (3) forward recompute + weight gradients (epilogue role) ----------------------------------------------------------
         if (kWgrad) {
             publish_tiles();
             if (tid == 0) {      // h1 = in1 W1^T ;  dW1^T += in1^T d_h1   (A tile and HG tile read MN-major, reduce over the points)
@@ -597,16 +629,10 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
             }
             TC_WAIT();
             {
-                uint32_t r[32];
-                tmem_ld_x32(trow + kColRH1, r);
+                uint32_t r[16];
+                tmem_ld_x16(trow + kColRH1 + 16 * half, r);
                 tmem_ld_wait();
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    float v[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) v[e] = ((m.x >> (c * 8 + e)) & 1u) ? __uint_as_float(r[c * 8 + e]) : 0.f;
-                    tile_store8(hg_hi, hg_lo, kHGS, tid, c, v);       // HG now holds relu(h1)
-                }
+                mask16_to_tile(r, m1, hg_hi, hg_lo, row, half);       // HG now holds relu(h1)
             }
             publish_tiles();
             if (tid == 0) {      // h2 = relu(h1) W2^T ;  dW2^T += relu(h1)^T d_h2
@@ -622,18 +648,19 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
                 tmem_ld_x16(trow + kColRH2, r);
                 tmem_ld_wait();
                 float v[8];
+                if (half == 0) {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[1 + e]);
-                tile_store8(a_hi, a_lo, kAGS, tid, 10, v);
+                    for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[1 + e]);
+                } else {
 #pragma unroll
-                for (int e = 0; e < 7; ++e) v[e] = __uint_as_float(r[9 + e]);
-                v[7] = 0.f;
-                tile_store8(a_hi, a_lo, kAGS, tid, 11, v);
+                    for (int e = 0; e < 7; ++e) v[e] = __uint_as_float(r[9 + e]);
+                    v[7] = 0.f;
+                }
+                tile_store8(a_hi, a_lo, kAGS, row, 10 + half, v);
                 // the d_h2 tile is dead now (dW2 completed): reuse it for d_rgb, the B operand of dW4
-                float u[8] = {g.x, g.y, g.z, 0.f, 0.f, 0.f, 0.f, 0.f};
-                tile_store8(g2_hi, g2_lo, kG2GS, tid, 0, u);
-                u[0] = u[1] = u[2] = 0.f;
-                tile_store8(g2_hi, g2_lo, kG2GS, tid, 1, u);
+                float u[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (half == 0) { u[0] = g.x; u[1] = g.y; u[2] = g.z; }
+                tile_store8(g2_hi, g2_lo, kG2GS, row, half, u);
             }
             publish_tiles();
             if (tid == 0) {      // h3 = [blob | geo] W3^T ;  dW3^T += [blob | geo]^T d_h3
@@ -645,16 +672,10 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
             }
             TC_WAIT();
             {
-                uint32_t r[32];
-                tmem_ld_x32(trow + kColRH3, r);
+                uint32_t r[16];
+                tmem_ld_x16(trow + kColRH3 + 16 * half, r);
                 tmem_ld_wait();
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    float v[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) v[e] = ((m.y >> (c * 8 + e)) & 1u) ? __uint_as_float(r[c * 8 + e]) : 0.f;
-                    tile_store8(hg_hi, hg_lo, kHGS, tid, c, v);       // HG now holds relu(h3)
-                }
+                mask16_to_tile(r, m3, hg_hi, hg_lo, row, half);       // HG now holds relu(h3)
             }
             publish_tiles();
             if (tid == 0) {      // dW4^T += relu(h3)^T d_rgb
@@ -665,43 +686,12 @@ __global__ void __launch_bounds__(tc::kTile) points_bwd_tc_kernel(PointsArgs a) 
             TC_WAIT();           // the tiles are rewritten by the next iteration
             first_tile = false;
         }
-
-        // ---- position gradient ------------------------------------------------------------------------------------------------
-        float dp[3];
-#pragma unroll
-        for (int d = 0; d < 3; ++d) dp[d] = valid ? (a.scene.normalise ? dx[d] / a.scene.bb_ext[d] : dx[d]) : 0.f;
-        if (a.d_pts && valid) {
-#pragma unroll
-            for (int d = 0; d < 3; ++d) a.d_pts[p * 3 + d] = dp[d];
-        }
-        if (a.d_rays_o) {
-            const int64_t ray = valid ? p / a.n_samples : -1;
-            float v6[6] = {dp[0], dp[1], dp[2], dp[0] * zray, dp[1] * zray, dp[2] * zray};
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int64_t r2 = __shfl_down_sync(0xffffffffu, ray, o);
-                const bool take = (lane + o < 32) && (r2 == ray);
-#pragma unroll
-                for (int i = 0; i < 6; ++i) {
-                    const float t = __shfl_down_sync(0xffffffffu, v6[i], o);
-                    if (take) v6[i] += t;
-                }
-            }
-            const int64_t rprev = __shfl_up_sync(0xffffffffu, ray, 1);
-            if (valid && (lane == 0 || rprev != ray)) {
-#pragma unroll
-                for (int d = 0; d < 3; ++d) {
-                    atomicAdd(a.d_rays_o + ray * 3 + d, v6[d]);
-                    atomicAdd(a.d_rays_d + ray * 3 + d, v6[3 + d]);
-                }
-            }
-        }
         tc_fence_before();
         __syncthreads();         // every lane has read its d_in1 columns before the next tile's MMAs overwrite TMEM
     }
 #undef TC_WAIT
 
-    if (kWgrad && !first_tile) {
+    if (kWgrad && !first_tile && half == 0) {
         // lane = row of the transposed weight gradients: dW1^T [80 x 32], dW3^T [63 x 32], dW2^T [32 x 16], dW4^T [32 x 3]
         tc_fence_after();
         uint32_t r[32];
@@ -748,11 +738,11 @@ cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st) {
     if (wgrad) {
         cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        points_bwd_tc_kernel<true><<<tc_persistent_grid(n_tiles, 2), tc::kTile, smem, st>>>(a);
+        points_bwd_tc_kernel<true><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     } else {
         cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        points_bwd_tc_kernel<false><<<tc_persistent_grid(n_tiles, 2), tc::kTile, smem, st>>>(a);
+        points_bwd_tc_kernel<false><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     }
     return cudaGetLastError();
 }
