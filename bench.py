@@ -31,6 +31,9 @@ METRIC = 'rays_per_sec_render_fwd_bwd'
 UNIT = 'rays/s'
 BYTES_PER_POINT_FWD = 1024          # 16 levels x 8 corners x 8 B gathered           
 BYTES_PER_POINT_BWD = 2048          # the same gathers again for dL/dx + 1024 B of gradient scattered to the table
+# dram__bytes_read.sum + dram__bytes_write.sum of points_bwd_tc_kernel<wgrad> per point, from the ncu --set full capture in
+# profiles/r1/ncu_full_v4_tc.txt (54.50 MB + 0.36 MB over 1 409 024 points): the table is L2-resident, HBM sees the per-point streams.
+NCU_DRAM_BYTES_PER_POINT_BWD = 38.93
 
 
 def parse():
@@ -263,6 +266,7 @@ def run_ours(args):
             pass
         peak = float(peaks.get('hbm_gbs', 6650.0))
         P = n * S
+        tc = os.environ.get('COSLAM_B200_DECODER', 'tc') != 'simt'
         achieved = P * BYTES_PER_POINT_BWD / (k_bwd * 1e-3) / 1e9
         out = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': max(3, args.warmup),
@@ -276,10 +280,11 @@ def run_ours(args):
             'clocks': clocks,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4, 'ms_per_step': ms_e2e / args.steps},
             'gpu_launches': launches,
-            'roofline': {'bound': 'hbm', 'kernel': 'points_bwd_kernel<wgrad>', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                         'frac': achieved / peak, 'traffic': None, 'peak_source': 'measured' if peaks else 'fallback',
+            'roofline': {'bound': 'hbm', 'kernel': 'points_bwd_tc_kernel<wgrad>' if tc else 'points_bwd_kernel<wgrad>', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                         'frac': achieved / peak, 'traffic': P * NCU_DRAM_BYTES_PER_POINT_BWD if tc else None,
+                         'traffic_source': 'ncu dram bytes per point (profiles/r1/ncu_full_v4_tc.txt) x points per launch', 'peak_source': 'measured' if peaks else 'fallback',
                          'algorithmic_bytes_per_launch': P * BYTES_PER_POINT_BWD, 'avg_launch_ms': k_bwd,
-                         'fwd_kernel': {'kernel': 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
+                         'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
                                         'achieved': P * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
                          'share_of_step': (k_fwd + k_bwd) / (ms / args.steps)},
             'cpu_baseline': cpu,
