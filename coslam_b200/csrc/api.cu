@@ -158,6 +158,26 @@ int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const 
     return cuda_result(cb200::launch_sample_rays(a, (cudaStream_t)stream), "sample_rays");
 }
 
+int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, const float* weights, const float* u, int64_t u_stride,
+                            const float* target_d, int64_t n_rays, int64_t n_samples, int64_t n_importance, float* z_out, float* z_std,
+                            int64_t* counts, void* stream) {
+    CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
+    CB_REQUIRE(n_samples >= 3 && n_importance >= 1 && n_samples + n_importance <= 256,
+               "importance_sample: need 3 <= n_samples, 1 <= n_importance, n_samples + n_importance <= 256 (got %lld + %lld)",
+               (long long)n_samples, (long long)n_importance);
+    CB_REQUIRE(n_rays >= 0, "negative ray count");
+    CB_REQUIRE(u_stride == 0 || u_stride == n_importance, "importance_sample: u_stride must be 0 or n_importance");
+    CB_REQUIRE(counts == nullptr || target_d != nullptr, "importance_sample: counts need target_d");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(z_vals && weights && u && z_out, "importance_sample: NULL buffer");
+    cb200::ImportanceArgs a{};
+    a.z_vals = z_vals; a.weights = weights; a.u = u; a.u_stride = u_stride; a.target_d = target_d; a.n_rays = n_rays;
+    a.n_samples = (int)n_samples; a.n_importance = (int)n_importance; a.z_out = z_out; a.z_std = z_std;
+    a.counts = reinterpret_cast<unsigned long long*>(counts);
+    a.trunc_sc = cfg->trunc_sc; a.depth_trunc = cfg->depth_trunc;
+    return cuda_result(cb200::launch_importance_sample(a, (cudaStream_t)stream), "importance_sample");
+}
+
 static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
                             const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples) {
     if (int rc = check_fused_scene(scene)) return rc;

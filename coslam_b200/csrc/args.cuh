@@ -44,6 +44,20 @@ struct SampleArgs {
     float trunc_sc, depth_trunc;
 };
 
+struct ImportanceArgs {
+    const float* z_vals;       // [N,S] coarse samples (ascending)
+    const float* weights;      // [N,S] coarse rendering weights
+    const float* u;            // uniforms: [N,I] (u_stride = I) or one shared row [I] (u_stride = 0, the det=True linspace)
+    int64_t u_stride;
+    const float* target_d;     // [N] or NULL (no counts)
+    int64_t n_rays;
+    int n_samples, n_importance;
+    float* z_out;              // [N,S+I] merged, ascending
+    float* z_std;              // [N] or NULL
+    unsigned long long* counts;
+    float trunc_sc, depth_trunc;
+};
+
 struct RenderArgs {
     const float* raw;          // [N,S,4]
     const float* z_vals;       // [N,S]
@@ -65,6 +79,7 @@ struct RenderArgs {
     float* d_raw;              // [N,S,4]
 };
 
+cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st);
 cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st);
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st);
 cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st);

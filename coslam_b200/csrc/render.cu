@@ -350,6 +350,116 @@ static inline int ray_grid(int64_t n_rays) {
     return (int)blocks;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Importance resampling (model/scene_rep.py:265-272 + sample_pdf, model/utils.py:32-71), one warp per ray:
+//   bins = mid-points of the coarse samples, pdf from weights[1:-1] + 1e-5, inverse-CDF samples, then the sorted union of
+//   coarse and new samples.  Also the mask counts of get_masks on the merged samples (the loss head uses the final z).
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kRayWarps * 32) importance_sample_kernel(ImportanceArgs a) {
+    extern __shared__ float smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int S = a.n_samples, I = a.n_importance, nb = S - 1;      // nb bins, nb - 1 pdf entries, nb cdf entries
+    float* zrow = smem + warp * (2 * S + I);
+    float* cdf = zrow + S;                                           // [nb]
+    float* samp = cdf + S;                                           // [I]  (one float of padding after cdf)
+    unsigned n_front = 0, n_sdf = 0, n_valid = 0;
+    for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
+        for (int s = lane; s < S; s += 32) zrow[s] = a.z_vals[ray * S + s];
+        float part = 0.f;
+        for (int k = lane; k < nb - 1; k += 32) part += a.weights[ray * S + k + 1] + 1e-5f;      // utils.py:44
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        __syncwarp();
+        if (lane == 0) {                                             // utils.py:45-47, cumulative sum in index order
+            float c = 0.f;
+            cdf[0] = 0.f;
+            for (int k = 0; k < nb - 1; ++k) {
+                c = __fadd_rn(c, __fdiv_rn(a.weights[ray * S + k + 1] + 1e-5f, part));
+                cdf[k + 1] = c;
+            }
+        }
+        __syncwarp();
+        for (int i = lane; i < I; i += 32) {
+            const float u = a.u[ray * a.u_stride + i];
+            int lo = 0, hi = nb;                                     // searchsorted(cdf, u, right=True): #{cdf <= u}
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
+            }
+            const int below = max(lo - 1, 0), above = min(lo, nb - 1);
+            const float cb = cdf[below], ca = cdf[above];
+            const float bb = __fmul_rn(0.5f, __fadd_rn(zrow[below + 1], zrow[below]));
+            const float ba = __fmul_rn(0.5f, __fadd_rn(zrow[above + 1], zrow[above]));
+            float denom = __fsub_rn(ca, cb);
+            if (denom < 1e-5f) denom = 1.f;
+            const float t = __fdiv_rn(__fsub_rn(u, cb), denom);
+            samp[i] = __fadd_rn(bb, __fmul_rn(t, __fsub_rn(ba, bb)));
+        }
+        __syncwarp();
+        const float d = a.target_d ? a.target_d[ray] : 0.f;
+        const float front_edge = __fsub_rn(d, a.trunc_sc), back_edge = __fadd_rn(d, a.trunc_sc);
+        float mean = 0.f;
+        // rank of every element in the sorted union (coarse samples first on ties)
+        for (int e = lane; e < S + I; e += 32) {
+            float v;
+            int pos;
+            if (e < S) {
+                v = zrow[e];
+                pos = e;
+                for (int j = 0; j < I; ++j) pos += samp[j] < v;
+            } else {
+                const int i = e - S;
+                v = samp[i];
+                mean += v;
+                pos = 0;
+                for (int j = 0; j < I; ++j) pos += (samp[j] < v) || (samp[j] == v && j < i);
+                int lo = 0, hi = S;                                  // #{z <= v}
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (zrow[mid] <= v) lo = mid + 1; else hi = mid;
+                }
+                pos += lo;
+            }
+            a.z_out[ray * (S + I) + pos] = v;
+            if (a.target_d) {
+                const bool front = v < front_edge, back = v > back_edge;
+                n_front += front;
+                n_sdf += (!front && !back && d > 0.0f);
+            }
+        }
+        if (a.z_std) {                                               // scene_rep.py:292, unbiased=False
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mean += __shfl_xor_sync(0xffffffffu, mean, o);
+            mean /= (float)I;
+            float var = 0.f;
+            for (int i = lane; i < I; i += 32) var += (samp[i] - mean) * (samp[i] - mean);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync(0xffffffffu, var, o);
+            if (lane == 0) a.z_std[ray] = sqrtf(var / (float)I);
+        }
+        if (lane == 0 && a.target_d) n_valid += (d > 0.0f && d < a.depth_trunc);
+        __syncwarp();
+    }
+    if (a.counts) {
+        __shared__ unsigned red[3][kRayWarps];
+        n_front = __reduce_add_sync(0xffffffffu, n_front);
+        n_sdf = __reduce_add_sync(0xffffffffu, n_sdf);
+        n_valid = __reduce_add_sync(0xffffffffu, n_valid);
+        if (lane == 0) { red[0][warp] = n_front; red[1][warp] = n_sdf; red[2][warp] = n_valid; }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            unsigned long long t = 0;
+            for (int w = 0; w < kRayWarps; ++w) t += red[threadIdx.x][w];
+            if (t) atomicAdd(a.counts + threadIdx.x, t);
+        }
+    }
+}
+
+cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st) {
+    const size_t smem = sizeof(float) * (size_t)kRayWarps * (size_t)(2 * a.n_samples + a.n_importance);
+    importance_sample_kernel<<<ray_grid(a.n_rays), kRayWarps * 32, smem, st>>>(a);
+    return cudaGetLastError();
+}
 cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st) {
     const int S = a.n_uniform + a.n_guided;
     const size_t smem = sizeof(float) * (size_t)(kRayWarps * S + a.n_uniform + 2 * a.n_guided);

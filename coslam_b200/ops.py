@@ -17,6 +17,7 @@ N_GEO = 15
 # tests set KEEP_LAST_MASK to read back the ReLU sign bits the last ray forward saved for its backward
 KEEP_LAST_MASK = False
 LAST_MASK = None
+MASK_LOG = []          # every mask saved while KEEP_LAST_MASK is set, in call order (two entries for an importance-pass step)
 
 # bench.py sets this to a list to collect (name, start_event, end_event) around the two per-point kernels
 KERNEL_EVENTS = None
@@ -171,6 +172,25 @@ def sample_rays(spec, target_d, noise=None, seed=0, counts=None, perturb=None):
     return z
 
 
+def importance_sample(spec, z_vals, weights, u, target_d=None, counts=None, want_std=True):
+    """sample_pdf + sorted merge (model/scene_rep.py:265-272, model/utils.py:32-71).  u is [N,I] or one shared row [I].
+    Returns (z [N,S+I], z_std [N] | None); accumulates the mask counts of the merged samples into counts when given."""
+    z, w = _f32c(z_vals), _f32c(weights)
+    n, s = z.shape
+    u = _f32c(u)
+    n_imp = u.shape[-1]
+    if u.dim() == 2 and u.shape[0] != n:
+        raise ValueError('u must be [N, I] or [I]')
+    stride = n_imp if u.dim() == 2 else 0
+    z_out = torch.empty((n, s + n_imp), dtype=torch.float32, device=z.device)
+    z_std = torch.empty((n,), dtype=torch.float32, device=z.device) if want_std else None
+    d = _f32c(target_d.reshape(-1)) if target_d is not None else None
+    check(_lib.load().cb200_importance_sample(ctypes.byref(spec.render_cfg()), ptr(z), ptr(w), ptr(u), ctypes.c_int64(stride), ptr(d),
+                                              ctypes.c_int64(n), ctypes.c_int64(s), ctypes.c_int64(n_imp), ptr(z_out), ptr(z_std),
+                                              ptr(counts), stream()), 'importance_sample')
+    return z_out, z_std
+
+
 def _mlp_block(w1, w2, w3, w4):
     m = _lib.Mlp()
     m.w_sdf0, m.w_sdf1, m.w_col0, m.w_col1 = w1.data_ptr(), w2.data_ptr(), w3.data_ptr(), w4.data_ptr()
@@ -260,6 +280,7 @@ class RayPointsFunction(torch.autograd.Function):
         if KEEP_LAST_MASK:
             global LAST_MASK
             LAST_MASK = mask
+            MASK_LOG.append(mask)
         ctx.spec = spec
         ctx.save_for_backward(o, d, z, tb, *w, mask if mask is not None else torch.empty(0))
         return raw.view(z.shape[0], z.shape[1], 4)

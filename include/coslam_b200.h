@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 3
+#define CB200_ABI_VERSION 4
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -130,6 +130,17 @@ int cb200_oneblob_bwd(const float* x, const float* dy, int64_t n_points, uint32_
 int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform,
                       const float* lin_guided, const float* lin_nodepth, const float* noise, uint64_t seed,
                       int64_t n_rays, float* z_vals, int64_t* counts, void* stream);
+
+/* Importance resampling of render_rays (model/scene_rep.py:265-272) with sample_pdf (model/utils.py:32-71):
+ *   z_vals [N,S] ascending coarse samples, weights [N,S] their rendering weights (cb200_render_fwd);
+ *   u: the uniforms of utils.py:53 as [N,I] (u_stride = I), or ONE row [I] shared by all rays (u_stride = 0) holding the
+ *   det=True linspace of utils.py:50;   z_out [N,S+I] = sort(cat(z_vals, samples)) (scene_rep.py:271);
+ *   z_std [N] = std(samples, unbiased=False) (scene_rep.py:292), may be NULL;
+ *   target_d [N] + counts [3] (ACCUMULATED n_front, n_sdf, n_valid_depth of the merged samples, as in cb200_sample_rays),
+ *   both may be NULL.  Requires 3 <= S, 1 <= I, S + I <= 256. */
+int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, const float* weights, const float* u,
+                            int64_t u_stride, const float* target_d, int64_t n_rays, int64_t n_samples,
+                            int64_t n_importance, float* z_out, float* z_std, int64_t* counts, void* stream);
 
 /* run_network / query_color_sdf / query_sdf forward (model/scene_rep.py:126-191 + model/decoder.py:165-180):
  * positions are either explicit (pts [P,3], rays_o == NULL) or pts = rays_o + rays_d * z (scene_rep.py:258,

@@ -137,19 +137,28 @@ class OracleScene(object):
     # `mask_override` = (m1 [P,32] bool, m3 [P,32] bool) replaces the ReLU activation pattern by a given one (used by the
     # parity tests to compare gradients under an identical activation pattern: the gradient of a ReLU network is
     # discontinuous where a pre-activation crosses zero, so two fp32-accurate forwards can legitimately disagree on a
-    # handful of units whose pre-activation is ~1e-6).  `last_pre` keeps the pre-activations for that audit.
+    # handful of units whose pre-activation is ~1e-6).  A LIST of such pairs is consumed one per decode call (coarse pass,
+    # importance pass).  `last_pre` keeps the pre-activations of the last call, `pre_log` of every call, for that audit.
     mask_override = None
     last_pre = None
+    pre_log = None
+    z_all_override = None
+    last_z_all = None
 
     def decode(self, embed, embed_pos):
+        ov = self.mask_override
+        if isinstance(ov, list):
+            ov = ov.pop(0)
         h1 = torch.cat([embed, embed_pos], -1) @ self.W1.t()
-        a1 = torch.relu(h1) if self.mask_override is None else torch.where(self.mask_override[0], h1, torch.zeros_like(h1))
+        a1 = torch.relu(h1) if ov is None else torch.where(ov[0], h1, torch.zeros_like(h1))
         h = a1 @ self.W2.t()
         sdf, geo = h[..., :1], h[..., 1:]
         h3 = torch.cat([embed_pos, geo], -1) @ self.W3.t()
-        a3 = torch.relu(h3) if self.mask_override is None else torch.where(self.mask_override[1], h3, torch.zeros_like(h3))
+        a3 = torch.relu(h3) if ov is None else torch.where(ov[1], h3, torch.zeros_like(h3))
         rgb = a3 @ self.W4.t()
         self.last_pre = (h1.detach(), h3.detach())
+        if self.pre_log is not None:
+            self.pre_log.append(self.last_pre)
         return torch.cat([rgb, sdf], -1)
 
     # ---- scene_rep.py:155-171 -------------------------------------------------------
@@ -243,6 +252,9 @@ class OracleScene(object):
             zi = sample_pdf(mid, coarse['weights'][..., 1:-1], n_imp,
                             det=(self.cfg['training']['perturb'] == 0.), u=noise_imp).detach()
             z, _ = torch.sort(torch.cat([z, zi], -1), -1)
+            self.last_z_all = z
+            if self.z_all_override is not None:                    # tests: continue from a given merged sample set
+                z = self.z_all_override
             pts = rays_o[..., None, :] + rays_d[..., None, :] * z[..., :, None]
             raw = self.run_network(pts)
             out = self.raw2outputs(raw, z)
