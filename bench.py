@@ -232,6 +232,11 @@ def run_ours(args):
     k_fwd = sum(kt['points_fwd']) / len(kt['points_fwd'])
     k_bwd = sum(kt['points_bwd']) / len(kt['points_bwd'])
     value = world * n * args.steps / (ms * 1e-3)
+    # fraction of points with a non-zero output gradient (the backward skips the rest: exact zeros), one untimed step
+    ops.KEEP_LAST_D_RAW = True
+    step(resident)
+    live_frac = float((ops.LAST_D_RAW.reshape(-1, 4) != 0).any(1).float().mean())
+    ops.KEEP_LAST_D_RAW, ops.LAST_D_RAW = False, None
 
     # ---- end to end through the public API: pinned host rays in, loss out, every step -----------------------------
     staging = [torch.empty_like(t, device=dev) for t in host]
@@ -267,7 +272,9 @@ def run_ours(args):
         peak = float(peaks.get('hbm_gbs', 6650.0))
         P = n * S
         tc = os.environ.get('COSLAM_B200_DECODER', 'tc') != 'simt'
-        achieved = P * BYTES_PER_POINT_BWD / (k_bwd * 1e-3) / 1e9
+        # algorithmic bytes of the backward: gathers + scatter only for the points that carry a gradient
+        bwd_bytes = P * live_frac * BYTES_PER_POINT_BWD
+        achieved = bwd_bytes / (k_bwd * 1e-3) / 1e9
         out = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': max(3, args.warmup),
             'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
@@ -283,7 +290,7 @@ def run_ours(args):
             'roofline': {'bound': 'hbm', 'kernel': 'points_bwd_tc_kernel<wgrad>' if tc else 'points_bwd_kernel<wgrad>', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak, 'traffic': P * NCU_DRAM_BYTES_PER_POINT_BWD if tc else None,
                          'traffic_source': 'ncu dram bytes per point (profiles/r1/ncu_full_v4_tc.txt) x points per launch', 'peak_source': 'measured' if peaks else 'fallback',
-                         'algorithmic_bytes_per_launch': P * BYTES_PER_POINT_BWD, 'avg_launch_ms': k_bwd,
+                         'algorithmic_bytes_per_launch': bwd_bytes, 'live_point_fraction': live_frac, 'avg_launch_ms': k_bwd,
                          'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
                                         'achieved': P * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
                          'share_of_step': (k_fwd + k_bwd) / (ms / args.steps)},

@@ -438,6 +438,10 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
         uint32_t m3 = mask16[p * 4 + 2 + half];
         if (!valid) g = make_float4(0.f, 0.f, 0.f, 0.f);
         if (a.sdf_only) { g.x = g.y = g.z = 0.f; m3 = 0u; }
+        // Points whose output gradient is exactly zero (samples behind the truncation band carry no loss and no rendering
+        // weight: typically a third of a batch, contiguous along each ray) contribute exact zeros to every gradient: their
+        // gathers and reductions are skipped.  Bit i of `dead` = row 32 q + i of this warp's TMEM quadrant.
+        const uint32_t dead = __ballot_sync(0xffffffffu, a.d_geo == nullptr && g.x == 0.f && g.y == 0.f && g.z == 0.f && g.w == 0.f);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             float v[8];
@@ -506,6 +510,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
         const int64_t pg_raw = tile * kTile + row_g;
         const bool valid_g = pg_raw < a.n_points;
         const int64_t pg = valid_g ? pg_raw : a.n_points - 1;
+        const bool live = valid_g && !((dead >> src_lane) & 1u);
         float x[3], zray;
         point_position(a, pg, x, zray);
         float dx[3] = {0.f, 0.f, 0.f};
@@ -523,7 +528,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     idx[q][j] = hc.idx[j];
-                    v[q][j] = ldg_f2(a.table + hc.idx[j]);
+                    v[q][j] = live ? ldg_f2(a.table + hc.idx[j]) : make_float2(0.f, 0.f);
                 }
                 wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
             }
@@ -551,7 +556,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
-                    if (a.dtable && valid_g) red_add_f2(a.dtable + idx[q][j], wc * de0, wc * de1);
+                    if (a.dtable && live) red_add_f2(a.dtable + idx[q][j], wc * de0, wc * de1);
                     if (kWgrad) {
                         f0 = fmaf(wc, v[q][j].x, f0);
                         f1 = fmaf(wc, v[q][j].y, f1);

@@ -21,6 +21,8 @@ MASK_LOG = []          # every mask saved while KEEP_LAST_MASK is set, in call o
 
 # bench.py sets this to a list to collect (name, start_event, end_event) around the two per-point kernels
 KERNEL_EVENTS = None
+KEEP_LAST_D_RAW = False   # bench.py: keep the last d_raw of the loss head to count the points that carry a gradient
+LAST_D_RAW = None
 
 
 def _timed(name, fn):
@@ -424,6 +426,9 @@ class RenderLossFunction(torch.autograd.Function):
         r, z, t_rgb, t_d, coef = ctx.saved_tensors
         d_raw = _render_backward(ctx.spec, r, z, t_rgb, t_d, (g0, g1, g2, g3), coef,
                                  _f32c(g_rgb) if g_rgb is not None else None, _f32c(g_depth) if g_depth is not None else None)
+        if KEEP_LAST_D_RAW:
+            global LAST_D_RAW
+            LAST_D_RAW = d_raw
         return d_raw, None, None, None, None, None, None, None
 
 
