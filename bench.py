@@ -293,7 +293,8 @@ def run_ours(args):
                          'algorithmic_bytes_per_launch': bwd_bytes, 'live_point_fraction': live_frac, 'avg_launch_ms': k_bwd,
                          'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
                                         'achieved': P * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
-                         'share_of_step': (k_fwd + k_bwd) / (ms / args.steps)},
+                         'share_of_step': (k_fwd + k_bwd) / (ms / args.steps),
+                         'kernel_ms': {k: sum(v) / len(v) for k, v in kt.items()}},
             'cpu_baseline': cpu,
         }
         out.update(extra)

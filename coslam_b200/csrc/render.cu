@@ -114,25 +114,26 @@ __global__ void __launch_bounds__(kRayWarps * 32) sample_rays_kernel(SampleArgs 
 // ------------------------------------------------------------------------------------------------------------------
 
 // everything the forward and the backward share for one ray, held in registers
+template <int kPerLane>
 struct RayState {
-    float4 raw[kMaxPerLane];
-    float z[kMaxPerLane];
-    float wn[kMaxPerLane];       // normalised weight
-    float bell[kMaxPerLane];     // sigmoid(a) * sigmoid(-a)
-    float sa[kMaxPerLane];       // sigmoid(a)
-    bool keep[kMaxPerLane];      // truncation mask of sdf2weights
+    float4 raw[kPerLane];
+    float z[kPerLane];
+    float wn[kPerLane];       // normalised weight
+    float bell[kPerLane];     // sigmoid(a) * sigmoid(-a)
+    float sa[kPerLane];       // sigmoid(a)
+    bool keep[kPerLane];      // truncation mask of sdf2weights
     float inv_den;               // 1 / (sum(bell * keep) + 1e-8)
     float rgb[3], depth, acc;
 };
 
-template <bool kNeedSig>
-__device__ __forceinline__ void ray_forward(const RenderArgs& a, int64_t ray, int lane, RayState& st) {
+template <int kPerLane>
+__device__ __forceinline__ void ray_forward(const RenderArgs& a, int64_t ray, int lane, RayState<kPerLane>& st) {
     const int S = a.n_samples;
     const float4* raw4 = reinterpret_cast<const float4*>(a.raw) + ray * S;
     const float* zrow = a.z_vals + ray * S;
     unsigned first = 0xffffffffu;
 #pragma unroll
-    for (int k = 0; k < kMaxPerLane; ++k) {
+    for (int k = 0; k < kPerLane; ++k) {
         const int s = lane + 32 * k;
         if (s < S) {
             st.raw[k] = raw4[s];
@@ -151,7 +152,7 @@ __device__ __forceinline__ void ray_forward(const RenderArgs& a, int64_t ray, in
     const float z_lim = __fadd_rn(zrow[first], a.trunc_sc);    // scene_rep.py:93-94
     float sum = 0.f;
 #pragma unroll
-    for (int k = 0; k < kMaxPerLane; ++k) {
+    for (int k = 0; k < kPerLane; ++k) {
         const int s = lane + 32 * k;
         const float arg = st.raw[k].w / a.trunc;
         const float sp = sigmoidf(arg), sn = sigmoidf(-arg);
@@ -164,7 +165,7 @@ __device__ __forceinline__ void ray_forward(const RenderArgs& a, int64_t ray, in
     st.inv_den = 1.0f / (sum + 1e-8f);
     float r = 0.f, g = 0.f, b = 0.f, dep = 0.f, acc = 0.f;
 #pragma unroll
-    for (int k = 0; k < kMaxPerLane; ++k) {
+    for (int k = 0; k < kPerLane; ++k) {
         const float w = st.keep[k] ? st.bell[k] * st.inv_den : 0.f;
         st.wn[k] = w;
         r += w * sigmoidf(st.raw[k].x);
@@ -180,16 +181,18 @@ __device__ __forceinline__ void ray_forward(const RenderArgs& a, int64_t ray, in
     st.acc = warp_sum(acc);
 }
 
+// kPerLane = ceil(n_samples / 32): sample slots per lane, so a 43-sample ray does 2 slots of work, not kMaxPerLane
+template <int kPerLane>
 __global__ void __launch_bounds__(kRayWarps * 32) render_fwd_kernel(RenderArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int S = a.n_samples;
     double part[4] = {0., 0., 0., 0.};     // lane 0 of each warp accumulates its rays' squared residuals
     for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
-        RayState st;
-        ray_forward<false>(a, ray, lane, st);
+        RayState<kPerLane> st;
+        ray_forward<kPerLane>(a, ray, lane, st);
         float var = 0.f;
 #pragma unroll
-        for (int k = 0; k < kMaxPerLane; ++k) {
+        for (int k = 0; k < kPerLane; ++k) {
             const float dz = st.z[k] - st.depth;
             var += st.wn[k] * dz * dz;
             if (a.weights && lane + 32 * k < S) a.weights[ray * S + lane + 32 * k] = st.wn[k];
@@ -211,7 +214,7 @@ __global__ void __launch_bounds__(kRayWarps * 32) render_fwd_kernel(RenderArgs a
             const float front_edge = __fsub_rn(d, a.trunc_sc), back_edge = __fadd_rn(d, a.trunc_sc);
             float fs = 0.f, sd = 0.f;
 #pragma unroll
-            for (int k = 0; k < kMaxPerLane; ++k) {
+            for (int k = 0; k < kPerLane; ++k) {
                 if (lane + 32 * k < S) {
                     const float z = st.z[k], sdf = st.raw[k].w;
                     const bool front = z < front_edge, back = z > back_edge;
@@ -269,6 +272,7 @@ __global__ void loss_finish_kernel(const double* sums, const long long* counts, 
     coef[3] = (float)inv_smp * fs_w;
 }
 
+template <int kPerLane>
 __global__ void __launch_bounds__(kRayWarps * 32) render_bwd_kernel(RenderArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int S = a.n_samples;
@@ -279,8 +283,8 @@ __global__ void __launch_bounds__(kRayWarps * 32) render_bwd_kernel(RenderArgs a
             if (a.g_loss[i]) gl[i] = 2.0f * a.g_loss[i][0] * a.coef[i];        // d(sum of squares) = 2 e de
     }
     for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
-        RayState st;
-        ray_forward<true>(a, ray, lane, st);
+        RayState<kPerLane> st;
+        ray_forward<kPerLane>(a, ray, lane, st);
         float d = 0.f, rw = 0.f;
         bool valid = false;
         float g_map[3] = {0.f, 0.f, 0.f}, g_dep = 0.f;
@@ -303,10 +307,10 @@ __global__ void __launch_bounds__(kRayWarps * 32) render_bwd_kernel(RenderArgs a
         const float g_acc = a.white_bkgd ? -(g_map[0] + g_map[1] + g_map[2]) : 0.f;
 
         // d wn_s and the normalisation term  sum_t d wn_t * wn_t
-        float gwn[kMaxPerLane];
+        float gwn[kPerLane];
         float dot = 0.f;
 #pragma unroll
-        for (int k = 0; k < kMaxPerLane; ++k) {
+        for (int k = 0; k < kPerLane; ++k) {
             const float cr = sigmoidf(st.raw[k].x), cg = sigmoidf(st.raw[k].y), cb = sigmoidf(st.raw[k].z);
             gwn[k] = g_map[0] * cr + g_map[1] * cg + g_map[2] * cb + g_dep * st.z[k] + g_acc;
             dot += gwn[k] * st.wn[k];
@@ -315,7 +319,7 @@ __global__ void __launch_bounds__(kRayWarps * 32) render_bwd_kernel(RenderArgs a
         const float front_edge = __fsub_rn(d, a.trunc_sc), back_edge = __fadd_rn(d, a.trunc_sc);
         float4* out = reinterpret_cast<float4*>(a.d_raw) + ray * S;
 #pragma unroll
-        for (int k = 0; k < kMaxPerLane; ++k) {
+        for (int k = 0; k < kPerLane; ++k) {
             const int s = lane + 32 * k;
             if (s < S) {
                 const float cr = sigmoidf(st.raw[k].x), cg = sigmoidf(st.raw[k].y), cb = sigmoidf(st.raw[k].z);
@@ -466,12 +470,22 @@ cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st) {
     sample_rays_kernel<<<ray_grid(a.n_rays), kRayWarps * 32, smem, st>>>(a);
     return cudaGetLastError();
 }
+#define CB200_DISPATCH_PER_LANE(kernel)                                                                    \
+    do {                                                                                                   \
+        const int per_lane = (a.n_samples + 31) / 32;                                                      \
+        const int grid = ray_grid(a.n_rays);                                                               \
+        if (per_lane <= 1) kernel<1><<<grid, kRayWarps * 32, 0, st>>>(a);                                  \
+        else if (per_lane == 2) kernel<2><<<grid, kRayWarps * 32, 0, st>>>(a);                             \
+        else if (per_lane <= 4) kernel<4><<<grid, kRayWarps * 32, 0, st>>>(a);                             \
+        else kernel<kMaxPerLane><<<grid, kRayWarps * 32, 0, st>>>(a);                                      \
+    } while (0)
+
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st) {
-    render_fwd_kernel<<<ray_grid(a.n_rays), kRayWarps * 32, 0, st>>>(a);
+    CB200_DISPATCH_PER_LANE(render_fwd_kernel);
     return cudaGetLastError();
 }
 cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st) {
-    render_bwd_kernel<<<ray_grid(a.n_rays), kRayWarps * 32, 0, st>>>(a);
+    CB200_DISPATCH_PER_LANE(render_bwd_kernel);
     return cudaGetLastError();
 }
 cudaError_t launch_loss_finish(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
