@@ -208,10 +208,12 @@ int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_m
     return cuda_result(cb200::launch_points_fwd(a, (cudaStream_t)stream), "points_fwd");
 }
 
+size_t cb200_points_bwd_workspace(int64_t n_points) { return 16 + sizeof(uint32_t) * (size_t)(n_points > 0 ? n_points : 0); }
+
 int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
                      const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
                      const float* d_geo, const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
-                     float* d_rays_o, float* d_rays_d, int sdf_only, void* stream) {
+                     float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace, size_t workspace_bytes, void* stream) {
     cb200::PointsArgs a{};
     if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
     if (a.n_points == 0) return 0;
@@ -225,7 +227,18 @@ int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_m
         a.dw1 = d_mlp->w_sdf0; a.dw2 = d_mlp->w_sdf1; a.dw3 = d_mlp->w_col0; a.dw4 = d_mlp->w_col1;
     }
     a.d_pts = d_pts; a.d_rays_o = d_rays_o; a.d_rays_d = d_rays_d;
-    if (g_decoder == 1) return cuda_result(cb200::launch_points_bwd_tc(a, (cudaStream_t)stream), "points_bwd_tc");
+    if (g_decoder == 1) {
+        if (workspace && rays_o && d_geo == nullptr && d_pts == nullptr) {
+            CB_REQUIRE(workspace_bytes >= cb200_points_bwd_workspace(a.n_points), "points_bwd: workspace too small (%zu bytes)", workspace_bytes);
+            CB_REQUIRE(a.n_points < (1ll << 32), "points_bwd: compaction indexes points with 32 bits");
+            unsigned long long* count = reinterpret_cast<unsigned long long*>(workspace);
+            uint32_t* idx = reinterpret_cast<uint32_t*>(count + 2);
+            if (int rc = cuda_result(cb200::launch_compact_live(d_raw, a.n_points, count, idx, (cudaStream_t)stream), "compact_live")) return rc;
+            a.live_idx = idx;
+            a.live_count = count;
+        }
+        return cuda_result(cb200::launch_points_bwd_tc(a, (cudaStream_t)stream), "points_bwd_tc");
+    }
     return cuda_result(cb200::launch_points_bwd(a, (cudaStream_t)stream), "points_bwd");
 }
 

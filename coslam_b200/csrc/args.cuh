@@ -15,6 +15,9 @@ struct PointsArgs {
     int64_t n_points;
     int n_samples;
     int sdf_only;
+    // backward, tensor-core decoder: optional compacted list of the points whose d_raw is non-zero (points_tc.cu)
+    const uint32_t* live_idx;
+    const unsigned long long* live_count;
     // forward outputs
     float* raw;
     float* geo;
@@ -86,6 +89,7 @@ cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st);
 cudaError_t launch_loss_finish(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
                                float* losses, float* coef, cudaStream_t st);
 cudaError_t launch_points_fwd(const PointsArgs& a, cudaStream_t st);
+cudaError_t launch_compact_live(const float* d_raw, int64_t n_points, unsigned long long* count, uint32_t* idx, cudaStream_t st);
 cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_points_bwd(const PointsArgs& a, cudaStream_t st);

@@ -426,11 +426,14 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
         tc_fence_after();         \
     } while (0)
 
-    const int64_t n_tiles = (a.n_points + kTile - 1) / kTile;
+    // with a compacted list the tiles run over the live points only (slot i -> point live_idx[i])
+    const int64_t n_slots = a.live_count ? (int64_t)*a.live_count : a.n_points;
+    const int64_t n_tiles = (n_slots + kTile - 1) / kTile;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t p_raw = tile * kTile + row;
-        const bool valid = p_raw < a.n_points;
-        const int64_t p = valid ? p_raw : a.n_points - 1;
+        const bool valid = p_raw < n_slots;
+        const int64_t p_slot = valid ? p_raw : n_slots - 1;
+        const int64_t p = a.live_idx ? (int64_t)a.live_idx[p_slot] : p_slot;
 
         // ---- (1) input-gradient chain (epilogue role: 16 columns per thread) --------------------------------------------
         float4 g = reinterpret_cast<const float4*>(a.d_raw)[p];
@@ -508,8 +511,9 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
 
         // ---- (2) one gather pass (gather role: lane pair per point): dL/dx, table scatter, features ---------------------
         const int64_t pg_raw = tile * kTile + row_g;
-        const bool valid_g = pg_raw < a.n_points;
-        const int64_t pg = valid_g ? pg_raw : a.n_points - 1;
+        const bool valid_g = pg_raw < n_slots;
+        const int64_t pg_slot = valid_g ? pg_raw : n_slots - 1;
+        const int64_t pg = a.live_idx ? (int64_t)a.live_idx[pg_slot] : pg_slot;
         const bool live = valid_g && !((dead >> src_lane) & 1u);
         float x[3], zray;
         point_position(a, pg, x, zray);
@@ -724,6 +728,43 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc<tc::kBwdTmemCols>(tmem);
+}
+
+// Order-preserving (within a 1024-point block) compaction of the points whose output gradient is non-zero.
+__global__ void __launch_bounds__(1024) compact_live_kernel(const float4* __restrict__ d_raw, int64_t n_points, unsigned long long* count,
+                                                            uint32_t* __restrict__ idx) {
+    __shared__ uint32_t warp_off[32];
+    __shared__ unsigned long long base;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t p = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+    bool live = false;
+    if (p < n_points) {
+        const float4 g = d_raw[p];
+        live = !(g.x == 0.f && g.y == 0.f && g.z == 0.f && g.w == 0.f);      // NaN counts as live
+    }
+    const uint32_t b = __ballot_sync(0xffffffffu, live);
+    if (lane == 0) warp_off[warp] = __popc(b);
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t v = warp_off[lane];
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        warp_off[lane] = incl - v;
+        if (lane == 31 && incl) base = atomicAdd(count, (unsigned long long)incl);
+    }
+    __syncthreads();
+    if (live) idx[base + warp_off[warp] + __popc(b & ((1u << lane) - 1u))] = (uint32_t)p;
+}
+
+cudaError_t launch_compact_live(const float* d_raw, int64_t n_points, unsigned long long* count, uint32_t* idx, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(count, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    compact_live_kernel<<<(unsigned)((n_points + 1023) / 1024), 1024, 0, st>>>(reinterpret_cast<const float4*>(d_raw), n_points, count, idx);
+    return cudaGetLastError();
 }
 
 static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {

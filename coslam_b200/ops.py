@@ -257,11 +257,18 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
         else:
             d_pts = torch.empty((n, 3), dtype=torch.float32, device=dev)
     mlp = _mlp_block(*w)
+    # scratch for the live-point compaction (ray mode): index list + counter, see cb200_points_bwd
+    wsp, wsp_bytes = None, 0
+    if rays is not None and d_geo is None:
+        wsp_bytes = int(_lib.load().cb200_points_bwd_workspace(ctypes.c_int64(n * s)))
+        wsp = torch.empty((wsp_bytes + 3) // 4, dtype=torch.int32, device=dev)
     _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd(
         ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
         ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(d_table),
         ctypes.byref(gblock) if gblock is not None else None, ptr(d_pts), ptr(d_o), ptr(d_d), 1 if sdf_only else 0,
-        stream()), 'points_bwd'))
+        ptr(wsp), ctypes.c_size_t(wsp_bytes), stream()), 'points_bwd'))
+    if wsp is not None and _lib.load().cb200_get_decoder() == 1:
+        _lib.KERNEL_LAUNCHES += 1          # the compaction kernel in front of the per-point kernel
     return d_table, d_w, (d_pts if rays is None else (d_o, d_d))
 
 

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 4
+#define CB200_ABI_VERSION 5
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -156,12 +156,16 @@ int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_m
 /* its backward.  d_raw [P,4] (d_geo [P,15] optional, NULL = zero).  Outputs, each optional (NULL = skip):
  *   dtable (+=)  [n_params]     d_mlp (+=) four matrices
  *   d_pts [P,3] (=)             d_rays_o, d_rays_d [N,3] (+=, ray mode only)
- * act_mask is the array written by cb200_points_fwd on the same inputs. */
+ * act_mask is the array written by cb200_points_fwd on the same inputs.
+ * workspace: optional device scratch of at least cb200_points_bwd_workspace(P) bytes.  When given (ray mode, tensor-core
+ * decoder) the points whose d_raw is exactly zero -- samples behind the truncation band carry no loss and no rendering
+ * weight -- are compacted away before the per-point kernel runs (they contribute exact zeros to every output). */
+size_t cb200_points_bwd_workspace(int64_t n_points);
 int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
                      const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
                      int64_t n_samples, const float* d_raw, const float* d_geo, const uint32_t* act_mask,
                      float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts, float* d_rays_o, float* d_rays_d,
-                     int sdf_only, void* stream);
+                     int sdf_only, void* workspace, size_t workspace_bytes, void* stream);
 
 /* raw2outputs + sdf2weights (model/scene_rep.py:77-124) and, when loss_sums != NULL, the loss head
  * (model/scene_rep.py:319-338, model/utils.py:138-161).
