@@ -140,6 +140,17 @@ int cb200_oneblob_bwd(const float* x, const float* dy, int64_t n_points, uint32_
     return cuda_result(cb200::launch_oneblob_bwd(x, dy, n_points * n_dims, (int)n_bins, dx, (cudaStream_t)stream), "oneblob_bwd");
 }
 
+int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1, float beta2, float eps,
+                    float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, void* stream) {
+    CB_REQUIRE(n >= 0, "adam_step: negative size");
+    if (n == 0) return 0;
+    CB_REQUIRE(param && grad && exp_avg && exp_avg_sq, "adam_step: NULL buffer");
+    CB_REQUIRE(step_dev != nullptr || step >= 1, "adam_step: step is 1-based");
+    CB_REQUIRE(beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f && eps >= 0.f, "adam_step: bad hyper-parameters");
+    return cuda_result(cb200::launch_adam_step(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step_dev, step,
+                                               zero_grad, (cudaStream_t)stream), "adam_step");
+}
+
 int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform, const float* lin_guided,
                       const float* lin_nodepth, const float* noise, uint64_t seed, int64_t n_rays, float* z_vals, int64_t* counts,
                       void* stream) {

@@ -82,6 +82,8 @@ struct RenderArgs {
     float* d_raw;              // [N,S,4]
 };
 
+cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+                             float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, cudaStream_t st);
 cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st);
 cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st);
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st);

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 5
+#define CB200_ABI_VERSION 6
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -118,6 +118,18 @@ int cb200_hash_indices(const cb200_grid* grid, const float* x, int64_t n_points,
 int cb200_oneblob_fwd(const float* x, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* out, void* stream);
 int cb200_oneblob_bwd(const float* x, const float* dy, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* dx,
                       void* stream);
+
+/* ---- optimiser ----------------------------------------------------------------- */
+
+/* One dense torch.optim.Adam step (amsgrad off, maximize off) over a flat fp32 parameter, as set up by
+ * CoSLAM.create_optimizer / get_pose_param_optim (coslam.py:610-634, 276-283):
+ *   g' = g + weight_decay * p;  m = m + (1-beta1)(g' - m);  v = beta2 v + (1-beta2) g'^2;
+ *   p -= lr / (1 - beta1^t) * m / (sqrt(v) / sqrt(1 - beta2^t) + eps)
+ * t = *step_dev when step_dev != NULL (device counter, for graph-captured loops) else `step` (1-based).
+ * zero_grad != 0 clears g in the same pass (set_to_none=False semantics). */
+int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                    float beta2, float eps, float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad,
+                    void* stream);
 
 /* ---- upper boundary: the fused JointEncoding path -------------------------------------------------------- */
 

@@ -397,3 +397,67 @@ def test_importance_pass_matches_oracle(monkeypatch):
         assert k in r
     util.assert_close(r['rgb0'], r_plain['rgb0'], 'rgb0')
     orc.z_all_override = None
+
+
+@pytest.mark.parametrize('cfg_name', ['room0', 'scannet0000'])
+def test_smoothness_term_matches_oracle(cfg_name):
+    """Row a12: CoSLAM.smoothness (coslam.py:251-274) runs unchanged on top of query_sdf(embed=True) -- the stand-alone
+    HashGrid operator -- value and table gradient against the oracle on the same lattice."""
+    cfg = synth.CONFIGS[cfg_name]()
+    weights = synth.decoder_init(seed=5)
+    probe = JointEncodingFor(cfg)
+    table = synth.table_init(probe.embed_fn.params.numel(), 'trained', seed=77)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    orc = util.make_oracle(cfg, table, weights)
+    g = torch.Generator().manual_seed(4)
+    offset_u, jitter_u = torch.rand(3, generator=g), torch.rand((1, 1, 1, 3), generator=g)
+    ref = orc.smoothness(offset_u, jitter_u)
+    ref.backward()
+
+    t = cfg['training']
+    n, vox, margin = t['smooth_pts'], t['smooth_vox'], t['smooth_margin']
+    bound = synth.bound_tensor(cfg).to(DEV)
+    lo, hi = bound[:, 0], bound[:, 1]
+    offset = offset_u.to(DEV) * (hi - lo - (n - 1) * vox - 2 * margin) + margin
+    ar = torch.arange(0, n - 1, dtype=torch.long, device=DEV)
+    coords = torch.stack(torch.meshgrid(ar, ar, ar, indexing='ij'), -1).float()
+    pts = (coords + jitter_u.to(DEV)) * vox + lo + offset
+    f = model.query_sdf((pts - lo) / (hi - lo), embed=True)
+    tv = ((f[1:] - f[:-1]) ** 2).sum() + ((f[:, 1:] - f[:, :-1]) ** 2).sum() + ((f[:, :, 1:] - f[:, :, :-1]) ** 2).sum()
+    loss = tv / (n ** 3)
+    loss.backward()
+    util.assert_close(loss, ref, 'smoothness')
+    util.assert_close(model.embed_fn.params.grad, orc.table.grad, 'd_table (smoothness)')
+
+
+def test_fused_adam_matches_torch_adam():
+    """the map optimiser of coslam.py:610-634 (decoder weight_decay 1e-6, table eps 1e-15, betas
+    (0.9, 0.99)) -- dense semantics: entries with zero gradient still decay their moments and move."""
+    from coslam_b200 import optim as cb_optim
+    g = torch.Generator().manual_seed(0)
+    shapes = [(32, 80), (16, 32), (32, 63), (3, 32), (1666576,), (7,)]
+    ref_p = [torch.nn.Parameter((torch.rand(s, generator=g) - 0.5).to(DEV)) for s in shapes]
+    our_p = [torch.nn.Parameter(p.detach().clone()) for p in ref_p]
+
+    def groups(ps):
+        return [{'params': ps[:4], 'weight_decay': 1e-6, 'lr': 1e-2}, {'params': ps[4:5], 'eps': 1e-15, 'lr': 1e-2},
+                {'params': ps[5:], 'lr': 1e-3}]
+    ref = torch.optim.Adam(groups(ref_p), betas=(0.9, 0.99))
+    ours = cb_optim.Adam(groups(our_p), betas=(0.9, 0.99))
+    for it in range(5):
+        for a, b in zip(ref_p, our_p):
+            grad = torch.randn(a.shape, generator=g).to(DEV) * (10.0 ** (it - 2))
+            if a.numel() > 1000:
+                grad[torch.rand(a.shape, generator=g).to(DEV) < 0.7] = 0.0        # most table entries see no gradient
+            a.grad, b.grad = grad.clone(), grad.clone()
+        ref.step()
+        ours.step()
+        for k, (a, b) in enumerate(zip(ref_p, our_p)):
+            assert float((a.detach() - b.detach()).abs().max()) <= 2e-6 * float(a.detach().abs().max()), (it, k)
+    sd = ours.state_dict()
+    assert set(sd['state'][0].keys()) == {'step', 'exp_avg', 'exp_avg_sq'}
+    # zero-gradient entries moved too (dense semantics)
+    ours2 = cb_optim.Adam([our_p[5]], lr=1e-3, fused_zero_grad=True)
+    our_p[5].grad = torch.ones_like(our_p[5])
+    ours2.step()
+    assert float(our_p[5].grad.abs().max()) == 0.0
