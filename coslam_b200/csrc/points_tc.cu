@@ -249,9 +249,9 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
             const int64_t pg = pg_raw < a.n_points ? pg_raw : a.n_points - 1;
             float x[3], zdummy;
             point_position(a, pg, x, zdummy);
-#pragma unroll 1
+#pragma unroll
             for (int c = 0; c < 4; ++c) encode_grid_chunk(a, x, xb, c, a_hi, a_lo, row_g);
-#pragma unroll 1
+#pragma unroll
             for (int d = 0; d < 3; ++d) {             // OneBlob: thread xb does bins 8 xb .. 8 xb + 7 of every coordinate
                 float v[8], unused[8];
                 blob_half<false>(x[d], xb, v, unused);
@@ -572,7 +572,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
             if (kWgrad) pair_combine_store(part, xb, a_hi, a_lo, row_g, c);
         }
         // OneBlob: thread xb owns bins 8 xb .. 8 xb + 7 of every coordinate (gradient columns 32 + 16 d + 8 xb .. of d_in1)
-#pragma unroll 1
+#pragma unroll
         for (int d = 0; d < 3; ++d) {
             uint32_t gb[16];
             tmem_ld_x16(trow + kColDin1 + 32 + 16 * d, gb);
