@@ -46,7 +46,8 @@ def parse():
     ap.add_argument('--workload', default='room0', choices=sorted(synth.CONFIGS))
     ap.add_argument('--cpu-rays', type=int, default=4096, help='rays per CPU-baseline step')
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--tracking', action='store_true', help='also time the 1024-ray x 10-iteration tracking loop')
+    ap.add_argument('--tracking', action='store_true', help='(default on one GPU) also time the tracking loop: ms/frame')
+    ap.add_argument('--no-tracking', action='store_true')
     return ap.parse_args()
 
 
@@ -254,7 +255,7 @@ def run_ours(args):
     h2d = sum(t.numel() * t.element_size() for t in host)
 
     extra = {}
-    if args.tracking and rank == 0:
+    if rank == 0 and (args.tracking or world == 1) and not args.no_tracking:
         extra['tracking'] = time_tracking(model, cfg, dev)
 
     cpu = None
@@ -303,34 +304,35 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def time_tracking(model, cfg, dev, n_rays=1024, iters=10, frames=20):
-    """Tracking shape (coslam.py:502-594): 10 dependent iterations of a 1024-ray fwd+bwd that only needs dL/d rays;
-    map parameters frozen.  Reports ms per frame (10 iterations), no pose optimiser."""
-    req = [p.requires_grad for p in model.parameters()]
-    for p in model.parameters():
-        p.requires_grad_(False)
-    batch = [t.to(dev) for t in synth.ray_batch(cfg, n_rays, seed=5)]
-    w = loss_weights(cfg)
-
-    def frame():
-        for _ in range(iters):
-            o = batch[0].detach().requires_grad_(True)
-            d = batch[1].detach().requires_grad_(True)
-            ret = model.forward(o, d, batch[2], batch[3])
-            (w[0] * ret['rgb_loss'] + w[1] * ret['depth_loss'] + w[2] * ret['sdf_loss'] + w[3] * ret['fs_loss']).backward()
-
-    for _ in range(3):
-        frame()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(frames):
-        frame()
-    e1.record()
-    torch.cuda.synchronize()
-    for p, r in zip(model.parameters(), req):
-        p.requires_grad_(r)
-    return {'ms_per_frame': e0.elapsed_time(e1) / frames, 'rays': n_rays, 'iters': iters}
+def time_tracking(model, cfg, dev, frames=20):
+    """Tracking ms/frame (BASELINE.json metric 2): `tracking.iter` dependent iterations of pose -> rays -> fwd -> loss -> bwd to
+    the pose -> pose Adam, with the best-pose bookkeeping (coslam.py:502-573), through coslam_b200.tracking.FrameTracker:
+    the loop as ONE CUDA graph per frame, and the same loop launched eagerly for comparison.  Inputs start on the host
+    (pinned), the estimated pose is read back every frame."""
+    from coslam_b200 import pose
+    from coslam_b200.tracking import FrameTracker
+    n_rays = int(cfg['tracking']['sample'])
+    g = torch.Generator().manual_seed(5)
+    bound = synth.bound_tensor(cfg)
+    dir_cam = torch.stack([(torch.rand(n_rays, generator=g) - 0.5) * 1.6, (torch.rand(n_rays, generator=g) - 0.5) * 1.0,
+                           -torch.ones(n_rays)], -1).pin_memory()
+    rgb = torch.rand(n_rays, 3, generator=g).pin_memory()
+    depth = (torch.rand(n_rays, 1, generator=g) * 3 + 0.5).pin_memory()
+    c2w0 = pose.pose_matrix(torch.tensor([[0.3, -0.5, 0.2]]), bound.mean(1)[None])[0]
+    out = {'rays': n_rays, 'iters': int(cfg['tracking']['iter'])}
+    noise_state = (model.noise_mode, model._noise_counter)
+    for name, use_graph in (('graph', True), ('eager', False)):
+        tr = FrameTracker(model, cfg, device=dev, use_graph=use_graph)
+        for _ in range(3):
+            tr.track(dir_cam, rgb, depth, c2w0)[0].cpu()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(frames):
+            tr.track(dir_cam, rgb, depth, c2w0)[0].cpu()          # the read-back is the per-frame sync
+        out['ms_per_frame_' + name] = (time.perf_counter() - t0) * 1e3 / frames
+    model.noise_mode, model._noise_counter = noise_state
+    out['ms_per_frame'] = out['ms_per_frame_graph']
+    return out
 
 
 if __name__ == '__main__':

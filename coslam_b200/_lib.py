@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p

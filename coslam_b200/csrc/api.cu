@@ -152,8 +152,8 @@ int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq
 }
 
 int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform, const float* lin_guided,
-                      const float* lin_nodepth, const float* noise, uint64_t seed, int64_t n_rays, float* z_vals, int64_t* counts,
-                      void* stream) {
+                      const float* lin_nodepth, const float* noise, uint64_t seed, const uint64_t* seed_dev, int64_t n_rays, float* z_vals,
+                      int64_t* counts, void* stream) {
     CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
     const int S = (int)(cfg->n_uniform + cfg->n_guided);
     CB_REQUIRE(cfg->n_guided >= 1 && S <= 256, "n_samples_d + n_range_d = %d must be in [1,256] with n_range_d >= 1", S);
@@ -162,7 +162,7 @@ int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const 
     CB_REQUIRE(target_d && lin_guided && lin_nodepth && z_vals && (cfg->n_uniform == 0 || lin_uniform), "sample_rays: NULL buffer");
     cb200::SampleArgs a{};
     a.target_d = target_d; a.lin_uniform = lin_uniform; a.lin_guided = lin_guided; a.lin_nodepth = lin_nodepth;
-    a.noise = noise; a.seed = seed; a.n_rays = n_rays; a.z_vals = z_vals;
+    a.noise = noise; a.seed = seed; a.seed_dev = reinterpret_cast<const unsigned long long*>(seed_dev); a.n_rays = n_rays; a.z_vals = z_vals;
     a.counts = reinterpret_cast<unsigned long long*>(counts);
     a.n_uniform = (int)cfg->n_uniform; a.n_guided = (int)cfg->n_guided; a.perturb = (int)cfg->perturb;
     a.trunc_sc = cfg->trunc_sc; a.depth_trunc = cfg->depth_trunc;

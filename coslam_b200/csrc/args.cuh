@@ -39,6 +39,7 @@ struct SampleArgs {
     const float* lin_nodepth;
     const float* noise;
     uint64_t seed;
+    const unsigned long long* seed_dev;   // optional device counter added to `seed` (graph-captured loops)
     int64_t n_rays;
     float* z_vals;
     unsigned long long* counts;

@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(kRayWarps * 32) sample_rays_kernel(SampleArgs 
     __syncthreads();
 
     unsigned n_front = 0, n_sdf = 0, n_valid = 0;
+    const uint64_t seed = a.seed + (a.seed_dev ? *a.seed_dev : 0ull);
     for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
         const float d = a.target_d[ray];
         const bool nodepth = d <= 0.0f;                      // scene_rep.py:239
@@ -79,7 +80,7 @@ __global__ void __launch_bounds__(kRayWarps * 32) sample_rays_kernel(SampleArgs 
                     u = a.noise[ray * S + s];
                 } else {
                     const uint4 r = philox4x32(make_uint4((uint32_t)ray, (uint32_t)(ray >> 32), (uint32_t)(s >> 2), 0u),
-                                               make_uint2((uint32_t)a.seed, (uint32_t)(a.seed >> 32)));
+                                               make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
                     const uint32_t pick = (s & 3) == 0 ? r.x : (s & 3) == 1 ? r.y : (s & 3) == 2 ? r.z : r.w;
                     u = u32_to_unit(pick);
                 }

@@ -157,7 +157,7 @@ class SceneSpec(object):
 # raw wrappers (no autograd)
 # --------------------------------------------------------------------------------------------------------------------
 
-def sample_rays(spec, target_d, noise=None, seed=0, counts=None, perturb=None):
+def sample_rays(spec, target_d, noise=None, seed=0, counts=None, perturb=None, seed_dev=None):
     """model/scene_rep.py:227-255.  target_d [N] or [N,1]; noise [N,S] CPU-drawn uniforms or None (device Philox).
     Returns z_vals [N,S]; accumulates (n_front, n_sdf, n_valid_depth) into counts (int64 [3]) when given."""
     d = _f32c(target_d.reshape(-1))
@@ -169,7 +169,7 @@ def sample_rays(spec, target_d, noise=None, seed=0, counts=None, perturb=None):
         if tuple(noise.shape) != (n, spec.n_samples):
             raise ValueError('noise must have shape [N, S]')
     check(_lib.load().cb200_sample_rays(ctypes.byref(spec.render_cfg(perturb)), ptr(d), ptr(lin_u), ptr(lin_g), ptr(lin_n),
-                                        ptr(noise), ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ctypes.c_int64(n), ptr(z),
+                                        ptr(noise), ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ptr(seed_dev), ctypes.c_int64(n), ptr(z),
                                         ptr(counts), stream()), 'sample_rays')
     return z
 

@@ -49,6 +49,7 @@ class JointEncoding(nn.Module):
         self.noise_seed = 0
         self.process_group = None          # set by coslam_b200.dist for ray-sharded mapping
         self._step = 0
+        self._noise_counter = None
         self.get_resolution()
         self.get_encoding(config)
         self.get_decoder(config)
@@ -98,8 +99,17 @@ class JointEncoding(nn.Module):
     def _noise(self, n_rays, n_samples, device):
         if self.noise_mode == 'host':
             return torch.rand((n_rays, n_samples)).to(device), 0       # CPU generator, model/scene_rep.py:255
+        if self._noise_counter is not None:                               # graph-captured loops: the step lives on the device
+            return None, int(self.noise_seed) << 32
         self._step += 1
         return None, (int(self.noise_seed) << 32) + self._step
+
+    def use_device_noise_counter(self, device):
+        """Device-Philox noise whose step counter is a device tensor (incremented by a captured torch op after every
+        sampling call), so a CUDA-graph replay of forward() draws fresh jitter.  Implies noise_mode = 'device'."""
+        self.noise_mode = 'device'
+        self._noise_counter = torch.zeros(1, dtype=torch.int64, device=device)
+        return self._noise_counter
 
     # ---- model/scene_rep.py:77-124 ---------------------------------------------------------------------------------
     def sdf2weights(self, sdf, z_vals, args=None):
@@ -166,7 +176,11 @@ class JointEncoding(nn.Module):
         noise, seed = (None, 0)
         if self.spec.perturb:
             noise, seed = self._noise(n, self.spec.n_samples, target_d.device)
-        return ops.sample_rays(self.spec, target_d, noise=noise, seed=seed, counts=counts)
+        z = ops.sample_rays(self.spec, target_d, noise=noise, seed=seed, counts=counts,
+                            seed_dev=self._noise_counter if noise is None else None)
+        if noise is None and self._noise_counter is not None:
+            self._noise_counter.add_(1)
+        return z
 
     def render_rays(self, rays_o, rays_d, target_d=None):
         self._require_cuda(rays_o)

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 6
+#define CB200_ABI_VERSION 7
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -138,10 +138,11 @@ int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq
  *   target_d [N]; lin_uniform [n_uniform], lin_guided [n_guided], lin_nodepth [n_guided] are the three
  *   torch.linspace constants of :227,:239,:242 (device copies);
  *   noise [N,S] = the torch.rand of :255, or NULL to draw Philox noise in-kernel from (seed, ray, sample);
+ *   seed_dev: optional device counter ADDED to seed when the kernel runs (a CUDA-graph replay then draws fresh noise);
  *   z_vals [N,S] out;  counts [3] int64, ACCUMULATED (+=): n_front, n_sdf, n_valid_depth  (may be NULL). */
 int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform,
                       const float* lin_guided, const float* lin_nodepth, const float* noise, uint64_t seed,
-                      int64_t n_rays, float* z_vals, int64_t* counts, void* stream);
+                      const uint64_t* seed_dev, int64_t n_rays, float* z_vals, int64_t* counts, void* stream);
 
 /* Importance resampling of render_rays (model/scene_rep.py:265-272) with sample_pdf (model/utils.py:32-71):
  *   z_vals [N,S] ascending coarse samples, weights [N,S] their rendering weights (cb200_render_fwd);

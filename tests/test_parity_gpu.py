@@ -461,3 +461,68 @@ def test_fused_adam_matches_torch_adam():
     our_p[5].grad = torch.ones_like(our_p[5])
     ours2.step()
     assert float(our_p[5].grad.abs().max()) == 0.0
+
+
+def _tracking_case(cfg, n_rays, seed=3):
+    g = torch.Generator().manual_seed(seed)
+    bound = synth.bound_tensor(cfg)
+    centre = bound.mean(1)
+    dir_cam = torch.stack([(torch.rand(n_rays, generator=g) - 0.5) * 1.6, (torch.rand(n_rays, generator=g) - 0.5) * 1.0,
+                           -torch.ones(n_rays)], -1)
+    rot0 = torch.tensor([[0.3, -0.5, 0.2]])
+    from coslam_b200 import pose
+    c2w = pose.pose_matrix(rot0, centre[None] + torch.tensor([[0.2, -0.1, 0.1]]))[0]
+    rgb = torch.rand(n_rays, 3, generator=g)
+    depth = torch.rand(n_rays, 1, generator=g) * 3 + 0.5
+    depth[::17] = 0.0
+    return dir_cam, rgb, depth, c2w
+
+
+@pytest.mark.parametrize('cfg_name', ['room0', 'scannet0000'])
+def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
+    """Tracking (coslam.py:502-573): the graph-captured loop against (a) the same loop run eagerly and (b) the reference's
+    loop restated on the oracle with torch.optim.Adam (perturb = 0 so both sides are deterministic)."""
+    from coslam_b200 import pose
+    from coslam_b200.tracking import FrameTracker
+    cfg = synth.CONFIGS[cfg_name]()
+    cfg['training']['perturb'] = 0.0
+    n_rays = 512
+    cfg['tracking']['sample'] = n_rays
+    weights = synth.decoder_init(seed=5)
+    probe = JointEncodingFor(cfg)
+    table = synth.table_init(probe.embed_fn.params.numel(), 'trained', seed=77)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    dir_cam, rgb, depth, c2w0 = _tracking_case(cfg, n_rays)
+
+    eager = FrameTracker(model, cfg, device=DEV, use_graph=False)
+    est_e, info_e = eager.track(dir_cam, rgb, depth, c2w0)
+    est_e, best_e = est_e.clone(), float(info_e['best_loss'])
+    graph = FrameTracker(model, cfg, device=DEV, use_graph=True)
+    for _ in range(2):                                   # second replay: the per-frame state reset is part of the graph
+        est_g, info_g = graph.track(dir_cam, rgb, depth, c2w0)
+        # not bit-identical: the ray-gradient atomics sum in a different order every run and Adam normalises the step
+        assert float((est_g - est_e).abs().max()) <= 2e-5
+        assert abs(float(info_g['best_loss']) - best_e) <= 1e-4 * abs(best_e)
+    assert all(p.requires_grad for p in model.parameters())
+    assert float((info_g['last_c2w'].cpu() - c2w0).abs().max()) > 1e-4          # the pose did move
+
+    # the reference loop on the oracle
+    orc = util.make_oracle(cfg, table, weights)
+    quat = cfg['training']['rot_rep'] != 'axis_angle'
+    rot = torch.nn.Parameter(pose.matrix_to_quaternion(c2w0[None, :3, :3]) if quat else pose.matrix_to_axis_angle(c2w0[None, :3, :3]))
+    trans = torch.nn.Parameter(c2w0[None, :3, 3].clone())
+    opt = torch.optim.Adam([{'params': rot, 'lr': cfg['tracking']['lr_rot']}, {'params': trans, 'lr': cfg['tracking']['lr_trans']}])
+    best, best_c2w, last_c2w = None, None, None
+    for _ in range(cfg['tracking']['iter']):
+        opt.zero_grad()
+        c2w = pose.pose_matrix(rot, trans)
+        ro, rd = pose.rays_from_pose(dir_cam, c2w)
+        loss = orc.total_loss(orc.forward(ro, rd, rgb, depth))
+        last_c2w = c2w.detach().clone()
+        if best is None or loss.item() < best:
+            best, best_c2w = loss.item(), c2w.detach().clone()
+        loss.backward()
+        opt.step()
+    assert abs(float(info_g['best_loss']) - best) <= 1e-3 * abs(best)
+    assert float((est_g.cpu() - best_c2w[0]).abs().max()) <= 3e-4
+    assert float((info_g['last_c2w'].cpu() - last_c2w[0]).abs().max()) <= 3e-4

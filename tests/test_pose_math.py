@@ -106,3 +106,26 @@ def test_per_frame_alignment_table():
     m = fa.PerFrameAlignment(10)
     ids = torch.tensor([0, 9, 3])
     assert torch.equal(m(ids), torch.tensor([[1., 1., 0., 0.]]).repeat(3, 1))
+
+
+def test_package_pose_helpers_match_reference_and_roundtrip():
+    """coslam_b200/pose.py (used by the graph-captured tracker) against optimization/utils.py and a rotation round trip."""
+    from coslam_b200 import pose
+    ou = _ref_module('optimization.utils')
+    g = torch.Generator().manual_seed(7)
+    rot, trans = torch.randn(32, 3, generator=g), torch.randn(32, 3, generator=g)
+    assert torch.equal(pose.pose_matrix(rot, trans), ou.at_to_transform_matrix(rot, trans))
+    quat = torch.randn(32, 4, generator=g)
+    assert torch.equal(pose.pose_matrix(quat, trans), ou.qt_to_transform_matrix(quat, trans))
+    R = pose.axis_angle_to_matrix(rot)
+    aa = pose.matrix_to_axis_angle(R)                          # principal value: compare through the rotation
+    assert torch.allclose(pose.axis_angle_to_matrix(aa), R, atol=2e-5)
+    q = pose.matrix_to_quaternion(R)
+    assert torch.allclose(q.norm(dim=-1), torch.ones(32), atol=1e-5)
+    assert torch.allclose(pose.quaternion_to_matrix(q), R, atol=2e-5)
+    dir_cam = torch.randn(50, 3, generator=g)
+    c2w = pose.pose_matrix(rot[:1], trans[:1])
+    ro, rd = pose.rays_from_pose(dir_cam, c2w)
+    ro_ref = c2w[..., :3, -1].repeat(50, 1)
+    rd_ref = torch.sum(dir_cam[..., None, :] * c2w[:, :3, :3], -1)
+    assert torch.equal(ro, ro_ref) and torch.equal(rd, rd_ref)
