@@ -140,6 +140,26 @@ int cb200_oneblob_bwd(const float* x, const float* dy, int64_t n_points, uint32_
     return cuda_result(cb200::launch_oneblob_bwd(x, dy, n_points * n_dims, (int)n_bins, dx, (cudaStream_t)stream), "oneblob_bwd");
 }
 
+int cb200_assemble_rays_fwd(const float* kf_rays, const int64_t* ray_idx, const int64_t* pose_slot, const float* poses, int64_t n_rays,
+                            int64_t n_poses, float* rays_o, float* rays_d, float* target_rgb, float* target_d, void* stream) {
+    CB_REQUIRE(n_rays >= 0 && n_poses >= 1, "assemble_rays: bad sizes");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(kf_rays && ray_idx && pose_slot && poses && rays_o && rays_d && target_rgb && target_d, "assemble_rays_fwd: NULL buffer");
+    return cuda_result(cb200::launch_assemble_rays_fwd(kf_rays, reinterpret_cast<const long long*>(ray_idx),
+                                                       reinterpret_cast<const long long*>(pose_slot), poses, n_rays, n_poses, rays_o, rays_d,
+                                                       target_rgb, target_d, (cudaStream_t)stream), "assemble_rays_fwd");
+}
+
+int cb200_assemble_rays_bwd(const float* kf_rays, const int64_t* ray_idx, const int64_t* pose_slot, const float* d_rays_o,
+                            const float* d_rays_d, int64_t n_rays, int64_t n_poses, float* d_poses, void* stream) {
+    CB_REQUIRE(n_rays >= 0 && n_poses >= 1, "assemble_rays: bad sizes");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(kf_rays && ray_idx && pose_slot && d_rays_o && d_rays_d && d_poses, "assemble_rays_bwd: NULL buffer");
+    return cuda_result(cb200::launch_assemble_rays_bwd(kf_rays, reinterpret_cast<const long long*>(ray_idx),
+                                                       reinterpret_cast<const long long*>(pose_slot), d_rays_o, d_rays_d, n_rays, n_poses,
+                                                       d_poses, (cudaStream_t)stream), "assemble_rays_bwd");
+}
+
 int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1, float beta2, float eps,
                     float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, void* stream) {
     CB_REQUIRE(n >= 0, "adam_step: negative size");

@@ -83,6 +83,11 @@ struct RenderArgs {
     float* d_raw;              // [N,S,4]
 };
 
+cudaError_t launch_assemble_rays_fwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* poses,
+                                     long long n, long long n_poses, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
+                                     cudaStream_t st);
+cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* d_rays_o,
+                                     const float* d_rays_d, long long n, long long n_poses, float* d_poses, cudaStream_t st);
 cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                              float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, cudaStream_t st);
 cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st);

@@ -1,0 +1,108 @@
+// Ray assembly for mapping / bundle adjustment (coslam.py:336-355, model/keyframe.py:96-106): gather the sampled 7-float
+// keyframe rays (camera-frame direction, rgb, depth) by index, gather each ray's pose by keyframe slot (negative slot =
+// counted from the end, slot -1 = current frame, like the Python indexing of `poses_all[ids_all]`), and rotate:
+//   rays_d = sum_k dir_cam[k] * R[:, k]   (same summation order as torch.sum(dir[..., None, :] * R, -1)),  rays_o = t.
+// Backward: dL/dposes[slot][:3, :3] += d_rays_d (outer) dir_cam,  dL/dposes[slot][:3, 3] += d_rays_o  -- a segment sum by
+// keyframe slot, accumulated per CTA in shared memory (few keyframes, thousands of rays) and flushed once.
+#include "args.cuh"
+
+namespace cb200 {
+
+struct AssembleArgs {
+    const float* kf_rays;        // [M,7]
+    const long long* ray_idx;    // [N] rows of kf_rays
+    const long long* pose_slot;  // [N]
+    const float* poses;          // [K,4,4] row-major
+    long long n, n_poses;
+    float* rays_o;
+    float* rays_d;
+    float* target_rgb;
+    float* target_d;
+    const float* d_rays_o;       // backward
+    const float* d_rays_d;
+    float* d_poses;              // [K,4,4] +=
+};
+
+__global__ void __launch_bounds__(256) assemble_rays_fwd_kernel(AssembleArgs a) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const float* r = a.kf_rays + a.ray_idx[i] * 7;
+    long long slot = a.pose_slot[i];
+    if (slot < 0) slot += a.n_poses;
+    const float* T = a.poses + slot * 16;
+    const float d0 = r[0], d1 = r[1], d2 = r[2];
+#pragma unroll
+    for (int row = 0; row < 3; ++row) {
+        // products rounded separately, summed left to right: what torch.sum over the last axis of 3 does
+        a.rays_d[i * 3 + row] = __fadd_rn(__fadd_rn(__fmul_rn(d0, T[row * 4 + 0]), __fmul_rn(d1, T[row * 4 + 1])), __fmul_rn(d2, T[row * 4 + 2]));
+        a.rays_o[i * 3 + row] = T[row * 4 + 3];
+        a.target_rgb[i * 3 + row] = r[3 + row];
+    }
+    a.target_d[i] = r[6];
+}
+
+constexpr int kMaxSharedPoses = 1024;     // 1024 x 12 floats = 48 KB
+
+__global__ void __launch_bounds__(256) assemble_rays_bwd_kernel(AssembleArgs a, int use_shared) {
+    extern __shared__ float acc[];         // [n_poses][12] when use_shared
+    if (use_shared) {
+        for (long long k = threadIdx.x; k < a.n_poses * 12; k += blockDim.x) acc[k] = 0.f;
+        __syncthreads();
+    }
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (long long)gridDim.x * blockDim.x) {
+        const float* r = a.kf_rays + a.ray_idx[i] * 7;
+        long long slot = a.pose_slot[i];
+        if (slot < 0) slot += a.n_poses;
+        const float d[3] = {r[0], r[1], r[2]};
+#pragma unroll
+        for (int row = 0; row < 3; ++row) {
+            const float gd = a.d_rays_d[i * 3 + row], go = a.d_rays_o[i * 3 + row];
+            if (use_shared) {
+                float* dst = acc + slot * 12 + row * 4;
+                atomicAdd(dst + 0, gd * d[0]);
+                atomicAdd(dst + 1, gd * d[1]);
+                atomicAdd(dst + 2, gd * d[2]);
+                atomicAdd(dst + 3, go);
+            } else {
+                float* dst = a.d_poses + slot * 16 + row * 4;
+                atomicAdd(dst + 0, gd * d[0]);
+                atomicAdd(dst + 1, gd * d[1]);
+                atomicAdd(dst + 2, gd * d[2]);
+                atomicAdd(dst + 3, go);
+            }
+        }
+    }
+    if (use_shared) {
+        __syncthreads();
+        for (long long k = threadIdx.x; k < a.n_poses * 12; k += blockDim.x) {
+            const float v = acc[k];
+            if (v != 0.f) atomicAdd(a.d_poses + (k / 12) * 16 + (k % 12), v);
+        }
+    }
+}
+
+cudaError_t launch_assemble_rays_fwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* poses,
+                                     long long n, long long n_poses, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
+                                     cudaStream_t st) {
+    AssembleArgs a{kf_rays, ray_idx, pose_slot, poses, n, n_poses, rays_o, rays_d, target_rgb, target_d, nullptr, nullptr, nullptr};
+    assemble_rays_fwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* d_rays_o,
+                                     const float* d_rays_d, long long n, long long n_poses, float* d_poses, cudaStream_t st) {
+    AssembleArgs a{kf_rays, ray_idx, pose_slot, nullptr, n, n_poses, nullptr, nullptr, nullptr, nullptr, d_rays_o, d_rays_d, d_poses};
+    const int use_shared = n_poses <= kMaxSharedPoses;
+    const size_t smem = use_shared ? sizeof(float) * 12 * (size_t)n_poses : 0;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(assemble_rays_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    long long blocks = (n + 256 * 8 - 1) / (256 * 8);          // 8 rays per thread: fewer shared-accumulator flushes
+    if (blocks < 1) blocks = 1;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    assemble_rays_bwd_kernel<<<(unsigned)blocks, 256, smem, st>>>(a, use_shared);
+    return cudaGetLastError();
+}
+
+}  // namespace cb200

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 7
+#define CB200_ABI_VERSION 8
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -118,6 +118,20 @@ int cb200_hash_indices(const cb200_grid* grid, const float* x, int64_t n_points,
 int cb200_oneblob_fwd(const float* x, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* out, void* stream);
 int cb200_oneblob_bwd(const float* x, const float* dy, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* dx,
                       void* stream);
+
+/* ---- keyframe ray assembly ----------------------------------------------------- */
+
+/* Mapping / BA ray assembly (coslam.py:346-355 after model/keyframe.py:96-106): for ray i
+ *   r = kf_rays[ray_idx[i]] (7 floats: camera-frame direction, rgb, depth);  T = poses[pose_slot[i]] (negative slot counts
+ *   from the end: -1 = current frame);  rays_d[i] = sum_k r.dir[k] * T[:3, k];  rays_o[i] = T[:3, 3];
+ *   target_rgb[i] = r[3:6];  target_d[i] = r[6].
+ * kf_rays [M,7], poses [K,4,4] row-major, all device memory. */
+int cb200_assemble_rays_fwd(const float* kf_rays, const int64_t* ray_idx, const int64_t* pose_slot, const float* poses,
+                            int64_t n_rays, int64_t n_poses, float* rays_o, float* rays_d, float* target_rgb,
+                            float* target_d, void* stream);
+/* its backward with respect to the poses: d_poses [K,4,4] += (rows 0..2: d_rays_d (outer) dir | d_rays_o), row 3 untouched */
+int cb200_assemble_rays_bwd(const float* kf_rays, const int64_t* ray_idx, const int64_t* pose_slot, const float* d_rays_o,
+                            const float* d_rays_d, int64_t n_rays, int64_t n_poses, float* d_poses, void* stream);
 
 /* ---- optimiser ----------------------------------------------------------------- */
 

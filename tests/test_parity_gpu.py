@@ -526,3 +526,58 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
     assert abs(float(info_g['best_loss']) - best) <= 1e-3 * abs(best)
     assert float((est_g.cpu() - best_c2w[0]).abs().max()) <= 3e-4
     assert float((info_g['last_c2w'].cpu() - last_c2w[0]).abs().max()) <= 3e-4
+
+
+def test_keyframe_database_and_ray_assembly_match_reference_lines():
+    """device-resident keyframe store with the reference's Python-`random` draws (ray
+    indices bit-exact) and the fused ray assembly of coslam.py:346-355 with its pose gradient."""
+    import random
+    from coslam_b200 import pose
+    from coslam_b200.keyframe import KeyFrameDatabase, assemble_rays
+    cfg = synth.room0_config()
+    H, W, R, n_kf, every = 40, 60, 200, 9, 5
+    g = torch.Generator().manual_seed(0)
+    db = KeyFrameDatabase(cfg, H, W, n_kf + 2, R, DEV)
+    host_rays = torch.zeros(n_kf + 2, R, 7)
+    random.seed(7)
+    state = random.getstate()
+    frames = []
+    for k in range(n_kf):
+        batch = {'direction': torch.randn(1, H, W, 3, generator=g), 'rgb': torch.rand(1, H, W, 3, generator=g),
+                 'depth': torch.rand(1, H, W, generator=g) * 4, 'frame_id': torch.tensor([k * every])}
+        frames.append(batch)
+        db.add_keyframe({k_: v.to(DEV) if k_ != 'frame_id' else v for k_, v in batch.items()})
+    random.setstate(state)                                    # replay the reference's host-side logic (keyframe.py:40-94)
+    for k, batch in enumerate(frames):
+        rays = torch.cat([batch['direction'], batch['rgb'], batch['depth'][..., None]], -1).reshape(1, -1, 7)
+        host_rays[k] = rays[:, random.sample(range(0, H * W), R)]
+    assert torch.equal(db.rays.cpu(), host_rays)
+    assert len(db) == n_kf
+
+    random.seed(11)
+    rays_dev, ids_dev = db.sample_global_rays(512)
+    random.seed(11)
+    idxs = torch.tensor(random.sample(range(n_kf * R), 512))
+    assert torch.equal(rays_dev.cpu(), host_rays[:n_kf].reshape(-1, 7)[idxs])
+    assert torch.equal(ids_dev, (torch.arange(n_kf) * every)[idxs // R])
+
+    # fused assembly against the reference's three lines, forward and pose gradient
+    rot = (torch.randn(n_kf + 1, 3, generator=g) * 0.5).to(DEV).requires_grad_(True)
+    trans = torch.randn(n_kf + 1, 3, generator=g).to(DEV).requires_grad_(True)
+    ids_all = torch.cat([ids_dev // every, -torch.ones(40)]).to(torch.int64).to(DEV)
+    cur = torch.rand(40, 7, generator=g).to(DEV)
+    store = torch.cat([db.rays[:n_kf].reshape(-1, 7), cur], 0)
+    idx_all = torch.cat([idxs, n_kf * R + torch.arange(40)]).to(DEV)
+    poses = pose.pose_matrix(rot, trans)
+    ro, rd, rgb, dep = assemble_rays(store, idx_all, ids_all, poses)
+    rays = store[idx_all]
+    rd_ref = torch.sum(rays[..., None, None, :3] * poses[ids_all, None, :3, :3], -1)
+    ro_ref = poses[ids_all, None, :3, -1].repeat(1, rd_ref.shape[1], 1).reshape(-1, 3)
+    rd_ref = rd_ref.reshape(-1, 3)
+    assert torch.equal(ro, ro_ref) and torch.equal(rgb, rays[:, 3:6]) and torch.equal(dep, rays[:, 6:7])
+    assert float((rd - rd_ref).detach().abs().max()) <= 1e-6
+    go, gd = torch.randn(552, 3, generator=g).to(DEV), torch.randn(552, 3, generator=g).to(DEV)
+    ref = torch.autograd.grad((ro_ref * go).sum() + (rd_ref * gd).sum(), (rot, trans), retain_graph=True)
+    got = torch.autograd.grad((ro * go).sum() + (rd * gd).sum(), (rot, trans))
+    for a, b, name in zip(got, ref, ('d_rot', 'd_trans')):
+        util.assert_close(a, b, name, tol=1e-5)
