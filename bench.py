@@ -44,6 +44,8 @@ def parse():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--rays', type=int, default=1 << 18, help='rays per GPU per step')
     ap.add_argument('--workload', default='room0', choices=sorted(synth.CONFIGS))
+    ap.add_argument('--hash-size', type=int, default=0, help='override grid.hash_size (scannet base file: 19)')
+    ap.add_argument('--n-importance', type=int, default=-1, help='override training.n_importance (tum.yaml: 128)')
     ap.add_argument('--cpu-rays', type=int, default=4096, help='rays per CPU-baseline step')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--tracking', action='store_true', help='(default on one GPU) also time the tracking loop: ms/frame')
@@ -139,6 +141,10 @@ def run_reference(args):
     if rank != 0:
         return
     cfg = synth.CONFIGS[args.workload]()
+    if args.hash_size:
+        cfg['grid']['hash_size'] = args.hash_size
+    if args.n_importance >= 0:
+        cfg['training']['n_importance'] = args.n_importance
     steps = max(1, args.steps)
     times, cores = time_cpu(cfg, args.cpu_rays, steps, max(1, min(args.warmup, 3)), budget_s=120.0)
     total = sum(times)
@@ -174,6 +180,10 @@ def run_ours(args):
         dist.init_process_group('nccl', device_id=dev)
 
     cfg = synth.CONFIGS[args.workload]()
+    if args.hash_size:
+        cfg['grid']['hash_size'] = args.hash_size
+    if args.n_importance >= 0:
+        cfg['training']['n_importance'] = args.n_importance
     S = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
     n = args.rays
     model = JointEncoding(cfg, synth.bound_tensor(cfg).to(dev)).to(dev)
