@@ -1,0 +1,91 @@
+"""Ray-sharded mapping step on 2 GPUs (NCCL) against the single-GPU step on the same global batch:
+losses are the GLOBAL ones on every rank, summed gradients agree within the 1e-3 gate (sharding changes summation order).
+Needs two visible GPUs; skipped otherwise (run with `gpurun --gpus 2`)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from coslam_b200 import synth
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _build(cfg, dev):
+    from coslam_b200.scene_rep import JointEncoding
+    model = JointEncoding(cfg, synth.bound_tensor(cfg).to(dev)).to(dev)
+    table = synth.table_init(model.embed_fn.params.numel(), 'trained', seed=77)
+    with torch.no_grad():
+        model.embed_fn.params.copy_(table.to(dev))
+        for dst, src in zip(model.decoder.fused_weights(), synth.decoder_init(seed=5)):
+            dst.copy_(src.to(dev))
+    model.train()
+    return model
+
+
+def _worker(rank, world, port, n_rays, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world)
+    try:
+        from coslam_b200.dist import ShardedMapper, equal_shard
+        dev = 'cuda:%d' % rank
+        cfg = synth.room0_config()
+        cfg['training']['perturb'] = 0.0
+        model = _build(cfg, dev)
+        batch = synth.keyframe_ray_batch(cfg, n_rays, n_kf=8, seed=3)
+        lo, hi = equal_shard(n_rays, world, rank)
+        o = batch[0][lo:hi].to(dev).requires_grad_(True)
+        d = batch[1][lo:hi].to(dev).requires_grad_(True)
+        t = cfg['training']
+        mapper = ShardedMapper(model, (t['rgb_weight'], t['depth_weight'], t['sdf_weight'], t['fs_weight']))
+        loss, ret = mapper.step(o, d, batch[2][lo:hi].to(dev), batch[3][lo:hi].to(dev))
+        out[rank] = {'loss': float(loss.detach()), 'losses': [float(ret[k].detach()) for k in ('rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss')],
+                     'd_table': model.embed_fn.params.grad.cpu(), 'dW1': model.decoder.fused_weights()[0].grad.cpu(),
+                     'd_rays_o': o.grad.cpu()}
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_sharded_step_matches_single_gpu():
+    n_rays, world = 4096, 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, _free_port(), n_rays, out), nprocs=world, join=True)
+
+    dev = 'cuda:0'
+    cfg = synth.room0_config()
+    cfg['training']['perturb'] = 0.0
+    model = _build(cfg, dev)
+    batch = synth.keyframe_ray_batch(cfg, n_rays, n_kf=8, seed=3)
+    o = batch[0].to(dev).requires_grad_(True)
+    d = batch[1].to(dev).requires_grad_(True)
+    ret = model.forward(o, d, batch[2].to(dev), batch[3].to(dev))
+    t = cfg['training']
+    loss = t['rgb_weight'] * ret['rgb_loss'] + t['depth_weight'] * ret['depth_loss'] + t['sdf_weight'] * ret['sdf_loss'] \
+        + t['fs_weight'] * ret['fs_loss']
+    loss.backward()
+
+    def rel(a, b):
+        return float((a.double() - b.double()).abs().max() / b.double().abs().max())
+    for r in range(world):
+        assert abs(out[r]['loss'] - float(loss.detach())) <= 1e-5 * abs(float(loss.detach()))
+        for a, k in zip(out[r]['losses'], ('rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss')):
+            assert abs(a - float(ret[k].detach())) <= 1e-5 * abs(float(ret[k].detach())) + 1e-9, k
+        assert rel(out[r]['d_table'], model.embed_fn.params.grad.cpu()) <= 1e-3
+        assert rel(out[r]['dW1'], model.decoder.fused_weights()[0].grad.cpu()) <= 1e-3
+    assert torch.equal(out[0]['d_table'], out[1]['d_table'])          # replicas stay identical after AR-2
+    got = torch.cat([out[0]['d_rays_o'], out[1]['d_rays_o']], 0)
+    assert rel(got, o.grad.cpu()) <= 1e-3
