@@ -29,7 +29,8 @@ def _stamp():
             with open(os.path.join(root, name), 'rb') as f:
                 h.update(name.encode())
                 h.update(f.read())
-    h.update(' '.join(NVCC_FLAGS).encode())
+    # flags without the absolute include path: the tree is built in one place and run from another (gpurun snapshot)
+    h.update(' '.join(f for f in NVCC_FLAGS if f != INCLUDE).encode())
     return h.hexdigest()
 
 
@@ -47,7 +48,19 @@ def build(force=False, verbose=False):
     if not os.path.isfile(NVCC):
         raise RuntimeError('nvcc not found at %s: libcoslam_b200.so cannot be built' % NVCC)
     os.makedirs(OBJ_DIR, exist_ok=True)
+    # one builder at a time (several ranks may import the package at once); the others wait, then find a fresh stamp
+    import fcntl
+    with open(os.path.join(OBJ_DIR, 'lock'), 'w') as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not needs_build():
+                return LIB_PATH
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
 
+
+def _build_locked(verbose):
     def compile_one(src):
         obj = os.path.join(OBJ_DIR, src.replace('.cu', '.o'))
         cmd = [NVCC] + NVCC_FLAGS + (['-Xptxas', '-v'] if verbose else []) + ['-c', os.path.join(CSRC, src), '-o', obj]
@@ -60,10 +73,12 @@ def build(force=False, verbose=False):
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [NVCC, '-shared', '-o', LIB_PATH] + objs + ['-gencode', 'arch=compute_100a,code=sm_100a', '-lcudart']
+    tmp = LIB_PATH + '.tmp.%d' % os.getpid()
+    cmd = [NVCC, '-shared', '-o', tmp] + objs + ['-gencode', 'arch=compute_100a,code=sm_100a', '-lcudart']
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError('link failed:\n%s\n%s' % (r.stdout, r.stderr))
+    os.replace(tmp, LIB_PATH)                  # atomic: a concurrent dlopen sees the old or the new library, never a partial one
     with open(os.path.join(OBJ_DIR, 'stamp'), 'w') as f:
         f.write(_stamp())
     return LIB_PATH
