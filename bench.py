@@ -240,14 +240,16 @@ def run_ours(args):
     kt = {}
     for name, a, b in events:
         kt.setdefault(name, []).append(a.elapsed_time(b))
-    k_fwd = sum(kt['points_fwd']) / len(kt['points_fwd'])
-    k_bwd = sum(kt['points_bwd']) / len(kt['points_bwd'])
+    k_fwd = sum(kt['points_fwd']) / args.steps          # per step: the lazy forward launches the per-point kernel twice
+    k_bwd = sum(kt['points_bwd']) / args.steps
     value = world * n * args.steps / (ms * 1e-3)
     # fraction of points with a non-zero output gradient (the backward skips the rest: exact zeros), one untimed step
-    ops.KEEP_LAST_D_RAW = True
+    ops.KEEP_LAST_D_RAW = ops.KEEP_LAST_MASK = True
     step(resident)
     live_frac = float((ops.LAST_D_RAW.reshape(-1, 4) != 0).any(1).float().mean())
-    ops.KEEP_LAST_D_RAW, ops.LAST_D_RAW = False, None
+    eval_frac = float(ops.LAST_EVALUATED.float().mean()) if ops.LAST_EVALUATED is not None else 1.0
+    ops.KEEP_LAST_D_RAW, ops.LAST_D_RAW, ops.KEEP_LAST_MASK, ops.LAST_MASK, ops.LAST_EVALUATED = False, None, False, None, None
+    del ops.MASK_LOG[:]
 
     # ---- end to end through the public API: pinned host rays in, loss out, every step -----------------------------
     staging = [torch.empty_like(t, device=dev) for t in host]
@@ -303,9 +305,10 @@ def run_ours(args):
                          'traffic_source': 'ncu dram bytes per point (profiles/r1/ncu_full_v5_tc.txt) x points per launch', 'peak_source': 'measured' if peaks else 'fallback',
                          'algorithmic_bytes_per_launch': bwd_bytes, 'live_point_fraction': live_frac, 'avg_launch_ms': k_bwd,
                          'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
-                                        'achieved': P * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
+                                        'evaluated_point_fraction': eval_frac,
+                                        'achieved': P * eval_frac * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
                          'share_of_step': (k_fwd + k_bwd) / (ms / args.steps),
-                         'kernel_ms': {k: sum(v) / len(v) for k, v in kt.items()}},
+                         'kernel_ms_per_step': {k: sum(v) / args.steps for k, v in kt.items()}},
             'cpu_baseline': cpu,
         }
         out.update(extra)

@@ -230,13 +230,57 @@ static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, cons
 
 int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
                      const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
-                     uint32_t* act_mask, int sdf_only, void* stream) {
+                     uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, void* stream) {
     cb200::PointsArgs a{};
     if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
     if (a.n_points == 0) return 0;
     a.raw = raw; a.geo = geo; a.act_mask = act_mask; a.sdf_only = sdf_only;
+    CB_REQUIRE((point_list == nullptr) == (point_count == nullptr), "points_fwd: point_list and point_count go together");
+    CB_REQUIRE(point_list == nullptr || g_decoder == 1, "points_fwd: point lists need the tensor-core decoder");
+    CB_REQUIRE(point_list == nullptr || a.n_points < (1ll << 32), "points_fwd: point lists index with 32 bits");
+    a.live_idx = point_list;
+    a.live_count = reinterpret_cast<const unsigned long long*>(point_count);
     if (g_decoder == 1) return cuda_result(cb200::launch_points_fwd_tc(a, (cudaStream_t)stream), "points_fwd_tc");
     return cuda_result(cb200::launch_points_fwd(a, (cudaStream_t)stream), "points_fwd");
+}
+
+size_t cb200_lazy_workspace(int64_t n_rays, int64_t n_samples) {
+    if (n_rays < 0 || n_samples < 0) return 0;
+    return 16 + sizeof(int) * (size_t)n_rays + sizeof(uint32_t) * (size_t)n_rays * (size_t)n_samples;
+}
+
+static int lazy_split(void* workspace, size_t bytes, int64_t n_rays, int64_t n_samples, unsigned long long** count, int** k_done,
+                      uint32_t** list) {
+    CB_REQUIRE(workspace != nullptr && bytes >= cb200_lazy_workspace(n_rays, n_samples), "lazy: workspace missing or too small");
+    CB_REQUIRE(n_rays * n_samples < (1ll << 32), "lazy: point lists index with 32 bits");
+    *count = reinterpret_cast<unsigned long long*>(workspace);
+    *k_done = reinterpret_cast<int*>(*count + 2);
+    *list = reinterpret_cast<uint32_t*>(*k_done + n_rays);
+    return 0;
+}
+
+int cb200_lazy_prefix(const cb200_render_cfg* cfg, const float* z_vals, const float* target_d, int64_t n_rays, int64_t n_samples,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+    CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
+    CB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples <= 256, "lazy_prefix: bad sizes");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(z_vals && target_d, "lazy_prefix: NULL buffer");
+    unsigned long long* count; int* k_done; uint32_t* list;
+    if (int rc = lazy_split(workspace, workspace_bytes, n_rays, n_samples, &count, &k_done, &list)) return rc;
+    return cuda_result(cb200::launch_lazy_prefix(z_vals, target_d, n_rays, (int)n_samples, cfg->trunc_sc, k_done, list, count,
+                                                 (cudaStream_t)stream), "lazy_prefix");
+}
+
+int cb200_lazy_resolve(const cb200_render_cfg* cfg, const float* z_vals, const float* target_d, const float* raw, int64_t n_rays,
+                       int64_t n_samples, void* workspace, size_t workspace_bytes, void* stream) {
+    CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
+    CB_REQUIRE(n_rays >= 0 && n_samples >= 1 && n_samples <= 256, "lazy_resolve: bad sizes");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(z_vals && target_d && raw, "lazy_resolve: NULL buffer");
+    unsigned long long* count; int* k_done; uint32_t* list;
+    if (int rc = lazy_split(workspace, workspace_bytes, n_rays, n_samples, &count, &k_done, &list)) return rc;
+    return cuda_result(cb200::launch_lazy_resolve(z_vals, target_d, raw, n_rays, (int)n_samples, cfg->trunc_sc, k_done, list, count,
+                                                  (cudaStream_t)stream), "lazy_resolve");
 }
 
 size_t cb200_points_bwd_workspace(int64_t n_points) { return 16 + sizeof(uint32_t) * (size_t)(n_points > 0 ? n_points : 0); }

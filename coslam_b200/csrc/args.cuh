@@ -15,7 +15,7 @@ struct PointsArgs {
     int64_t n_points;
     int n_samples;
     int sdf_only;
-    // backward, tensor-core decoder: optional compacted list of the points whose d_raw is non-zero (points_tc.cu)
+    // tensor-core decoder: optional list of the points to process (backward: non-zero d_raw; forward: lazy evaluation)
     const uint32_t* live_idx;
     const unsigned long long* live_count;
     // forward outputs
@@ -90,6 +90,10 @@ cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_
                                      const float* d_rays_d, long long n, long long n_poses, float* d_poses, cudaStream_t st);
 cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                              float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, cudaStream_t st);
+cudaError_t launch_lazy_prefix(const float* z_vals, const float* target_d, int64_t n_rays, int n_samples, float trunc_sc, int* k_done,
+                               uint32_t* list, unsigned long long* count, cudaStream_t st);
+cudaError_t launch_lazy_resolve(const float* z_vals, const float* target_d, const float* raw, int64_t n_rays, int n_samples, float trunc_sc,
+                                int* k_done, uint32_t* list, unsigned long long* count, cudaStream_t st);
 cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st);
 cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st);
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st);

@@ -239,14 +239,18 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
         tc_fence_after();         \
     } while (0)
 
-    const int64_t n_tiles = (a.n_points + kTile - 1) / kTile;
+    // with a point list (lazy forward, render.cu) the tiles run over the listed points only: slot i -> point live_idx[i]
+    const int64_t n_slots = a.live_count ? (int64_t)*a.live_count : a.n_points;
+    const int64_t n_tiles = (n_slots + kTile - 1) / kTile;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t p_raw = tile * kTile + row;
-        const bool valid = p_raw < a.n_points;
-        const int64_t p = valid ? p_raw : a.n_points - 1;
+        const bool valid = p_raw < n_slots;
+        const int64_t p_slot = valid ? p_raw : n_slots - 1;
+        const int64_t p = a.live_idx ? (int64_t)a.live_idx[p_slot] : p_slot;
         {
             const int64_t pg_raw = tile * kTile + row_g;
-            const int64_t pg = pg_raw < a.n_points ? pg_raw : a.n_points - 1;
+            const int64_t pg_slot = pg_raw < n_slots ? pg_raw : n_slots - 1;
+            const int64_t pg = a.live_idx ? (int64_t)a.live_idx[pg_slot] : pg_slot;
             float x[3], zdummy;
             point_position(a, pg, x, zdummy);
 #pragma unroll

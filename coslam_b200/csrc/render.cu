@@ -460,6 +460,99 @@ __global__ void __launch_bounds__(kRayWarps * 32) importance_sample_kernel(Impor
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Lazy forward (training): which sample points does the step need at all?
+//   * the losses read the SDF of the samples in front of the truncation band and inside it: z <= d + T  (get_masks,
+//     model/utils.py:103-109) -- a PREFIX of the ascending samples of a ray;
+//   * rendering weights are non-zero only below z[first sign change] + T (sdf2weights, scene_rep.py:89-95) -- a prefix too.
+// Pass 1 evaluates the loss prefix (+ one sample); `lazy_resolve_kernel` then looks for the first sign change inside it: if
+// there is one, only the samples below its cut-off are still missing, otherwise the rest of the ray is.  Everything not
+// listed keeps raw = 0, which the rendering kernels mask out exactly as the reference's `mask` does, so the step's outputs
+// and gradients are unchanged; the points behind the band are simply never encoded or decoded.
+// ------------------------------------------------------------------------------------------------------------------
+struct LazyArgs {
+    const float* z_vals;       // [N,S]
+    const float* target_d;     // [N]
+    const float* raw;          // [N,S,4]   (resolve only)
+    int64_t n_rays;
+    int n_samples;
+    float trunc_sc;
+    int* k_done;               // [N] samples evaluated so far per ray (written by prefix, read + written by resolve)
+    uint32_t* list;            // point indices to evaluate next
+    unsigned long long* count;
+};
+
+__device__ __forceinline__ void lazy_append(const LazyArgs& a, int64_t ray, int lo, int hi, int lane) {
+    const int n = hi - lo;
+    if (n <= 0) return;
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(a.count, (unsigned long long)n);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    for (int i = lane; i < n; i += 32) a.list[base + i] = (uint32_t)(ray * a.n_samples + lo + i);
+}
+
+__global__ void __launch_bounds__(kRayWarps * 32) lazy_prefix_kernel(LazyArgs a) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int S = a.n_samples;
+    for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
+        const float d = a.target_d[ray];
+        int k = S;
+        if (d > 0.0f) {
+            const float band_end = __fadd_rn(d, a.trunc_sc);
+            int c = 0;
+            for (int s = lane; s < S; s += 32) c += a.z_vals[ray * S + s] <= band_end;
+            c = __reduce_add_sync(0xffffffffu, c);
+            k = min(S, c + 1);
+        }
+        if (lane == 0) a.k_done[ray] = k;
+        lazy_append(a, ray, 0, k, lane);
+    }
+}
+
+__global__ void __launch_bounds__(kRayWarps * 32) lazy_resolve_kernel(LazyArgs a) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int S = a.n_samples;
+    for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
+        const int k = a.k_done[ray];
+        if (k >= S) continue;                                  // warp-uniform
+        const float4* raw4 = reinterpret_cast<const float4*>(a.raw) + ray * S;
+        unsigned first = 0xffffffffu;
+        for (int s = lane; s + 1 < k; s += 32) {
+            if (__fmul_rn(raw4[s + 1].w, raw4[s].w) < 0.0f) first = min(first, (unsigned)s);      // scene_rep.py:89-91
+        }
+        first = __reduce_min_sync(0xffffffffu, first);
+        int need = S;
+        if (first != 0xffffffffu) {
+            const float z_lim = __fadd_rn(a.z_vals[ray * S + first], a.trunc_sc);                 // scene_rep.py:93-94
+            int c = 0;
+            for (int s = lane; s < S; s += 32) c += a.z_vals[ray * S + s] < z_lim;
+            need = __reduce_add_sync(0xffffffffu, c);
+        }
+        if (need > k) {
+            lazy_append(a, ray, k, need, lane);
+            if (lane == 0) a.k_done[ray] = need;
+        }
+    }
+}
+
+cudaError_t launch_lazy_prefix(const float* z_vals, const float* target_d, int64_t n_rays, int n_samples, float trunc_sc, int* k_done,
+                               uint32_t* list, unsigned long long* count, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(count, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    LazyArgs a{z_vals, target_d, nullptr, n_rays, n_samples, trunc_sc, k_done, list, count};
+    lazy_prefix_kernel<<<ray_grid(n_rays), kRayWarps * 32, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lazy_resolve(const float* z_vals, const float* target_d, const float* raw, int64_t n_rays, int n_samples, float trunc_sc,
+                                int* k_done, uint32_t* list, unsigned long long* count, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(count, 0, sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    LazyArgs a{z_vals, target_d, raw, n_rays, n_samples, trunc_sc, k_done, list, count};
+    lazy_resolve_kernel<<<ray_grid(n_rays), kRayWarps * 32, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st) {
     const size_t smem = sizeof(float) * (size_t)kRayWarps * (size_t)(2 * a.n_samples + a.n_importance);
     importance_sample_kernel<<<ray_grid(a.n_rays), kRayWarps * 32, smem, st>>>(a);

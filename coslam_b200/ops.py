@@ -17,6 +17,7 @@ N_GEO = 15
 # tests set KEEP_LAST_MASK to read back the ReLU sign bits the last ray forward saved for its backward
 KEEP_LAST_MASK = False
 LAST_MASK = None
+LAST_EVALUATED = None   # bool [P]: the points the (lazy) forward evaluated, None = all; kept with LAST_MASK
 MASK_LOG = []          # every mask saved while KEEP_LAST_MASK is set, in call order (two entries for an importance-pass step)
 
 # bench.py sets this to a list to collect (name, start_event, end_event) around the two per-point kernels
@@ -206,8 +207,13 @@ def _check_weights(w1, w2, w3, w4):
                            [tuple(w.shape) for w in (w1, w2, w3, w4)])
 
 
-def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo=False, want_mask=True, sdf_only=False):
-    """query_color_sdf / run_network forward through the fused kernel.  rays = (rays_o [N,3], rays_d [N,3], z [N,S])."""
+LAZY_FORWARD = True      # training forward evaluates only the sample points the step can depend on (lazy_ray_forward)
+
+
+def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo=False, want_mask=True, sdf_only=False,
+                   out=None, point_list=None):
+    """query_color_sdf / run_network forward through the fused kernel.  rays = (rays_o [N,3], rays_d [N,3], z [N,S]).
+    out = (raw, mask) to write into existing buffers; point_list = (list ptr, count ptr) restricts the launch to them."""
     _check_weights(*w)
     if rays is not None:
         o, d, z = rays
@@ -218,14 +224,43 @@ def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo
         dev = pts.device
         o = d = z = None
     P = n * s
-    raw = torch.empty((P, 4), dtype=torch.float32, device=dev) if want_raw else None
+    if out is not None:
+        raw, mask = out
+    else:
+        raw = torch.empty((P, 4), dtype=torch.float32, device=dev) if want_raw else None
+        mask = torch.empty((P, 2), dtype=torch.int32, device=dev) if want_mask else None
     geo = torch.empty((P, N_GEO), dtype=torch.float32, device=dev) if want_geo else None
-    mask = torch.empty((P, 2), dtype=torch.int32, device=dev) if want_mask else None
     mlp = _mlp_block(*w)
+    lst, cnt = point_list if point_list is not None else (None, None)
     _timed('points_fwd', lambda: check(_lib.load().cb200_points_fwd(
         ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
-        ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask), 1 if sdf_only else 0, stream()), 'points_fwd'))
+        ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask), 1 if sdf_only else 0, lst, cnt, stream()), 'points_fwd'))
     return raw, geo, mask
+
+
+def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True):
+    """Training forward over the sample points the step can depend on (cb200_lazy_prefix / cb200_lazy_resolve): the loss
+    prefix of every ray first, then whatever the first sign change found there still exposes.  Points never listed keep
+    raw = 0; the rendering mask gives them zero weight and the loss masks exclude them, as in the reference."""
+    o, d, z = rays
+    n, s = z.shape
+    dev = z.device
+    lib = _lib.load()
+    raw = torch.zeros((n * s, 4), dtype=torch.float32, device=dev)
+    mask = torch.empty((n * s, 2), dtype=torch.int32, device=dev) if want_mask else None
+    nbytes = int(lib.cb200_lazy_workspace(ctypes.c_int64(n), ctypes.c_int64(s)))
+    wsp = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
+    base = wsp.data_ptr()
+    plist = (ctypes.c_void_p(base + 16 + 4 * n), ctypes.c_void_p(base))
+    td = _f32c(target_d.reshape(-1))
+    cfg = spec.render_cfg()
+    check(lib.cb200_lazy_prefix(ctypes.byref(cfg), ptr(z), ptr(td), ctypes.c_int64(n), ctypes.c_int64(s), ptr(wsp),
+                                ctypes.c_size_t(nbytes), stream()), 'lazy_prefix')
+    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist)
+    check(lib.cb200_lazy_resolve(ctypes.byref(cfg), ptr(z), ptr(td), ptr(raw), ctypes.c_int64(n), ctypes.c_int64(s), ptr(wsp),
+                                 ctypes.c_size_t(nbytes), stream()), 'lazy_resolve')
+    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist)
+    return raw, mask
 
 
 def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=None, need_table=True, need_mlp=True,
@@ -280,15 +315,21 @@ class RayPointsFunction(torch.autograd.Function):
     """raw[N,S,4] = decoder(encodings(normalise(rays_o + rays_d * z)))   (model/scene_rep.py:258 + run_network)."""
 
     @staticmethod
-    def forward(ctx, rays_o, rays_d, z_vals, table, w1, w2, w3, w4, spec):
+    def forward(ctx, rays_o, rays_d, z_vals, table, w1, w2, w3, w4, spec, target_d=None):
         o, d, z = _f32c(rays_o), _f32c(rays_d), _f32c(z_vals)
         tb, w = _f32c(table), tuple(_f32c(x) for x in (w1, w2, w3, w4))
         need_grad = any(ctx.needs_input_grad)
         ctx.set_materialize_grads(False)
-        raw, _, mask = points_forward(spec.scene(), tb, w, rays=(o, d, z), want_mask=need_grad)
+        lazy = target_d is not None and LAZY_FORWARD and _lib.load().cb200_get_decoder() == 1 and z.numel() < 2 ** 32
+        if lazy:
+            _check_weights(*w)
+            raw, mask = lazy_ray_forward(spec, tb, w, (o, d, z), target_d, want_mask=need_grad)
+        else:
+            raw, _, mask = points_forward(spec.scene(), tb, w, rays=(o, d, z), want_mask=need_grad)
         if KEEP_LAST_MASK:
-            global LAST_MASK
+            global LAST_MASK, LAST_EVALUATED
             LAST_MASK = mask
+            LAST_EVALUATED = (raw != 0).any(-1) if lazy else None
             MASK_LOG.append(mask)
         ctx.spec = spec
         ctx.save_for_backward(o, d, z, tb, *w, mask if mask is not None else torch.empty(0))
@@ -297,14 +338,14 @@ class RayPointsFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_raw):
         if g_raw is None:
-            return (None,) * 9
+            return (None,) * 10
         o, d, z, tb, w1, w2, w3, w4, mask = ctx.saved_tensors
         need = ctx.needs_input_grad
         d_table, d_w, d_ray = points_backward(ctx.spec.scene(), tb, (w1, w2, w3, w4), mask, _f32c(g_raw), rays=(o, d, z),
                                               need_table=need[3], need_mlp=any(need[4:8]), need_pos=need[0] or need[1])
         d_o, d_d = d_ray if d_ray is not None else (None, None)
         d_w = d_w or (None, None, None, None)
-        return d_o, d_d, None, d_table, d_w[0], d_w[1], d_w[2], d_w[3], None
+        return d_o, d_d, None, d_table, d_w[0], d_w[1], d_w[2], d_w[3], None, None
 
 
 class PointsFunction(torch.autograd.Function):

@@ -210,7 +210,8 @@ class JointEncoding(nn.Module):
             return forward_with_importance(self, rays_o, rays_d, target_rgb, target_d)
         ws = ops.new_step_workspace(rays_o.device)
         z_vals = self._sample(target_d, counts=ws[:4].view(torch.int64))
-        raw = ops.RayPointsFunction.apply(rays_o, rays_d, z_vals, *self._fused(), self.spec)
+        # training needs rgb / depth / losses only: sample points no loss mask and no rendering weight can reach are skipped
+        raw = ops.RayPointsFunction.apply(rays_o, rays_d, z_vals, *self._fused(), self.spec, target_d)
         n_total = rays_o.shape[0]
         if self.process_group is not None:
             import torch.distributed as dist

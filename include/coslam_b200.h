@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 8
+#define CB200_ABI_VERSION 9
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -175,10 +175,27 @@ int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, co
  *   raw   [P,4]  (rgb logits, sdf)            -- may be NULL
  *   geo   [P,15] geometric feature            -- may be NULL
  *   act_mask [P,2] uint32: ReLU sign bits of the two hidden layers, saved for the backward -- may be NULL
- *   sdf_only != 0 skips the colour network (query_sdf). */
+ *   sdf_only != 0 skips the colour network (query_sdf).
+ *   point_list / point_count (device, optional, tensor-core decoder): process only the listed point indices. */
 int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
                      const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
-                     int64_t n_samples, float* raw, float* geo, uint32_t* act_mask, int sdf_only, void* stream);
+                     int64_t n_samples, float* raw, float* geo, uint32_t* act_mask, int sdf_only,
+                     const uint32_t* point_list, const uint64_t* point_count, void* stream);
+
+/* Lazy training forward: the step only needs the SDF of the samples up to the end of the truncation band (loss masks,
+ * model/utils.py:103-109) and, for rendering, of the samples below z[first sign change] + T (sdf2weights mask,
+ * scene_rep.py:89-95) -- both prefixes of a ray's ascending samples.  Everything else keeps raw = 0 (the caller zero-fills
+ * raw), which the rendering mask removes exactly as in the reference, so outputs and gradients are unchanged.
+ *   workspace (device): [count u64 | pad u64 | k_done int32 x N | list u32 x N*S], cb200_lazy_workspace bytes;
+ *   cb200_lazy_prefix  fills `list`/`count` with the loss prefix of every ray (all samples where target_d <= 0);
+ *   after cb200_points_fwd(point_list = list, point_count = count) on it, cb200_lazy_resolve rewrites `list`/`count`
+ *   with the samples still missing (up to the cut-off of the first sign change, or the rest of the ray if the prefix has
+ *   none); a second cb200_points_fwd on that list completes the forward.  Tensor-core decoder only. */
+size_t cb200_lazy_workspace(int64_t n_rays, int64_t n_samples);
+int cb200_lazy_prefix(const cb200_render_cfg* cfg, const float* z_vals, const float* target_d, int64_t n_rays,
+                      int64_t n_samples, void* workspace, size_t workspace_bytes, void* stream);
+int cb200_lazy_resolve(const cb200_render_cfg* cfg, const float* z_vals, const float* target_d, const float* raw,
+                       int64_t n_rays, int64_t n_samples, void* workspace, size_t workspace_bytes, void* stream);
 
 /* its backward.  d_raw [P,4] (d_geo [P,15] optional, NULL = zero).  Outputs, each optional (NULL = skip):
  *   dtable (+=)  [n_params]     d_mlp (+=) four matrices

@@ -118,12 +118,15 @@ def test_forward_backward_matches_oracle(cfg_name, n_rays, kind, decoder):
         ops.KEEP_LAST_MASK = True
         ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
         ops.KEEP_LAST_MASK = False
-        masks = util.unpack_masks(ops.LAST_MASK)
         _weighted_loss(cfg, ret).backward()
 
-        # 1. forward values against the plain oracle + activation-pattern audit
+        # 1. forward values against the plain oracle + activation-pattern audit (over the points the lazy forward evaluated)
         with torch.no_grad():
             r_plain = orc.forward(rays_o, rays_d, rgb, depth, noise=noise)
+        masks = util.unpack_masks(ops.LAST_MASK, ops.LAST_EVALUATED, orc.last_pre)
+        if ops.LAST_EVALUATED is not None:
+            frac = float(ops.LAST_EVALUATED.float().mean())
+            assert 0.2 < frac < 1.0, frac                      # some points are skipped, the loss prefix never is
         util.audit_activation_flips(masks, orc.last_pre)
         util.assert_close(ret['rgb'], r_plain['rgb'], 'rgb')
         util.assert_close(ret['depth'], r_plain['depth'], 'depth')
@@ -581,3 +584,51 @@ def test_keyframe_database_and_ray_assembly_match_reference_lines():
     got = torch.autograd.grad((ro * go).sum() + (rd * gd).sum(), (rot, trans))
     for a, b, name in zip(got, ref, ('d_rot', 'd_trans')):
         util.assert_close(a, b, name, tol=1e-5)
+
+
+@pytest.mark.parametrize('cfg_name,kind', [('room0', 'trained'), ('room0', 'small'), ('room0', 'flat'), ('scannet0000', 'trained'),
+                                           ('tum_desk', 'trained')])
+def test_lazy_forward_is_exact(cfg_name, kind):
+    """The training forward skips sample points that no loss mask and no rendering weight can reach (cb200_lazy_prefix /
+    cb200_lazy_resolve).  Rendered maps and losses must be IDENTICAL to the forward over all points, gradients equal up to
+    the summation order of their atomics; with an SDF head that outputs 0 everywhere ('flat': no sign change on any ray, the
+    reference's argmax falls back to sample 0) nothing may be skipped."""
+    cfg = synth.CONFIGS[cfg_name]()
+    n_rays = 3000
+    rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n_rays, seed=13, over_trunc_frac=0.02 if cfg_name == 'tum_desk' else 0.0)
+    weights = [w.clone() for w in synth.decoder_init(seed=5)]
+    if kind == 'flat':
+        weights[1][0] = 0.0                                     # sdf = row 0 of the second SDF-net matrix
+    probe = JointEncodingFor(cfg)
+    table = synth.table_init(probe.embed_fn.params.numel(), 'trained' if kind == 'flat' else kind, seed=77)
+    res = {}
+    for lazy in (True, False):
+        model = util.make_cuda_model(cfg, table, weights, DEV)
+        o = rays_o.to(DEV).requires_grad_(True)
+        d = rays_d.to(DEV).requires_grad_(True)
+        ops.LAZY_FORWARD = lazy
+        try:
+            torch.manual_seed(3)
+            ops.KEEP_LAST_MASK = True
+            ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
+            ops.KEEP_LAST_MASK = False
+            evaluated = ops.LAST_EVALUATED
+            _weighted_loss(cfg, ret).backward()
+        finally:
+            ops.LAZY_FORWARD = True
+            ops.KEEP_LAST_MASK = False
+        res[lazy] = (ret, o.grad, d.grad, model.embed_fn.params.grad, [w.grad for w in model.decoder.fused_weights()], evaluated)
+    a, b = res[True], res[False]
+    for k in ('rgb', 'depth', 'rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):
+        assert torch.equal(a[0][k], b[0][k]) or (torch.isnan(a[0][k]).all() and torch.isnan(b[0][k]).all()), k
+    for x, y, name in ((a[1], b[1], 'd_rays_o'), (a[2], b[2], 'd_rays_d'), (a[3], b[3], 'd_table')):
+        util.assert_close(x, y, name, tol=2e-5)
+    for x, y in zip(a[4], b[4]):
+        util.assert_close(x, y, 'dW', tol=2e-5)
+    ev = a[5].reshape(n_rays, -1)
+    if kind == 'flat':
+        # raw = (rgb logits, 0): the evaluated points are those with non-zero colour logits -- all of them
+        assert float(ev.float().mean()) > 0.999
+    else:
+        assert 0.2 < float(ev.float().mean()) < 0.9
+        assert bool((ev[:, 1:] <= ev[:, :-1]).all())        # what is evaluated is a prefix of every ray

@@ -74,11 +74,16 @@ def assert_close(a, b, what, tol=REL_TOL):
     return e
 
 
-def unpack_masks(mask):
-    """[P,2] int32 ReLU sign words (hidden layer of the SDF net, hidden layer of the colour net) -> two bool [P,32]."""
+def unpack_masks(mask, evaluated=None, oracle_pre=None):
+    """[P,2] int32 ReLU sign words (hidden layer of the SDF net, hidden layer of the colour net) -> two bool [P,32].
+    Rows the lazy forward never evaluated (`evaluated` [P] bool) hold no sign bits: they take the oracle's own pattern."""
     m = mask.detach().cpu().to(torch.int64) & 0xFFFFFFFF
     bits = torch.arange(32, dtype=torch.int64)
-    return ((m[:, 0:1] >> bits) & 1).bool(), ((m[:, 1:2] >> bits) & 1).bool()
+    out = [((m[:, 0:1] >> bits) & 1).bool(), ((m[:, 1:2] >> bits) & 1).bool()]
+    if evaluated is not None:
+        ev = evaluated.detach().cpu()[:, None]
+        out = [torch.where(ev, o, h > 0) for o, h in zip(out, oracle_pre)]
+    return tuple(out)
 
 
 def audit_activation_flips(cuda_masks, oracle_pre, max_frac=2e-5, band=1e-4):
