@@ -208,6 +208,7 @@ def _check_weights(w1, w2, w3, w4):
 
 
 LAZY_FORWARD = True      # training forward evaluates only the sample points the step can depend on (lazy_ray_forward)
+LAZY_MIN_POINTS = 1 << 16   # below this (tracking batches) the two extra launches cost more than the skipped points save
 
 
 def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo=False, want_mask=True, sdf_only=False,
@@ -320,7 +321,7 @@ class RayPointsFunction(torch.autograd.Function):
         tb, w = _f32c(table), tuple(_f32c(x) for x in (w1, w2, w3, w4))
         need_grad = any(ctx.needs_input_grad)
         ctx.set_materialize_grads(False)
-        lazy = target_d is not None and LAZY_FORWARD and _lib.load().cb200_get_decoder() == 1 and z.numel() < 2 ** 32
+        lazy = target_d is not None and LAZY_FORWARD and _lib.load().cb200_get_decoder() == 1 and LAZY_MIN_POINTS <= z.numel() < 2 ** 32
         if lazy:
             _check_weights(*w)
             raw, mask = lazy_ray_forward(spec, tb, w, (o, d, z), target_d, want_mask=need_grad)
