@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
         }
         // ---- SDF net layer 1: h1[128,32] = in1[128,80] W1^T ----------------------------------------------------------
         publish_tiles();
-        if (tid == 0) {
+        if (warp == 0 && elect_one()) {
             umma_split3(tmem + kColH1, a_hi, a_lo, 128u, kAGS, 256u, sbase + kOffW1Hi, sbase + kOffW1Lo, 128u, kW1GS, 256u, 5,
                         umma_idesc_bf16(128, 32, false, false), false);
             umma_commit(&bar);
@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
         }
         // ---- layer 2: h2[128,16] = relu(h1) W2^T ------------------------------------------------------------------------
         publish_tiles();
-        if (tid == 0) {
+        if (warp == 0 && elect_one()) {
             umma_split3(tmem + kColH2, h_hi, h_lo, 128u, kHGS, 256u, sbase + kOffW2Hi, sbase + kOffW2Lo, 128u, kW2GS, 256u, 2,
                         umma_idesc_bf16(128, 16, false, false), false);
             umma_commit(&bar);
@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
         if (!a.sdf_only) {
             // ---- colour net layer 1: h3[128,32] = [blob | geo][128,64] W3^T ------------------------------------------------
             publish_tiles();
-            if (tid == 0) {
+            if (warp == 0 && elect_one()) {
                 umma_split3(tmem + kColH3, a_hi + 4 * 128, a_lo + 4 * 128, 128u, kAGS, 256u, sbase + kOffW3Hi, sbase + kOffW3Lo, 128u, kW3GS,
                             256u, 4, umma_idesc_bf16(128, 32, false, false), false);
                 umma_commit(&bar);
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
             }
             // ---- colour net layer 2: rgb[128,16(3)] = relu(h3) W4^T --------------------------------------------------------
             publish_tiles();
-            if (tid == 0) {
+            if (warp == 0 && elect_one()) {
                 umma_split3(tmem + kColRgb, h_hi, h_lo, 128u, kHGS, 256u, sbase + kOffW4Hi, sbase + kOffW4Lo, 128u, kW4GS, 256u, 2,
                             umma_idesc_bf16(128, 16, false, false), false);
                 umma_commit(&bar);
@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
             tile_store8(g3_hi, g3_lo, kHGS, row, 2 * half + c, v);
         }
         publish_tiles();
-        if (tid == 0) {      // round b: d_in2 = d_h3 W3   (B = W3 tile read MN-major: reduce over its rows)
+        if (warp == 0 && elect_one()) {      // round b: d_in2 = d_h3 W3   (B = W3 tile read MN-major: reduce over its rows)
             umma_split3(tmem + kColDin2, g3_hi, g3_lo, 128u, kHGS, 256u, sbase + kOffW3Hi, sbase + kOffW3Lo, kW3GS, 128u, 2 * kW3GS, 2,
                         umma_idesc_bf16(128, 64, false, true), false);
             umma_commit(&bar);
@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
             tile_store8(g2_hi, g2_lo, kG2GS, row, half, v);
         }
         publish_tiles();
-        if (tid == 0) {      // round c: d_h1 (pre-mask) = d_h2 W2
+        if (warp == 0 && elect_one()) {      // round c: d_h1 (pre-mask) = d_h2 W2
             umma_split3(tmem + kColDh1, g2_hi, g2_lo, 128u, kG2GS, 256u, sbase + kOffW2Hi, sbase + kOffW2Lo, kW2GS, 128u, 2 * kW2GS, 1,
                         umma_idesc_bf16(128, 32, false, true), false);
             umma_commit(&bar);
@@ -504,7 +504,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
             mask16_to_tile(r, m1, hg_hi, hg_lo, row, half);
         }
         publish_tiles();
-        if (tid == 0) {      // round d: d_in1 = d_h1 W1, then the OneBlob columns += d_h3 W3[:, :48]
+        if (warp == 0 && elect_one()) {      // round d: d_in1 = d_h1 W1, then the OneBlob columns += d_h3 W3[:, :48]
             umma_split3(tmem + kColDin1, hg_hi, hg_lo, 128u, kHGS, 256u, sbase + kOffW1Hi, sbase + kOffW1Lo, kW1GS, 128u, 2 * kW1GS, 2,
                         umma_idesc_bf16(128, 80, false, true), false);
             umma_split3(tmem + kColDin1 + 32, g3_hi, g3_lo, 128u, kHGS, 256u, sbase + kOffW3Hi, sbase + kOffW3Lo, kW3GS, 128u, 2 * kW3GS, 2,
@@ -633,7 +633,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
         // ---- (3) forward recompute + weight gradients (epilogue role) ----------------------------------------------------------
         if (kWgrad) {
             publish_tiles();
-            if (tid == 0) {      // h1 = in1 W1^T ;  dW1^T += in1^T d_h1   (A tile and HG tile read MN-major, reduce over the points)
+            if (warp == 0 && elect_one()) {      // h1 = in1 W1^T ;  dW1^T += in1^T d_h1   (A tile and HG tile read MN-major, reduce over the points)
                 umma_split3(tmem + kColRH1, a_hi, a_lo, 128u, kAGS, 256u, sbase + kOffW1Hi, sbase + kOffW1Lo, 128u, kW1GS, 256u, 5,
                             umma_idesc_bf16(128, 32, false, false), false);
                 umma_split3(tmem + kColDW1, a_hi, a_lo, kAGS, 128u, 2 * kAGS, hg_hi, hg_lo, kHGS, 128u, 2 * kHGS, 8,
@@ -648,7 +648,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
                 mask16_to_tile(r, m1, hg_hi, hg_lo, row, half);       // HG now holds relu(h1)
             }
             publish_tiles();
-            if (tid == 0) {      // h2 = relu(h1) W2^T ;  dW2^T += relu(h1)^T d_h2
+            if (warp == 0 && elect_one()) {      // h2 = relu(h1) W2^T ;  dW2^T += relu(h1)^T d_h2
                 umma_split3(tmem + kColRH2, hg_hi, hg_lo, 128u, kHGS, 256u, sbase + kOffW2Hi, sbase + kOffW2Lo, 128u, kW2GS, 256u, 2,
                             umma_idesc_bf16(128, 16, false, false), false);
                 umma_split3(tmem + kColDW2, hg_hi, hg_lo, kHGS, 128u, 2 * kHGS, g2_hi, g2_lo, kG2GS, 128u, 2 * kG2GS, 8,
@@ -676,7 +676,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
                 tile_store8(g2_hi, g2_lo, kG2GS, row, half, u);
             }
             publish_tiles();
-            if (tid == 0) {      // h3 = [blob | geo] W3^T ;  dW3^T += [blob | geo]^T d_h3
+            if (warp == 0 && elect_one()) {      // h3 = [blob | geo] W3^T ;  dW3^T += [blob | geo]^T d_h3
                 umma_split3(tmem + kColRH3, a_hi + 4 * 128, a_lo + 4 * 128, 128u, kAGS, 256u, sbase + kOffW3Hi, sbase + kOffW3Lo, 128u, kW3GS,
                             256u, 4, umma_idesc_bf16(128, 32, false, false), false);
                 umma_split3(tmem + kColDW3, a_hi + 4 * 128, a_lo + 4 * 128, kAGS, 128u, 2 * kAGS, g3_hi, g3_lo, kHGS, 128u, 2 * kHGS, 8,
@@ -691,7 +691,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
                 mask16_to_tile(r, m3, hg_hi, hg_lo, row, half);       // HG now holds relu(h3)
             }
             publish_tiles();
-            if (tid == 0) {      // dW4^T += relu(h3)^T d_rgb
+            if (warp == 0 && elect_one()) {      // dW4^T += relu(h3)^T d_rgb
                 umma_split3(tmem + kColDW4, hg_hi, hg_lo, kHGS, 128u, 2 * kHGS, g2_hi, g2_lo, kG2GS, 128u, 2 * kG2GS, 8,
                             umma_idesc_bf16(128, 16, true, true), !first_tile);
                 umma_commit(&bar);

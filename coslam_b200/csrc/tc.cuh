@@ -70,6 +70,14 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// one lane of a fully active warp (the MMA issue / commit blocks run under `warp == 0 && elect_one()`: a warp-uniform
+// branch plus elect.sync, so the compiler emits straight-line UTCHMMA issue instead of a per-instruction election loop)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 // D[tmem] (+)= A[smem] * B[smem]^T ; one thread issues
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -112,13 +120,17 @@ __device__ __forceinline__ void umma_split3(uint32_t tmem_d, uint32_t a_hi, uint
                                             uint32_t b_hi, uint32_t b_lo, uint32_t b_lbo, uint32_t b_sbo, uint32_t b_kstep, int ksteps,
                                             uint32_t idesc, bool accumulate_first) {
     uint32_t acc = accumulate_first ? 1u : 0u;
+    // base descriptors once, then the start-address field (bits 0..13, units of 16 bytes) advances per reduction step
+    uint64_t ah = umma_desc(a_hi, a_lbo, a_sbo), al = umma_desc(a_lo, a_lbo, a_sbo);
+    uint64_t bh = umma_desc(b_hi, b_lbo, b_sbo), bl = umma_desc(b_lo, b_lbo, b_sbo);
+    const uint64_t a_inc = a_kstep >> 4, b_inc = b_kstep >> 4;
+#pragma unroll
     for (int k = 0; k < ksteps; ++k) {
-        const uint64_t ah = umma_desc(a_hi + k * a_kstep, a_lbo, a_sbo), al = umma_desc(a_lo + k * a_kstep, a_lbo, a_sbo);
-        const uint64_t bh = umma_desc(b_hi + k * b_kstep, b_lbo, b_sbo), bl = umma_desc(b_lo + k * b_kstep, b_lbo, b_sbo);
         umma_bf16(tmem_d, ah, bh, idesc, acc);
         umma_bf16(tmem_d, al, bh, idesc, 1u);
         umma_bf16(tmem_d, ah, bl, idesc, 1u);
         acc = 1u;
+        ah += a_inc; al += a_inc; bh += b_inc; bl += b_inc;
     }
 }
 

@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_slot;
-    if (tid == 0) {
+    if (tid < 32 && elect_one()) {
         if (mode == 0) {
             umma_split3(tmem, a_hi, a_lo, 128u, a_gs, 256u, b_hi, b_lo, 128u, b_gs, 256u, K / 16, umma_idesc_bf16(128, N, false, false), false);
         } else {
