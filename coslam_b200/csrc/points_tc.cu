@@ -694,13 +694,18 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
             if (warp == 0 && elect_one()) {      // dW4^T += relu(h3)^T d_rgb
                 umma_split3(tmem + kColDW4, hg_hi, hg_lo, kHGS, 128u, 2 * kHGS, g2_hi, g2_lo, kG2GS, 128u, 2 * kG2GS, 8,
                             umma_idesc_bf16(128, 16, true, true), !first_tile);
-                umma_commit(&bar);
             }
-            TC_WAIT();           // the tiles are rewritten by the next iteration
+            // Not waited for here: the tensor core executes in issue order and the next commit (round b of the next tile, or
+            // the one after the loop) covers these MMAs too.  Until that wait returns, the next tile only writes G3, which
+            // this product does not read (HG and G2 are rewritten after the waits of rounds b / c).
             first_tile = false;
         }
         tc_fence_before();
         __syncthreads();         // every lane has read its d_in1 columns before the next tile's MMAs overwrite TMEM
+    }
+    if (kWgrad && !first_tile) {                 // the last tile's dW4 product
+        if (warp == 0 && elect_one()) umma_commit(&bar);
+        TC_WAIT();
     }
 #undef TC_WAIT
 
