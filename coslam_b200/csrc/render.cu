@@ -482,56 +482,73 @@ struct LazyArgs {
     unsigned long long* count;
 };
 
-__device__ __forceinline__ void lazy_append(const LazyArgs& a, int64_t ray, int lo, int hi, int lane) {
-    const int n = hi - lo;
-    if (n <= 0) return;
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(a.count, (unsigned long long)n);
-    base = __shfl_sync(0xffffffffu, base, 0);
+// Appends the points [lo, hi) of each warp's ray to the list.  One reservation (atomicAdd) per CTA and loop trip instead of
+// one per ray: every warp of the CTA calls this in every trip (n = 0 when it has nothing to add).
+__device__ __forceinline__ void lazy_append(const LazyArgs& a, int64_t ray, int lo, int hi, int lane, int warp) {
+    __shared__ int warp_n[kRayWarps];
+    __shared__ unsigned long long cta_base;
+    const int n = max(hi - lo, 0);
+    if (lane == 0) warp_n[warp] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tot = 0;
+#pragma unroll
+        for (int w = 0; w < kRayWarps; ++w) tot += warp_n[w];
+        cta_base = tot ? atomicAdd(a.count, (unsigned long long)tot) : 0ull;
+    }
+    __syncthreads();
+    unsigned long long base = cta_base;
+    for (int w = 0; w < warp; ++w) base += warp_n[w];
     for (int i = lane; i < n; i += 32) a.list[base + i] = (uint32_t)(ray * a.n_samples + lo + i);
+    __syncthreads();                                  // warp_n / cta_base are rewritten by the next trip
 }
 
 __global__ void __launch_bounds__(kRayWarps * 32) lazy_prefix_kernel(LazyArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int S = a.n_samples;
-    for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
-        const float d = a.target_d[ray];
-        int k = S;
-        if (d > 0.0f) {
-            const float band_end = __fadd_rn(d, a.trunc_sc);
-            int c = 0;
-            for (int s = lane; s < S; s += 32) c += a.z_vals[ray * S + s] <= band_end;
-            c = __reduce_add_sync(0xffffffffu, c);
-            k = min(S, c + 1);
+    // CTA-uniform trip count: lazy_append synchronises the CTA
+    for (int64_t ray0 = (int64_t)blockIdx.x * kRayWarps; ray0 < a.n_rays; ray0 += (int64_t)gridDim.x * kRayWarps) {
+        const int64_t ray = ray0 + warp;
+        int k = 0;
+        if (ray < a.n_rays) {
+            const float d = a.target_d[ray];
+            k = S;
+            if (d > 0.0f) {
+                const float band_end = __fadd_rn(d, a.trunc_sc);
+                int c = 0;
+                for (int s = lane; s < S; s += 32) c += a.z_vals[ray * S + s] <= band_end;
+                c = __reduce_add_sync(0xffffffffu, c);
+                k = min(S, c + 1);
+            }
+            if (lane == 0) a.k_done[ray] = k;
         }
-        if (lane == 0) a.k_done[ray] = k;
-        lazy_append(a, ray, 0, k, lane);
+        lazy_append(a, ray, 0, k, lane, warp);
     }
 }
 
 __global__ void __launch_bounds__(kRayWarps * 32) lazy_resolve_kernel(LazyArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int S = a.n_samples;
-    for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
-        const int k = a.k_done[ray];
-        if (k >= S) continue;                                  // warp-uniform
-        const float4* raw4 = reinterpret_cast<const float4*>(a.raw) + ray * S;
-        unsigned first = 0xffffffffu;
-        for (int s = lane; s + 1 < k; s += 32) {
-            if (__fmul_rn(raw4[s + 1].w, raw4[s].w) < 0.0f) first = min(first, (unsigned)s);      // scene_rep.py:89-91
+    for (int64_t ray0 = (int64_t)blockIdx.x * kRayWarps; ray0 < a.n_rays; ray0 += (int64_t)gridDim.x * kRayWarps) {
+        const int64_t ray = ray0 + warp;
+        int k = S, need = S;
+        if (ray < a.n_rays) k = a.k_done[ray];
+        if (k < S) {                                             // warp-uniform
+            const float4* raw4 = reinterpret_cast<const float4*>(a.raw) + ray * S;
+            unsigned first = 0xffffffffu;
+            for (int s = lane; s + 1 < k; s += 32) {
+                if (__fmul_rn(raw4[s + 1].w, raw4[s].w) < 0.0f) first = min(first, (unsigned)s);      // scene_rep.py:89-91
+            }
+            first = __reduce_min_sync(0xffffffffu, first);
+            if (first != 0xffffffffu) {
+                const float z_lim = __fadd_rn(a.z_vals[ray * S + first], a.trunc_sc);                 // scene_rep.py:93-94
+                int c = 0;
+                for (int s = lane; s < S; s += 32) c += a.z_vals[ray * S + s] < z_lim;
+                need = __reduce_add_sync(0xffffffffu, c);
+            }
+            if (need > k && lane == 0) a.k_done[ray] = need;
         }
-        first = __reduce_min_sync(0xffffffffu, first);
-        int need = S;
-        if (first != 0xffffffffu) {
-            const float z_lim = __fadd_rn(a.z_vals[ray * S + first], a.trunc_sc);                 // scene_rep.py:93-94
-            int c = 0;
-            for (int s = lane; s < S; s += 32) c += a.z_vals[ray * S + s] < z_lim;
-            need = __reduce_add_sync(0xffffffffu, c);
-        }
-        if (need > k) {
-            lazy_append(a, ray, k, need, lane);
-            if (lane == 0) a.k_done[ray] = need;
-        }
+        lazy_append(a, ray, k, need, lane, warp);                 // empty when nothing is missing (need <= k)
     }
 }
 
