@@ -95,13 +95,9 @@ class ColorSDFNet(nn.Module):
                               hidden_dim=d['hidden_dim'], num_layers=d['num_layers'])
 
     def forward(self, embed, embed_pos, embed_color):
-        if embed_pos is not None:
-            h = self.sdf_net(torch.cat([embed, embed_pos], dim=-1), return_geo=True)
-        else:
-            h = self.sdf_net(embed, return_geo=True)
-        sdf, geo_feat = h[..., :1], h[..., 1:]
-        if embed_pos is not None:
-            rgb = self.color_net(torch.cat([embed_pos, embed_color, geo_feat], dim=-1))
-        else:
-            rgb = self.color_net(torch.cat([embed_color, geo_feat], dim=-1))
-        return torch.cat([rgb, sdf], -1)
+        """[sdf-grid feature (| OneBlob)] -> SDF head; [(OneBlob |) colour-grid feature | geometric feature] -> colour head."""
+        with_pos = embed_pos is not None
+        sdf_in = (embed, embed_pos) if with_pos else (embed,)
+        out = self.sdf_net(torch.cat(sdf_in, dim=-1), return_geo=True)
+        col_in = ((embed_pos,) if with_pos else ()) + (embed_color, out[..., 1:])
+        return torch.cat([self.color_net(torch.cat(col_in, dim=-1)), out[..., :1]], -1)
