@@ -26,7 +26,7 @@ def _resample(model, z_vals, weights, target_d=None, counts=None):
 def importance_pass(model, rays_o, rays_d, z_vals, weights, coarse):
     """Second pass for render_rays; returns (ret, z_vals, raw) with the coarse maps kept under the '*0' keys."""
     z_all, z_std = _resample(model, z_vals, weights)
-    raw = ops.RayPointsFunction.apply(rays_o, rays_d, z_all, *model._fused(), model.spec)
+    raw = model.ray_points(rays_o, rays_d, z_all)
     rgb_map, depth_map, aux, _ = ops.RenderFunction.apply(raw, z_all, model.spec)
     ret = {'rgb': rgb_map, 'depth': depth_map, 'disp_map': aux[1], 'acc_map': aux[2], 'depth_var': aux[0],
            'rgb0': coarse['rgb'], 'disp0': coarse['disp_map'], 'acc0': coarse['acc_map'], 'depth0': coarse['depth'],
@@ -50,10 +50,10 @@ def forward_with_importance(model, rays_o, rays_d, target_rgb, target_d):
     ws = ops.new_step_workspace(rays_o.device)
     counts = ws[:4].view(torch.int64)
     z0 = model._sample(target_d)                                   # the mask counts belong to the FINAL samples
-    raw0 = ops.RayPointsFunction.apply(rays_o, rays_d, z0, *model._fused(), spec)
+    raw0 = model.ray_points(rays_o, rays_d, z0)
     rgb0, depth0, _, weights0 = ops.RenderFunction.apply(raw0, z0, spec)
     z_all, _ = _resample(model, z0, weights0, target_d=target_d, counts=counts)
-    raw = ops.RayPointsFunction.apply(rays_o, rays_d, z_all, *model._fused(), spec)
+    raw = model.ray_points(rays_o, rays_d, z_all)
     n_total = rays_o.shape[0]
     if group is not None:
         import torch.distributed as dist

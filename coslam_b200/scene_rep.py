@@ -91,6 +91,15 @@ class JointEncoding(nn.Module):
             raise NotImplementedError('coslam_b200: the fused path serves the 2-layer SDF / 2-layer colour decoder')
         return (self.embed_fn.params,) + tuple(w)
 
+    def ray_points(self, rays_o, rays_d, z_vals, target_d=None):
+        """raw [N,S,4] of the sample points o + d z.  oneGrid (every shipped config): the fused per-point kernels, lazily over
+        the points the step can depend on when `target_d` is given (training).  Two-grid variant (`oneGrid: False`,
+        model/scene_rep.py:56-58, 168-170): the stand-alone CUDA encodings and the torch decoder, like the reference."""
+        if self.config['grid']['oneGrid']:
+            return ops.RayPointsFunction.apply(rays_o, rays_d, z_vals, *self._fused(), self.spec, target_d)
+        pts = rays_o[..., None, :] + rays_d[..., None, :] * z_vals[..., :, None]        # model/scene_rep.py:258
+        return self.run_network(pts)
+
     @staticmethod
     def _require_cuda(t):
         if not t.is_cuda:
@@ -190,7 +199,7 @@ class JointEncoding(nn.Module):
             raise KeyError("n_samples: render_rays without target_d is not configured in any Co-SLAM YAML")
         t = self.config['training']
         z_vals = self._sample(target_d)
-        raw = ops.RayPointsFunction.apply(rays_o, rays_d, z_vals, *self._fused(), self.spec)
+        raw = self.ray_points(rays_o, rays_d, z_vals)
         rgb_map, depth_map, aux, weights = ops.RenderFunction.apply(raw, z_vals, self.spec)
         ret = {'rgb': rgb_map, 'depth': depth_map, 'disp_map': aux[1], 'acc_map': aux[2], 'depth_var': aux[0]}
         if t['n_importance'] > 0:
@@ -211,7 +220,7 @@ class JointEncoding(nn.Module):
         ws = ops.new_step_workspace(rays_o.device)
         z_vals = self._sample(target_d, counts=ws[:4].view(torch.int64))
         # training needs rgb / depth / losses only: sample points no loss mask and no rendering weight can reach are skipped
-        raw = ops.RayPointsFunction.apply(rays_o, rays_d, z_vals, *self._fused(), self.spec, target_d)
+        raw = self.ray_points(rays_o, rays_d, z_vals, target_d)
         n_total = rays_o.shape[0]
         if self.process_group is not None:
             import torch.distributed as dist

@@ -632,3 +632,34 @@ def test_lazy_forward_is_exact(cfg_name, kind):
     else:
         assert 0.2 < float(ev.float().mean()) < 0.9
         assert bool((ev[:, 1:] <= ev[:, :-1]).all())        # what is evaluated is a prefix of every ray
+
+
+def test_two_grid_variant_runs_through_standalone_operators():
+    """`oneGrid: False` (model/scene_rep.py:56-58, 168-170): second hash grid for colour and the
+    ColorSDFNet decoder.  Not served by the fused kernels; the training step composes the stand-alone CUDA encodings, the torch
+    decoder and the rendering / loss kernels.  Checked against the same composition written out with the rendering oracle."""
+    cfg = synth.room0_config()
+    cfg['grid']['oneGrid'] = False
+    cfg['training']['perturb'] = 0.0
+    model = JointEncodingFor(cfg)
+    assert hasattr(model, 'embed_fn_color') and type(model.decoder).__name__ == 'ColorSDFNet'
+    with torch.no_grad():
+        model.embed_fn.params.uniform_(-0.5, 0.5)
+        model.embed_fn_color.params.uniform_(-0.5, 0.5)
+    model.train()
+    n = 300
+    rays_o, rays_d, rgb, depth = (t.to(DEV) for t in synth.ray_batch(cfg, n, seed=2))
+    o = rays_o.clone().requires_grad_(True)
+    ret = model.forward(o, rays_d, rgb, depth)
+    _weighted_loss(cfg, ret).backward()
+    assert model.embed_fn_color.params.grad is not None and float(model.embed_fn_color.params.grad.abs().max()) > 0
+    assert model.embed_fn.params.grad is not None and o.grad is not None
+    # same raw -> the oracle's sdf2weights / raw2outputs on the CPU
+    from oracle.coslam_oracle import OracleScene
+    orc = OracleScene(synth.room0_config(), synth.bound_tensor(cfg))
+    with torch.no_grad():
+        z = model._sample(depth)
+        raw = model.ray_points(rays_o, rays_d, z)
+        out = orc.raw2outputs(raw.cpu(), z.cpu())
+    util.assert_close(ret['rgb'], out['rgb'], 'rgb')
+    util.assert_close(ret['depth'], out['depth'], 'depth')
