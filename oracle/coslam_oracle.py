@@ -124,6 +124,14 @@ class OracleScene(object):
     def table(self):
         return self.grid.params
 
+    def to(self, device):
+        """The restatement is plain torch, so it also runs on a CUDA device (used by the trajectory test to keep it short)."""
+        self.bound = self.bound.to(device)
+        self.grid.to(device)
+        for k in ('W1', 'W2', 'W3', 'W4'):
+            setattr(self, k, getattr(self, k).detach().to(device).requires_grad_(True))
+        return self
+
     def parameters(self):
         return [self.grid.params, self.W1, self.W2, self.W3, self.W4]
 
@@ -277,7 +285,7 @@ class OracleScene(object):
         rgb_w = valid.clone().unsqueeze(-1)
         rgb_w[rgb_w == 0] = self.cfg['training']['rgb_missing']
         rgb_loss = F.mse_loss(r['rgb'] * rgb_w, target_rgb * rgb_w)
-        psnr = -10. * torch.log(rgb_loss + 1e-6) / torch.log(torch.Tensor([10.]))       # model/utils.py:8-12
+        psnr = -10. * torch.log(rgb_loss + 1e-6) / torch.log(torch.Tensor([10.])).to(rgb_loss.device)   # model/utils.py:8-12
         depth_loss = F.mse_loss(r['depth'][valid], d[valid])
         if 'rgb0' in r:
             rgb_loss = rgb_loss + F.mse_loss(r['rgb0'] * rgb_w, target_rgb * rgb_w)
@@ -319,7 +327,7 @@ class OracleScene(object):
         offset_max = hi - lo - grid_size - 2 * margin
         offset_u = torch.rand(3) if offset_u is None else offset_u
         offset = offset_u.to(offset_max) * offset_max + margin
-        ar = torch.arange(0, n - 1, dtype=torch.long)
+        ar = torch.arange(0, n - 1, dtype=torch.long, device=lo.device)
         gx, gy, gz = torch.meshgrid(ar, ar, ar, indexing='ij')
         coords = torch.stack([gx, gy, gz], -1).float()
         jitter_u = torch.rand((1, 1, 1, 3)) if jitter_u is None else jitter_u
