@@ -19,7 +19,7 @@ SOURCES = ['api.cu', 'render.cu', 'points.cu', 'encoding.cu', 'tc_selftest.cu', 
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr',
-              '-I', INCLUDE]
+              '-I', INCLUDE] + os.environ.get('CB200_EXTRA_NVCC_FLAGS', '').split()
 
 
 def _stamp():

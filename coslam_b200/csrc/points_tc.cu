@@ -12,6 +12,9 @@
 //   H   [128 x 32]  relu(h1) then relu(h3)                                 group stride  512   hi + lo = 16 KB
 //   W1  [32 x 96] (cols 80.. zero)  W2 [16 x 32]  W3 [32 x 64] (col 63 zero)  W4 [16 x 32] (rows 3.. zero)   24 KB
 // TMEM columns: h1 0..31 | h2 32..47 | h3 48..79 | rgb 80..95   (128 allocated)
+#include <cstdio>
+#include <type_traits>
+
 #include "args.cuh"
 #include "point_common.cuh"
 #include "tc.cuh"
@@ -78,11 +81,14 @@ struct HalfCorners {
     float wx, w1, w2;
 };
 
+// kDense >= 0: levels below kDense are dense-indexed and the rest hashed (known when the kernel is compiled: no per-level branch,
+// one index formula per unrolled level); kDense < 0: read the flag of every level from the scene (any geometry).
+template <int kDense>
 __device__ __forceinline__ void level_corners_x(const SceneDev& sc, int l, const float x[3], int xb, HalfCorners& hc) {
     const float scale = sc.scale[l];
     const uint32_t res = sc.res[l];
     const uint32_t size = sc.offset[l + 1] - sc.offset[l];
-    const bool hashed = sc.hashed[l] != 0;
+    const bool hashed = kDense >= 0 ? (l >= kDense) : (sc.hashed[l] != 0);
     uint32_t cell[3];
     float w0;
     grid_pos(scale, x[0], cell[0], w0);
@@ -91,6 +97,10 @@ __device__ __forceinline__ void level_corners_x(const SceneDev& sc, int l, const
     hc.wx = xb ? w0 : 1.f - w0;
 #pragma unroll
     for (int j = 0; j < 4; ++j) hc.idx[j] = sc.offset[l] + grid_index(hashed, size, res, cell[0] + xb, cell[1] + (j & 1), cell[2] + (j >> 1));
+#ifdef CB200_EXP_COALESCED      // experiment: same arithmetic, but the warp's addresses fall into one or two lines
+#pragma unroll
+    for (int j = 0; j < 4; ++j) hc.idx[j] = sc.offset[l] + ((hc.idx[j] & 1u) | ((threadIdx.x & 31u) << 1)) + 64u * j;
+#endif
 }
 
 __device__ __forceinline__ float yz_weight(float w1, float w2, int j) { return ((j & 1) ? w1 : 1.f - w1) * ((j & 2) ? w2 : 1.f - w2); }
@@ -118,17 +128,33 @@ __device__ __forceinline__ void pair_combine_store(const float (&part)[8], int x
 }
 
 // one chunk (4 levels, 8 features) of hash-grid features -> A tile; 16 gathers in flight per thread
-__device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row) {
+template <int kDense>
+__device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row
+#ifdef CB200_PHASE_CLOCKS
+                                                  , long long* sub
+#endif
+) {
+#ifdef CB200_PHASE_CLOCKS
+    long long t0 = clock64();
+#endif
     float2 v[4][4];
     float wx[4], w1[4], w2[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         HalfCorners hc;
-        level_corners_x(a.scene, 4 * c + q, x, xb, hc);
+        level_corners_x<kDense>(a.scene, 4 * c + q, x, xb, hc);
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[q][j] = ldg_f2(a.table + hc.idx[j]);
         wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
     }
+#ifdef CB200_PHASE_CLOCKS
+    long long t1 = clock64();
+    {
+        float dummy = v[0][0].x + v[1][1].x + v[2][2].x + v[3][3].y;      // wait for (most of) the loads
+        asm volatile("" ::"f"(dummy));
+    }
+    long long t2 = clock64();
+#endif
     float part[8];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -143,28 +169,43 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
         part[2 * q + 1] = f1;
     }
     pair_combine_store(part, xb, a_hi, a_lo, row, c);
+#ifdef CB200_PHASE_CLOCKS
+    long long t3 = clock64();
+    sub[0] += t1 - t0; sub[1] += t2 - t1; sub[2] += t3 - t2;
+#endif
 }
 
-// OneBlob bins 8*hb .. 8*hb+7 of one coordinate: values (and optionally d value / d x) from the 9 bin-edge CDFs
-template <bool kDeriv>
-__device__ __forceinline__ void blob_half(float xd, int hb, float (&val)[8], float (&dval)[8]) {
+// OneBlob bins 8*hb .. 8*hb+7 of one coordinate: values (and optionally d value / d x) from the 9 bin-edge CDFs.
+// kImages: evaluate the two periodic images of the kernel as well.  For 0 <= x <= 15/16 they are saturated at every edge used
+// (edges 0/16 .. 15/16; the 16th is edge 0 plus one): cdf(t - 1) == 0, cdf(t + 1) == 1 and both pdf images == 0 exactly, so
+// (cdf(t) + 0) + 1 is the same fp32 value the three-image sum produces.
+template <bool kDeriv, bool kImages>
+__device__ __forceinline__ void blob_half_impl(float xd, int hb, float (&val)[8], float (&dval)[8]) {
     const float nb = (float)kBins;
-    float f_prev = blob_edge_cdf((float)(8 * hb) / nb, xd, nb);
-    float k_prev = kDeriv ? blob_edge_pdf((float)(8 * hb) / nb, xd, nb) : 0.f;
+    auto cdf = [&](float e) { return kImages ? blob_edge_cdf(e, xd, nb) : quartic_cdf(e - xd, nb) + 1.0f; };
+    auto pdf = [&](float e) { return kImages ? blob_edge_pdf(e, xd, nb) : quartic_pdf(e - xd, nb); };
+    float f_prev = cdf((float)(8 * hb) / nb);
+    float k_prev = kDeriv ? pdf((float)(8 * hb) / nb) : 0.f;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
         const int b = 8 * hb + e + 1;                    // right edge index
         // the last right edge wraps: F(1 - x) = F(0 - x) + 1, identical kernel value
         const float edge = (b == kBins) ? 0.f : (float)b / nb;
-        const float f_next = blob_edge_cdf(edge, xd, nb) + ((b == kBins) ? 1.0f : 0.f);
+        const float f_next = cdf(edge) + ((b == kBins) ? 1.0f : 0.f);
         val[e] = f_next - f_prev;
         f_prev = f_next;
         if (kDeriv) {
-            const float k_next = blob_edge_pdf(edge, xd, nb);
+            const float k_next = pdf(edge);
             dval[e] = k_prev - k_next;
             k_prev = k_next;
         }
     }
+}
+
+template <bool kDeriv>
+__device__ __forceinline__ void blob_half(float xd, int hb, float (&val)[8], float (&dval)[8]) {
+    if (xd >= 0.f && xd <= 15.0f / 16.0f) blob_half_impl<kDeriv, false>(xd, hb, val, dval);
+    else blob_half_impl<kDeriv, true>(xd, hb, val, dval);
 }
 
 // make this thread's shared-memory writes visible to the tensor core, then CTA barrier
@@ -209,6 +250,7 @@ __device__ __forceinline__ void mask16_to_tile(const uint32_t (&r)[16], uint32_t
 // ------------------------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------------------------
+template <int kDense>
 __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsArgs a) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smem[];
@@ -242,11 +284,19 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
     // with a point list (lazy forward, render.cu) the tiles run over the listed points only: slot i -> point live_idx[i]
     const int64_t n_slots = a.live_count ? (int64_t)*a.live_count : a.n_points;
     const int64_t n_tiles = (n_slots + kTile - 1) / kTile;
+#ifdef CB200_PHASE_CLOCKS
+    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, t_prev = clock64(), sub[3] = {0, 0, 0};
+    int n_done = 0;
+#define PH(i) do { const long long t_now = clock64(); ph[i] += t_now - t_prev; t_prev = t_now; } while (0)
+#else
+#define PH(i)
+#endif
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t p_raw = tile * kTile + row;
         const bool valid = p_raw < n_slots;
         const int64_t p_slot = valid ? p_raw : n_slots - 1;
         const int64_t p = a.live_idx ? (int64_t)a.live_idx[p_slot] : p_slot;
+        PH(7);
         {
             const int64_t pg_raw = tile * kTile + row_g;
             const int64_t pg_slot = pg_raw < n_slots ? pg_raw : n_slots - 1;
@@ -254,22 +304,30 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
             float x[3], zdummy;
             point_position(a, pg, x, zdummy);
 #pragma unroll
-            for (int c = 0; c < 4; ++c) encode_grid_chunk(a, x, xb, c, a_hi, a_lo, row_g);
+#ifdef CB200_PHASE_CLOCKS
+            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g, sub);
+#else
+            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g);
+#endif
+            PH(0);
 #pragma unroll
             for (int d = 0; d < 3; ++d) {             // OneBlob: thread xb does bins 8 xb .. 8 xb + 7 of every coordinate
                 float v[8], unused[8];
                 blob_half<false>(x[d], xb, v, unused);
                 tile_store8(a_hi, a_lo, kAGS, row_g, 4 + 2 * d + xb, v);
             }
+            PH(1);
         }
         // ---- SDF net layer 1: h1[128,32] = in1[128,80] W1^T ----------------------------------------------------------
         publish_tiles();
+        PH(2);
         if (warp == 0 && elect_one()) {
             umma_split3(tmem + kColH1, a_hi, a_lo, 128u, kAGS, 256u, sbase + kOffW1Hi, sbase + kOffW1Lo, 128u, kW1GS, 256u, 5,
                         umma_idesc_bf16(128, 32, false, false), false);
             umma_commit(&bar);
         }
         TC_WAIT();
+        PH(3);
         uint32_t m1;
         {
             uint32_t r[16];
@@ -342,6 +400,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
                 rgb[2] = __uint_as_float(r[2]);
             }
         }
+        PH(4);
         if (valid) {
             if (a.raw && half == 0) reinterpret_cast<float4*>(a.raw)[p] = make_float4(rgb[0], rgb[1], rgb[2], sdf);
             if (a.act_mask) {                     // [P,2] uint32 seen as [P,4] uint16: m1 low, m1 high, m3 low, m3 high
@@ -351,7 +410,17 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
         }
         tc_fence_before();
         __syncthreads();
+        PH(5);
+#ifdef CB200_PHASE_CLOCKS
+        ++n_done;
+#endif
     }
+#ifdef CB200_PHASE_CLOCKS
+    if ((blockIdx.x == 0 || blockIdx.x == 100) && (tid == 0 || tid == 200))
+        printf("fwd cta %d tid %d tiles %d: gather %lld blob %lld publish %lld mma1wait %lld rounds2-4 %lld stores+sync %lld head %lld | per chunk: index+issue %lld wait %lld consume %lld (cycles per tile)\n",
+               blockIdx.x, tid, n_done, ph[0] / n_done, ph[1] / n_done, ph[2] / n_done, ph[3] / n_done, ph[4] / n_done, ph[5] / n_done, ph[7] / n_done, sub[0] / n_done / 4, sub[1] / n_done / 4, sub[2] / n_done / 4);
+#endif
+#undef PH
 #undef TC_WAIT
     if (warp == 0) tmem_dealloc<tc::kTmemCols>(tmem);
 }
@@ -532,7 +601,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 HalfCorners hc;
-                level_corners_x(a.scene, 4 * c + q, x, xb, hc);
+                level_corners_x<-1>(a.scene, 4 * c + q, x, xb, hc);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     idx[q][j] = hc.idx[j];
@@ -786,29 +855,46 @@ static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
     return (int)g;
 }
 
-cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st) {
-    const bool wgrad = a.dw1 != nullptr;
-    const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
+template <bool kWgrad>
+static cudaError_t launch_points_bwd_tc_as(const PointsArgs& a, cudaStream_t st) {
     const size_t smem = tc::kBwdSmem;
-    if (wgrad) {
-        cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        points_bwd_tc_kernel<true><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
-    } else {
-        cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        points_bwd_tc_kernel<false><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
-    }
+    const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
+    cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<kWgrad>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    points_bwd_tc_kernel<kWgrad><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st) {
+    return a.dw1 != nullptr ? launch_points_bwd_tc_as<true>(a, st) : launch_points_bwd_tc_as<false>(a, st);
+}
+
+// number of leading dense levels when the scene is "dense levels first, hashed levels after" over all 16 levels, else -1
+static int dense_prefix(const SceneDev& sc) {
+    if (sc.n_levels != (uint32_t)kLevels) return -1;
+    int k = 0;
+    while (k < kLevels && !sc.hashed[k]) ++k;
+    for (int l = k; l < kLevels; ++l)
+        if (!sc.hashed[l]) return -1;
+    return k;
+}
+
+template <int kDense>
+static cudaError_t launch_points_fwd_tc_as(const PointsArgs& a, cudaStream_t st) {
+    const size_t smem = tc::kFwdSmem;
+    cudaError_t e = cudaFuncSetAttribute(points_fwd_tc_kernel<kDense>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
+    points_fwd_tc_kernel<kDense><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
 cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st) {
-    const size_t smem = tc::kFwdSmem;
-    cudaError_t e = cudaFuncSetAttribute(points_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
-    points_fwd_tc_kernel<<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
-    return cudaGetLastError();
+    switch (dense_prefix(a.scene)) {          // 5: room0 / fr1_desk (and every Replica / TUM scene), 6: scene0000
+        case 5: return launch_points_fwd_tc_as<5>(a, st);
+        case 6: return launch_points_fwd_tc_as<6>(a, st);
+        default: return launch_points_fwd_tc_as<-1>(a, st);
+    }
 }
 
 }  // namespace cb200

@@ -46,6 +46,39 @@ def test_bit_exact_samples_positions_indices(name):
     assert np.array_equal(idx.cpu().numpy().view(np.uint32), g['hash_idx'])
 
 
+def test_hash_indices_at_edge_positions():
+    """Cell boundaries, tiny negatives, points outside the unit cube (negative cells wrap like tiny-cuda-nn's (uint32)(int)
+    cast) and far-away points: the grid position arithmetic (common.cuh: grid_pos) against the shim, bit-exact."""
+    from oracle import tcnn_shim
+    cfg = synth.room0_config()
+    from coslam_b200.scene_rep import JointEncoding
+    model = JointEncoding(cfg, synth.bound_tensor(cfg).to(DEV)).to(DEV)
+    with torch.no_grad():
+        model.embed_fn.params.copy_(synth.table_init(model.embed_fn.params.numel(), 'trained', seed=3).to(DEV))
+    meta = tcnn_shim.grid_meta(16, cfg['grid']['hash_size'], 16, float(model.embed_fn.grid_cfg['per_level_scale']))
+    rng = np.random.default_rng(5)
+    special = np.array([0.0, -0.0, 1.0, 0.5, -1e-30, 1e-30, -1e-7, 1 - 1e-7, -0.03, 1.04, -0.5, 1.5, -3.0, 4.0, 30.0, -30.0,
+                        1e4, -1e4, 2e5, -2e5], dtype=np.float32)
+    cells = (np.arange(0, 64, dtype=np.float32) + 0.5) / np.float32(meta['scale'][15])      # on / next to fine-level cell edges
+    vals = np.concatenate([special, cells, np.nextafter(cells, np.float32(0)), np.nextafter(cells, np.float32(2))])
+    x = rng.choice(vals, size=(4096, 3)).astype(np.float32)
+    x[:len(vals)] = vals[:, None]
+    xt = torch.from_numpy(x)
+    ref = np.stack([tcnn_shim.hash_corner_indices(xt, meta, l)[0].numpy() for l in range(16)], 1).astype(np.uint32)
+    idx = torch.empty((x.shape[0], 16, 8), dtype=torch.int32, device=DEV)
+    xs = xt.to(DEV).contiguous()
+    _lib.check(_lib.load().cb200_hash_indices(ctypes.byref(model.spec.grid()), _lib.ptr(xs), ctypes.c_int64(x.shape[0]),
+                                              _lib.ptr(idx), _lib.stream()), 'hash_indices')
+    assert np.array_equal(idx.cpu().numpy().view(np.uint32), ref)
+    # and the encodings built on it (interpolation fractions) on the same points
+    out = model.embed_fn(xs)
+    shim = tcnn_shim.Encoding(3, model.embed_fn.encoding_config)
+    with torch.no_grad():
+        shim.params.copy_(model.embed_fn.params.detach().cpu())
+        want = shim(xt)
+    util.assert_close(out, want, 'hash encoding at edge positions')
+
+
 @pytest.mark.parametrize('name', util.GOLDEN_CASES)
 def test_forward_backward_matches_reference_golden(name):
     g = util.load_golden(name)
