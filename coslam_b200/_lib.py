@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p
@@ -46,8 +46,16 @@ class Mlp(ctypes.Structure):
                 ('w_col1', ctypes.c_void_p)]
 
 
+class TrackStep(ctypes.Structure):
+    """cb200_track_step (include/coslam_b200.h)."""
+    _fields_ = [(n, ctypes.c_void_p) for n in ('rot', 'trans', 'adam', 'step', 'losses', 'd_c2w', 'c2w', 'best_loss', 'best_c2w',
+                                               'last_loss', 'last_c2w', 'psnr', 'loss', 'g_rot_out', 'patience', 'alive')] + \
+               [('loss_w', ctypes.c_float * 4), ('lr_rot', ctypes.c_float), ('lr_trans', ctypes.c_float), ('n_rot', ctypes.c_int32),
+                ('first_iter', ctypes.c_int32), ('may_stop', ctypes.c_int32), ('wait_iters', ctypes.c_int32)]
+
+
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
-           'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd',
+           'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update',
            'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd',
            'cb200_debug_positions', 'cb200_selftest_mma', 'cb200_set_decoder',
            'cb200_get_decoder']

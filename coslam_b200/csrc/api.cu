@@ -171,6 +171,21 @@ int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq
                                                zero_grad, (cudaStream_t)stream), "adam_step");
 }
 
+int cb200_track_pose(const float* rot, const float* trans, int n_rot, float* c2w, void* stream) {
+    CB_REQUIRE(rot && trans && c2w, "track_pose: NULL buffer");
+    CB_REQUIRE(n_rot == 3 || n_rot == 4, "track_pose: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    return cuda_result(cb200::launch_track_pose(rot, trans, n_rot, c2w, (cudaStream_t)stream), "track_pose");
+}
+
+int cb200_track_update(const cb200_track_step* s, void* stream) {
+    CB_REQUIRE(s != nullptr, "track_update: NULL step");
+    CB_REQUIRE(s->rot && s->trans && s->adam && s->step && s->losses && s->d_c2w && s->c2w && s->best_loss && s->best_c2w && s->last_loss &&
+                   s->last_c2w && s->patience && s->alive,
+               "track_update: NULL buffer");
+    CB_REQUIRE(s->n_rot == 3 || s->n_rot == 4, "track_update: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    return cuda_result(cb200::launch_track_update(*s, (cudaStream_t)stream), "track_update");
+}
+
 int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform, const float* lin_guided,
                       const float* lin_nodepth, const float* noise, uint64_t seed, const uint64_t* seed_dev, int64_t n_rays, float* z_vals,
                       int64_t* counts, void* stream) {

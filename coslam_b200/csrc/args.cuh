@@ -88,6 +88,8 @@ cudaError_t launch_assemble_rays_fwd(const float* kf_rays, const long long* ray_
                                      cudaStream_t st);
 cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* d_rays_o,
                                      const float* d_rays_d, long long n, long long n_poses, float* d_poses, cudaStream_t st);
+cudaError_t launch_track_pose(const float* rot, const float* trans, int n_rot, float* c2w, cudaStream_t st);
+cudaError_t launch_track_update(const cb200_track_step& s, cudaStream_t st);
 cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                              float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, cudaStream_t st);
 cudaError_t launch_lazy_prefix(const float* z_vals, const float* target_d, int64_t n_rays, int n_samples, float trunc_sc, int* k_done,

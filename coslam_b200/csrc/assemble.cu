@@ -43,40 +43,63 @@ __global__ void __launch_bounds__(256) assemble_rays_fwd_kernel(AssembleArgs a) 
 
 constexpr int kMaxSharedPoses = 1024;     // 1024 x 12 floats = 48 KB
 
+// One ray's contribution is 12 sums; consecutive rays usually share their keyframe (tracking: ONE pose for the whole batch),
+// so a thread first accumulates its own rays in registers while the slot does not change, then a warp whose lanes all ended
+// on the same slot combines them with shuffles and issues one set of 12 atomics (a batch of 1024 same-slot rays would
+// otherwise serialise 12 288 atomics on 12 addresses).
 __global__ void __launch_bounds__(256) assemble_rays_bwd_kernel(AssembleArgs a, int use_shared) {
     extern __shared__ float acc[];         // [n_poses][12] when use_shared
     if (use_shared) {
         for (long long k = threadIdx.x; k < a.n_poses * 12; k += blockDim.x) acc[k] = 0.f;
         __syncthreads();
     }
+    float v[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) v[k] = 0.f;
+    long long cur = -1;
+    auto emit = [&](long long slot, const float (&w)[12]) {
+        float* dst = use_shared ? acc + slot * 12 : a.d_poses + slot * 16;
+#pragma unroll
+        for (int k = 0; k < 12; ++k) atomicAdd(dst + k, w[k]);           // rows of 4: [slot][row][0..3] is contiguous in both layouts
+    };
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (long long)gridDim.x * blockDim.x) {
         const float* r = a.kf_rays + a.ray_idx[i] * 7;
         long long slot = a.pose_slot[i];
         if (slot < 0) slot += a.n_poses;
+        if (slot != cur) {
+            if (cur >= 0) emit(cur, v);
+#pragma unroll
+            for (int k = 0; k < 12; ++k) v[k] = 0.f;
+            cur = slot;
+        }
         const float d[3] = {r[0], r[1], r[2]};
 #pragma unroll
         for (int row = 0; row < 3; ++row) {
             const float gd = a.d_rays_d[i * 3 + row], go = a.d_rays_o[i * 3 + row];
-            if (use_shared) {
-                float* dst = acc + slot * 12 + row * 4;
-                atomicAdd(dst + 0, gd * d[0]);
-                atomicAdd(dst + 1, gd * d[1]);
-                atomicAdd(dst + 2, gd * d[2]);
-                atomicAdd(dst + 3, go);
-            } else {
-                float* dst = a.d_poses + slot * 16 + row * 4;
-                atomicAdd(dst + 0, gd * d[0]);
-                atomicAdd(dst + 1, gd * d[1]);
-                atomicAdd(dst + 2, gd * d[2]);
-                atomicAdd(dst + 3, go);
-            }
+            v[row * 4 + 0] = fmaf(gd, d[0], v[row * 4 + 0]);
+            v[row * 4 + 1] = fmaf(gd, d[1], v[row * 4 + 1]);
+            v[row * 4 + 2] = fmaf(gd, d[2], v[row * 4 + 2]);
+            v[row * 4 + 3] += go;
         }
+    }
+    // lanes without rays (cur < 0) hold zeros and may join any group
+    const long long lead = __shfl_sync(0xffffffffu, cur, __ffs(__ballot_sync(0xffffffffu, cur >= 0) | 0x80000000u) - 1);
+    const bool uniform = __all_sync(0xffffffffu, cur < 0 || cur == lead);
+    if (uniform) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+        }
+        if ((threadIdx.x & 31) == 0 && lead >= 0) emit(lead, v);
+    } else if (cur >= 0) {
+        emit(cur, v);
     }
     if (use_shared) {
         __syncthreads();
         for (long long k = threadIdx.x; k < a.n_poses * 12; k += blockDim.x) {
-            const float v = acc[k];
-            if (v != 0.f) atomicAdd(a.d_poses + (k / 12) * 16 + (k % 12), v);
+            const float w = acc[k];
+            if (w != 0.f) atomicAdd(a.d_poses + (k / 12) * 16 + (k % 12), w);
         }
     }
 }
@@ -98,7 +121,7 @@ cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_
         cudaError_t e = cudaFuncSetAttribute(assemble_rays_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    long long blocks = (n + 256 * 8 - 1) / (256 * 8);          // 8 rays per thread: fewer shared-accumulator flushes
+    long long blocks = (n + 255) / 256;                        // one ray per thread up to 4 CTAs per SM, grid-stride beyond
     if (blocks < 1) blocks = 1;
     if (blocks > 148 * 4) blocks = 148 * 4;
     assemble_rays_bwd_kernel<<<(unsigned)blocks, 256, smem, st>>>(a, use_shared);

@@ -9,18 +9,31 @@ the device, so the whole frame is one graph launch and one read-back.
 
 coslam.py stays unchanged by design; this class is the opt-in fast path with the same inputs
 (`batch['direction']` pixels, rgb, depth, initial c2w) and the same result (`est_c2w_data[frame_id]`).
+
+Two implementations of one iteration:
+  * `fused=True` (default for the shipped single-grid configs without importance samples): no autograd graph at all.  The
+    iteration is 11 library launches -- ray assembly from the device c2w, sampling, per-point forward, render + loss sums,
+    loss finish, render backward, live-point compaction, per-point backward (dL/d rays only), pose-gradient segment sum,
+    and ONE single-thread kernel (`cb200_track_update`, csrc/track.cu) for the weighted loss, the best / last bookkeeping,
+    the backward of the pose parametrisation, both Adam steps and the next c2w -- plus two memsets.
+  * `fused=False`: the same arithmetic through torch autograd (`pose.py`, `JointEncoding.forward`), ~100 graph nodes per
+    iteration; kept as the A/B twin and for the two-grid / importance-sampling variants.
 """
 import ctypes
 
 import torch
 
-from . import _lib, pose
+from . import _lib, ops, pose
 from ._lib import check, ptr, stream
 
 
 class FrameTracker(object):
-    def __init__(self, model, config, n_rays=None, device='cuda:0', use_graph=True):
+    def __init__(self, model, config, n_rays=None, device='cuda:0', use_graph=True, fused=None):
         t, tr = config['tracking'], config['training']
+        can_fuse = bool(config['grid']['oneGrid']) and int(tr['n_importance']) == 0
+        if fused and not can_fuse:
+            raise NotImplementedError('FrameTracker(fused=True) serves oneGrid: True without importance samples')
+        self.fused = can_fuse if fused is None else bool(fused)
         self.model, self.config, self.device = model, config, torch.device(device)
         self.n_rays = int(n_rays if n_rays is not None else t['sample'])
         self.iters, self.wait_iters, self.use_best = int(t['iter']), int(t['wait_iters']), bool(t['best'])
@@ -44,6 +57,71 @@ class FrameTracker(object):
         self._graph = None
         if self.use_graph:
             model.use_device_noise_counter(dev)                     # CPU torch.rand cannot be replayed by a graph
+        if self.fused:
+            nr = self.rot.shape[1]
+            self.rot.requires_grad_(False)
+            self.trans.requires_grad_(False)
+            # [rot | trans | exp_avg(rot) | exp_avg_sq(rot) | exp_avg(trans) | exp_avg_sq(trans)]: one copy resets a frame
+            self.pstate, self.pinit = torch.zeros(3 * nr + 9, **f32), torch.zeros(3 * nr + 9, **f32)
+            self.rot, self.trans, self.adam = self.pstate[:nr].view(1, nr), self.pstate[nr:nr + 3].view(1, 3), self.pstate[nr + 3:]
+            self.init_rot, self.init_trans = self.pinit[:nr].view(1, nr), self.pinit[nr:nr + 3].view(1, 3)
+            self.istate = torch.zeros(2, dtype=torch.int64, device=dev)            # Adam step, patience
+            self.step, self.patience = self.istate[0:1], self.istate[1:2]
+            self.alive = torch.ones(1, dtype=torch.uint8, device=dev)
+            self.best_loss, self.last_loss, self.loss = torch.zeros(1, **f32), torch.zeros(1, **f32), torch.zeros(1, **f32)
+            self.c2w = torch.zeros((1, 4, 4), **f32)
+            self.kf7 = torch.zeros((n, 7), **f32)                                   # (camera-frame direction, rgb, depth) per ray
+            self.ray_idx = torch.arange(n, dtype=torch.int64, device=dev)
+            self.pose_slot = torch.zeros(n, dtype=torch.int64, device=dev)
+            self.rays_o, self.rays_d = torch.zeros((n, 3), **f32), torch.zeros((n, 3), **f32)
+            self.zbuf = torch.zeros(16, dtype=torch.float64, device=dev)           # step workspace (8) | dL/d c2w (16 floats)
+            self.d_c2w = self.zbuf[8:].view(torch.float32)
+            self.loss_out = torch.zeros(8, **f32)                                   # 4 losses | 4 d loss / d sum
+            self.w_dev = torch.tensor(self.loss_w, **f32).unbind(0)
+            self.g_rot = torch.zeros(nr, **f32)
+            self._steps = [self._track_step(first) for first in (True, False)]
+
+    def _track_step(self, first):
+        s = _lib.TrackStep()
+        for name, t in (('rot', self.rot), ('trans', self.trans), ('adam', self.adam), ('step', self.step), ('losses', self.loss_out),
+                        ('d_c2w', self.d_c2w), ('c2w', self.c2w), ('best_loss', self.best_loss), ('best_c2w', self.best_c2w),
+                        ('last_loss', self.last_loss), ('last_c2w', self.last_c2w), ('psnr', self.psnr), ('loss', self.loss),
+                        ('g_rot_out', self.g_rot), ('patience', self.patience), ('alive', self.alive)):
+            setattr(s, name, t.data_ptr())
+        s.loss_w = (ctypes.c_float * 4)(*self.loss_w)
+        s.lr_rot, s.lr_trans, s.n_rot = self.lr_rot, self.lr_trans, self.rot.shape[1]
+        s.first_iter, s.may_stop, s.wait_iters = int(first), int(self.wait_iters < self.iters), self.wait_iters
+        return s
+
+    # ---- one frame without autograd -----------------------------------------------------------------------------------
+    def _reset_fused(self):
+        self.pstate.copy_(self.pinit)
+        self.istate.zero_()
+        self.alive.fill_(1)
+        check(_lib.load().cb200_track_pose(ptr(self.rot), ptr(self.trans), self.rot.shape[1], ptr(self.c2w), stream()), 'track_pose')
+
+    def _iteration_fused(self, k):
+        lib, m, n = _lib.load(), self.model, self.n_rays
+        spec = m.spec
+        fw = m._fused()
+        tb, w = fw[0].detach(), tuple(x.detach() for x in fw[1:])
+        self.zbuf.zero_()
+        ws = self.zbuf[:8]
+        td = self.target_d.view(-1)
+        check(lib.cb200_assemble_rays_fwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(self.c2w), ctypes.c_int64(n),
+                                          ctypes.c_int64(1), ptr(self.rays_o), ptr(self.rays_d), ptr(self.target_s), ptr(td),
+                                          stream()), 'assemble_rays_fwd')
+        z = m._sample(td, counts=ws[:4].view(torch.int64))
+        rays = (self.rays_o, self.rays_d, z)
+        raw, _, mask = ops.points_forward(spec.scene(), tb, w, rays=rays)
+        ops._render_forward(spec, raw, z, self.target_s, td, loss_sums=ws[4:8])
+        check(lib.cb200_loss_finish(ptr(ws[4:8]), ptr(ws[:4].view(torch.int64)), ctypes.c_int64(n), ctypes.c_int64(z.shape[1]),
+                                    ptr(self.loss_out[:4]), ptr(self.loss_out[4:]), stream()), 'loss_finish')
+        d_raw = ops._render_backward(spec, raw, z, self.target_s, td, self.w_dev, self.loss_out[4:], None, None)
+        _, _, (d_o, d_d) = ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, need_table=False, need_mlp=False)
+        check(lib.cb200_assemble_rays_bwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(d_o), ptr(d_d), ctypes.c_int64(n),
+                                          ctypes.c_int64(1), ptr(self.d_c2w), stream()), 'assemble_rays_bwd')
+        check(lib.cb200_track_update(ctypes.byref(self._steps[0 if k == 0 else 1]), stream()), 'track_update')
 
     # ---- one frame, eager or under capture --------------------------------------------------------------------------
     def _adam(self, p, g, m, v, lr):
@@ -98,6 +176,12 @@ class FrameTracker(object):
                 self.trans.copy_(torch.where(self.alive, self.trans, old[1]))
 
     def _frame(self):
+        if self.fused:
+            with torch.no_grad():
+                self._reset_fused()
+                for k in range(self.iters):
+                    self._iteration_fused(k)
+            return
         self._reset()
         for k in range(self.iters):
             self._iteration(k)
@@ -110,9 +194,14 @@ class FrameTracker(object):
         rot0 = pose.matrix_to_quaternion(c2w0[:, :3, :3]) if self.quat else pose.matrix_to_axis_angle(c2w0[:, :3, :3])
         self.init_rot.copy_(rot0, non_blocking=True)
         self.init_trans.copy_(c2w0[:, :3, 3], non_blocking=True)
-        self.dir_cam.copy_(dir_cam.reshape(self.n_rays, 3), non_blocking=True)
-        self.target_s.copy_(target_s.reshape(self.n_rays, 3), non_blocking=True)
-        self.target_d.copy_(target_d.reshape(self.n_rays, 1), non_blocking=True)
+        if self.fused:                                               # the kernels read (direction, rgb, depth) rows: one upload
+            n = self.n_rays
+            self.kf7.copy_(torch.cat([dir_cam.reshape(n, 3), target_s.reshape(n, 3), target_d.reshape(n, 1)], -1).float(),
+                           non_blocking=True)
+        else:
+            self.dir_cam.copy_(dir_cam.reshape(self.n_rays, 3), non_blocking=True)
+            self.target_s.copy_(target_s.reshape(self.n_rays, 3), non_blocking=True)
+            self.target_d.copy_(target_d.reshape(self.n_rays, 1), non_blocking=True)
         frozen = [p for p in self.model.parameters() if p.requires_grad]
         for p in frozen:                                             # tracking needs dL/d rays only (no table scatter, no dW)
             p.requires_grad_(False)
@@ -127,8 +216,8 @@ class FrameTracker(object):
             for p in frozen:
                 p.requires_grad_(True)
         est = (self.best_c2w if self.use_best else self.last_c2w)[0]
-        return est, {'best_loss': self.best_loss, 'last_loss': self.last_loss, 'psnr': self.psnr, 'last_c2w': self.last_c2w[0],
-                     'best_c2w': self.best_c2w[0]}
+        return est, {'best_loss': self.best_loss.reshape(()), 'last_loss': self.last_loss.reshape(()), 'psnr': self.psnr,
+                     'last_c2w': self.last_c2w[0], 'best_c2w': self.best_c2w[0]}
 
     def _capture(self):
         side = torch.cuda.Stream(device=self.device)

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 9
+#define CB200_ABI_VERSION 10
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -144,6 +144,43 @@ int cb200_assemble_rays_bwd(const float* kf_rays, const int64_t* ray_idx, const 
 int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
                     float beta2, float eps, float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad,
                     void* stream);
+
+/* ---- tracking-loop glue (coslam.py:502-573 tracking_render) ---------------------------------------------------- */
+
+/* matrix_from_tensor (coslam.py:526 -> optimization/utils.py:30-55): rot [n_rot] (3: axis-angle, 4: real-first quaternion,
+ * un-normalised) + trans [3] -> c2w [4,4] row-major.  Device pointers. */
+int cb200_track_pose(const float* rot, const float* trans, int n_rot, float* c2w, void* stream);
+
+/* One tracking iteration's glue after the render backward, on the device (no host sync): weighted loss
+ * (get_loss_from_ret, coslam.py:140-160), best / last pose bookkeeping with the patience counter and early stop
+ * (coslam.py:552-566), pose-parameter gradients from dL/d c2w (backward of optimization/utils.py:5-55), one Adam step
+ * on rot / trans (torch.optim.Adam defaults: betas (0.9, 0.999), eps 1e-8; coslam.py:276-283) unless the loop has
+ * stopped, and the c2w of the updated parameters.  Host struct of DEVICE pointers. */
+typedef struct cb200_track_step {
+    float* rot;             /* [n_rot] in/out */
+    float* trans;           /* [3] in/out */
+    float* adam;            /* [2 n_rot + 6]: exp_avg(rot), exp_avg_sq(rot), exp_avg(trans), exp_avg_sq(trans) */
+    int64_t* step;          /* Adam step counter, incremented here */
+    const float* losses;    /* [4] rgb, depth, sdf, fs losses (cb200_loss_finish) */
+    const float* d_c2w;     /* [4,4] dL/d c2w (cb200_assemble_rays_bwd) */
+    float* c2w;             /* [4,4] in: the pose this iteration rendered with; out: the pose of the updated parameters */
+    float* best_loss;       /* [1] */
+    float* best_c2w;        /* [4,4] */
+    float* last_loss;       /* [1] */
+    float* last_c2w;        /* [4,4] */
+    float* psnr;            /* [1], may be NULL */
+    float* loss;            /* [1] this iteration's weighted loss, may be NULL */
+    float* g_rot_out;       /* [n_rot] the rotation gradient (test hook), may be NULL */
+    int64_t* patience;      /* [1] */
+    uint8_t* alive;         /* [1] 0 once the patience counter exceeded wait_iters */
+    float loss_w[4];        /* rgb_weight, depth_weight, sdf_weight, fs_weight */
+    float lr_rot, lr_trans;
+    int32_t n_rot;          /* 3 or 4 */
+    int32_t first_iter;     /* != 0 for iteration 0 of a frame */
+    int32_t may_stop;       /* wait_iters < iters */
+    int32_t wait_iters;
+} cb200_track_step;
+int cb200_track_update(const cb200_track_step* step, void* stream);
 
 /* ---- upper boundary: the fused JointEncoding path -------------------------------------------------------- */
 

@@ -533,6 +533,17 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
     eager = FrameTracker(model, cfg, device=DEV, use_graph=False)
     est_e, info_e = eager.track(dir_cam, rgb, depth, c2w0)
     est_e, best_e = est_e.clone(), float(info_e['best_loss'])
+    assert eager.fused                                   # the library-only iteration is the default for the shipped configs
+    auto = FrameTracker(model, cfg, device=DEV, use_graph=False, fused=False)      # same loop through torch autograd
+    est_a, info_a = auto.track(dir_cam, rgb, depth, c2w0)
+    # Same mathematics, different rounding: the pose matrix comes out of one kernel instead of ~30 torch ops and differs in the
+    # last bit, i.e. rays_d differs by one ulp.  That moves the gradient of ~2 % of the rays by O(1) (a ReLU pre-activation or
+    # an SDF sign change of sdf2weights sitting exactly at the kink) and dL/d c2w by ~2e-3 relative -- checked by feeding the
+    # kernel's rays to the autograd path, which then reproduces the fused dL/d c2w to 4e-8.  Adam's normalised steps carry
+    # that into the pose: the same bound as against the reference loop below.
+    assert float((est_a - est_e).abs().max()) <= 3e-4
+    assert abs(float(info_a['best_loss']) - best_e) <= 1e-3 * abs(best_e)
+    assert float((info_a['last_c2w'] - info_e['last_c2w']).abs().max()) <= 3e-4
     graph = FrameTracker(model, cfg, device=DEV, use_graph=True)
     for _ in range(2):                                   # second replay: the per-frame state reset is part of the graph
         est_g, info_g = graph.track(dir_cam, rgb, depth, c2w0)
@@ -562,6 +573,77 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
     assert abs(float(info_g['best_loss']) - best) <= 1e-3 * abs(best)
     assert float((est_g.cpu() - best_c2w[0]).abs().max()) <= 3e-4
     assert float((info_g['last_c2w'].cpu() - last_c2w[0]).abs().max()) <= 3e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('n_rot', [3, 4])
+def test_track_update_kernel_matches_autograd_and_adam(n_rot):
+    """cb200_track_pose / cb200_track_update (csrc/track.cu) against torch: pose matrix, dL/d(rot, trans) from dL/d c2w
+    (autograd through coslam_b200.pose, i.e. optimization/utils.py:5-55), torch.optim.Adam on both parameters, and the
+    best / last / patience bookkeeping of coslam.py:552-566 over a short scripted loss sequence."""
+    import ctypes
+    from coslam_b200 import _lib, pose
+    from coslam_b200._lib import check, ptr, stream
+    g = torch.Generator().manual_seed(3 + n_rot)
+    rot0 = torch.randn(1, n_rot, generator=g) * (0.5 if n_rot == 3 else 1.0)
+    trans0 = torch.randn(1, 3, generator=g)
+    f32 = dict(dtype=torch.float32, device=DEV)
+    pstate = torch.cat([rot0.view(-1), trans0.view(-1), torch.zeros(2 * n_rot + 6)]).to(DEV)
+    rot, trans, adam = pstate[:n_rot], pstate[n_rot:n_rot + 3], pstate[n_rot + 3:]
+    istate = torch.zeros(2, dtype=torch.int64, device=DEV)
+    alive = torch.ones(1, dtype=torch.uint8, device=DEV)
+    losses, d_c2w, c2w = torch.zeros(4, **f32), torch.zeros(16, **f32), torch.zeros(16, **f32)
+    best_loss, last_loss, loss, psnr = (torch.zeros(1, **f32) for _ in range(4))
+    best_c2w, last_c2w, g_rot = torch.zeros(16, **f32), torch.zeros(16, **f32), torch.zeros(n_rot, **f32)
+    lib = _lib.load()
+    check(lib.cb200_track_pose(ptr(rot), ptr(trans), n_rot, ptr(c2w), stream()), 'track_pose')
+    ref_rot, ref_trans = torch.nn.Parameter(rot0.clone()), torch.nn.Parameter(trans0.clone())
+    assert float((c2w.cpu().view(4, 4) - pose.pose_matrix(ref_rot, ref_trans)[0].detach()).abs().max()) <= 2e-6
+    lr_rot, lr_trans, w, wait = 1e-3, 2e-3, (5.0, 0.1, 1000.0, 10.0), 2
+    opt = torch.optim.Adam([{'params': ref_rot, 'lr': lr_rot}, {'params': ref_trans, 'lr': lr_trans}])
+    seq = [1.0, 0.8, 0.9, 0.95, 0.7, 0.9, 0.9, 0.9, 0.5, 0.4]       # patience exceeds 2 at iteration 7: frozen afterwards
+    ref_best, ref_best_c2w, ref_pat, ref_alive, ref_last_c2w = None, None, 0, True, None
+    for k, base in enumerate(seq):
+        lk = torch.tensor([base, 0.5 * base, 1e-3 * base, 1e-2 * base])
+        gk = torch.randn(4, 4, generator=g)
+        losses.copy_(lk)
+        d_c2w.copy_(gk.view(-1))
+        s = _lib.TrackStep()
+        for name, t in (('rot', rot), ('trans', trans), ('adam', adam), ('step', istate[0:1]), ('losses', losses), ('d_c2w', d_c2w),
+                        ('c2w', c2w), ('best_loss', best_loss), ('best_c2w', best_c2w), ('last_loss', last_loss), ('last_c2w', last_c2w),
+                        ('psnr', psnr), ('loss', loss), ('g_rot_out', g_rot), ('patience', istate[1:2]), ('alive', alive)):
+            setattr(s, name, t.data_ptr())
+        s.loss_w = (ctypes.c_float * 4)(*w)
+        s.lr_rot, s.lr_trans, s.n_rot, s.first_iter, s.may_stop, s.wait_iters = lr_rot, lr_trans, n_rot, int(k == 0), 1, wait
+        c2w_in = c2w.cpu().clone()
+        check(lib.cb200_track_update(ctypes.byref(s), stream()), 'track_update')
+        torch.cuda.synchronize()
+        # reference: coslam.py:546-573 on the same numbers
+        if ref_alive:
+            lv = float(sum(wi * li for wi, li in zip(w, lk.tolist())))
+            cur = pose.pose_matrix(ref_rot, ref_trans)
+            assert float((c2w_in.view(4, 4) - cur[0].detach()).abs().max()) <= 5e-6
+            ref_last_c2w = cur.detach().clone()
+            if k == 0:
+                ref_best, ref_best_c2w = lv, cur.detach().clone()
+            if lv < ref_best:
+                ref_best, ref_best_c2w, ref_pat = lv, cur.detach().clone(), 0
+            else:
+                ref_pat += 1
+            if ref_pat > wait:
+                ref_alive = False
+            else:
+                opt.zero_grad()
+                (cur[0] * gk).sum().backward()
+                assert float((g_rot.cpu() - ref_rot.grad.view(-1)).abs().max()) <= 1e-4 * float(ref_rot.grad.abs().max()) + 1e-6
+                opt.step()
+        assert bool(alive.item()) == ref_alive
+        assert abs(float(best_loss) - ref_best) <= 1e-6 * abs(ref_best)
+        assert float((best_c2w.cpu().view(4, 4) - ref_best_c2w[0]).abs().max()) <= 5e-6
+        assert float((last_c2w.cpu().view(4, 4) - ref_last_c2w[0]).abs().max()) <= 5e-6
+        assert float((rot.cpu() - ref_rot.detach().view(-1)).abs().max()) <= 5e-6
+        assert float((trans.cpu() - ref_trans.detach().view(-1)).abs().max()) <= 5e-6
+    assert not ref_alive and int(istate[1]) == wait + 1
 
 
 def test_keyframe_database_and_ray_assembly_match_reference_lines():
