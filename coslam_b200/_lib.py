@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 10
+ABI_VERSION = 12
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p
@@ -54,8 +54,44 @@ class TrackStep(ctypes.Structure):
                 ('first_iter', ctypes.c_int32), ('may_stop', ctypes.c_int32), ('wait_iters', ctypes.c_int32)]
 
 
+class MlpGrad(ctypes.Structure):
+    _fields_ = [('w_sdf0', ctypes.c_void_p), ('w_sdf1', ctypes.c_void_p), ('w_col0', ctypes.c_void_p), ('w_col1', ctypes.c_void_p)]
+
+
+class LossGradPtrs(ctypes.Structure):
+    _fields_ = [('rgb', ctypes.c_void_p), ('depth', ctypes.c_void_p), ('sdf', ctypes.c_void_p), ('fs', ctypes.c_void_p)]
+
+
+class AdamParam(ctypes.Structure):
+    """cb200_adam_param."""
+    _fields_ = [('param', ctypes.c_void_p), ('grad', ctypes.c_void_p), ('exp_avg', ctypes.c_void_p), ('exp_avg_sq', ctypes.c_void_p),
+                ('n', ctypes.c_int64), ('lr', ctypes.c_float), ('beta1', ctypes.c_float), ('beta2', ctypes.c_float),
+                ('eps', ctypes.c_float), ('weight_decay', ctypes.c_float)]
+
+
+class BaPlan(ctypes.Structure):
+    """cb200_ba_plan (include/coslam_b200.h), field for field."""
+    _fields_ = [('scene', ctypes.c_void_p), ('render', ctypes.c_void_p), ('grid', ctypes.c_void_p), ('table', ctypes.c_void_p),
+                ('mlp', Mlp), ('lin_uniform', ctypes.c_void_p), ('lin_guided', ctypes.c_void_p), ('lin_nodepth', ctypes.c_void_p),
+                ('kf_rays', ctypes.c_void_p), ('idx_global', ctypes.c_void_p), ('slot_global', ctypes.c_void_p), ('n_global', ctypes.c_int64),
+                ('cur_rays', ctypes.c_void_p), ('idx_cur', ctypes.c_void_p), ('slot_cur', ctypes.c_void_p), ('n_cur', ctypes.c_int64),
+                ('poses_all', ctypes.c_void_p), ('n_poses', ctypes.c_int64), ('n_samples', ctypes.c_int64),
+                ('noise', ctypes.c_void_p), ('seeds', ctypes.c_void_p), ('seed_dev', ctypes.c_void_p),
+                ('rays_o', ctypes.c_void_p), ('rays_d', ctypes.c_void_p), ('target_rgb', ctypes.c_void_p), ('target_d', ctypes.c_void_p),
+                ('z_vals', ctypes.c_void_p), ('raw', ctypes.c_void_p), ('act_mask', ctypes.c_void_p), ('d_raw', ctypes.c_void_p),
+                ('lazy_ws', ctypes.c_void_p), ('lazy_ws_bytes', ctypes.c_size_t), ('bwd_ws', ctypes.c_void_p), ('bwd_ws_bytes', ctypes.c_size_t),
+                ('ws', ctypes.c_void_p), ('loss_out', ctypes.c_void_p), ('loss_w', LossGradPtrs),
+                ('g_table', ctypes.c_void_p), ('g_mlp', MlpGrad), ('d_rays', ctypes.c_void_p), ('d_poses', ctypes.c_void_p),
+                ('smooth_side', ctypes.c_int64), ('smooth_feat', ctypes.c_int64), ('smooth_voxel', ctypes.c_float),
+                ('smooth_grad_scale', ctypes.c_float), ('smooth_jitter', ctypes.c_void_p), ('smooth_offset', ctypes.c_void_p),
+                ('smooth_x', ctypes.c_void_p), ('smooth_f', ctypes.c_void_p), ('smooth_df', ctypes.c_void_p),
+                ('map_params', ctypes.c_void_p), ('n_map_params', ctypes.c_int64),
+                ('rot', ctypes.c_void_p), ('trans', ctypes.c_void_p), ('pose_adam', ctypes.c_void_p), ('n_free', ctypes.c_int64),
+                ('n_rot', ctypes.c_int32), ('lr_rot', ctypes.c_float), ('lr_trans', ctypes.c_float)]
+
+
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
-           'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update',
+           'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update', 'cb200_pose_matrices', 'cb200_pose_adam', 'cb200_smooth_points', 'cb200_smooth_tv', 'cb200_ba_iteration', 'cb200_sizeof', 'cb200_host_random_sample',
            'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd',
            'cb200_debug_positions', 'cb200_selftest_mma', 'cb200_set_decoder',
            'cb200_get_decoder']
@@ -91,6 +127,11 @@ def load():
     if lib.cb200_abi_version() != ABI_VERSION:
         raise RuntimeError('coslam_b200: ABI version mismatch (library %d, binding %d); rebuild with '
                            '`python -m coslam_b200.build --force`' % (lib.cb200_abi_version(), ABI_VERSION))
+    lib.cb200_sizeof.restype = ctypes.c_size_t
+    for which, cls in ((0, BaPlan), (1, TrackStep), (2, AdamParam)):
+        if lib.cb200_sizeof(which) != ctypes.sizeof(cls):
+            raise RuntimeError('coslam_b200: %s layout differs from the library (%d vs %d bytes)'
+                               % (cls.__name__, ctypes.sizeof(cls), lib.cb200_sizeof(which)))
     _lib = lib
     if os.environ.get('COSLAM_B200_DECODER'):
         lib.cb200_set_decoder({'simt': 0, 'tc': 1}[os.environ['COSLAM_B200_DECODER']])

@@ -174,7 +174,40 @@ int cb200_adam_step(float* param, float* grad, float* exp_avg, float* exp_avg_sq
 int cb200_track_pose(const float* rot, const float* trans, int n_rot, float* c2w, void* stream) {
     CB_REQUIRE(rot && trans && c2w, "track_pose: NULL buffer");
     CB_REQUIRE(n_rot == 3 || n_rot == 4, "track_pose: n_rot must be 3 (axis-angle) or 4 (quaternion)");
-    return cuda_result(cb200::launch_track_pose(rot, trans, n_rot, c2w, (cudaStream_t)stream), "track_pose");
+    return cuda_result(cb200::launch_pose_matrices(rot, trans, 1, n_rot, c2w, (cudaStream_t)stream), "track_pose");
+}
+
+int cb200_pose_matrices(const float* rot, const float* trans, int64_t n_poses, int n_rot, float* c2w, void* stream) {
+    CB_REQUIRE(n_poses >= 0, "pose_matrices: negative count");
+    if (n_poses == 0) return 0;
+    CB_REQUIRE(rot && trans && c2w, "pose_matrices: NULL buffer");
+    CB_REQUIRE(n_rot == 3 || n_rot == 4, "pose_matrices: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    return cuda_result(cb200::launch_pose_matrices(rot, trans, n_poses, n_rot, c2w, (cudaStream_t)stream), "pose_matrices");
+}
+
+int cb200_pose_adam(float* rot, float* trans, float* exp_avg_rot, float* exp_avg_sq_rot, float* exp_avg_trans, float* exp_avg_sq_trans,
+                    float* d_c2w, float* c2w, int64_t n_poses, int n_rot, float lr_rot, float lr_trans, int64_t step, int zero_grad,
+                    void* stream) {
+    CB_REQUIRE(n_poses >= 0, "pose_adam: negative count");
+    if (n_poses == 0) return 0;
+    CB_REQUIRE(rot && trans && exp_avg_rot && exp_avg_sq_rot && exp_avg_trans && exp_avg_sq_trans && d_c2w && c2w, "pose_adam: NULL buffer");
+    CB_REQUIRE(n_rot == 3 || n_rot == 4, "pose_adam: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    CB_REQUIRE(step >= 1, "pose_adam: step is 1-based");
+    return cuda_result(cb200::launch_pose_adam(rot, trans, exp_avg_rot, exp_avg_sq_rot, exp_avg_trans, exp_avg_sq_trans, d_c2w, c2w, n_poses,
+                                               n_rot, lr_rot, lr_trans, step, zero_grad, (cudaStream_t)stream), "pose_adam");
+}
+
+int cb200_smooth_points(int64_t n_side, float voxel, const float* jitter, const float* offset, const float* bb_lo, const float* bb_ext,
+                        float* x, void* stream) {
+    CB_REQUIRE(n_side >= 1 && n_side <= 1024, "smooth_points: lattice side %lld out of range", (long long)n_side);
+    CB_REQUIRE(jitter && offset && bb_lo && bb_ext && x, "smooth_points: NULL buffer");
+    return cuda_result(cb200::launch_smooth_points((int)n_side, voxel, jitter, offset, bb_lo, bb_ext, x, (cudaStream_t)stream), "smooth_points");
+}
+
+int cb200_smooth_tv(const float* f, int64_t n_side, int64_t n_feat, float grad_scale, float* d_f, double* tv_sum, void* stream) {
+    CB_REQUIRE(n_side >= 1 && n_side <= 1024 && n_feat >= 1 && n_feat <= 1024, "smooth_tv: bad lattice shape");
+    CB_REQUIRE(f && d_f, "smooth_tv: NULL buffer");
+    return cuda_result(cb200::launch_smooth_tv(f, (int)n_side, (int)n_feat, grad_scale, d_f, tv_sum, (cudaStream_t)stream), "smooth_tv");
 }
 
 int cb200_track_update(const cb200_track_step* s, void* stream) {

@@ -88,7 +88,12 @@ cudaError_t launch_assemble_rays_fwd(const float* kf_rays, const long long* ray_
                                      cudaStream_t st);
 cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* d_rays_o,
                                      const float* d_rays_d, long long n, long long n_poses, float* d_poses, cudaStream_t st);
-cudaError_t launch_track_pose(const float* rot, const float* trans, int n_rot, float* c2w, cudaStream_t st);
+cudaError_t launch_pose_matrices(const float* rot, const float* trans, long long n, int n_rot, float* c2w, cudaStream_t st);
+cudaError_t launch_pose_adam(float* rot, float* trans, float* m_rot, float* v_rot, float* m_trans, float* v_trans, float* d_c2w, float* c2w,
+                             long long n, int n_rot, float lr_rot, float lr_trans, long long step, int zero_grad, cudaStream_t st);
+cudaError_t launch_smooth_tv(const float* f, int n, int n_feat, float scale, float* d_f, double* tv_sum, cudaStream_t st);
+cudaError_t launch_smooth_points(int n, float vox, const float* jitter, const float* offset, const float* lo, const float* ext, float* x,
+                                 cudaStream_t st);
 cudaError_t launch_track_update(const cb200_track_step& s, cudaStream_t st);
 cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                              float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, cudaStream_t st);

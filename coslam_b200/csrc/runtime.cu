@@ -1,0 +1,207 @@
+// Native iteration runtime: one C call issues every launch of a bundle-adjustment iteration (coslam.py:336-390), so the
+// host pays ~30 cudaLaunchKernel calls instead of ~30 Python -> ctypes round trips with tensor bookkeeping in between
+// (1.5 ms -> the GPU time of the kernels at room0's 2048 + rays).  It only sequences the library's own public entry
+// points (include/coslam_b200.h) on the caller's stream; no allocation, no synchronisation.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include <vector>
+
+#include "../../include/coslam_b200.h"
+
+namespace {
+
+int cuda_rc(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
+
+}  // namespace
+
+extern "C" size_t cb200_sizeof(int which) {       // binding self-check: 0 = cb200_ba_plan, 1 = cb200_track_step, 2 = cb200_adam_param
+    switch (which) {
+        case 0: return sizeof(cb200_ba_plan);
+        case 1: return sizeof(cb200_track_step);
+        case 2: return sizeof(cb200_adam_param);
+        default: return 0;
+    }
+}
+
+extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t map_step, int zero_map_grads, int64_t pose_step,
+                                  void* stream) {
+    if (p == nullptr || it < 0) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n = p->n_global + p->n_cur, S = p->n_samples;
+    int rc;
+#define CB_TRY(call)             \
+    do {                         \
+        rc = (call);             \
+        if (rc != 0) return rc;  \
+    } while (0)
+
+    CB_TRY(cuda_rc(cudaMemsetAsync(p->ws, 0, 10 * sizeof(double), st)));
+    if (p->d_rays) CB_TRY(cuda_rc(cudaMemsetAsync(p->d_rays, 0, sizeof(float) * 6 * n, st)));
+    int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
+    double* sums = p->ws + 4;
+
+    // ---- rays (coslam.py:336-355) -------------------------------------------------------------------------------------
+    CB_TRY(cb200_assemble_rays_fwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->poses_all, p->n_global,
+                                   p->n_poses, p->rays_o, p->rays_d, p->target_rgb, p->target_d, stream));
+    const int64_t g = p->n_global;
+    CB_TRY(cb200_assemble_rays_fwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->poses_all, p->n_cur, p->n_poses, p->rays_o + 3 * g,
+                                   p->rays_d + 3 * g, p->target_rgb + 3 * g, p->target_d + g, stream));
+    // ---- JointEncoding.forward (scene_rep.py:297-351) ---------------------------------------------------------------------
+    CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, p->noise ? p->noise + it * n * S : nullptr,
+                             p->seeds ? p->seeds[it] : 0, p->seed_dev, n, p->z_vals, counts, stream));
+    if (p->lazy_ws) {
+        CB_TRY(cuda_rc(cudaMemsetAsync(p->raw, 0, sizeof(float) * 4 * n * S, st)));
+        unsigned char* base = static_cast<unsigned char*>(p->lazy_ws);
+        const uint64_t* count = reinterpret_cast<const uint64_t*>(base);
+        const uint32_t* list = reinterpret_cast<const uint32_t*>(base + 16 + 4 * n);      // layout of cb200_lazy_workspace
+        CB_TRY(cb200_lazy_prefix(p->render, p->z_vals, p->target_d, n, S, p->lazy_ws, p->lazy_ws_bytes, stream));
+        CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0, list,
+                                count, stream));
+        CB_TRY(cb200_lazy_resolve(p->render, p->z_vals, p->target_d, p->raw, n, S, p->lazy_ws, p->lazy_ws_bytes, stream));
+        CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0, list,
+                                count, stream));
+    } else {
+        CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0,
+                                nullptr, nullptr, stream));
+    }
+    CB_TRY(cb200_render_fwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, sums, stream));
+    CB_TRY(cb200_loss_finish(sums, counts, n, S, p->loss_out, p->loss_out + 4, stream));
+    // ---- backward ---------------------------------------------------------------------------------------------------------
+    CB_TRY(cb200_render_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, &p->loss_w, p->loss_out + 4, nullptr, nullptr, p->d_raw,
+                            stream));
+    CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask, p->g_table,
+                            &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes, stream));
+    if (p->d_rays) {
+        CB_TRY(cb200_assemble_rays_bwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->d_rays,
+                                       p->d_rays + 3 * n, p->n_global, p->n_poses, p->d_poses, stream));
+        CB_TRY(cb200_assemble_rays_bwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->d_rays + 3 * g, p->d_rays + 3 * n + 3 * g, p->n_cur,
+                                       p->n_poses, p->d_poses, stream));
+    }
+    // ---- smoothness (coslam.py:154-158, :251-274) -------------------------------------------------------------------------
+    if (p->smooth_side > 0) {
+        const int64_t m = p->smooth_side * p->smooth_side * p->smooth_side;
+        CB_TRY(cb200_smooth_points(p->smooth_side, p->smooth_voxel, p->smooth_jitter + 3 * it, p->smooth_offset + 3 * it, p->scene->bb_lo,
+                                   p->scene->bb_ext, p->smooth_x, stream));
+        CB_TRY(cb200_hash_fwd(p->grid, p->smooth_x, p->table, m, p->smooth_f, stream));
+        CB_TRY(cb200_smooth_tv(p->smooth_f, p->smooth_side, p->smooth_feat, p->smooth_grad_scale, p->smooth_df, p->ws + 8, stream));
+        CB_TRY(cb200_hash_bwd(p->grid, p->smooth_x, p->table, p->smooth_df, m, p->g_table, nullptr, stream));
+    }
+    // ---- optimisers (coslam.py:363-390) -----------------------------------------------------------------------------------
+    for (int64_t k = 0; k < p->n_map_params; ++k) {
+        const cb200_adam_param& a = p->map_params[k];
+        if (map_step > 0) {
+            CB_TRY(cb200_adam_step(a.param, a.grad, a.exp_avg, a.exp_avg_sq, a.n, a.lr, a.beta1, a.beta2, a.eps, a.weight_decay, nullptr, map_step,
+                                   zero_map_grads ? 1 : 0, stream));
+        } else if (zero_map_grads) {
+            CB_TRY(cuda_rc(cudaMemsetAsync(a.grad, 0, sizeof(float) * a.n, st)));
+        }
+    }
+    if (pose_step > 0 && p->n_free > 0) {
+        const int64_t nf = p->n_free, nr = p->n_rot;
+        float* m_rot = p->pose_adam;
+        float* v_rot = m_rot + nf * nr;
+        float* m_tr = v_rot + nf * nr;
+        float* v_tr = m_tr + 3 * nf;
+        CB_TRY(cb200_pose_adam(p->rot, p->trans, m_rot, v_rot, m_tr, v_tr, p->d_poses + 16, p->poses_all + 16, nf, (int)nr, p->lr_rot, p->lr_trans,
+                               pose_step, 1, stream));
+        CB_TRY(cuda_rc(cudaMemsetAsync(p->d_poses, 0, sizeof(float) * 16 * p->n_poses, st)));
+    }
+#undef CB_TRY
+    return 0;
+}
+
+// ---- host: CPython's random.sample(range(n), k), bit for bit ----------------------------------------------------------
+// The reference draws its ray / pixel indices with Python's `random.sample` (model/keyframe.py:45-46, :100; coslam.py:131-138,
+// :339-341): ~1 us per element in the interpreter, i.e. more host time per BA iteration than the GPU needs for the whole
+// iteration.  This is the same algorithm (Lib/random.py `sample` + `_randbelow_with_getrandbits`, Modules/_randommodule.c
+// genrand_uint32) on the caller's copy of the generator state, so the indices -- and every later draw -- are unchanged.
+namespace {
+
+struct Mt19937 {
+    uint32_t* mt;      // [624]
+    uint32_t& idx;     // position, 624 = regenerate
+    uint32_t next() {
+        constexpr int N = 624, M = 397;
+        constexpr uint32_t A = 0x9908b0dfu, UP = 0x80000000u, LO = 0x7fffffffu;
+        if (idx >= (uint32_t)N) {
+            int kk;
+            uint32_t y;
+            for (kk = 0; kk < N - M; ++kk) {
+                y = (mt[kk] & UP) | (mt[kk + 1] & LO);
+                mt[kk] = mt[kk + M] ^ (y >> 1) ^ ((y & 1u) ? A : 0u);
+            }
+            for (; kk < N - 1; ++kk) {
+                y = (mt[kk] & UP) | (mt[kk + 1] & LO);
+                mt[kk] = mt[kk + (M - N)] ^ (y >> 1) ^ ((y & 1u) ? A : 0u);
+            }
+            y = (mt[N - 1] & UP) | (mt[0] & LO);
+            mt[N - 1] = mt[M - 1] ^ (y >> 1) ^ ((y & 1u) ? A : 0u);
+            idx = 0;
+        }
+        uint32_t y = mt[idx++];
+        y ^= (y >> 11);
+        y ^= (y << 7) & 0x9d2c5680u;
+        y ^= (y << 15) & 0xefc60000u;
+        y ^= (y >> 18);
+        return y;
+    }
+    uint32_t below(uint32_t n, int bits) {      // _randbelow_with_getrandbits, n < 2^32
+        uint32_t r = next() >> (32 - bits);
+        while (r >= n) r = next() >> (32 - bits);
+        return r;
+    }
+};
+
+}  // namespace
+
+extern "C" int cb200_host_random_sample(uint32_t* state, int64_t n_draws, const int64_t* n, const int64_t* k, int64_t* out) {
+    if (!state || !n || !k || !out || n_draws < 0) return -1;
+    if (state[624] > 624u) return -1;
+    Mt19937 g{state, state[624]};
+    std::vector<uint32_t> table;
+    std::vector<int64_t> pool;
+    for (int64_t d = 0; d < n_draws; ++d) {
+        const int64_t nn = n[d], kk = k[d];
+        if (kk < 0 || kk > nn || nn >= (int64_t)1 << 32) return -2;
+        if (kk == 0) continue;
+        int bits = 0;
+        while ((nn >> bits) != 0) ++bits;
+        double setsize = 21.0;
+        if (kk > 5) setsize += pow(4.0, ceil(log((double)(kk * 3)) / log(4.0)));
+        if ((double)nn <= setsize) {                          // pool branch
+            pool.resize((size_t)nn);
+            for (int64_t i = 0; i < nn; ++i) pool[(size_t)i] = i;
+            for (int64_t i = 0; i < kk; ++i) {
+                const uint32_t m = (uint32_t)(nn - i);
+                int b = 0;
+                while ((m >> b) != 0) ++b;
+                const uint32_t j = g.below(m, b);
+                out[i] = pool[j];
+                pool[j] = pool[(size_t)(nn - i - 1)];
+            }
+        } else {                                              // set branch: redraw while already selected
+            size_t cap = 16;
+            while (cap < (size_t)kk * 4) cap <<= 1;
+            table.assign(cap, 0u);                            // stores j + 1 (j < 2^32 - 1 because j < n <= 2^32 - 1)
+            for (int64_t i = 0; i < kk; ++i) {
+                for (;;) {
+                    const uint32_t j = g.below((uint32_t)nn, bits);
+                    size_t h = ((size_t)j * 2654435761u) & (cap - 1);
+                    bool seen = false;
+                    while (table[h] != 0u) {
+                        if (table[h] == j + 1u) { seen = true; break; }
+                        h = (h + 1) & (cap - 1);
+                    }
+                    if (seen) continue;
+                    table[h] = j + 1u;
+                    out[i] = (int64_t)j;
+                    break;
+                }
+            }
+        }
+        out += kk;
+    }
+    return 0;
+}

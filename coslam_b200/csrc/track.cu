@@ -1,4 +1,6 @@
-// Tracking-loop glue on the device (coslam.py:502-573 `tracking_render`): everything between two renders of one
+// Pose / optimiser glue of the tracking and bundle-adjustment loops on the device.
+//
+// Tracking (coslam.py:502-573 `tracking_render`): everything between two renders of one
 // tracking iteration that the reference does with ~100 tiny autograd / optimiser / bookkeeping kernels and two
 // `.cpu().item()` syncs, as ONE single-thread kernel:
 //   loss = sum_k w_k loss_k (get_loss_from_ret, coslam.py:140-160)
@@ -136,11 +138,12 @@ __device__ void write_c2w(const Dual R[9], const float* trans, float* c2w) {
     c2w[12] = 0.f; c2w[13] = 0.f; c2w[14] = 0.f; c2w[15] = 1.f;
 }
 
-__global__ void track_pose_kernel(const float* rot, const float* trans, int n_rot, float* c2w) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+__global__ void pose_matrices_kernel(const float* rot, const float* trans, long long n, int n_rot, float* c2w) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
     Dual R[9];
-    rotation_dual(rot, n_rot, R);
-    write_c2w(R, trans, c2w);
+    rotation_dual(rot + i * n_rot, n_rot, R);
+    write_c2w(R, trans + i * 3, c2w + i * 16);
 }
 
 __device__ __forceinline__ void adam_scalar(float& p, float g, float& m, float& v, float step_size, float inv_sqrt_bc2, bool write) {
@@ -149,6 +152,92 @@ __device__ __forceinline__ void adam_scalar(float& p, float g, float& m, float& 
     v = fmaf((1.f - 0.999f) * g, g, 0.999f * v);
     const float denom = fmaf(sqrtf(v), inv_sqrt_bc2, 1e-8f);
     if (write) p = p - step_size * (m / denom);
+}
+
+// Bundle adjustment (coslam.py:285-397): one Adam step of torch.optim.Adam([rot, trans]) for n poses from the accumulated
+// dL/d c2w, thread per pose.  Between two pose steps the reference back-propagates every iteration through the SAME
+// pose matrices (`retain_graph=True`, coslam.py:361), so summing dL/d c2w over those iterations and applying the (fixed)
+// Jacobian once is the same gradient.
+struct PoseAdamArgs {
+    float *rot, *trans, *m_rot, *v_rot, *m_trans, *v_trans;
+    float* d_c2w;       // [n,4,4] accumulated gradient, cleared here when zero_grad
+    float* c2w;         // [n,4,4] out: matrices of the updated parameters
+    long long n;
+    int n_rot, zero_grad;
+    float ss_rot, ss_trans, inv_sqrt_bc2;
+};
+
+__global__ void pose_adam_kernel(PoseAdamArgs a) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    float* rot = a.rot + i * a.n_rot;
+    float* trans = a.trans + i * 3;
+    float* g = a.d_c2w + i * 16;
+    Dual R[9];
+    rotation_dual(rot, a.n_rot, R);
+    float g_rot[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c)
+            for (int k = 0; k < a.n_rot; ++k) g_rot[k] = fmaf(g[r * 4 + c], R[r * 3 + c].d[k], g_rot[k]);
+    for (int k = 0; k < a.n_rot; ++k)
+        adam_scalar(rot[k], g_rot[k], a.m_rot[i * a.n_rot + k], a.v_rot[i * a.n_rot + k], a.ss_rot, a.inv_sqrt_bc2, true);
+    for (int k = 0; k < 3; ++k) adam_scalar(trans[k], g[k * 4 + 3], a.m_trans[i * 3 + k], a.v_trans[i * 3 + k], a.ss_trans, a.inv_sqrt_bc2, true);
+    if (a.zero_grad)
+        for (int k = 0; k < 16; ++k) g[k] = 0.f;
+    rotation_dual(rot, a.n_rot, R);
+    write_c2w(R, trans, a.c2w + i * 16);
+}
+
+// Smoothness regulariser (coslam.py:251-274): TV = sum of squared forward differences of the lattice features along x, y, z.
+// f [n,n,n,F]; d_f = scale * dTV/df (each difference enters the gradient of both of its end points); tv_sum += TV.
+__global__ void __launch_bounds__(256) smooth_tv_kernel(const float* __restrict__ f, int n, int F, float scale, float* __restrict__ d_f,
+                                                        double* tv_sum) {
+    const long long total = (long long)n * n * n * F;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    float local = 0.f;
+    if (idx < total) {
+        const long long p = idx / F;
+        const int c[3] = {(int)(p / ((long long)n * n)), (int)((p / n) % n), (int)(p % n)};
+        const long long stride[3] = {(long long)n * n * F, (long long)n * F, (long long)F};
+        const float v = f[idx];
+        float g = 0.f;
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            if (c[ax] + 1 < n) {
+                const float d = f[idx + stride[ax]] - v;
+                local = fmaf(d, d, local);
+                g -= 2.f * d;
+            }
+            if (c[ax] > 0) g += 2.f * (v - f[idx - stride[ax]]);
+        }
+        d_f[idx] = scale * g;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    __shared__ float part[8];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = local;
+    __syncthreads();
+    if (threadIdx.x == 0 && tv_sum) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += (double)part[w];
+        atomicAdd(tv_sum, t);
+    }
+}
+
+// lattice positions of the regulariser, normalised to the unit cube, with torch's operation order (separately rounded):
+//   pts = (coords + jitter) * vox + lo + offset;   x = (pts - lo) / ext          (coslam.py:258-266)
+__global__ void __launch_bounds__(256) smooth_points_kernel(int n, float vox, float3 jitter, float3 offset, float3 lo, float3 ext,
+                                                            float* __restrict__ x) {
+    const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= (long long)n * n * n) return;
+    const float c[3] = {(float)(p / ((long long)n * n)), (float)((p / n) % n), (float)(p % n)};
+    const float j[3] = {jitter.x, jitter.y, jitter.z}, o[3] = {offset.x, offset.y, offset.z}, l[3] = {lo.x, lo.y, lo.z},
+                e[3] = {ext.x, ext.y, ext.z};
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float pt = __fadd_rn(__fadd_rn(__fmul_rn(__fadd_rn(c[d], j[d]), vox), l[d]), o[d]);
+        x[p * 3 + d] = __fdiv_rn(__fsub_rn(pt, l[d]), e[d]);
+    }
 }
 
 __global__ void track_update_kernel(cb200_track_step s) {
@@ -215,8 +304,33 @@ __global__ void track_update_kernel(cb200_track_step s) {
 
 }  // namespace
 
-cudaError_t launch_track_pose(const float* rot, const float* trans, int n_rot, float* c2w, cudaStream_t st) {
-    track_pose_kernel<<<1, 32, 0, st>>>(rot, trans, n_rot, c2w);
+cudaError_t launch_pose_matrices(const float* rot, const float* trans, long long n, int n_rot, float* c2w, cudaStream_t st) {
+    pose_matrices_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(rot, trans, n, n_rot, c2w);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pose_adam(float* rot, float* trans, float* m_rot, float* v_rot, float* m_trans, float* v_trans, float* d_c2w, float* c2w,
+                             long long n, int n_rot, float lr_rot, float lr_trans, long long step, int zero_grad, cudaStream_t st) {
+    // bias corrections in double like the Python scalars of torch.optim.Adam (betas 0.9 / 0.999), rounded once
+    const double bc1 = 1.0 - pow(0.9, (double)step), bc2 = 1.0 - pow(0.999, (double)step);
+    PoseAdamArgs a{rot, trans, m_rot, v_rot, m_trans, v_trans, d_c2w, c2w, n, n_rot, zero_grad,
+                   (float)((double)lr_rot / bc1), (float)((double)lr_trans / bc1), (float)(1.0 / sqrt(bc2))};
+    pose_adam_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_smooth_tv(const float* f, int n, int n_feat, float scale, float* d_f, double* tv_sum, cudaStream_t st) {
+    const long long total = (long long)n * n * n * n_feat;
+    smooth_tv_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(f, n, n_feat, scale, d_f, tv_sum);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_smooth_points(int n, float vox, const float* jitter, const float* offset, const float* lo, const float* ext, float* x,
+                                 cudaStream_t st) {
+    const long long total = (long long)n * n * n;
+    smooth_points_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(n, vox, make_float3(jitter[0], jitter[1], jitter[2]),
+                                                                          make_float3(offset[0], offset[1], offset[2]),
+                                                                          make_float3(lo[0], lo[1], lo[2]), make_float3(ext[0], ext[1], ext[2]), x);
     return cudaGetLastError();
 }
 

@@ -13,10 +13,43 @@ to the reference's for the same seed; `sample_global_indices_device` is the non-
 import ctypes
 import random
 
+import numpy as np
 import torch
 
 from . import _lib
 from ._lib import check, ptr, stream
+
+
+def sample_ranges(draws):
+    """[`random.sample(range(n), k)` for (n, k) in draws] -- the same values in the same order and the same state of Python's
+    global generator afterwards -- computed by the library's host routine `cb200_host_random_sample` (CPython's algorithm over
+    a copy of the Mersenne-Twister state, written back with `random.setstate`) instead of the interpreter: the reference draws
+    2048 + ray indices per BA iteration and 40 800 per keyframe this way (model/keyframe.py:45-46, :100; coslam.py:339-341),
+    ~1 us per element in CPython.  Returns a list of int64 numpy arrays."""
+    draws = [(int(n), int(k)) for n, k in draws]
+    for n, k in draws:
+        if not 0 <= k <= n:
+            raise ValueError('Sample larger than population or is negative')
+    if not draws:
+        return []
+    if any(n >= 2 ** 32 for n, _ in draws):
+        return [np.asarray(random.sample(range(n), k), dtype=np.int64) for n, k in draws]
+    version, mt, gauss = random.getstate()
+    state = np.array(mt, dtype=np.uint32)
+    ns = np.array([n for n, _ in draws], dtype=np.int64)
+    ks = np.array([k for _, k in draws], dtype=np.int64)
+    out = np.empty(int(ks.sum()), dtype=np.int64)
+    rc = _lib.load().cb200_host_random_sample(ctypes.c_void_p(state.ctypes.data), ctypes.c_int64(len(draws)), ctypes.c_void_p(ns.ctypes.data),
+                                              ctypes.c_void_p(ks.ctypes.data), ctypes.c_void_p(out.ctypes.data))
+    if rc != 0:
+        raise RuntimeError('cb200_host_random_sample failed (%d)' % rc)
+    random.setstate((version, tuple(state.tolist()), gauss))
+    return np.split(out, np.cumsum(ks)[:-1])
+
+
+def sample_range(n, k):
+    """`random.sample(range(n), k)` as an int64 numpy array (see sample_ranges)."""
+    return sample_ranges([(n, k)])[0]
 
 
 class _AssembleRays(torch.autograd.Function):
@@ -89,11 +122,11 @@ class KeyFrameDatabase(object):
     def sample_single_keyframe_rays(self, rays, option='random'):
         """model/keyframe.py:40-63: same Python-`random` draws, the gather runs where `rays` lives."""
         if option == 'random':
-            idxs = random.sample(range(0, self.H * self.W), self.num_rays_to_save)
+            idxs = sample_range(self.H * self.W, self.num_rays_to_save)
         elif option == 'filter_depth':
             valid = (rays[..., -1] > 0.0) & (rays[..., -1] <= self.config['cam']['depth_trunc'])
             rays_valid = rays[valid, :]
-            idxs = random.sample(range(0, len(rays_valid)), self.num_rays_to_save)
+            idxs = sample_range(len(rays_valid), self.num_rays_to_save)
         else:
             raise NotImplementedError()
         return rays[:, torch.as_tensor(idxs, device=rays.device)]
@@ -114,7 +147,7 @@ class KeyFrameDatabase(object):
     # ---- model/keyframe.py:96-106 ------------------------------------------------------------------------------------
     def sample_global_indices(self, bs):
         """The reference's draw: `random.sample(range(num_kf * R), bs)` (without replacement) as an int64 tensor (host)."""
-        return torch.tensor(random.sample(range(len(self) * self.num_rays_to_save), bs))
+        return torch.from_numpy(sample_range(len(self) * self.num_rays_to_save, bs))
 
     def sample_global_indices_device(self, bs, generator=None):
         """Non-parity sampler for the large sweeps: device uniform draws (with replacement)."""
@@ -146,7 +179,7 @@ class KeyFrameDatabase(object):
         out = assemble_rays(store, idxs, ids, poses_all)
         ids = ids.to(self.device)
         if current_rays is not None and n_current > 0:              # the store is never copied: second, small assembly
-            idx_cur = torch.tensor(random.sample(range(0, self.H * self.W), n_current))
+            idx_cur = torch.from_numpy(sample_range(self.H * self.W, n_current))
             cur = current_rays.reshape(-1, 7).to(self.device)
             ids_cur = -torch.ones(n_current, dtype=torch.int64, device=self.device)
             out_cur = assemble_rays(cur, idx_cur, ids_cur, poses_all)

@@ -1,0 +1,249 @@
+"""Global bundle adjustment without an autograd graph.
+
+`CoSLAM.global_BA` (coslam.py:285-397) runs `mapping.iters` iterations of: sample rays from the keyframe database and the
+current frame -> pose gather and ray rotation -> JointEncoding.forward -> weighted loss (+ smoothness) -> backward into the
+hash table, the decoder and the keyframe poses -> optimiser steps every `map_accum_step` / `pose_accum_step` iterations.
+Through torch autograd one such iteration is ~250 small kernels and is bound by the host (6.9 ms on a B200 at room0's 2048 +
+rays); `BundleAdjuster.run` issues the same arithmetic as ~25 library launches per iteration with no host synchronisation:
+
+    host (once per call, the reference's draws in the reference's order): `random.sample` ray indices of every iteration
+        (model/keyframe.py:96-106, coslam.py:339-341), the CPU `torch.rand` of the stratified jitter (scene_rep.py:255, host
+        noise mode only) and of the smoothness lattice (coslam.py:260-262) -> one upload
+    per iteration: cb200_assemble_rays_fwd x2 | cb200_sample_rays | cb200_points_fwd (lazy above 2^16 points) |
+        cb200_render_fwd | cb200_loss_finish | cb200_render_bwd | cb200_points_bwd (table, decoder, ray gradients) |
+        cb200_assemble_rays_bwd x2 | smoothness: cb200_smooth_points, cb200_hash_fwd, cb200_smooth_tv, cb200_hash_bwd |
+        when due: cb200_adam_step per map parameter (coslam_b200.optim.Adam), cb200_pose_adam
+
+Gradients accumulate in the parameters' `.grad` buffers (the map optimiser is the caller's, as in coslam.py:610-624) and in
+one [K,4,4] pose-gradient buffer: between two pose steps the reference back-propagates through the same pose matrices
+(`retain_graph=True`), so chaining the summed dL/d c2w through the pose parametrisation once is the same gradient.
+coslam.py stays unchanged by design; this class is the opt-in fast path (tools/slam_synth.py uses it).
+"""
+import ctypes
+import random
+
+import torch
+
+from . import _lib, ops, pose
+from ._lib import check, ptr, stream
+from .keyframe import sample_ranges
+
+
+class BundleAdjuster(object):
+    def __init__(self, model, config, kfdb, map_optimizer, device='cuda:0'):
+        if not config['grid']['oneGrid'] or int(config['training']['n_importance']) > 0:
+            raise NotImplementedError('BundleAdjuster serves oneGrid: True without importance samples (every Replica / ScanNet '
+                                      'config); use the autograd path for the other variants')
+        self.model, self.config, self.kfdb, self.opt, self.device = model, config, kfdb, map_optimizer, torch.device(device)
+        t = config['training']
+        self.loss_w = [float(t[k]) for k in ('rgb_weight', 'depth_weight', 'sdf_weight', 'fs_weight')]
+        self.w_dev = torch.tensor(self.loss_w, dtype=torch.float32, device=self.device).unbind(0)
+        self.n_rot = 3 if t['rot_rep'] == 'axis_angle' else 4
+        self.smooth_w = float(t['smooth_weight'])
+        self.last_losses = None                   # device [4] of the last iteration (rgb, depth, sdf, fs)
+        self.last_tv = None                       # device double [1]: raw TV sum of the last iteration
+        self.last_d_poses = None                  # [K+1,4,4] pose gradient accumulated since the last pose step
+        self._noise_calls = 0
+        bb = model.bounding_box.detach().float().cpu()
+        self._lo = (ctypes.c_float * 3)(*bb[:, 0].tolist())
+        self._ext = (ctypes.c_float * 3)(*(bb[:, 1] - bb[:, 0]).tolist())
+        self._bb = bb
+
+    # ---- host-side draws of one BA call, in the reference's order ------------------------------------------------------
+    def _draw(self, iters, bs, n_cur, n_rays, n_samples):
+        kf, every = self.kfdb, self.config['mapping']['keyframe_every']
+        t = self.config['training']
+        host_noise = self.model.spec.perturb and self.model.noise_mode == 'host'
+        noise, smooth = [], []
+        # Python-`random` and torch's CPU generator are independent streams: the index draws of all iterations go first, in the
+        # reference's order (keyframe.py:100 then coslam.py:339-341 per iteration), as ONE call of the host sampler
+        n_store = len(kf) * kf.num_rays_to_save
+        draws = sample_ranges([(n_store, bs), (kf.H * kf.W, n_cur)] * iters)
+        idx_g = [torch.from_numpy(d) for d in draws[0::2]]
+        idx_c = [torch.from_numpy(d) for d in draws[1::2]]
+        slot_g = [(kf.frame_ids[i // kf.num_rays_to_save] // every).to(torch.int64) for i in idx_g]     # keyframe.py:103, coslam.py:345
+        for _ in range(iters):
+            if host_noise:
+                noise.append(torch.rand((n_rays, n_samples)))                     # scene_rep.py:255
+            if self.smooth_w > 0:
+                vol = self._bb[:, 1] - self._bb[:, 0]
+                n = t['smooth_pts']
+                offset_max = vol - (n - 1) * t['smooth_vox'] - 2 * t['smooth_margin']
+                offset = torch.rand(3).to(offset_max) * offset_max + t['smooth_margin']              # coslam.py:260
+                smooth.append((offset, torch.rand((1, 1, 1, 3)).reshape(3)))                         # coslam.py:262
+        dev = self.device
+        up = lambda xs: torch.stack(xs).to(dev, non_blocking=True)
+        return up(idx_g), up(slot_g), up(idx_c), (up(noise) if host_noise else None), smooth
+
+    def _map_grads(self):
+        """(table.grad, [dW1..dW4]) as zero-initialised persistent buffers of the caller's parameters."""
+        fw = self.model._fused()
+        for p in fw:
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)
+        return fw[0].grad, [p.grad for p in fw[1:]]
+
+    def _adam_params(self):
+        """The map optimiser's parameters as a cb200_adam_param array (state created like coslam_b200.optim.Adam.step does);
+        every parameter must share one step count, as they do when only this class and Adam.step drive the optimiser."""
+        items, states = [], []
+        for group in self.opt.param_groups:
+            b1, b2 = group['betas']
+            for p in group['params']:
+                if p.grad is None:
+                    continue
+                st = self.opt.state[p]
+                if len(st) == 0:
+                    st['step'] = torch.zeros((), dtype=torch.float32)
+                    st['exp_avg'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    st['exp_avg_sq'] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                a = _lib.AdamParam(p.data_ptr(), p.grad.data_ptr(), st['exp_avg'].data_ptr(), st['exp_avg_sq'].data_ptr(), p.numel(),
+                                   group['lr'], b1, b2, group['eps'], group['weight_decay'])
+                items.append(a)
+                states.append(st)
+        if len({int(s['step']) for s in states}) > 1:
+            raise RuntimeError('BundleAdjuster: the map parameters have different optimiser step counts')
+        return (_lib.AdamParam * len(items))(*items), states
+
+    def _zero_map_grads(self):
+        for p in self.model._fused():
+            if p.grad is not None:
+                p.grad.zero_()
+
+    # ---- coslam.py:285-397 -----------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def run(self, kf_poses, cur_pose, current_rays):
+        """kf_poses [K,4,4]: estimated poses of the keyframes 0, every, 2 every, ... (coslam.py:299-300); cur_pose [4,4]: the
+        current frame's estimate; current_rays [H*W,7] on the device (direction, rgb, depth; coslam.py:333-334).
+        Returns (kf_poses_new [K,4,4], cur_pose_new [4,4]) -- unchanged tensors where the reference leaves them unchanged."""
+        lib, model, m, dev = _lib.load(), self.model, self.config['mapping'], self.device
+        spec = model.spec
+        kf = self.kfdb
+        iters, bs = int(m['iters']), int(m['sample'])
+        n_cur = max(bs // len(kf), int(m['min_pixels_cur']))
+        n, S = bs + n_cur, spec.n_samples
+        K = kf_poses.shape[0]
+        nr = self.n_rot
+        f32 = dict(dtype=torch.float32, device=dev)
+        # ---- pose parameters (coslam.py:305-323) -------------------------------------------------------------------------
+        optimise = len(kf) >= 2
+        optim_cur = bool(m['optim_cur'])
+        poses_all = torch.cat([kf_poses.to(dev).float(), cur_pose.to(dev).float()[None]]).contiguous()     # slot -1 = current frame
+        n_free = 0
+        if optimise:
+            free = poses_all[1:] if optim_cur else poses_all[1:K]
+            n_free = free.shape[0]
+        if n_free > 0:
+            to_param = pose.matrix_to_axis_angle if nr == 3 else pose.matrix_to_quaternion
+            rot = to_param(free[:, :3, :3].cpu()).to(dev).contiguous()                  # matrix_to_tensor on the host, like coslam.py:279
+            trans = free[:, :3, 3].clone().contiguous()
+            state = torch.zeros(2 * n_free * (nr + 3), **f32)
+            m_rot, v_rot = state[:n_free * nr], state[n_free * nr:2 * n_free * nr]
+            m_tr, v_tr = state[2 * n_free * nr:2 * n_free * nr + 3 * n_free], state[2 * n_free * nr + 3 * n_free:]
+            free_c2w = poses_all[1:1 + n_free]                                           # view: the kernels write the matrices in place
+            check(lib.cb200_pose_matrices(ptr(rot), ptr(trans), ctypes.c_int64(n_free), nr, ptr(free_c2w), stream()), 'pose_matrices')
+        d_poses = torch.zeros((K + 1, 4, 4), **f32)
+        pose_step = 0
+        # ---- buffers and the plan of the native iteration runtime (csrc/runtime.cu) ---------------------------------------
+        idx_g, slot_g, idx_c, noise, smooth = self._draw(iters, bs, n_cur, n, S)
+        slot_c = torch.full((n_cur,), -1, dtype=torch.int64, device=dev)
+        store = kf.rays[:len(kf)].reshape(-1, 7)
+        cur = current_rays.reshape(-1, 7)
+        if cur.device != dev or cur.dtype != torch.float32 or not cur.is_contiguous():
+            cur = cur.to(dev, torch.float32).contiguous()
+        rays_o, rays_d, t_rgb = (torch.empty((n, 3), **f32) for _ in range(3))
+        t_d = torch.empty((n,), **f32)
+        z = torch.empty((n, S), **f32)
+        raw, d_raw = torch.empty((n, S, 4), **f32), torch.empty((n, S, 4), **f32)
+        mask = torch.empty((n, S, 2), dtype=torch.int32, device=dev)
+        d_rays = torch.empty((2, n, 3), **f32) if n_free > 0 else None
+        ws = torch.empty(10, dtype=torch.float64, device=dev)           # 4 counts | 4 loss sums | tv sum | pad
+        loss_out = torch.empty(8, **f32)
+        fw = model._fused()
+        self._zero_map_grads()                                           # map_optimizer.zero_grad(), coslam.py:326
+        g_table, g_w = self._map_grads()
+        scene, render = spec.scene(), spec.render_cfg()
+        lin_u, lin_g, lin_n = spec.linspaces(dev)
+        lazy = ops.LAZY_FORWARD and lib.cb200_get_decoder() == 1 and ops.LAZY_MIN_POINTS <= n * S < 2 ** 32
+        keep = [idx_g, slot_g, idx_c, slot_c, noise, cur]               # referenced by raw pointer below
+        P = _lib.BaPlan()
+        dp = lambda t: t.data_ptr() if t is not None else None
+        P.scene, P.render = ctypes.addressof(scene), ctypes.addressof(render)
+        P.table = dp(fw[0])
+        P.mlp = ops._mlp_block(*fw[1:])
+        P.lin_uniform, P.lin_guided, P.lin_nodepth = dp(lin_u), dp(lin_g), dp(lin_n)
+        P.kf_rays, P.idx_global, P.slot_global, P.n_global = dp(store), dp(idx_g), dp(slot_g), bs
+        P.cur_rays, P.idx_cur, P.slot_cur, P.n_cur = dp(cur), dp(idx_c), dp(slot_c), n_cur
+        P.poses_all, P.n_poses, P.n_samples = dp(poses_all), K + 1, S
+        seeds = (ctypes.c_uint64 * iters)()
+        if noise is not None:
+            P.noise = dp(noise)
+        elif spec.perturb:
+            for it in range(iters):                                      # device Philox: one fresh seed per iteration
+                seeds[it] = model._noise(n, S, dev)[1] & (2 ** 64 - 1)
+                if model._noise_counter is not None:                     # graph-tracker mode: `_noise` hands out one constant seed and
+                    self._noise_calls += 1                               # the device counter only moves with the tracker's replays
+                    seeds[it] = (seeds[it] + (1 << 31) + self._noise_calls) & (2 ** 64 - 1)
+            if model._noise_counter is not None:
+                P.seed_dev = dp(model._noise_counter)
+        P.seeds = ctypes.cast(seeds, ctypes.c_void_p).value
+        P.rays_o, P.rays_d, P.target_rgb, P.target_d = dp(rays_o), dp(rays_d), dp(t_rgb), dp(t_d)
+        P.z_vals, P.raw, P.act_mask, P.d_raw = dp(z), dp(raw), dp(mask), dp(d_raw)
+        if lazy:
+            nbytes = int(lib.cb200_lazy_workspace(ctypes.c_int64(n), ctypes.c_int64(S)))
+            lazy_ws = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
+            P.lazy_ws, P.lazy_ws_bytes = dp(lazy_ws), nbytes
+        bbytes = int(lib.cb200_points_bwd_workspace(ctypes.c_int64(n * S)))
+        bwd_ws = torch.empty((bbytes + 3) // 4, dtype=torch.int32, device=dev)
+        P.bwd_ws, P.bwd_ws_bytes = dp(bwd_ws), bbytes
+        P.ws, P.loss_out = dp(ws), dp(loss_out)
+        P.loss_w.rgb, P.loss_w.depth, P.loss_w.sdf, P.loss_w.fs = (t_.data_ptr() for t_ in self.w_dev)
+        P.g_table = dp(g_table)
+        P.g_mlp.w_sdf0, P.g_mlp.w_sdf1, P.g_mlp.w_col0, P.g_mlp.w_col1 = (g.data_ptr() for g in g_w)
+        P.d_rays, P.d_poses = dp(d_rays), dp(d_poses)
+        if self.smooth_w > 0:                                            # coslam.py:154-158, :251-274
+            t = self.config['training']
+            n_side = int(t['smooth_pts']) - 1
+            grid = model.embed_fn.grid()
+            n_feat = model.embed_fn.n_output_dims
+            sx = torch.empty((n_side ** 3, 3), **f32)
+            sf = torch.empty((n_side ** 3, n_feat), **f32)
+            sdf_ = torch.empty_like(sf)
+            jit = (ctypes.c_float * (3 * iters))(*[v for _, j in smooth for v in j.tolist()])
+            off = (ctypes.c_float * (3 * iters))(*[v for o, _ in smooth for v in o.tolist()])
+            P.grid = ctypes.addressof(grid)
+            P.smooth_side, P.smooth_feat, P.smooth_voxel = n_side, n_feat, float(t['smooth_vox'])
+            P.smooth_grad_scale = self.smooth_w / float(int(t['smooth_pts']) ** 3)
+            P.smooth_jitter, P.smooth_offset = ctypes.cast(jit, ctypes.c_void_p).value, ctypes.cast(off, ctypes.c_void_p).value
+            P.smooth_x, P.smooth_f, P.smooth_df = dp(sx), dp(sf), dp(sdf_)
+            keep += [sx, sf, sdf_, jit, off, grid]
+        adam, states = self._adam_params()
+        P.map_params, P.n_map_params = ctypes.cast(adam, ctypes.c_void_p).value, len(adam)
+        if n_free > 0:
+            P.rot, P.trans, P.pose_adam, P.n_free, P.n_rot = dp(rot), dp(trans), dp(state), n_free, nr
+            P.lr_rot, P.lr_trans = float(m['lr_rot']), float(m['lr_trans'])
+
+        st = stream()
+        for it in range(iters):
+            map_step, zero, p_step = 0, 0, 0
+            if (it + 1) % int(m['map_accum_step']) == 0:                 # coslam.py:363-370
+                zero = 1
+                if (it + 1) > int(m['map_wait_step']):
+                    for s_ in states:
+                        s_['step'] += 1
+                    map_step = int(states[0]['step'])
+            if n_free > 0 and (it + 1) % int(m['pose_accum_step']) == 0:   # coslam.py:372-390
+                pose_step += 1
+                p_step = pose_step
+            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
+                  'ba_iteration')
+        _lib.KERNEL_LAUNCHES += iters * (17 + (3 if lazy else 0) + (4 if self.smooth_w > 0 else 0)) - iters
+        del keep
+        self.last_losses, self.last_tv, self.last_d_poses = loss_out[:4], ws[8:9], d_poses
+        # ---- coslam.py:392-397 --------------------------------------------------------------------------------------------
+        if n_free == 0:
+            return kf_poses, cur_pose
+        check(lib.cb200_pose_matrices(ptr(rot), ptr(trans), ctypes.c_int64(n_free), nr, ptr(free_c2w), stream()), 'pose_matrices')
+        new_kf = poses_all[:K].clone()
+        new_cur = poses_all[K].clone() if optim_cur else cur_pose
+        return new_kf, new_cur

@@ -208,7 +208,7 @@ def _check_weights(w1, w2, w3, w4):
 
 
 LAZY_FORWARD = True      # training forward evaluates only the sample points the step can depend on (lazy_ray_forward)
-LAZY_MIN_POINTS = 1 << 16   # below this (tracking batches) the two extra launches cost more than the skipped points save
+LAZY_MIN_POINTS = 1 << 18   # below ~7 waves of tiles (tracking / BA batches) the three extra launches cost more than the skipped points save
 
 
 def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo=False, want_mask=True, sdf_only=False,
@@ -265,8 +265,10 @@ def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True):
 
 
 def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=None, need_table=True, need_mlp=True,
-                    need_pos=True, sdf_only=False):
-    """Backward of points_forward.  Returns (d_table, (dW1..dW4), d_pts | (d_rays_o, d_rays_d))."""
+                    need_pos=True, sdf_only=False, accumulate=None):
+    """Backward of points_forward.  Returns (d_table, (dW1..dW4), d_pts | (d_rays_o, d_rays_d)).
+    accumulate = (d_table, (dW1..dW4), d_rays [2,N,3]): existing buffers the kernel adds into (any entry may be None = not
+    needed) instead of fresh zero-filled ones -- the autograd-free loops (mapping.py) keep their gradient buffers."""
     if rays is not None:
         o, d, z = rays
         n, s = z.shape
@@ -275,9 +277,16 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
         n, s = pts.shape[0], 1
         dev = pts.device
         o = d = z = None
-    d_table = torch.zeros_like(table) if need_table else None
-    d_w = None
-    gblock = None
+    if accumulate is not None:
+        d_table, d_w, d_od = accumulate
+        gblock = _mlp_block(*d_w) if d_w is not None else None
+        d_pts, d_o, d_d = None, (d_od[0] if d_od is not None else None), (d_od[1] if d_od is not None else None)
+        need_mlp = need_pos = False               # buffers are set up: skip the allocations below
+    else:
+        d_table = torch.zeros_like(table) if need_table else None
+        d_w = None
+        gblock = None
+        d_pts = d_o = d_d = None
     if need_mlp:
         flat = torch.zeros(sum(x.numel() for x in w), dtype=torch.float32, device=dev)
         d_w, off = [], 0
@@ -285,7 +294,6 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
             d_w.append(flat[off:off + x.numel()].view_as(x))
             off += x.numel()
         gblock = _mlp_block(*d_w)
-    d_pts = d_o = d_d = None
     if need_pos:
         if rays is not None:
             d_od = torch.zeros((2, n, 3), dtype=torch.float32, device=dev)

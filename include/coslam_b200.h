@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 10
+#define CB200_ABI_VERSION 12
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -182,6 +182,30 @@ typedef struct cb200_track_step {
 } cb200_track_step;
 int cb200_track_update(const cb200_track_step* step, void* stream);
 
+/* ---- bundle-adjustment glue (coslam.py:285-397 global_BA, :251-274 smoothness) -------------------------------------- */
+
+/* matrix_from_tensor for n poses (coslam.py:317, :378): rot [n, n_rot], trans [n, 3] -> c2w [n, 4, 4] */
+int cb200_pose_matrices(const float* rot, const float* trans, int64_t n_poses, int n_rot, float* c2w, void* stream);
+
+/* pose_optimizer.step() of get_pose_param_optim (coslam.py:276-283, :374): torch.optim.Adam defaults on rot / trans of n
+ * poses, gradients taken from the accumulated d_c2w [n,4,4] (cb200_assemble_rays_bwd) through the backward of
+ * optimization/utils.py:5-55; writes the matrices of the updated parameters to c2w [n,4,4]; zero_grad != 0 clears d_c2w.
+ * `step` is the 1-based optimiser step (host). */
+int cb200_pose_adam(float* rot, float* trans, float* exp_avg_rot, float* exp_avg_sq_rot, float* exp_avg_trans,
+                    float* exp_avg_sq_trans, float* d_c2w, float* c2w, int64_t n_poses, int n_rot, float lr_rot,
+                    float lr_trans, int64_t step, int zero_grad, void* stream);
+
+/* lattice of CoSLAM.smoothness (coslam.py:258-266), normalised: x [n^3, 3] = (((coords + jitter) * voxel + lo + offset) - lo)
+ * / ext with torch's operation order; jitter / offset / bb_lo / bb_ext are HOST arrays of 3 floats. */
+int cb200_smooth_points(int64_t n_side, float voxel, const float* jitter, const float* offset, const float* bb_lo,
+                        const float* bb_ext, float* x, void* stream);
+
+/* total variation of the lattice features (coslam.py:268-270): f [n,n,n,F] (cb200_hash_fwd on the lattice) ->
+ * tv_sum (double, +=, may be NULL) = tv_x + tv_y + tv_z,  d_f [n,n,n,F] (=) = grad_scale * d tv / d f.
+ * The caller passes grad_scale = smooth_weight / smooth_pts^3 and feeds d_f to cb200_hash_bwd. */
+int cb200_smooth_tv(const float* f, int64_t n_side, int64_t n_feat, float grad_scale, float* d_f, double* tv_sum,
+                    void* stream);
+
 /* ---- upper boundary: the fused JointEncoding path -------------------------------------------------------- */
 
 /* render_rays sampling (model/scene_rep.py:227-255) + the mask counts of get_masks (model/utils.py:103-115)
@@ -278,6 +302,92 @@ typedef struct cb200_loss_grads {
 int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb,
                      const float* target_d, int64_t n_rays, int64_t n_samples, const cb200_loss_grads* g_loss,
                      const float* coef, const float* g_rgb, const float* g_depth, float* d_raw, void* stream);
+
+/* ---- native iteration runtime of global_BA (coslam.py:336-390) ------------------------------------------------------ */
+
+typedef struct cb200_adam_param {
+    float* param;
+    float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int64_t n;
+    float lr, beta1, beta2, eps, weight_decay;
+} cb200_adam_param;
+
+/* Everything one bundle-adjustment call needs, set up once by the host; cb200_ba_iteration then issues all launches of
+ * iteration `it` (ray assembly from the keyframe store and the current frame, sampling, per-point forward -- lazily when
+ * lazy_ws is given --, rendering + losses, backward into the gradient buffers, pose-gradient segment sums, the smoothness
+ * term, and the optimiser steps that are due) on `stream` without touching the host again.  All pointers are device memory
+ * unless marked HOST. */
+typedef struct cb200_ba_plan {
+    const cb200_scene* scene;          /* HOST */
+    const cb200_render_cfg* render;    /* HOST */
+    const cb200_grid* grid;            /* HOST: geometry of the hash grid for the smoothness term */
+    const float* table;
+    cb200_mlp mlp;
+    const float *lin_uniform, *lin_guided, *lin_nodepth;
+    /* rays */
+    const float* kf_rays;              /* [M,7] keyframe store */
+    const int64_t* idx_global;         /* [iters, n_global] rows of kf_rays */
+    const int64_t* slot_global;        /* [iters, n_global] keyframe slots */
+    int64_t n_global;
+    const float* cur_rays;             /* [H*W,7] current frame */
+    const int64_t* idx_cur;            /* [iters, n_cur] */
+    const int64_t* slot_cur;           /* [n_cur], all -1 */
+    int64_t n_cur;
+    float* poses_all;                  /* [n_poses,4,4] */
+    int64_t n_poses;
+    int64_t n_samples;
+    const float* noise;                /* [iters, N, S] host-drawn jitter, or NULL: device Philox with seeds[it] */
+    const uint64_t* seeds;             /* HOST [iters] */
+    const uint64_t* seed_dev;          /* optional device counter added to the seed */
+    /* per-iteration buffers, N = n_global + n_cur */
+    float *rays_o, *rays_d, *target_rgb, *target_d;      /* [N,3] x3, [N] */
+    float* z_vals;                     /* [N,S] */
+    float* raw;                        /* [N,S,4] */
+    uint32_t* act_mask;                /* [N,S,2] */
+    float* d_raw;                      /* [N,S,4] */
+    void* lazy_ws;                     /* cb200_lazy_workspace bytes, or NULL: plain forward */
+    size_t lazy_ws_bytes;
+    void* bwd_ws;                      /* cb200_points_bwd_workspace bytes */
+    size_t bwd_ws_bytes;
+    double* ws;                        /* [10]: 4 int64 counts | 4 loss sums | tv sum | pad */
+    float* loss_out;                   /* [8]: 4 losses | 4 d loss / d sum */
+    cb200_loss_grads loss_w;           /* device scalars: the four loss weights */
+    /* gradients */
+    float* g_table;
+    cb200_mlp_grad g_mlp;
+    float* d_rays;                     /* [2,N,3], or NULL when no pose is optimised */
+    float* d_poses;                    /* [n_poses,4,4] accumulated between pose steps */
+    /* smoothness (coslam.py:251-274); n_side == 0 disables it */
+    int64_t smooth_side, smooth_feat;
+    float smooth_voxel, smooth_grad_scale;
+    const float* smooth_jitter;        /* HOST [iters,3] */
+    const float* smooth_offset;        /* HOST [iters,3] */
+    float *smooth_x, *smooth_f, *smooth_df;
+    /* optimisers */
+    const cb200_adam_param* map_params;   /* HOST [n_map_params] */
+    int64_t n_map_params;
+    float *rot, *trans, *pose_adam;    /* [n_free, n_rot], [n_free,3], Adam state [2 n_free (n_rot + 3)] as in mapping.py */
+    int64_t n_free;
+    int32_t n_rot;
+    float lr_rot, lr_trans;
+} cb200_ba_plan;
+
+/* map_step / pose_step: 1-based optimiser step to take after this iteration's backward, 0 = none;
+ * zero_map_grads != 0 clears the map gradients afterwards (map_optimizer.zero_grad(), coslam.py:370). */
+int cb200_ba_iteration(const cb200_ba_plan* plan, int64_t it, int64_t map_step, int zero_map_grads, int64_t pose_step,
+                       void* stream);
+
+/* HOST: `random.sample(range(n[d]), k[d])` for d = 0 .. n_draws-1 with CPython's exact algorithm (Lib/random.py sample /
+ * _randbelow_with_getrandbits over the MT19937 of Modules/_randommodule.c), replacing the reference's Python-level draws of
+ * model/keyframe.py:45-46, :100 and coslam.py:131-138, :339-341.  state [625]: the generator state of `random.getstate()[1]`
+ * (624 words + position), updated in place; out: the samples, concatenated.  Requires n < 2^32.  No CUDA involved. */
+int cb200_host_random_sample(uint32_t* state, int64_t n_draws, const int64_t* n, const int64_t* k, int64_t* out);
+
+/* sizeof of the host structs above, for the bindings' layout self-check: 0 = cb200_ba_plan, 1 = cb200_track_step,
+ * 2 = cb200_adam_param */
+size_t cb200_sizeof(int which);
 
 /* test hook for the bit-exact sample-position gate: pts [P,3] and normalised x [P,3] exactly as the fused
  * kernels compute them (model/scene_rep.py:258 and :186) */

@@ -722,6 +722,7 @@ def test_lazy_forward_is_exact(cfg_name, kind):
         o = rays_o.to(DEV).requires_grad_(True)
         d = rays_d.to(DEV).requires_grad_(True)
         ops.LAZY_FORWARD = lazy
+        min_points, ops.LAZY_MIN_POINTS = ops.LAZY_MIN_POINTS, 1      # the size threshold is a tuning choice, not a precondition
         try:
             torch.manual_seed(3)
             ops.KEEP_LAST_MASK = True
@@ -731,6 +732,7 @@ def test_lazy_forward_is_exact(cfg_name, kind):
             _weighted_loss(cfg, ret).backward()
         finally:
             ops.LAZY_FORWARD = True
+            ops.LAZY_MIN_POINTS = min_points
             ops.KEEP_LAST_MASK = False
         res[lazy] = (ret, o.grad, d.grad, model.embed_fn.params.grad, [w.grad for w in model.decoder.fused_weights()], evaluated)
     a, b = res[True], res[False]

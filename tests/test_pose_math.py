@@ -129,3 +129,29 @@ def test_package_pose_helpers_match_reference_and_roundtrip():
     ro_ref = c2w[..., :3, -1].repeat(50, 1)
     rd_ref = torch.sum(dir_cam[..., None, :] * c2w[:, :3, :3], -1)
     assert torch.equal(ro, ro_ref) and torch.equal(rd, rd_ref)
+
+
+def test_sample_range_is_random_sample_bit_for_bit():
+    """coslam_b200.keyframe.sample_range: the vectorised `random.sample(range(n), k)` (model/keyframe.py:45-46, :100;
+    coslam.py:131-138, :339-341) -- same values, same order, same generator state afterwards -- over the population / sample
+    sizes of the shipped configs, powers of two (acceptance 1/2), tiny populations (pool branch) and near-exhaustive draws."""
+    import random
+    from coslam_b200.keyframe import sample_range
+    cases = [(816000, 2048), (816000, 40800), (816000, 100), (40800 * 7, 2048), (40800 * 401, 2048), (1 << 16, 1000), ((1 << 16) + 1, 1000),
+             (285200, 14260), (5000, 4990), (100, 7), (30, 20), (16405, 2048), (16406, 2048), (1, 1), (9, 0), (768, 300)]
+    for seed, (n, k) in enumerate(cases):
+        random.seed(100 + seed)
+        for _ in range(seed % 3):
+            random.random()                                   # start from a state in the middle of a block of 624
+        state = random.getstate()
+        want = random.sample(range(n), k)
+        after = [random.random(), random.getrandbits(17), random.sample(range(1000), 5)]
+        random.setstate(state)
+        got = sample_range(n, k)
+        assert got.dtype.kind == 'i' and got.tolist() == want, (n, k)
+        assert [random.random(), random.getrandbits(17), random.sample(range(1000), 5)] == after, (n, k)
+    # consecutive calls chain exactly like consecutive random.sample calls
+    random.seed(7)
+    want = [random.sample(range(326400), 2048) for _ in range(5)]
+    random.seed(7)
+    assert [sample_range(326400, 2048).tolist() for _ in range(5)] == want

@@ -71,6 +71,12 @@ def _oracle_slam_class():
         def make_tracker(self):
             return None
 
+        def make_bundle_adjuster(self):
+            return None
+
+        def sample_pixels(self, n, k):                                                    # coslam.py:131-138
+            return torch.tensor(random.sample(range(n), k), device=self.dev)
+
         def track_pose(self, d_cam, rgb, depth, c2w_init):                                # coslam.py:526-573
             t = self.cfg['tracking']
             c2w0 = c2w_init[None]

@@ -99,6 +99,7 @@ class SynthSLAM(object):
         n_kf = n_frames // m['keyframe_every'] + 2
         self.kfdb = self.make_kfdb(n_kf, int(self.H * self.W * m['n_pixels']))
         self.tracker = self.make_tracker()
+        self.adjuster = self.make_bundle_adjuster()
         self.est, self.est_rel = {}, {}
         self.t_track, self.t_map, self.n_map_iters = [], [], 0
 
@@ -119,6 +120,18 @@ class SynthSLAM(object):
 
     def make_tracker(self):
         return FrameTracker(self.model, self.cfg, device=self.dev, use_graph=self.noise == 'device')
+
+    def make_bundle_adjuster(self):
+        """The autograd-free BA of coslam_b200/mapping.py (None: the torch-autograd loop below, which the oracle arm uses)."""
+        if os.environ.get('COSLAM_B200_AUTOGRAD_BA'):
+            return None
+        from coslam_b200.mapping import BundleAdjuster
+        return BundleAdjuster(self.model, self.cfg, self.kfdb, self.map_optimizer, self.dev)
+
+    def sample_pixels(self, n, k):
+        """select_samples (coslam.py:131-138): `random.sample(range(n), k)`, drawn by the library's host sampler (bit-identical)."""
+        from coslam_b200.keyframe import sample_range
+        return torch.from_numpy(sample_range(n, k)).to(self.dev)
 
     def track_pose(self, d_cam, rgb, depth, c2w_init):
         return self.tracker.track(d_cam, rgb, depth, c2w_init)[0]
@@ -161,7 +174,7 @@ class SynthSLAM(object):
         n = self.cfg['mapping']['sample']
         for _ in range(n_iters):
             self.map_optimizer.zero_grad()
-            idx = torch.tensor(random.sample(range(self.H * self.W), n), device=self.dev)
+            idx = self.sample_pixels(self.H * self.W, n)
             d_cam, rgb, depth = self.pixels(frame, idx)
             rays_o, rays_d = pose.rays_from_pose(d_cam, c2w)
             self.loss(self.model.forward(rays_o, rays_d, rgb, depth)).backward()
@@ -176,7 +189,7 @@ class SynthSLAM(object):
     def track(self, frame, i):                                      # coslam.py:502-573
         t = self.cfg['tracking']
         iH, iW = t['ignore_edge_H'], t['ignore_edge_W']
-        idx = torch.tensor(random.sample(range((self.H - 2 * iH) * (self.W - 2 * iW)), t['sample']), device=self.dev)
+        idx = self.sample_pixels((self.H - 2 * iH) * (self.W - 2 * iW), t['sample'])
         d_cam, rgb, depth = self.pixels(frame, idx, iH, iW, self.H - 2 * iH)
         t0 = time.perf_counter()
         self.est[i] = self.track_pose(d_cam, rgb, depth, self.predict_pose(i)).detach().clone()
@@ -191,6 +204,18 @@ class SynthSLAM(object):
         every = m['keyframe_every']
         kf_ids = list(range(0, cur, every))
         poses = torch.stack([self.est[k] for k in kf_ids])
+        if self.adjuster is not None:
+            current = torch.cat([frame['direction'], frame['rgb'], frame['depth'][..., None]], -1).reshape(-1, 7)
+            self.sync()
+            t0 = time.perf_counter()
+            new_kf, new_cur = self.adjuster.run(poses, self.est[cur], current)
+            self.sync()
+            self.t_map.append(time.perf_counter() - t0)
+            self.n_map_iters += m['iters']
+            for j, k in enumerate(kf_ids):
+                self.est[k] = new_kf[j].clone()
+            self.est[cur] = new_cur.clone()
+            return
         fixed = poses[:1]
         rot = trans = pose_opt = None
         if len(self.kfdb) >= 2:
