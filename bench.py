@@ -269,6 +269,8 @@ def run_ours(args):
     extra = {}
     if rank == 0 and (args.tracking or world == 1) and not args.no_tracking:
         extra['tracking'] = time_tracking(model, cfg, dev)
+        if cfg['grid']['oneGrid'] and cfg['training']['n_importance'] == 0:
+            extra['mapping'] = time_mapping(model, cfg, dev)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -334,8 +336,9 @@ def time_tracking(model, cfg, dev, frames=20):
     c2w0 = pose.pose_matrix(torch.tensor([[0.3, -0.5, 0.2]]), bound.mean(1)[None])[0]
     out = {'rays': n_rays, 'iters': int(cfg['tracking']['iter'])}
     noise_state = (model.noise_mode, model._noise_counter)
-    for name, use_graph in (('graph', True), ('eager', False)):
-        tr = FrameTracker(model, cfg, device=dev, use_graph=use_graph)
+    fusable = bool(cfg['grid']['oneGrid']) and cfg['training']['n_importance'] == 0
+    for name, use_graph, fused in (('graph', True, None), ('eager', False, None)) + ((('autograd_graph', True, False),) if fusable else ()):
+        tr = FrameTracker(model, cfg, device=dev, use_graph=use_graph, fused=fused)
         for _ in range(3):
             tr.track(dir_cam, rgb, depth, c2w0)[0].cpu()
         torch.cuda.synchronize()
@@ -346,6 +349,53 @@ def time_tracking(model, cfg, dev, frames=20):
     model.noise_mode, model._noise_counter = noise_state
     out['ms_per_frame'] = out['ms_per_frame_graph']
     return out
+
+
+def time_mapping(model, cfg, dev, n_kf=8, calls=5):
+    """Mapping ms/iteration (BASELINE.json configs 2-3: "mapping iters/sec"): global_BA (coslam.py:285-397) over a synthetic
+    keyframe store of `n_kf` keyframes x `mapping.n_pixels` H W rays, `mapping.sample` + current-frame rays per iteration,
+    `mapping.iters` iterations per call, through coslam_b200.mapping.BundleAdjuster (no autograd, one native call per
+    iteration; host-side index draws bit-identical to the reference's `random.sample`).  Runs on a copy of the model."""
+    import copy
+    import random
+    from coslam_b200 import optim as cb_optim
+    from coslam_b200 import pose
+    from coslam_b200.keyframe import KeyFrameDatabase
+    from coslam_b200.mapping import BundleAdjuster
+    model = copy.deepcopy(model)
+    model.noise_mode, model._noise_counter = 'device', None
+    m, cam = cfg['mapping'], cfg['cam']
+    H, W = cam['H'], cam['W']
+    R = int(H * W * m['n_pixels'])
+    g = torch.Generator().manual_seed(9)
+    bound = synth.bound_tensor(cfg)
+    centre, ext = bound.mean(1), bound[:, 1] - bound[:, 0]
+    dirs = synth.camera_ray_dirs(H, W, cam['fx'], cam['fy'], cam['cx'], cam['cy']).to(dev)
+    db = KeyFrameDatabase(cfg, H, W, n_kf + 1, R, dev)
+    poses = []
+    random.seed(9)
+    for k in range(n_kf + 1):
+        r = torch.randn(1, 3, generator=g)
+        poses.append(pose.pose_matrix(r / r.norm() * (0.2 + 0.02 * k), (centre + 0.1 * ext * (torch.rand(3, generator=g) - 0.5))[None])[0])
+        batch = {'direction': dirs[None], 'rgb': torch.rand(1, H, W, 3, generator=g).to(dev),
+                 'depth': (torch.rand(1, H, W, generator=g) * 3.0 + 0.5).to(dev), 'frame_id': torch.tensor([k * m['keyframe_every']])}
+        if k < n_kf:
+            db.add_keyframe(batch)
+    current = torch.cat([batch['direction'], batch['rgb'], batch['depth'][..., None]], -1).reshape(-1, 7)
+    kf_poses, cur_pose = torch.stack(poses[:n_kf]).to(dev), poses[n_kf].to(dev)
+    opt = cb_optim.Adam([{'params': model.decoder.parameters(), 'weight_decay': 1e-6, 'lr': m['lr_decoder']},
+                         {'params': model.embed_fn.parameters(), 'eps': 1e-15, 'lr': m['lr_embed']}], betas=(0.9, 0.99))
+    ba = BundleAdjuster(model, cfg, db, opt, dev)
+    for _ in range(2):
+        ba.run(kf_poses, cur_pose, current)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(calls):
+        ba.run(kf_poses, cur_pose, current)[0].cpu()              # the updated poses are read back every call
+    ms = (time.perf_counter() - t0) * 1e3 / (calls * m['iters'])
+    n_rays = m['sample'] + max(m['sample'] // n_kf, m['min_pixels_cur'])
+    return {'keyframes': n_kf, 'rays': n_rays, 'iters_per_call': m['iters'], 'ms_per_iter': ms, 'iters_per_s': 1e3 / ms,
+            'smoothness_points': (cfg['training']['smooth_pts'] - 1) ** 3 if cfg['training']['smooth_weight'] > 0 else 0}
 
 
 if __name__ == '__main__':

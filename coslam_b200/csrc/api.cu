@@ -219,6 +219,18 @@ int cb200_track_update(const cb200_track_step* s, void* stream) {
     return cuda_result(cb200::launch_track_update(*s, (cudaStream_t)stream), "track_update");
 }
 
+int cb200_adam_multi(const cb200_adam_param* params, int64_t n_params, int64_t step, int zero_grad, void* stream) {
+    CB_REQUIRE(n_params >= 0 && n_params <= 64, "adam_multi: bad tensor count");
+    if (n_params == 0) return 0;
+    CB_REQUIRE(params != nullptr && step >= 1, "adam_multi: NULL list or step < 1");
+    for (int64_t i = 0; i < n_params; ++i) {
+        const cb200_adam_param& q = params[i];
+        CB_REQUIRE(q.n >= 0 && (q.n == 0 || (q.param && q.grad && q.exp_avg && q.exp_avg_sq)), "adam_multi: NULL buffer in tensor %lld", (long long)i);
+        CB_REQUIRE(q.beta1 >= 0.f && q.beta1 < 1.f && q.beta2 >= 0.f && q.beta2 < 1.f && q.eps >= 0.f, "adam_multi: bad hyper-parameters");
+    }
+    return cuda_result(cb200::launch_adam_multi(params, (int)n_params, step, zero_grad, (cudaStream_t)stream), "adam_multi");
+}
+
 int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const float* lin_uniform, const float* lin_guided,
                       const float* lin_nodepth, const float* noise, uint64_t seed, const uint64_t* seed_dev, int64_t n_rays, float* z_vals,
                       int64_t* counts, void* stream) {

@@ -59,6 +59,63 @@ __global__ void __launch_bounds__(256) adam_step_kernel(AdamArgs a) {
     }
 }
 
+// The same update for up to 8 parameter tensors in one launch (map optimiser: hash table + four decoder matrices; the four
+// matrices alone are launch-bound as separate kernels).  Blocks are assigned to tensors by a prefix table.
+constexpr int kAdamMulti = 8;
+struct AdamMultiArgs {
+    cb200_adam_param p[kAdamMulti];
+    int block_end[kAdamMulti];     // exclusive prefix of blocks per tensor
+    int n;
+    int64_t step;
+    int zero_grad;
+};
+
+__global__ void __launch_bounds__(256) adam_multi_kernel(AdamMultiArgs a) {
+    int t = 0;
+    while (t < a.n - 1 && (int)blockIdx.x >= a.block_end[t]) ++t;
+    const cb200_adam_param& q = a.p[t];
+    const int first = t == 0 ? 0 : a.block_end[t - 1];
+    const int64_t nblk = a.block_end[t] - first;
+    const double bc1 = 1.0 - pow((double)q.beta1, (double)a.step);
+    const double bc2 = 1.0 - pow((double)q.beta2, (double)a.step);
+    const float step_size = (float)((double)q.lr / bc1);
+    const float inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+    const float one_m_b1 = 1.f - q.beta1, one_m_b2 = 1.f - q.beta2;
+    for (int64_t i = ((int64_t)blockIdx.x - first) * blockDim.x + threadIdx.x; i < q.n; i += nblk * blockDim.x) {
+        float p = q.param[i], g = q.grad[i], m = q.exp_avg[i], v = q.exp_avg_sq[i];
+        const float gr = q.weight_decay != 0.f ? fmaf(q.weight_decay, p, g) : g;
+        m = fmaf(one_m_b1, gr - m, m);
+        v = fmaf(one_m_b2 * gr, gr, q.beta2 * v);
+        const float denom = fmaf(sqrtf(v), inv_sqrt_bc2, q.eps);
+        q.param[i] = p - step_size * (m / denom);
+        q.exp_avg[i] = m;
+        q.exp_avg_sq[i] = v;
+        if (a.zero_grad) q.grad[i] = 0.f;
+    }
+}
+
+cudaError_t launch_adam_multi(const cb200_adam_param* params, int n, int64_t step, int zero_grad, cudaStream_t st) {
+    for (int base = 0; base < n; base += kAdamMulti) {
+        AdamMultiArgs a{};
+        a.n = n - base < kAdamMulti ? n - base : kAdamMulti;
+        a.step = step;
+        a.zero_grad = zero_grad;
+        int blocks = 0;
+        for (int t = 0; t < a.n; ++t) {
+            a.p[t] = params[base + t];
+            int64_t b = (a.p[t].n + 1023) / 1024;                 // 4 elements per thread
+            if (b < 1) b = 1;
+            if (b > 148 * 8) b = 148 * 8;
+            blocks += (int)b;
+            a.block_end[t] = blocks;
+        }
+        adam_multi_kernel<<<blocks, 256, 0, st>>>(a);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
 cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                              float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, cudaStream_t st) {
     AdamArgs a{p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, step_dev, step, zero_grad};

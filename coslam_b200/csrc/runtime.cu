@@ -89,14 +89,11 @@ extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t ma
         CB_TRY(cb200_hash_bwd(p->grid, p->smooth_x, p->table, p->smooth_df, m, p->g_table, nullptr, stream));
     }
     // ---- optimisers (coslam.py:363-390) -----------------------------------------------------------------------------------
-    for (int64_t k = 0; k < p->n_map_params; ++k) {
-        const cb200_adam_param& a = p->map_params[k];
-        if (map_step > 0) {
-            CB_TRY(cb200_adam_step(a.param, a.grad, a.exp_avg, a.exp_avg_sq, a.n, a.lr, a.beta1, a.beta2, a.eps, a.weight_decay, nullptr, map_step,
-                                   zero_map_grads ? 1 : 0, stream));
-        } else if (zero_map_grads) {
-            CB_TRY(cuda_rc(cudaMemsetAsync(a.grad, 0, sizeof(float) * a.n, st)));
-        }
+    if (map_step > 0) {
+        CB_TRY(cb200_adam_multi(p->map_params, p->n_map_params, map_step, zero_map_grads ? 1 : 0, stream));
+    } else if (zero_map_grads) {
+        for (int64_t k = 0; k < p->n_map_params; ++k)
+            CB_TRY(cuda_rc(cudaMemsetAsync(p->map_params[k].grad, 0, sizeof(float) * p->map_params[k].n, st)));
     }
     if (pose_step > 0 && p->n_free > 0) {
         const int64_t nf = p->n_free, nr = p->n_rot;

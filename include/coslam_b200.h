@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 12
+#define CB200_ABI_VERSION 13
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -313,6 +313,9 @@ typedef struct cb200_adam_param {
     int64_t n;
     float lr, beta1, beta2, eps, weight_decay;
 } cb200_adam_param;
+
+/* cb200_adam_step for several parameter tensors in ONE launch (HOST array of descriptors; all share the 1-based `step`) */
+int cb200_adam_multi(const cb200_adam_param* params, int64_t n_params, int64_t step, int zero_grad, void* stream);
 
 /* Everything one bundle-adjustment call needs, set up once by the host; cb200_ba_iteration then issues all launches of
  * iteration `it` (ray assembly from the keyframe store and the current frame, sampling, per-point forward -- lazily when
