@@ -32,8 +32,8 @@ UNIT = 'rays/s'
 BYTES_PER_POINT_FWD = 1024          # 16 levels x 8 corners x 8 B gathered           
 BYTES_PER_POINT_BWD = 2048          # the same gathers again for dL/dx + 1024 B of gradient scattered to the table
 # dram__bytes_read.sum + dram__bytes_write.sum of points_bwd_tc_kernel<wgrad> per point, from the ncu --set full capture in
-# profiles/r1/ncu_full_v5_tc.txt (51.32 MB + 0.30 MB over 1 409 024 points): the table is L2-resident, HBM sees the per-point streams.
-NCU_DRAM_BYTES_PER_POINT_BWD = 36.63
+# profiles/r1/ncu_full_v9_tc.txt (51.32 MB + 0.30 MB over 1 409 024 points): the table is L2-resident, HBM sees the per-point streams.
+NCU_DRAM_BYTES_PER_POINT_BWD = 28.87     # (316.86 MB read + 8.59 MB written) / 11 272 192 points
 
 
 def parse():
@@ -304,7 +304,7 @@ def run_ours(args):
             'gpu_launches': launches,
             'roofline': {'bound': 'hbm', 'kernel': 'points_bwd_tc_kernel<wgrad>' if tc else 'points_bwd_kernel<wgrad>', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak, 'traffic': P * NCU_DRAM_BYTES_PER_POINT_BWD if tc else None,
-                         'traffic_source': 'ncu dram bytes per point (profiles/r1/ncu_full_v5_tc.txt) x points per launch', 'peak_source': 'measured' if peaks else 'fallback',
+                         'traffic_source': 'ncu dram bytes per point (profiles/r1/ncu_full_v9_tc.txt) x points per launch', 'peak_source': 'measured' if peaks else 'fallback',
                          'algorithmic_bytes_per_launch': bwd_bytes, 'live_point_fraction': live_frac, 'avg_launch_ms': k_bwd,
                          'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
                                         'evaluated_point_fraction': eval_frac,

@@ -242,44 +242,49 @@ __global__ void __launch_bounds__(256) smooth_points_kernel(int n, float vox, fl
 
 __global__ void track_update_kernel(cb200_track_step s) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    const float lv = s.loss_w[0] * s.losses[0] + s.loss_w[1] * s.losses[1] + s.loss_w[2] * s.losses[2] + s.loss_w[3] * s.losses[3];
+    // every input first, into registers: the buffers may alias as far as the compiler knows, so loads interleaved with the
+    // stores below would each wait for the previous store (a chain of ~20 dependent global round trips)
+    const float l0 = s.losses[0], l1 = s.losses[1], l2 = s.losses[2], l3 = s.losses[3];
     bool alive = *s.alive != 0;
+    const float best_in = *s.best_loss;
+    int64_t patience = *s.patience;
+    const int64_t t = *s.step + 1;
+    const int nr = s.n_rot;
+    float c2w[16], g[12], rot[4], trans[3], ad[14];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) c2w[i] = s.c2w[i];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) g[i] = s.d_c2w[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) rot[i] = i < nr ? s.rot[i] : 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) trans[i] = s.trans[i];
+#pragma unroll
+    for (int i = 0; i < 14; ++i) ad[i] = i < 2 * nr + 6 ? s.adam[i] : 0.f;
+
+    const float lv = s.loss_w[0] * l0 + s.loss_w[1] * l1 + s.loss_w[2] * l2 + s.loss_w[3] * l3;
     const bool keep = alive;                       // the loop was still running when this iteration rendered
     // ---- best / last bookkeeping (coslam.py:552-566) ----------------------------------------------------------------------
+    bool new_best;
     if (s.first_iter) {
-        *s.best_loss = lv;
-        for (int i = 0; i < 16; ++i) s.best_c2w[i] = s.c2w[i];
-        *s.patience = 1;
+        new_best = true;
+        patience = 1;
     } else {
-        const bool better = lv < *s.best_loss && alive;
-        if (better) {
-            *s.best_loss = lv;
-            for (int i = 0; i < 16; ++i) s.best_c2w[i] = s.c2w[i];
-        }
-        if (s.may_stop && alive) *s.patience = better ? 0 : *s.patience + 1;
+        new_best = lv < best_in && alive;
+        if (s.may_stop && alive) patience = new_best ? 0 : patience + 1;
     }
-    if (!s.may_stop || keep) {
-        for (int i = 0; i < 16; ++i) s.last_c2w[i] = s.c2w[i];
-        *s.last_loss = lv;
-    }
-    if (s.psnr) *s.psnr = -10.f * logf(s.losses[0] + 1e-6f) / logf(10.f);      // mse2psnr, model/utils.py:8-12
-    if (s.loss) *s.loss = lv;
-    if (s.may_stop) {
-        alive = alive && (*s.patience <= (int64_t)s.wait_iters);                // coslam.py:565-566: break before the update
-        *s.alive = alive ? 1 : 0;
-    }
+    if (s.may_stop) alive = alive && (patience <= (int64_t)s.wait_iters);      // coslam.py:565-566: break before the update
     // ---- dL/d(rot, trans) from dL/d c2w -----------------------------------------------------------------------------------
     Dual R[9];
-    rotation_dual(s.rot, s.n_rot, R);
+    rotation_dual(rot, nr, R);
     float g_rot[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
     for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) {
-            const float g = s.d_c2w[i * 4 + j];
-            for (int k = 0; k < s.n_rot; ++k) g_rot[k] = fmaf(g, R[i * 3 + j].d[k], g_rot[k]);
-        }
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) g_rot[k] = fmaf(g[i * 4 + j], R[i * 3 + j].d[k], g_rot[k]);      // d[k] = 0 for k >= n_rot
     // ---- Adam (skipped for the parameters once the loop has stopped) --------------------------------------------------------
-    const int64_t t = *s.step + 1;
-    *s.step = t;
     double b1t = 1.0, b2t = 1.0;                 // beta^t by repeated multiplication (a tracking loop runs 10-20 steps)
     if (t <= 64) {
         for (int64_t i = 0; i < t; ++i) { b1t *= 0.9; b2t *= 0.999; }
@@ -290,16 +295,33 @@ __global__ void track_update_kernel(cb200_track_step s) {
     const double bc1 = 1.0 - b1t, bc2 = 1.0 - b2t;
     const float inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
     const float ss_rot = (float)((double)s.lr_rot / bc1), ss_trans = (float)((double)s.lr_trans / bc1);
-    float* m_rot = s.adam;
-    float* v_rot = s.adam + s.n_rot;
-    float* m_tr = s.adam + 2 * s.n_rot;
+    float* m_rot = ad;
+    float* v_rot = ad + nr;
+    float* m_tr = ad + 2 * nr;
     float* v_tr = m_tr + 3;
-    for (int k = 0; k < s.n_rot; ++k) adam_scalar(s.rot[k], g_rot[k], m_rot[k], v_rot[k], ss_rot, inv_sqrt_bc2, alive);
-    for (int k = 0; k < 3; ++k) adam_scalar(s.trans[k], s.d_c2w[k * 4 + 3], m_tr[k], v_tr[k], ss_trans, inv_sqrt_bc2, alive);
-    if (s.g_rot_out) for (int k = 0; k < s.n_rot; ++k) s.g_rot_out[k] = g_rot[k];
+    for (int k = 0; k < nr; ++k) adam_scalar(rot[k], g_rot[k], m_rot[k], v_rot[k], ss_rot, inv_sqrt_bc2, alive);
+    for (int k = 0; k < 3; ++k) adam_scalar(trans[k], g[k * 4 + 3], m_tr[k], v_tr[k], ss_trans, inv_sqrt_bc2, alive);
     // ---- pose of the updated parameters -----------------------------------------------------------------------------------
-    rotation_dual(s.rot, s.n_rot, R);
-    write_c2w(R, s.trans, s.c2w);
+    rotation_dual(rot, nr, R);
+    // ---- all outputs ------------------------------------------------------------------------------------------------------
+    if (new_best) {
+        *s.best_loss = lv;
+        for (int i = 0; i < 16; ++i) s.best_c2w[i] = c2w[i];
+    }
+    if (!s.may_stop || keep) {
+        for (int i = 0; i < 16; ++i) s.last_c2w[i] = c2w[i];
+        *s.last_loss = lv;
+    }
+    *s.patience = patience;
+    if (s.may_stop) *s.alive = alive ? 1 : 0;
+    if (s.psnr) *s.psnr = -10.f * logf(l0 + 1e-6f) / logf(10.f);      // mse2psnr, model/utils.py:8-12
+    if (s.loss) *s.loss = lv;
+    *s.step = t;
+    for (int k = 0; k < nr; ++k) s.rot[k] = rot[k];
+    for (int k = 0; k < 3; ++k) s.trans[k] = trans[k];
+    for (int k = 0; k < 2 * nr + 6; ++k) s.adam[k] = ad[k];
+    if (s.g_rot_out) for (int k = 0; k < nr; ++k) s.g_rot_out[k] = g_rot[k];
+    write_c2w(R, trans, s.c2w);
 }
 
 }  // namespace
