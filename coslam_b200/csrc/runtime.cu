@@ -43,8 +43,9 @@ extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t ma
     double* sums = p->ws + 4;
 
     // ---- rays (coslam.py:336-355) -------------------------------------------------------------------------------------
-    CB_TRY(cb200_assemble_rays_fwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->poses_all, p->n_global,
-                                   p->n_poses, p->rays_o, p->rays_d, p->target_rgb, p->target_d, stream));
+    if (p->n_global > 0)
+        CB_TRY(cb200_assemble_rays_fwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->poses_all,
+                                       p->n_global, p->n_poses, p->rays_o, p->rays_d, p->target_rgb, p->target_d, stream));
     const int64_t g = p->n_global;
     CB_TRY(cb200_assemble_rays_fwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->poses_all, p->n_cur, p->n_poses, p->rays_o + 3 * g,
                                    p->rays_d + 3 * g, p->target_rgb + 3 * g, p->target_d + g, stream));
@@ -74,8 +75,9 @@ extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t ma
     CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask, p->g_table,
                             &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes, stream));
     if (p->d_rays) {
-        CB_TRY(cb200_assemble_rays_bwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->d_rays,
-                                       p->d_rays + 3 * n, p->n_global, p->n_poses, p->d_poses, stream));
+        if (p->n_global > 0)
+            CB_TRY(cb200_assemble_rays_bwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->d_rays,
+                                           p->d_rays + 3 * n, p->n_global, p->n_poses, p->d_poses, stream));
         CB_TRY(cb200_assemble_rays_bwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->d_rays + 3 * g, p->d_rays + 3 * n + 3 * g, p->n_cur,
                                        p->n_poses, p->d_poses, stream));
     }

@@ -50,11 +50,21 @@ class BundleAdjuster(object):
         self._bb = bb
 
     # ---- host-side draws of one BA call, in the reference's order ------------------------------------------------------
-    def _draw(self, iters, bs, n_cur, n_rays, n_samples):
+    def _draw(self, iters, bs, n_cur, n_rays, n_samples, smooth_on=True):
         kf, every = self.kfdb, self.config['mapping']['keyframe_every']
         t = self.config['training']
         host_noise = self.model.spec.perturb and self.model.noise_mode == 'host'
         noise, smooth = [], []
+        if bs == 0:
+            # first-frame mapping (coslam.py:183-189): select_samples draws i in range(H W) and reads pixel (i % H, i // H)
+            draws = sample_ranges([(kf.H * kf.W, n_cur)] * iters)
+            idx_c = [torch.from_numpy((d % kf.H) * kf.W + d // kf.H) for d in draws]
+            if host_noise:
+                noise = [torch.rand((n_rays, n_samples)) for _ in range(iters)]
+            dev = self.device
+            empty = torch.zeros((iters, 0), dtype=torch.int64, device=dev)
+            return empty, empty, torch.stack(idx_c).to(dev, non_blocking=True), \
+                (torch.stack(noise).to(dev, non_blocking=True) if host_noise else None), []
         # Python-`random` and torch's CPU generator are independent streams: the index draws of all iterations go first, in the
         # reference's order (keyframe.py:100 then coslam.py:339-341 per iteration), as ONE call of the host sampler
         n_store = len(kf) * kf.num_rays_to_save
@@ -65,7 +75,7 @@ class BundleAdjuster(object):
         for _ in range(iters):
             if host_noise:
                 noise.append(torch.rand((n_rays, n_samples)))                     # scene_rep.py:255
-            if self.smooth_w > 0:
+            if self.smooth_w > 0 and smooth_on:
                 vol = self._bb[:, 1] - self._bb[:, 0]
                 n = t['smooth_pts']
                 offset_max = vol - (n - 1) * t['smooth_vox'] - 2 * t['smooth_margin']
@@ -112,21 +122,35 @@ class BundleAdjuster(object):
 
     # ---- coslam.py:285-397 -----------------------------------------------------------------------------------------------
     @torch.no_grad()
-    def run(self, kf_poses, cur_pose, current_rays):
+    def first_frame(self, c2w, current_rays, n_iters):
+        """first_frame_mapping (coslam.py:162-207): `n_iters` map-only iterations on `mapping.sample` pixels of the first frame
+        under its fixed pose (no smoothness term, an optimiser step every iteration).  current_rays [H*W,7] on the device."""
+        empty = torch.zeros((0, 4, 4), dtype=torch.float32, device=self.device)
+        self.run(empty, c2w, current_rays, _first_iters=int(n_iters))
+
+    @torch.no_grad()
+    def run(self, kf_poses, cur_pose, current_rays, _first_iters=None):
         """kf_poses [K,4,4]: estimated poses of the keyframes 0, every, 2 every, ... (coslam.py:299-300); cur_pose [4,4]: the
         current frame's estimate; current_rays [H*W,7] on the device (direction, rgb, depth; coslam.py:333-334).
         Returns (kf_poses_new [K,4,4], cur_pose_new [4,4]) -- unchanged tensors where the reference leaves them unchanged."""
-        lib, model, m, dev = _lib.load(), self.model, self.config['mapping'], self.device
+        lib, model, dev = _lib.load(), self.model, self.device
+        m = dict(self.config['mapping'])
         spec = model.spec
         kf = self.kfdb
-        iters, bs = int(m['iters']), int(m['sample'])
-        n_cur = max(bs // len(kf), int(m['min_pixels_cur']))
+        first = _first_iters is not None
+        if first:
+            m.update({'iters': _first_iters, 'map_accum_step': 1, 'map_wait_step': 0})
+            iters, bs, n_cur = _first_iters, 0, int(m['sample'])
+        else:
+            iters, bs = int(m['iters']), int(m['sample'])
+            n_cur = max(bs // len(kf), int(m['min_pixels_cur']))
+        smooth_w = 0.0 if first else self.smooth_w
         n, S = bs + n_cur, spec.n_samples
         K = kf_poses.shape[0]
         nr = self.n_rot
         f32 = dict(dtype=torch.float32, device=dev)
         # ---- pose parameters (coslam.py:305-323) -------------------------------------------------------------------------
-        optimise = len(kf) >= 2
+        optimise = (not first) and len(kf) >= 2
         optim_cur = bool(m['optim_cur'])
         poses_all = torch.cat([kf_poses.to(dev).float(), cur_pose.to(dev).float()[None]]).contiguous()     # slot -1 = current frame
         n_free = 0
@@ -145,9 +169,9 @@ class BundleAdjuster(object):
         d_poses = torch.zeros((K + 1, 4, 4), **f32)
         pose_step = 0
         # ---- buffers and the plan of the native iteration runtime (csrc/runtime.cu) ---------------------------------------
-        idx_g, slot_g, idx_c, noise, smooth = self._draw(iters, bs, n_cur, n, S)
+        idx_g, slot_g, idx_c, noise, smooth = self._draw(iters, bs, n_cur, n, S, smooth_on=not first)
         slot_c = torch.full((n_cur,), -1, dtype=torch.int64, device=dev)
-        store = kf.rays[:len(kf)].reshape(-1, 7)
+        store = kf.rays[:len(kf)].reshape(-1, 7) if not first else kf.rays[:1].reshape(-1, 7)
         cur = current_rays.reshape(-1, 7)
         if cur.device != dev or cur.dtype != torch.float32 or not cur.is_contiguous():
             cur = cur.to(dev, torch.float32).contiguous()
@@ -201,7 +225,7 @@ class BundleAdjuster(object):
         P.g_table = dp(g_table)
         P.g_mlp.w_sdf0, P.g_mlp.w_sdf1, P.g_mlp.w_col0, P.g_mlp.w_col1 = (g.data_ptr() for g in g_w)
         P.d_rays, P.d_poses = dp(d_rays), dp(d_poses)
-        if self.smooth_w > 0:                                            # coslam.py:154-158, :251-274
+        if smooth_w > 0:                                                 # coslam.py:154-158, :251-274
             t = self.config['training']
             n_side = int(t['smooth_pts']) - 1
             grid = model.embed_fn.grid()
@@ -213,7 +237,7 @@ class BundleAdjuster(object):
             off = (ctypes.c_float * (3 * iters))(*[v for o, _ in smooth for v in o.tolist()])
             P.grid = ctypes.addressof(grid)
             P.smooth_side, P.smooth_feat, P.smooth_voxel = n_side, n_feat, float(t['smooth_vox'])
-            P.smooth_grad_scale = self.smooth_w / float(int(t['smooth_pts']) ** 3)
+            P.smooth_grad_scale = smooth_w / float(int(t['smooth_pts']) ** 3)
             P.smooth_jitter, P.smooth_offset = ctypes.cast(jit, ctypes.c_void_p).value, ctypes.cast(off, ctypes.c_void_p).value
             P.smooth_x, P.smooth_f, P.smooth_df = dp(sx), dp(sf), dp(sdf_)
             keep += [sx, sf, sdf_, jit, off, grid]
@@ -237,7 +261,7 @@ class BundleAdjuster(object):
                 p_step = pose_step
             check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
                   'ba_iteration')
-        _lib.KERNEL_LAUNCHES += iters * (17 + (3 if lazy else 0) + (4 if self.smooth_w > 0 else 0)) - iters
+        _lib.KERNEL_LAUNCHES += iters * (17 + (3 if lazy else 0) + (4 if smooth_w > 0 else 0)) - iters
         del keep
         self.last_losses, self.last_tv, self.last_d_poses = loss_out[:4], ws[8:9], d_poses
         # ---- coslam.py:392-397 --------------------------------------------------------------------------------------------

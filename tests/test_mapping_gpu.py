@@ -178,3 +178,34 @@ def test_ba_call_matches_autograd_loop(cfg_name):
             assert dev_mean <= 0.05 * moved_mean + 1e-9, 'parameter update differs'
             if i > 0:                                                           # decoder matrices: dense, well-scaled gradients
                 assert dev_max <= 0.1 * moved_max
+
+
+def test_first_frame_mapping_matches_autograd_loop():
+    """first_frame_mapping (coslam.py:162-207): map-only iterations on pixels (i % H, i // H) of the first frame under its
+    fixed pose, an optimiser step per iteration -- BundleAdjuster.first_frame against the loop through autograd."""
+    cfg, model, db, kf_poses, cur_pose, current = _setup('room0')
+    H, W = db.H, db.W
+    ref_model = copy.deepcopy(model)
+    before = [p.detach().clone() for p in model._fused()]
+    n_iters, n = 4, cfg['mapping']['sample']
+    fresh = KeyFrameDatabase(cfg, H, W, 2, db.num_rays_to_save, DEV)              # nothing inserted yet, as at coslam.py:660
+    random.seed(21); torch.manual_seed(21)
+    BundleAdjuster(model, cfg, fresh, _map_optimizer(cfg, model), DEV).first_frame(cur_pose, current, n_iters)
+    random.seed(21); torch.manual_seed(21)
+    opt = _map_optimizer(cfg, ref_model)
+    t = cfg['training']
+    w = [t[k] for k in ('rgb_weight', 'depth_weight', 'sdf_weight', 'fs_weight')]
+    frame = current.reshape(H, W, 7)
+    for _ in range(n_iters):
+        opt.zero_grad()
+        idx = torch.tensor(random.sample(range(H * W), n))
+        rays = frame[idx % H, idx // H]
+        rays_o, rays_d = pose.rays_from_pose(rays[:, :3], cur_pose[None])
+        ret = ref_model.forward(rays_o, rays_d, rays[:, 3:6], rays[:, 6:7])
+        (w[0] * ret['rgb_loss'] + w[1] * ret['depth_loss'] + w[2] * ret['sdf_loss'] + w[3] * ret['fs_loss']).backward()
+        opt.step()
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        for b, p, q in zip(before, model._fused(), ref_model._fused()):
+            moved = float((q - b).abs().mean())
+            assert moved > 0 and float((p - q).abs().mean()) <= 0.05 * moved + 1e-9
