@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 13
+ABI_VERSION = 14
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p
@@ -75,7 +75,7 @@ class BaPlan(ctypes.Structure):
                 ('mlp', Mlp), ('lin_uniform', ctypes.c_void_p), ('lin_guided', ctypes.c_void_p), ('lin_nodepth', ctypes.c_void_p),
                 ('kf_rays', ctypes.c_void_p), ('idx_global', ctypes.c_void_p), ('slot_global', ctypes.c_void_p), ('n_global', ctypes.c_int64),
                 ('cur_rays', ctypes.c_void_p), ('idx_cur', ctypes.c_void_p), ('slot_cur', ctypes.c_void_p), ('n_cur', ctypes.c_int64),
-                ('poses_all', ctypes.c_void_p), ('n_poses', ctypes.c_int64), ('n_samples', ctypes.c_int64),
+                ('poses_all', ctypes.c_void_p), ('n_poses', ctypes.c_int64), ('n_samples', ctypes.c_int64), ('n_rays_total', ctypes.c_int64),
                 ('noise', ctypes.c_void_p), ('seeds', ctypes.c_void_p), ('seed_dev', ctypes.c_void_p),
                 ('rays_o', ctypes.c_void_p), ('rays_d', ctypes.c_void_p), ('target_rgb', ctypes.c_void_p), ('target_d', ctypes.c_void_p),
                 ('z_vals', ctypes.c_void_p), ('raw', ctypes.c_void_p), ('act_mask', ctypes.c_void_p), ('d_raw', ctypes.c_void_p),

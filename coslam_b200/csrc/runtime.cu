@@ -25,31 +25,26 @@ extern "C" size_t cb200_sizeof(int which) {       // binding self-check: 0 = cb2
     }
 }
 
-extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t map_step, int zero_map_grads, int64_t pose_step,
-                                  void* stream) {
-    if (p == nullptr || it < 0) return -1;
-    cudaStream_t st = (cudaStream_t)stream;
-    const int64_t n = p->n_global + p->n_cur, S = p->n_samples;
-    int rc;
 #define CB_TRY(call)             \
     do {                         \
-        rc = (call);             \
-        if (rc != 0) return rc;  \
+        int rc_ = (call);        \
+        if (rc_ != 0) return rc_; \
     } while (0)
 
+namespace {
+
+// rays (coslam.py:336-355) -> JointEncoding.forward up to the loss sums (scene_rep.py:297-338)
+int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t g = p->n_global, n = p->n_global + p->n_cur, S = p->n_samples;
+    int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
     CB_TRY(cuda_rc(cudaMemsetAsync(p->ws, 0, 10 * sizeof(double), st)));
     if (p->d_rays) CB_TRY(cuda_rc(cudaMemsetAsync(p->d_rays, 0, sizeof(float) * 6 * n, st)));
-    int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
-    double* sums = p->ws + 4;
-
-    // ---- rays (coslam.py:336-355) -------------------------------------------------------------------------------------
-    if (p->n_global > 0)
-        CB_TRY(cb200_assemble_rays_fwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->poses_all,
-                                       p->n_global, p->n_poses, p->rays_o, p->rays_d, p->target_rgb, p->target_d, stream));
-    const int64_t g = p->n_global;
+    if (g > 0)
+        CB_TRY(cb200_assemble_rays_fwd(p->kf_rays, p->idx_global + it * g, p->slot_global + it * g, p->poses_all, g, p->n_poses, p->rays_o,
+                                       p->rays_d, p->target_rgb, p->target_d, stream));
     CB_TRY(cb200_assemble_rays_fwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->poses_all, p->n_cur, p->n_poses, p->rays_o + 3 * g,
                                    p->rays_d + 3 * g, p->target_rgb + 3 * g, p->target_d + g, stream));
-    // ---- JointEncoding.forward (scene_rep.py:297-351) ---------------------------------------------------------------------
     CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, p->noise ? p->noise + it * n * S : nullptr,
                              p->seeds ? p->seeds[it] : 0, p->seed_dev, n, p->z_vals, counts, stream));
     if (p->lazy_ws) {
@@ -67,21 +62,27 @@ extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t ma
         CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0,
                                 nullptr, nullptr, stream));
     }
-    CB_TRY(cb200_render_fwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, sums, stream));
-    CB_TRY(cb200_loss_finish(sums, counts, n, S, p->loss_out, p->loss_out + 4, stream));
-    // ---- backward ---------------------------------------------------------------------------------------------------------
+    return cb200_render_fwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                            p->ws + 4, stream);
+}
+
+// losses from the (global) sums, backward into the gradient buffers, pose-gradient sums, smoothness (coslam.py:154-158, :251-274)
+int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
+    const int64_t g = p->n_global, n = p->n_global + p->n_cur, S = p->n_samples;
+    int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
+    double* sums = p->ws + 4;
+    CB_TRY(cb200_loss_finish(sums, counts, p->n_rays_total > 0 ? p->n_rays_total : n, S, p->loss_out, p->loss_out + 4, stream));
     CB_TRY(cb200_render_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, &p->loss_w, p->loss_out + 4, nullptr, nullptr, p->d_raw,
                             stream));
     CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask, p->g_table,
                             &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes, stream));
     if (p->d_rays) {
-        if (p->n_global > 0)
-            CB_TRY(cb200_assemble_rays_bwd(p->kf_rays, p->idx_global + it * p->n_global, p->slot_global + it * p->n_global, p->d_rays,
-                                           p->d_rays + 3 * n, p->n_global, p->n_poses, p->d_poses, stream));
+        if (g > 0)
+            CB_TRY(cb200_assemble_rays_bwd(p->kf_rays, p->idx_global + it * g, p->slot_global + it * g, p->d_rays, p->d_rays + 3 * n, g, p->n_poses,
+                                           p->d_poses, stream));
         CB_TRY(cb200_assemble_rays_bwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->d_rays + 3 * g, p->d_rays + 3 * n + 3 * g, p->n_cur,
                                        p->n_poses, p->d_poses, stream));
     }
-    // ---- smoothness (coslam.py:154-158, :251-274) -------------------------------------------------------------------------
     if (p->smooth_side > 0) {
         const int64_t m = p->smooth_side * p->smooth_side * p->smooth_side;
         CB_TRY(cb200_smooth_points(p->smooth_side, p->smooth_voxel, p->smooth_jitter + 3 * it, p->smooth_offset + 3 * it, p->scene->bb_lo,
@@ -90,7 +91,12 @@ extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t ma
         CB_TRY(cb200_smooth_tv(p->smooth_f, p->smooth_side, p->smooth_feat, p->smooth_grad_scale, p->smooth_df, p->ws + 8, stream));
         CB_TRY(cb200_hash_bwd(p->grid, p->smooth_x, p->table, p->smooth_df, m, p->g_table, nullptr, stream));
     }
-    // ---- optimisers (coslam.py:363-390) -----------------------------------------------------------------------------------
+    return 0;
+}
+
+// optimiser steps that are due (coslam.py:363-390)
+int ba_optimise(const cb200_ba_plan* p, int64_t map_step, int zero_map_grads, int64_t pose_step, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
     if (map_step > 0) {
         CB_TRY(cb200_adam_multi(p->map_params, p->n_map_params, map_step, zero_map_grads ? 1 : 0, stream));
     } else if (zero_map_grads) {
@@ -107,9 +113,20 @@ extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int64_t ma
                                pose_step, 1, stream));
         CB_TRY(cuda_rc(cudaMemsetAsync(p->d_poses, 0, sizeof(float) * 16 * p->n_poses, st)));
     }
-#undef CB_TRY
     return 0;
 }
+
+}  // namespace
+
+extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int phases, int64_t map_step, int zero_map_grads, int64_t pose_step,
+                                  void* stream) {
+    if (p == nullptr || it < 0) return -1;
+    if (phases & CB200_BA_FORWARD) CB_TRY(ba_forward(p, it, stream));
+    if (phases & CB200_BA_BACKWARD) CB_TRY(ba_backward(p, it, stream));
+    if (phases & CB200_BA_OPTIMISE) CB_TRY(ba_optimise(p, map_step, zero_map_grads, pose_step, stream));
+    return 0;
+}
+#undef CB_TRY
 
 // ---- host: CPython's random.sample(range(n), k), bit for bit ----------------------------------------------------------
 // The reference draws its ray / pixel indices with Python's `random.sample` (model/keyframe.py:45-46, :100; coslam.py:131-138,

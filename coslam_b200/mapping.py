@@ -23,14 +23,16 @@ import ctypes
 import random
 
 import torch
+import torch.distributed as dist
 
 from . import _lib, ops, pose
+from .dist import shard_bounds
 from ._lib import check, ptr, stream
 from .keyframe import sample_ranges
 
 
 class BundleAdjuster(object):
-    def __init__(self, model, config, kfdb, map_optimizer, device='cuda:0'):
+    def __init__(self, model, config, kfdb, map_optimizer, device='cuda:0', group=None, device_sampler=False):
         if not config['grid']['oneGrid'] or int(config['training']['n_importance']) > 0:
             raise NotImplementedError('BundleAdjuster serves oneGrid: True without importance samples (every Replica / ScanNet '
                                       'config); use the autograd path for the other variants')
@@ -44,6 +46,15 @@ class BundleAdjuster(object):
         self.last_tv = None                       # device double [1]: raw TV sum of the last iteration
         self.last_d_poses = None                  # [K+1,4,4] pose gradient accumulated since the last pose step
         self._noise_calls = 0
+        # non-parity index draws on the device (uniform, with replacement) for the large sweeps of BASELINE.json config 4:
+        # `random.sample` of 2^22 out of 16 M rays is host-bound even in C
+        self.device_sampler = bool(device_sampler)
+        # rays sharded over the ranks of `group`: parameters, poses and the keyframe store are replicated,
+        # every rank works on a contiguous shard of each iteration's globally drawn ray lists (rank 0's draws, broadcast)
+        self.group = group
+        self.world = dist.get_world_size(group) if group is not None else 1
+        self.rank = dist.get_rank(group) if group is not None else 0
+        self._flat = None
         bb = model.bounding_box.detach().float().cpu()
         self._lo = (ctypes.c_float * 3)(*bb[:, 0].tolist())
         self._ext = (ctypes.c_float * 3)(*(bb[:, 1] - bb[:, 0]).tolist())
@@ -68,6 +79,19 @@ class BundleAdjuster(object):
         # Python-`random` and torch's CPU generator are independent streams: the index draws of all iterations go first, in the
         # reference's order (keyframe.py:100 then coslam.py:339-341 per iteration), as ONE call of the host sampler
         n_store = len(kf) * kf.num_rays_to_save
+        if self.device_sampler:
+            dev = self.device
+            idx_g = torch.randint(0, n_store, (iters, bs), device=dev)
+            idx_c = torch.randint(0, kf.H * kf.W, (iters, n_cur), device=dev)
+            slot_g = (kf.frame_ids.to(dev)[idx_g // kf.num_rays_to_save] // every).to(torch.int64)
+            for _ in range(iters):
+                if host_noise:
+                    noise.append(torch.rand((n_rays, n_samples)))
+                if self.smooth_w > 0 and smooth_on:
+                    vol = self._bb[:, 1] - self._bb[:, 0]
+                    offset_max = vol - (t['smooth_pts'] - 1) * t['smooth_vox'] - 2 * t['smooth_margin']
+                    smooth.append((torch.rand(3).to(offset_max) * offset_max + t['smooth_margin'], torch.rand((1, 1, 1, 3)).reshape(3)))
+            return idx_g, slot_g, idx_c, (torch.stack(noise).to(dev, non_blocking=True) if host_noise else None), smooth
         draws = sample_ranges([(n_store, bs), (kf.H * kf.W, n_cur)] * iters)
         idx_g = [torch.from_numpy(d) for d in draws[0::2]]
         idx_c = [torch.from_numpy(d) for d in draws[1::2]]
@@ -88,10 +112,25 @@ class BundleAdjuster(object):
     def _map_grads(self):
         """(table.grad, [dW1..dW4]) as zero-initialised persistent buffers of the caller's parameters."""
         fw = self.model._fused()
+        if self.world > 1:                        # one flat bucket so that AR-2 is a single all-reduce; the .grad tensors are views
+            n = sum(p.numel() for p in fw)
+            if self._flat is None or self._flat.numel() != n or any(p.grad is None or p.grad.data_ptr() != self._flat.data_ptr() + 4 * o
+                                                                    for p, o in zip(fw, self._offsets(fw))):
+                self._flat = torch.zeros(n, dtype=torch.float32, device=fw[0].device)
+                for p, o in zip(fw, self._offsets(fw)):
+                    p.grad = self._flat[o:o + p.numel()].view_as(p)
         for p in fw:
             if p.grad is None:
                 p.grad = torch.zeros_like(p)
         return fw[0].grad, [p.grad for p in fw[1:]]
+
+    @staticmethod
+    def _offsets(params):
+        out, o = [], 0
+        for p in params:
+            out.append(o)
+            o += p.numel()
+        return out
 
     def _adam_params(self):
         """The map optimiser's parameters as a cb200_adam_param array (state created like coslam_b200.optim.Adam.step does);
@@ -170,6 +209,22 @@ class BundleAdjuster(object):
         pose_step = 0
         # ---- buffers and the plan of the native iteration runtime (csrc/runtime.cu) ---------------------------------------
         idx_g, slot_g, idx_c, noise, smooth = self._draw(iters, bs, n_cur, n, S, smooth_on=not first)
+        n_total = n
+        if self.world > 1:
+            for t_ in (idx_g, slot_g, idx_c) + ((noise,) if noise is not None else ()):
+                if t_.numel() > 0:
+                    dist.broadcast(t_, src=dist.get_global_rank(self.group, 0), group=self.group)
+            if smooth:
+                sm = torch.stack([torch.cat(p_) for p_ in smooth]).to(dev)
+                dist.broadcast(sm, src=dist.get_global_rank(self.group, 0), group=self.group)
+                smooth = [(r_[:3], r_[3:]) for r_ in sm.cpu()]
+            (g0, g1), (c0, c1) = shard_bounds(bs, self.world, self.rank), shard_bounds(n_cur, self.world, self.rank)
+            if noise is not None:
+                noise = torch.cat([noise[:, g0:g1], noise[:, bs + c0:bs + c1]], 1).contiguous()
+            idx_g, slot_g, idx_c = idx_g[:, g0:g1].contiguous(), slot_g[:, g0:g1].contiguous(), idx_c[:, c0:c1].contiguous()
+            bs, n_cur = g1 - g0, c1 - c0
+            n = bs + n_cur
+            smooth_w = smooth_w / self.world       # every rank adds the full regulariser gradient before AR-2 sums them
         slot_c = torch.full((n_cur,), -1, dtype=torch.int64, device=dev)
         store = kf.rays[:len(kf)].reshape(-1, 7) if not first else kf.rays[:1].reshape(-1, 7)
         cur = current_rays.reshape(-1, 7)
@@ -198,13 +253,13 @@ class BundleAdjuster(object):
         P.lin_uniform, P.lin_guided, P.lin_nodepth = dp(lin_u), dp(lin_g), dp(lin_n)
         P.kf_rays, P.idx_global, P.slot_global, P.n_global = dp(store), dp(idx_g), dp(slot_g), bs
         P.cur_rays, P.idx_cur, P.slot_cur, P.n_cur = dp(cur), dp(idx_c), dp(slot_c), n_cur
-        P.poses_all, P.n_poses, P.n_samples = dp(poses_all), K + 1, S
+        P.poses_all, P.n_poses, P.n_samples, P.n_rays_total = dp(poses_all), K + 1, S, n_total
         seeds = (ctypes.c_uint64 * iters)()
         if noise is not None:
             P.noise = dp(noise)
         elif spec.perturb:
             for it in range(iters):                                      # device Philox: one fresh seed per iteration
-                seeds[it] = model._noise(n, S, dev)[1] & (2 ** 64 - 1)
+                seeds[it] = (model._noise(n, S, dev)[1] + (self.rank << 24)) & (2 ** 64 - 1)
                 if model._noise_counter is not None:                     # graph-tracker mode: `_noise` hands out one constant seed and
                     self._noise_calls += 1                               # the device counter only moves with the tracker's replays
                     seeds[it] = (seeds[it] + (1 << 31) + self._noise_calls) & (2 ** 64 - 1)
@@ -259,7 +314,19 @@ class BundleAdjuster(object):
             if n_free > 0 and (it + 1) % int(m['pose_accum_step']) == 0:   # coslam.py:372-390
                 pose_step += 1
                 p_step = pose_step
-            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
+            if self.world == 1:
+                check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 7, ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
+                      'ba_iteration')
+                continue
+            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 1, ctypes.c_int64(0), 0, ctypes.c_int64(0), st), 'ba_iteration')
+            dist.all_reduce(ws[:4].view(torch.int64), group=self.group)        # AR-1: batch-global mask counts ...
+            dist.all_reduce(ws[4:8], group=self.group)                         #       ... and loss sums
+            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 2, ctypes.c_int64(0), 0, ctypes.c_int64(0), st), 'ba_iteration')
+            if map_step > 0:                                                   # AR-2, only in front of a step that consumes the sums
+                dist.all_reduce(self._flat, group=self.group)
+            if p_step > 0:
+                dist.all_reduce(d_poses, group=self.group)
+            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 4, ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
                   'ba_iteration')
         _lib.KERNEL_LAUNCHES += iters * (17 + (3 if lazy else 0) + (4 if smooth_w > 0 else 0)) - iters
         del keep

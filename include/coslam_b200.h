@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 13
+#define CB200_ABI_VERSION 14
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -341,6 +341,7 @@ typedef struct cb200_ba_plan {
     float* poses_all;                  /* [n_poses,4,4] */
     int64_t n_poses;
     int64_t n_samples;
+    int64_t n_rays_total;              /* rays of the GLOBAL batch when this rank holds a shard (0: N) */
     const float* noise;                /* [iters, N, S] host-drawn jitter, or NULL: device Philox with seeds[it] */
     const uint64_t* seeds;             /* HOST [iters] */
     const uint64_t* seed_dev;          /* optional device counter added to the seed */
@@ -377,10 +378,18 @@ typedef struct cb200_ba_plan {
     float lr_rot, lr_trans;
 } cb200_ba_plan;
 
-/* map_step / pose_step: 1-based optimiser step to take after this iteration's backward, 0 = none;
+/* phases: which part of iteration `it` to issue.  One GPU: all three in one call.  Rays sharded over several GPUs
+ * (SURVEY.md section 8e): FORWARD, then the caller all-reduces ws[0..7] (mask counts and loss sums are batch-global,
+ * model/utils.py:111-115), BACKWARD, then the caller all-reduces the gradient buffers that an optimiser step is about to
+ * consume, OPTIMISE.
+ * map_step / pose_step: 1-based optimiser step to take after this iteration's backward, 0 = none;
  * zero_map_grads != 0 clears the map gradients afterwards (map_optimizer.zero_grad(), coslam.py:370). */
-int cb200_ba_iteration(const cb200_ba_plan* plan, int64_t it, int64_t map_step, int zero_map_grads, int64_t pose_step,
-                       void* stream);
+#define CB200_BA_FORWARD 1
+#define CB200_BA_BACKWARD 2
+#define CB200_BA_OPTIMISE 4
+#define CB200_BA_ALL 7
+int cb200_ba_iteration(const cb200_ba_plan* plan, int64_t it, int phases, int64_t map_step, int zero_map_grads,
+                       int64_t pose_step, void* stream);
 
 /* HOST: `random.sample(range(n[d]), k[d])` for d = 0 .. n_draws-1 with CPython's exact algorithm (Lib/random.py sample /
  * _randbelow_with_getrandbits over the MT19937 of Modules/_randommodule.c), replacing the reference's Python-level draws of

@@ -89,3 +89,55 @@ def test_two_gpu_sharded_step_matches_single_gpu():
     assert torch.equal(out[0]['d_table'], out[1]['d_table'])          # replicas stay identical after AR-2
     got = torch.cat([out[0]['d_rays_o'], out[1]['d_rays_o']], 0)
     assert rel(got, o.grad.cpu()) <= 1e-3
+
+
+def _ba_worker(rank, world, port, out):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world)
+    try:
+        import random
+        from coslam_b200.mapping import BundleAdjuster
+        from tests.test_mapping_gpu import _map_optimizer, _setup
+        dev = 'cuda:%d' % rank
+        cfg, model, db, kf_poses, cur_pose, current = _setup('room0', dev=dev)
+        cfg['mapping'].update({'iters': 6, 'map_accum_step': 2, 'map_wait_step': 2, 'pose_accum_step': 3})
+        random.seed(5 + 100 * rank); torch.manual_seed(5 + 100 * rank)        # rank 0's draws are the ones that count (broadcast)
+        ba = BundleAdjuster(model, cfg, db, _map_optimizer(cfg, model), dev, group=dist.group.WORLD)
+        new_kf, new_cur = ba.run(kf_poses, cur_pose, current)
+        torch.cuda.synchronize()
+        out[rank] = {'kf': new_kf.cpu(), 'cur': new_cur.cpu(), 'params': [p.detach().cpu() for p in model._fused()],
+                     'losses': ba.last_losses.cpu()}
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_sharded_bundle_adjustment_matches_single_gpu():
+    """BundleAdjuster with the rays of every iteration sharded over 2 ranks (AR-1 on the counts / loss sums, AR-2 on the flat
+    gradient bucket and the pose gradients in front of the optimiser steps) against the single-GPU call on the same draws:
+    replicas identical, poses and parameter updates equal up to the summation order."""
+    import copy
+    import random
+    from coslam_b200.mapping import BundleAdjuster
+    from tests.test_mapping_gpu import _map_optimizer, _setup
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_ba_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    cfg, model, db, kf_poses, cur_pose, current = _setup('room0', dev='cuda:0')
+    cfg['mapping'].update({'iters': 6, 'map_accum_step': 2, 'map_wait_step': 2, 'pose_accum_step': 3})
+    before = [p.detach().clone().cpu() for p in model._fused()]
+    random.seed(5); torch.manual_seed(5)
+    ba = BundleAdjuster(model, cfg, db, _map_optimizer(cfg, model), 'cuda:0')
+    ref_kf, ref_cur = ba.run(kf_poses, cur_pose, current)
+    torch.cuda.synchronize()
+    a, b = out[0], out[1]
+    assert torch.equal(a['kf'], b['kf']) and torch.equal(a['cur'], b['cur'])
+    for x, y in zip(a['params'], b['params']):
+        assert torch.equal(x, y)                                        # replicas stay bit-identical without a broadcast
+    assert float((a['kf'] - ref_kf.cpu()).abs().max()) <= 3e-4 and float((a['cur'] - ref_cur.cpu()).abs().max()) <= 3e-4
+    assert float((a['losses'] - ba.last_losses.cpu()).abs().max()) <= 1e-3 * float(ba.last_losses.abs().max())
+    for b0, p, q in zip(before, a['params'], [p.detach().cpu() for p in model._fused()]):
+        moved = float((q - b0).abs().mean())
+        assert moved > 0 and float((p - q).abs().mean()) <= 0.05 * moved + 1e-9

@@ -19,7 +19,7 @@ pytestmark = pytest.mark.gpu
 DEV = 'cuda:0'
 
 
-def _setup(cfg_name, seed=0):
+def _setup(cfg_name, seed=0, dev=DEV):
     cfg = synth.CONFIGS[cfg_name]()
     cfg['training']['perturb'] = 0.0                       # deterministic sampling: both arms see the same sample positions
     cfg['training']['smooth_pts'] = 12
@@ -29,14 +29,14 @@ def _setup(cfg_name, seed=0):
     g = torch.Generator().manual_seed(seed)
     weights = synth.decoder_init(seed=5)
     from coslam_b200.scene_rep import JointEncoding
-    m0 = JointEncoding(cfg, synth.bound_tensor(cfg).to(DEV)).to(DEV)
+    m0 = JointEncoding(cfg, synth.bound_tensor(cfg).to(dev)).to(dev)
     table = synth.table_init(m0.embed_fn.params.numel(), 'trained', seed=77)
-    model = util.make_cuda_model(cfg, table, weights, DEV)
+    model = util.make_cuda_model(cfg, table, weights, dev)
     model.noise_mode = 'host'
     model.train()
     bound = synth.bound_tensor(cfg)
     centre, ext = bound.mean(1), (bound[:, 1] - bound[:, 0])
-    db = KeyFrameDatabase(cfg, H, W, n_kf + 2, R, DEV)
+    db = KeyFrameDatabase(cfg, H, W, n_kf + 2, R, dev)
     dirs = synth.camera_ray_dirs(H, W, 30.0, 30.0, W / 2 - 0.5, H / 2 - 0.5)
     poses = []
     random.seed(3)
@@ -45,12 +45,12 @@ def _setup(cfg_name, seed=0):
         r = r / r.norm() * (0.2 + 0.1 * k)
         c2w = pose.pose_matrix(r, (centre + 0.1 * ext * (torch.rand(3, generator=g) - 0.5))[None])[0]
         poses.append(c2w)
-        batch = {'direction': dirs[None].to(DEV), 'rgb': torch.rand(1, H, W, 3, generator=g).to(DEV),
-                 'depth': (torch.rand(1, H, W, generator=g) * 2.0 + 0.5).to(DEV), 'frame_id': torch.tensor([k * every])}
+        batch = {'direction': dirs[None].to(dev), 'rgb': torch.rand(1, H, W, 3, generator=g).to(dev),
+                 'depth': (torch.rand(1, H, W, generator=g) * 2.0 + 0.5).to(dev), 'frame_id': torch.tensor([k * every])}
         if k < n_kf:
             db.add_keyframe(batch)
     current = torch.cat([batch['direction'], batch['rgb'], batch['depth'][..., None]], -1).reshape(-1, 7)
-    return cfg, model, db, torch.stack(poses[:n_kf]).to(DEV), poses[n_kf].to(DEV), current
+    return cfg, model, db, torch.stack(poses[:n_kf]).to(dev), poses[n_kf].to(dev), current
 
 
 def _map_optimizer(cfg, model):
