@@ -780,3 +780,41 @@ def test_two_grid_variant_runs_through_standalone_operators():
         out = orc.raw2outputs(raw.cpu(), z.cpu())
     util.assert_close(ret['rgb'], out['rgb'], 'rgb')
     util.assert_close(ret['depth'], out['depth'], 'depth')
+
+
+def test_mesh_lattice_query_matches_chunked_loop():
+    """the dense-lattice SDF query and the vertex-colour query of extract_mesh (utils.py:80-176).  The
+    reference builds the lattice on the CPU and feeds 65 536-point chunks through `query_sdf` with a host copy per chunk;
+    coslam_b200.meshing does one device-side pass.  Same query points, so the values must be IDENTICAL."""
+    from coslam_b200 import meshing
+    cfg = synth.room0_config()
+    weights = synth.decoder_init(seed=5)
+    probe = JointEncodingFor(cfg)
+    table = synth.table_init(probe.embed_fn.params.numel(), 'trained', seed=77)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    model.eval()
+    bound = synth.bound_tensor(cfg).to(DEV)
+    voxel = 0.11
+    sdf, (tx, ty, tz) = meshing.query_sdf_lattice(model, cfg, bound, voxel_size=voxel, chunk=100000)
+    # the reference's loop (utils.py:96-131), verbatim in structure
+    x_min, y_min, z_min = bound[:, 0]
+    x_max, y_max, z_max = bound[:, 1]
+    rx, ry, rz = meshing.get_voxels(x_max, x_min, y_max, y_min, z_max, z_min, voxel)
+    assert torch.equal(rx, tx) and rx.shape[0] == round(8.0 / voxel + 0.0005) + 1
+    query_pts = torch.stack(torch.meshgrid(rx, ry, rz, indexing='ij'), -1).to(torch.float32)
+    flat = query_pts.reshape([-1, 3])
+    bb = bound.cpu()
+    flat = (flat - bb[:, 0]) / (bb[:, 1] - bb[:, 0])
+    chunk = 1024 * 64
+    with torch.no_grad():
+        raw = [model.query_sdf(flat[i:i + chunk, None, :].to(DEV)).cpu() for i in range(0, flat.shape[0], chunk)]
+    ref = torch.cat(raw, 0).reshape(query_pts.shape[:-1])
+    assert sdf.shape == ref.shape and torch.equal(sdf.cpu(), ref)
+    # vertex colours: utils.py:160-176
+    g = torch.Generator().manual_seed(2)
+    verts = (bb[:, 0] + torch.rand(70001, 3, generator=g) * (bb[:, 1] - bb[:, 0])).numpy()
+    col = meshing.query_vertex_colors(model, cfg, bound, verts, chunk=30000)
+    vf = (torch.from_numpy(verts).to(bound) - bound[:, 0]) / (bound[:, 1] - bound[:, 0])
+    with torch.no_grad():
+        raw = [model.query_color(vf[i:i + chunk, None, :]).cpu() for i in range(0, vf.shape[0], chunk)]
+    assert torch.equal(col.cpu(), torch.cat(raw, 0).reshape(-1, 3))
