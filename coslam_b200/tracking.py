@@ -30,9 +30,10 @@ from ._lib import check, ptr, stream
 class FrameTracker(object):
     def __init__(self, model, config, n_rays=None, device='cuda:0', use_graph=True, fused=None):
         t, tr = config['tracking'], config['training']
-        can_fuse = bool(config['grid']['oneGrid']) and int(tr['n_importance']) == 0
+        can_fuse = bool(config['grid']['oneGrid'])
         if fused and not can_fuse:
-            raise NotImplementedError('FrameTracker(fused=True) serves oneGrid: True without importance samples')
+            raise NotImplementedError('FrameTracker(fused=True) serves oneGrid: True (every shipped config)')
+        self.n_imp = int(tr['n_importance'])
         self.fused = can_fuse if fused is None else bool(fused)
         self.model, self.config, self.device = model, config, torch.device(device)
         self.n_rays = int(n_rays if n_rays is not None else t['sample'])
@@ -111,14 +112,40 @@ class FrameTracker(object):
         check(lib.cb200_assemble_rays_fwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(self.c2w), ctypes.c_int64(n),
                                           ctypes.c_int64(1), ptr(self.rays_o), ptr(self.rays_d), ptr(self.target_s), ptr(td),
                                           stream()), 'assemble_rays_fwd')
-        z = m._sample(td, counts=ws[:4].view(torch.int64))
+        counts = ws[:4].view(torch.int64)
+        coarse = None
+        if self.n_imp > 0:
+            # hierarchical pass (scene_rep.py:262-277, :327-329): coarse samples -> rendering weights -> n_importance extra depths
+            # per ray (cb200_importance_sample, counts of the MERGED samples) -> all samples again.  The coarse colour / depth
+            # terms share the normalisers of the fine ones, so their squared-residual sums are simply added to the fine sums.
+            from .hierarchical import draw_uniforms
+            z0 = m._sample(td)
+            rays0 = (self.rays_o, self.rays_d, z0)
+            raw0, _, mask0 = ops.points_forward(spec.scene(), tb, w, rays=rays0)
+            sums0 = torch.zeros(4, dtype=torch.float64, device=z0.device)
+            _, _, _, weights0 = ops._render_forward(spec, raw0, z0, self.target_s, td, loss_sums=sums0, want_weights=True)
+            u = draw_uniforms(n, self.n_imp, z0.device, det=(self.config['training']['perturb'] == 0.))
+            z, _ = ops.importance_sample(spec, z0, weights0, u, target_d=td, counts=counts, want_std=False)
+            coarse = (rays0, raw0, mask0, sums0)
+        else:
+            z = m._sample(td, counts=counts)
         rays = (self.rays_o, self.rays_d, z)
         raw, _, mask = ops.points_forward(spec.scene(), tb, w, rays=rays)
         ops._render_forward(spec, raw, z, self.target_s, td, loss_sums=ws[4:8])
-        check(lib.cb200_loss_finish(ptr(ws[4:8]), ptr(ws[:4].view(torch.int64)), ctypes.c_int64(n), ctypes.c_int64(z.shape[1]),
+        if coarse is not None:
+            ws[4:6].add_(coarse[3][:2])                              # colour and depth only: the coarse pass has no SDF / free-space terms
+        check(lib.cb200_loss_finish(ptr(ws[4:8]), ptr(counts), ctypes.c_int64(n), ctypes.c_int64(z.shape[1]),
                                     ptr(self.loss_out[:4]), ptr(self.loss_out[4:]), stream()), 'loss_finish')
         d_raw = ops._render_backward(spec, raw, z, self.target_s, td, self.w_dev, self.loss_out[4:], None, None)
-        _, _, (d_o, d_d) = ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, need_table=False, need_mlp=False)
+        _, _, d_od = ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, need_table=False, need_mlp=False)
+        if coarse is not None:
+            rays0, raw0, mask0, _ = coarse
+            d_raw0 = ops._render_backward(spec, raw0, rays0[2], self.target_s, td, (self.w_dev[0], self.w_dev[1], None, None),
+                                          self.loss_out[4:], None, None)
+            _, _, d_od0 = ops.points_backward(spec.scene(), tb, w, mask0, d_raw0, rays=rays0, need_table=False, need_mlp=False)
+            d_od[0].add_(d_od0[0])
+            d_od[1].add_(d_od0[1])
+        d_o, d_d = d_od
         check(lib.cb200_assemble_rays_bwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(d_o), ptr(d_d), ctypes.c_int64(n),
                                           ctypes.c_int64(1), ptr(self.d_c2w), stream()), 'assemble_rays_bwd')
         check(lib.cb200_track_update(ctypes.byref(self._steps[0 if k == 0 else 1]), stream()), 'track_update')

@@ -575,6 +575,36 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
     assert float((info_g['last_c2w'].cpu() - last_c2w[0]).abs().max()) <= 3e-4
 
 
+def test_frame_tracker_with_importance_samples_matches_autograd_loop():
+    """This fork's TUM config (tum.yaml:89, n_importance 128): the autograd-free tracking iteration with the hierarchical pass
+    (coarse render -> cb200_importance_sample -> fine render, coarse colour / depth terms added to the loss sums, two backward
+    launches accumulating the ray gradients) against the same loop through torch autograd (hierarchical.forward_with_importance)."""
+    from coslam_b200.tracking import FrameTracker
+    cfg = synth.tum_desk_config(n_importance=128)
+    cfg['training']['perturb'] = 0.0                      # deterministic: stratified mid-points and the det=True linspace of sample_pdf
+    n_rays = 512
+    cfg['tracking']['sample'] = n_rays
+    weights = synth.decoder_init(seed=5)
+    probe = JointEncodingFor(cfg)
+    table = synth.table_init(probe.embed_fn.params.numel(), 'trained', seed=77)
+    model = util.make_cuda_model(cfg, table, weights, DEV)
+    dir_cam, rgb, depth, c2w0 = _tracking_case(cfg, n_rays)
+    fused = FrameTracker(model, cfg, device=DEV, use_graph=False)
+    assert fused.fused and fused.n_imp == 128
+    est_f, info_f = fused.track(dir_cam, rgb, depth, c2w0)
+    est_f, best_f, last_f = est_f.clone(), float(info_f['best_loss']), info_f['last_c2w'].clone()
+    auto = FrameTracker(model, cfg, device=DEV, use_graph=False, fused=False)
+    est_a, info_a = auto.track(dir_cam, rgb, depth, c2w0)
+    assert abs(float(info_a['best_loss']) - best_f) <= 2e-3 * abs(best_f)
+    assert float((est_a - est_f).abs().max()) <= 3e-4
+    assert float((info_a['last_c2w'] - last_f).abs().max()) <= 3e-4
+    assert float((last_f.cpu() - c2w0).abs().max()) > 1e-4
+    graph = FrameTracker(model, cfg, device=DEV, use_graph=True)
+    for _ in range(2):
+        est_g, info_g = graph.track(dir_cam, rgb, depth, c2w0)
+        assert float((est_g - est_f).abs().max()) <= 3e-4
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize('n_rot', [3, 4])
 def test_track_update_kernel_matches_autograd_and_adam(n_rot):
