@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 14
+ABI_VERSION = 15
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p
@@ -81,6 +81,9 @@ class BaPlan(ctypes.Structure):
                 ('z_vals', ctypes.c_void_p), ('raw', ctypes.c_void_p), ('act_mask', ctypes.c_void_p), ('d_raw', ctypes.c_void_p),
                 ('lazy_ws', ctypes.c_void_p), ('lazy_ws_bytes', ctypes.c_size_t), ('bwd_ws', ctypes.c_void_p), ('bwd_ws_bytes', ctypes.c_size_t),
                 ('ws', ctypes.c_void_p), ('loss_out', ctypes.c_void_p), ('loss_w', LossGradPtrs),
+                ('n_importance', ctypes.c_int64), ('z0', ctypes.c_void_p), ('raw0', ctypes.c_void_p), ('act_mask0', ctypes.c_void_p),
+                ('weights0', ctypes.c_void_p), ('d_raw0', ctypes.c_void_p), ('u', ctypes.c_void_p), ('u_stride', ctypes.c_int64),
+                ('sums0', ctypes.c_void_p),
                 ('g_table', ctypes.c_void_p), ('g_mlp', MlpGrad), ('d_rays', ctypes.c_void_p), ('d_poses', ctypes.c_void_p),
                 ('smooth_side', ctypes.c_int64), ('smooth_feat', ctypes.c_int64), ('smooth_voxel', ctypes.c_float),
                 ('smooth_grad_scale', ctypes.c_float), ('smooth_jitter', ctypes.c_void_p), ('smooth_offset', ctypes.c_void_p),

@@ -33,10 +33,18 @@ extern "C" size_t cb200_sizeof(int which) {       // binding self-check: 0 = cb2
 
 namespace {
 
+// the coarse pass has colour and depth terms only (scene_rep.py:327-329): its two squared-residual sums join the fine ones
+__global__ void add_coarse_sums_kernel(double* sums, const double* sums0) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        sums[0] += sums0[0];
+        sums[1] += sums0[1];
+    }
+}
+
 // rays (coslam.py:336-355) -> JointEncoding.forward up to the loss sums (scene_rep.py:297-338)
 int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    const int64_t g = p->n_global, n = p->n_global + p->n_cur, S = p->n_samples;
+    const int64_t g = p->n_global, n = p->n_global + p->n_cur, S0 = p->n_samples, I = p->n_importance, S = S0 + I;
     int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
     CB_TRY(cuda_rc(cudaMemsetAsync(p->ws, 0, 10 * sizeof(double), st)));
     if (p->d_rays) CB_TRY(cuda_rc(cudaMemsetAsync(p->d_rays, 0, sizeof(float) * 6 * n, st)));
@@ -45,8 +53,23 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
                                        p->rays_d, p->target_rgb, p->target_d, stream));
     CB_TRY(cb200_assemble_rays_fwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->poses_all, p->n_cur, p->n_poses, p->rays_o + 3 * g,
                                    p->rays_d + 3 * g, p->target_rgb + 3 * g, p->target_d + g, stream));
-    CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, p->noise ? p->noise + it * n * S : nullptr,
-                             p->seeds ? p->seeds[it] : 0, p->seed_dev, n, p->z_vals, counts, stream));
+    const float* noise = p->noise ? p->noise + it * n * S0 : nullptr;
+    const uint64_t seed = p->seeds ? p->seeds[it] : 0;
+    if (I > 0) {
+        // coarse samples -> weights -> I extra depths per ray, merged and sorted; the mask counts belong to the merged samples
+        CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, noise, seed, p->seed_dev, n, p->z0,
+                                 nullptr, stream));
+        CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z0, n, S0, p->raw0, nullptr, p->act_mask0, 0,
+                                nullptr, nullptr, stream));
+        CB_TRY(cuda_rc(cudaMemsetAsync(p->sums0, 0, 4 * sizeof(double), st)));
+        CB_TRY(cb200_render_fwd(p->render, p->raw0, p->z0, p->target_rgb, p->target_d, n, S0, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                p->weights0, p->sums0, stream));
+        CB_TRY(cb200_importance_sample(p->render, p->z0, p->weights0, p->u + (p->u_stride ? it * n * I : 0), p->u_stride, p->target_d, n, S0, I,
+                                       p->z_vals, nullptr, counts, stream));
+    } else {
+        CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, noise, seed, p->seed_dev, n, p->z_vals,
+                                 counts, stream));
+    }
     if (p->lazy_ws) {
         CB_TRY(cuda_rc(cudaMemsetAsync(p->raw, 0, sizeof(float) * 4 * n * S, st)));
         unsigned char* base = static_cast<unsigned char*>(p->lazy_ws);
@@ -62,13 +85,18 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
         CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0,
                                 nullptr, nullptr, stream));
     }
-    return cb200_render_fwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
-                            p->ws + 4, stream);
+    CB_TRY(cb200_render_fwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                            p->ws + 4, stream));
+    if (I > 0) {
+        add_coarse_sums_kernel<<<1, 32, 0, st>>>(p->ws + 4, p->sums0);
+        CB_TRY(cuda_rc(cudaGetLastError()));
+    }
+    return 0;
 }
 
 // losses from the (global) sums, backward into the gradient buffers, pose-gradient sums, smoothness (coslam.py:154-158, :251-274)
 int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
-    const int64_t g = p->n_global, n = p->n_global + p->n_cur, S = p->n_samples;
+    const int64_t g = p->n_global, n = p->n_global + p->n_cur, S0 = p->n_samples, I = p->n_importance, S = S0 + I;
     int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
     double* sums = p->ws + 4;
     CB_TRY(cb200_loss_finish(sums, counts, p->n_rays_total > 0 ? p->n_rays_total : n, S, p->loss_out, p->loss_out + 4, stream));
@@ -76,6 +104,16 @@ int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
                             stream));
     CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask, p->g_table,
                             &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes, stream));
+    if (I > 0) {                                 // the coarse maps carry the colour and depth terms only
+        cb200_loss_grads lw = p->loss_w;
+        lw.sdf = nullptr;
+        lw.fs = nullptr;
+        CB_TRY(cb200_render_bwd(p->render, p->raw0, p->z0, p->target_rgb, p->target_d, n, S0, &lw, p->loss_out + 4, nullptr, nullptr, p->d_raw0,
+                                stream));
+        CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z0, n, S0, p->d_raw0, nullptr, p->act_mask0,
+                                p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes,
+                                stream));
+    }
     if (p->d_rays) {
         if (g > 0)
             CB_TRY(cb200_assemble_rays_bwd(p->kf_rays, p->idx_global + it * g, p->slot_global + it * g, p->d_rays, p->d_rays + 3 * n, g, p->n_poses,

@@ -33,9 +33,9 @@ from .keyframe import sample_ranges
 
 class BundleAdjuster(object):
     def __init__(self, model, config, kfdb, map_optimizer, device='cuda:0', group=None, device_sampler=False):
-        if not config['grid']['oneGrid'] or int(config['training']['n_importance']) > 0:
-            raise NotImplementedError('BundleAdjuster serves oneGrid: True without importance samples (every Replica / ScanNet '
-                                      'config); use the autograd path for the other variants')
+        if not config['grid']['oneGrid']:
+            raise NotImplementedError('BundleAdjuster serves oneGrid: True (every shipped config); use the autograd path otherwise')
+        self.n_imp = int(config['training']['n_importance'])
         self.model, self.config, self.kfdb, self.opt, self.device = model, config, kfdb, map_optimizer, torch.device(device)
         t = config['training']
         self.loss_w = [float(t[k]) for k in ('rgb_weight', 'depth_weight', 'sdf_weight', 'fs_weight')]
@@ -232,9 +232,11 @@ class BundleAdjuster(object):
             cur = cur.to(dev, torch.float32).contiguous()
         rays_o, rays_d, t_rgb = (torch.empty((n, 3), **f32) for _ in range(3))
         t_d = torch.empty((n,), **f32)
-        z = torch.empty((n, S), **f32)
-        raw, d_raw = torch.empty((n, S, 4), **f32), torch.empty((n, S, 4), **f32)
-        mask = torch.empty((n, S, 2), dtype=torch.int32, device=dev)
+        I = self.n_imp
+        Sf = S + I                                                       # samples per ray of the (fine) pass the losses are taken on
+        z = torch.empty((n, Sf), **f32)
+        raw, d_raw = torch.empty((n, Sf, 4), **f32), torch.empty((n, Sf, 4), **f32)
+        mask = torch.empty((n, Sf, 2), dtype=torch.int32, device=dev)
         d_rays = torch.empty((2, n, 3), **f32) if n_free > 0 else None
         ws = torch.empty(10, dtype=torch.float64, device=dev)           # 4 counts | 4 loss sums | tv sum | pad
         loss_out = torch.empty(8, **f32)
@@ -243,7 +245,7 @@ class BundleAdjuster(object):
         g_table, g_w = self._map_grads()
         scene, render = spec.scene(), spec.render_cfg()
         lin_u, lin_g, lin_n = spec.linspaces(dev)
-        lazy = ops.LAZY_FORWARD and lib.cb200_get_decoder() == 1 and ops.LAZY_MIN_POINTS <= n * S < 2 ** 32
+        lazy = ops.LAZY_FORWARD and lib.cb200_get_decoder() == 1 and ops.LAZY_MIN_POINTS <= n * Sf < 2 ** 32
         keep = [idx_g, slot_g, idx_c, slot_c, noise, cur]               # referenced by raw pointer below
         P = _lib.BaPlan()
         dp = lambda t: t.data_ptr() if t is not None else None
@@ -269,12 +271,23 @@ class BundleAdjuster(object):
         P.rays_o, P.rays_d, P.target_rgb, P.target_d = dp(rays_o), dp(rays_d), dp(t_rgb), dp(t_d)
         P.z_vals, P.raw, P.act_mask, P.d_raw = dp(z), dp(raw), dp(mask), dp(d_raw)
         if lazy:
-            nbytes = int(lib.cb200_lazy_workspace(ctypes.c_int64(n), ctypes.c_int64(S)))
+            nbytes = int(lib.cb200_lazy_workspace(ctypes.c_int64(n), ctypes.c_int64(Sf)))
             lazy_ws = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
             P.lazy_ws, P.lazy_ws_bytes = dp(lazy_ws), nbytes
-        bbytes = int(lib.cb200_points_bwd_workspace(ctypes.c_int64(n * S)))
+        bbytes = int(lib.cb200_points_bwd_workspace(ctypes.c_int64(n * Sf)))
         bwd_ws = torch.empty((bbytes + 3) // 4, dtype=torch.int32, device=dev)
         P.bwd_ws, P.bwd_ws_bytes = dp(bwd_ws), bbytes
+        if I > 0:                                                        # hierarchical pass, model/scene_rep.py:262-277
+            from .hierarchical import draw_uniforms
+            det = self.config['training']['perturb'] == 0.
+            u = draw_uniforms(n, I, dev, det) if det else torch.stack([draw_uniforms(n, I, dev, det) for _ in range(iters)])
+            z0, w0 = torch.empty((n, S), **f32), torch.empty((n, S), **f32)
+            raw0, d_raw0 = torch.empty((n, S, 4), **f32), torch.empty((n, S, 4), **f32)
+            mask0 = torch.empty((n, S, 2), dtype=torch.int32, device=dev)
+            sums0 = torch.empty(4, dtype=torch.float64, device=dev)
+            P.n_importance, P.z0, P.raw0, P.act_mask0, P.weights0, P.d_raw0 = I, dp(z0), dp(raw0), dp(mask0), dp(w0), dp(d_raw0)
+            P.u, P.u_stride, P.sums0 = dp(u), (0 if det else I), dp(sums0)
+            keep += [u, z0, w0, raw0, d_raw0, mask0, sums0]
         P.ws, P.loss_out = dp(ws), dp(loss_out)
         P.loss_w.rgb, P.loss_w.depth, P.loss_w.sdf, P.loss_w.fs = (t_.data_ptr() for t_ in self.w_dev)
         P.g_table = dp(g_table)

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 14
+#define CB200_ABI_VERSION 15
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -358,6 +358,17 @@ typedef struct cb200_ba_plan {
     double* ws;                        /* [10]: 4 int64 counts | 4 loss sums | tv sum | pad */
     float* loss_out;                   /* [8]: 4 losses | 4 d loss / d sum */
     cb200_loss_grads loss_w;           /* device scalars: the four loss weights */
+    /* hierarchical pass (model/scene_rep.py:262-277, :327-329); n_importance == 0 disables it.  n_samples is then the number of
+     * COARSE samples; z_vals / raw / act_mask / d_raw hold n_samples + n_importance samples per ray */
+    int64_t n_importance;
+    float* z0;                         /* [N,S] coarse samples */
+    float* raw0;                       /* [N,S,4] */
+    uint32_t* act_mask0;               /* [N,S,2] */
+    float* weights0;                   /* [N,S] coarse rendering weights */
+    float* d_raw0;                     /* [N,S,4] */
+    const float* u;                    /* uniforms of sample_pdf: [iters,N,I] (u_stride = I) or one row [I] (u_stride = 0) */
+    int64_t u_stride;
+    double* sums0;                     /* [4] scratch: loss sums of the coarse pass (colour and depth are added to ws) */
     /* gradients */
     float* g_table;
     cb200_mlp_grad g_mlp;

@@ -20,7 +20,8 @@ DEV = 'cuda:0'
 
 
 def _setup(cfg_name, seed=0, dev=DEV):
-    cfg = synth.CONFIGS[cfg_name]()
+    # 'tum_desk_importance': this fork's tum.yaml:89 (128 importance samples, the hierarchical pass of scene_rep.py:262-295)
+    cfg = synth.tum_desk_config(n_importance=128) if cfg_name == 'tum_desk_importance' else synth.CONFIGS[cfg_name]()
     cfg['training']['perturb'] = 0.0                       # deterministic sampling: both arms see the same sample positions
     cfg['training']['smooth_pts'] = 12
     cfg['mapping']['sample'] = 512
@@ -123,7 +124,7 @@ def _rel(a, b):
     return float((a - b).abs().max()) / max(float(b.abs().max()), 1e-30)
 
 
-@pytest.mark.parametrize('cfg_name', ['room0', 'scannet0000'])
+@pytest.mark.parametrize('cfg_name', ['room0', 'scannet0000', 'tum_desk_importance'])
 def test_one_iteration_gradients_match_autograd(cfg_name):
     cfg, model, db, kf_poses, cur_pose, current = _setup(cfg_name)
     cfg['mapping'].update({'iters': 1, 'map_accum_step': 2, 'pose_accum_step': 2})       # no optimiser step: gradients stay
