@@ -33,20 +33,21 @@ ROOM_HI = torch.tensor([6.6, 3.3, 1.1])
 SPHERES = torch.tensor([[2.0, 1.2, -0.9, 0.5], [4.2, 0.3, -0.8, 0.6], [3.2, 2.4, -0.2, 0.45]])
 
 
-SHIFT = torch.zeros(3)                        # the same room translated into another config's bound (scene0000: see main)
+SHIFT = torch.zeros(3)                        # the same room translated / scaled into another config's bound (see main)
+SCALE = [1.0]
 
 
 def scene_distance(p):
     """Distance to the nearest surface for points inside the room (walls from the inside, spheres from the outside)."""
-    p = p - SHIFT.to(p)
+    p = (p - SHIFT.to(p)) / SCALE[0]
     lo, hi, sph = ROOM_LO.to(p), ROOM_HI.to(p), SPHERES.to(p)
     d_wall = torch.minimum(p - lo, hi - p).min(-1)[0]
     d_sph = (torch.norm(p[..., None, :] - sph[:, :3], dim=-1) - sph[:, 3]).min(-1)[0]
-    return torch.minimum(d_wall, d_sph)
+    return torch.minimum(d_wall, d_sph) * SCALE[0]
 
 
 def scene_colour(p):
-    p = p - SHIFT.to(p)
+    p = (p - SHIFT.to(p)) / SCALE[0]
     k = torch.tensor([1.7, 2.3, 2.9], device=p.device)
     return 0.5 + 0.5 * torch.stack([torch.sin(k[0] * p[..., 0] + 0.5 * p[..., 1]), torch.sin(k[1] * p[..., 1] + 0.7 * p[..., 2]),
                                     torch.sin(k[2] * p[..., 2] + 0.3 * p[..., 0])], -1) * 0.8
@@ -80,7 +81,7 @@ def trajectory(n_frames):
         right = right / torch.norm(right)
         up2 = torch.linalg.cross(right, fwd)
         T = torch.eye(4)
-        T[:3, 0], T[:3, 1], T[:3, 2], T[:3, 3] = right, up2, -fwd, eye + SHIFT
+        T[:3, 0], T[:3, 1], T[:3, 2], T[:3, 3] = right, up2, -fwd, eye * SCALE[0] + SHIFT
         poses.append(T)
     return torch.stack(poses)
 
@@ -323,7 +324,7 @@ def main():
     ap.add_argument('--scale', type=float, default=1.0)
     ap.add_argument('--first-iters', type=int, default=None)
     ap.add_argument('--noise', default='device', choices=('device', 'host'))
-    ap.add_argument('--workload', default='room0', choices=('room0', 'scannet0000'))
+    ap.add_argument('--workload', default='room0', choices=('room0', 'scannet0000', 'tum_desk'))
     a = ap.parse_args()
     dev = 'cuda:0'
     seed_everything(0)
@@ -331,7 +332,16 @@ def main():
         # BASELINE.json config 3 in miniature: scene0000's hyper-parameters (640x480, S = 117, far 8, quaternion poses,
         # optim_cur False, smoothness lattice 63^3) on the same room, moved into scene0000's bound [[-0.1,8.6],[-0.1,8.9],[-0.3,3.3]]
         SHIFT.copy_(torch.tensor([0.9, 1.3, 1.4]))
-    cfg = scaled_config(synth.CONFIGS[a.workload](), a.scale)
+    if a.workload == 'tum_desk':
+        # BASELINE.json config 5's SHAPE in one process: this fork's fr1_desk hyper-parameters (368x496 frames after resize + crop,
+        # S = 64 + 21 = 85 plus 128 importance samples, trunc 0.05, 20 BA iterations) on the room at 0.8 scale inside TUM's bound
+        SCALE[0] = 0.8
+        SHIFT.copy_(torch.tensor([-2.9, -1.0, 0.0]))
+        cfg = synth.tum_desk_config(n_importance=128)
+        cfg['cam'].update({'H': 368, 'W': 496, 'fx': 413.84, 'fy': 413.2, 'cx': 246.88, 'cy': 196.24})
+        cfg = scaled_config(cfg, a.scale)
+    else:
+        cfg = scaled_config(synth.CONFIGS[a.workload](), a.scale)
     first_iters = cfg['mapping']['first_iters'] if a.first_iters is None else a.first_iters
     frames = make_frames(cfg, a.frames, dev)
     gt = torch.stack([f['c2w'] for f in frames])
