@@ -318,6 +318,25 @@ def seed_everything(seed=0):                                        # coslam.py:
     np.random.seed(seed)
 
 
+def workload_config(workload, scale=1.0):
+    """Config of a synthetic workload; places the room inside the config's bound (module-level SHIFT / SCALE)."""
+    if workload == 'scannet0000':
+        # BASELINE.json config 3 in miniature: scene0000's hyper-parameters (640x480, S = 117, far 8, quaternion poses,
+        # optim_cur False, smoothness lattice 63^3) on the same room, moved into scene0000's bound [[-0.1,8.6],[-0.1,8.9],[-0.3,3.3]]
+        SHIFT.copy_(torch.tensor([0.9, 1.3, 1.4]))
+    if workload == 'tum_desk':
+        # BASELINE.json config 5's SHAPE in one process: this fork's fr1_desk hyper-parameters (368x496 frames after resize + crop,
+        # S = 64 + 21 = 85 plus 128 importance samples, trunc 0.05, 20 BA iterations) on the room at 0.8 scale inside TUM's bound
+        SCALE[0] = 0.8
+        SHIFT.copy_(torch.tensor([-2.9, -1.0, 0.0]))
+        cfg = synth.tum_desk_config(n_importance=128)
+        cfg['cam'].update({'H': 368, 'W': 496, 'fx': 413.84, 'fy': 413.2, 'cx': 246.88, 'cy': 196.24})
+        cfg = scaled_config(cfg, scale)
+    else:
+        cfg = scaled_config(synth.CONFIGS[workload](), scale)
+    return cfg
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--frames', type=int, default=60)
@@ -328,20 +347,7 @@ def main():
     a = ap.parse_args()
     dev = 'cuda:0'
     seed_everything(0)
-    if a.workload == 'scannet0000':
-        # BASELINE.json config 3 in miniature: scene0000's hyper-parameters (640x480, S = 117, far 8, quaternion poses,
-        # optim_cur False, smoothness lattice 63^3) on the same room, moved into scene0000's bound [[-0.1,8.6],[-0.1,8.9],[-0.3,3.3]]
-        SHIFT.copy_(torch.tensor([0.9, 1.3, 1.4]))
-    if a.workload == 'tum_desk':
-        # BASELINE.json config 5's SHAPE in one process: this fork's fr1_desk hyper-parameters (368x496 frames after resize + crop,
-        # S = 64 + 21 = 85 plus 128 importance samples, trunc 0.05, 20 BA iterations) on the room at 0.8 scale inside TUM's bound
-        SCALE[0] = 0.8
-        SHIFT.copy_(torch.tensor([-2.9, -1.0, 0.0]))
-        cfg = synth.tum_desk_config(n_importance=128)
-        cfg['cam'].update({'H': 368, 'W': 496, 'fx': 413.84, 'fy': 413.2, 'cx': 246.88, 'cy': 196.24})
-        cfg = scaled_config(cfg, a.scale)
-    else:
-        cfg = scaled_config(synth.CONFIGS[a.workload](), a.scale)
+    cfg = workload_config(a.workload, a.scale)
     first_iters = cfg['mapping']['first_iters'] if a.first_iters is None else a.first_iters
     frames = make_frames(cfg, a.frames, dev)
     gt = torch.stack([f['c2w'] for f in frames])
