@@ -27,7 +27,9 @@ class SDFNet(nn.Module):
         self.config, self.input_ch, self.geo_feat_dim = config, input_ch, geo_feat_dim
         self.hidden_dim, self.num_layers = hidden_dim, num_layers
         if config['decoder']['tcnn_network']:
-            self.model = tcnn.Network(input_ch, 1 + geo_feat_dim, {})
+            self.model = tcnn.Network(input_ch, 1 + geo_feat_dim, {
+                'otype': 'FullyFusedMLP', 'activation': 'ReLU', 'output_activation': 'None',
+                'n_neurons': hidden_dim, 'n_hidden_layers': num_layers - 1})
         else:
             self.model = _stack([input_ch] + [hidden_dim] * (num_layers - 1) + [1 + geo_feat_dim])
 
@@ -44,7 +46,9 @@ class ColorNet(nn.Module):
         self.config, self.input_ch, self.geo_feat_dim = config, input_ch, geo_feat_dim
         self.hidden_dim_color, self.num_layers_color = hidden_dim_color, num_layers_color
         if config['decoder']['tcnn_network']:
-            self.model = tcnn.Network(input_ch + geo_feat_dim, 3, {})
+            self.model = tcnn.Network(input_ch + geo_feat_dim, 3, {
+                'otype': 'FullyFusedMLP', 'activation': 'ReLU', 'output_activation': 'None',
+                'n_neurons': hidden_dim_color, 'n_hidden_layers': num_layers_color - 1})
         else:
             self.model = _stack([input_ch + geo_feat_dim] + [hidden_dim_color] * (num_layers_color - 1) + [3])
 

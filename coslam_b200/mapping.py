@@ -33,8 +33,9 @@ from .keyframe import sample_ranges
 
 class BundleAdjuster(object):
     def __init__(self, model, config, kfdb, map_optimizer, device='cuda:0', group=None, device_sampler=False):
-        if not config['grid']['oneGrid']:
-            raise NotImplementedError('BundleAdjuster serves oneGrid: True (every shipped config); use the autograd path otherwise')
+        if not config['grid']['oneGrid'] or config['decoder']['tcnn_network']:
+            raise NotImplementedError('BundleAdjuster serves oneGrid: True, tcnn_network: False (every shipped config); '
+                                      'use the autograd path otherwise')
         self.n_imp = int(config['training']['n_importance'])
         self.model, self.config, self.kfdb, self.opt, self.device = model, config, kfdb, map_optimizer, torch.device(device)
         t = config['training']

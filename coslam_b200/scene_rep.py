@@ -84,18 +84,30 @@ class JointEncoding(nn.Module):
     # ---- helpers -----------------------------------------------------------------------------------------------
     def _fused(self):
         """(table, W1..W4) when the configuration is the one the fused kernels serve, else a loud error."""
-        if not self.config['grid']['oneGrid']:
-            raise NotImplementedError('coslam_b200: the fused path serves oneGrid: True (every shipped config)')
+        if self._modular():
+            raise NotImplementedError('coslam_b200: the fused path serves oneGrid: True, tcnn_network: False (every shipped config)')
         w = self.decoder.fused_weights()
         if w is None:
             raise NotImplementedError('coslam_b200: the fused path serves the 2-layer SDF / 2-layer colour decoder')
         return (self.embed_fn.params,) + tuple(w)
 
+    def _modular(self):
+        """True for the two config-reachable variants no shipped config uses: `oneGrid: False` and
+        `tcnn_network: True`.  They compose the stand-alone CUDA encodings with the torch decoder, like the reference does."""
+        return (not self.config['grid']['oneGrid']) or bool(self.config['decoder']['tcnn_network'])
+
+    def _decode_modular(self, flat):
+        if self.config['grid']['oneGrid']:
+            out = self.decoder(self.embed_fn(flat), self.embedpos_fn(flat))
+        else:
+            out = self.decoder(self.embed_fn(flat), self.embedpos_fn(flat), self.embed_fn_color(flat))
+        return out.float()                                           # fp16 from tcnn.Network; the rendering kernels take fp32
+
     def ray_points(self, rays_o, rays_d, z_vals, target_d=None):
         """raw [N,S,4] of the sample points o + d z.  oneGrid (every shipped config): the fused per-point kernels, lazily over
         the points the step can depend on when `target_d` is given (training).  Two-grid variant (`oneGrid: False`,
         model/scene_rep.py:56-58, 168-170): the stand-alone CUDA encodings and the torch decoder, like the reference."""
-        if self.config['grid']['oneGrid']:
+        if not self._modular():
             return ops.RayPointsFunction.apply(rays_o, rays_d, z_vals, *self._fused(), self.spec, target_d)
         pts = rays_o[..., None, :] + rays_d[..., None, :] * z_vals[..., :, None]        # model/scene_rep.py:258
         return self.run_network(pts)
@@ -142,7 +154,11 @@ class JointEncoding(nn.Module):
         if embed:
             e = self.embed_fn(flat)
             return torch.reshape(e, lead + [e.shape[-1]])
-        raw, geo = ops.PointsFunction.apply(flat, *self._fused(), self.spec, True, True)
+        if self._modular():
+            h = self.sdf_net(torch.cat([self.embed_fn(flat), self.embedpos_fn(flat)], dim=-1), return_geo=True).float()
+            raw, geo = h[..., :1].expand(-1, 4), h[..., 1:]
+        else:
+            raw, geo = ops.PointsFunction.apply(flat, *self._fused(), self.spec, True, True)
         sdf = torch.reshape(raw[..., 3], lead)
         if not return_geo:
             return sdf
@@ -154,15 +170,15 @@ class JointEncoding(nn.Module):
     def query_color_sdf(self, query_points):
         self._require_cuda(query_points)
         flat = torch.reshape(query_points, [-1, query_points.shape[-1]])
-        if not self.config['grid']['oneGrid']:
-            return self.decoder(self.embed_fn(flat), self.embedpos_fn(flat), self.embed_fn_color(flat))
+        if self._modular():
+            return self._decode_modular(flat)
         return ops.PointsFunction.apply(flat, *self._fused(), self.spec, True, False)[0]
 
     # ---- model/scene_rep.py:173-209 --------------------------------------------------------------------------------
     def run_network(self, inputs):
         self._require_cuda(inputs)
         flat = torch.reshape(inputs, [-1, inputs.shape[-1]])
-        if not self.config['grid']['oneGrid']:
+        if self._modular():
             if self.config['grid']['tcnn_encoding']:
                 flat = (flat - self.bounding_box[:, 0]) / (self.bounding_box[:, 1] - self.bounding_box[:, 0])
             out = self.query_color_sdf(flat)

@@ -141,11 +141,76 @@ class Encoding(nn.Module):
         return _OneBlobFunction.apply(x2, self.n_bins)
 
 
-class Network(nn.Module):
-    """tinycudann.Network is reachable only with decoder.tcnn_network: True (model/decoder.py:26,79); every shipped
-    config sets it False (configs/Replica/replica.yaml:60)."""
+class _HalfMlpFunction(torch.autograd.Function):
+    """bias-free ReLU MLP in tcnn's FullyFusedMLP arithmetic: fp16 operands and activations, fp32 accumulation inside each
+    product, fp16 output; backward in fp16 under tcnn's loss scale of 128 (bindings/torch/tinycudann/modules.py), parameter
+    gradients returned in fp32.  The products are library half GEMMs (cuBLAS through torch): this variant is config-reachable
+    but unused by every shipped config, so it is served, not fused."""
+    LOSS_SCALE = 128.0
 
-    def __init__(self, *args, **kwargs):
+    @staticmethod
+    def forward(ctx, x, params, shapes):
+        ws, off = [], 0
+        for o, i in shapes:
+            ws.append(params[off:off + o * i].view(o, i).to(torch.float16))
+            off += o * i
+        h = x.to(torch.float16)
+        pad = shapes[0][1] - h.shape[-1]
+        if pad:
+            h = torch.nn.functional.pad(h, (0, pad))
+        acts = [h]
+        for k, w in enumerate(ws):
+            h = h @ w.t()
+            if k != len(ws) - 1:
+                h = torch.relu_(h)
+            acts.append(h)
+        ctx.ws, ctx.acts, ctx.shapes, ctx.n_in, ctx.x_dtype = ws, acts[:-1], shapes, x.shape[-1], x.dtype
+        return h
+
+    @staticmethod
+    def backward(ctx, dy):
+        scale = _HalfMlpFunction.LOSS_SCALE
+        g = (dy.float() * scale).to(torch.float16)
+        d_params = []
+        for k in range(len(ctx.ws) - 1, -1, -1):
+            a = ctx.acts[k]
+            d_params.append((g.t() @ a).float().reshape(-1) / scale)
+            g = g @ ctx.ws[k]
+            if k:
+                g = g * (a > 0)
+        d_x = (g[..., :ctx.n_in].float() / scale).to(ctx.x_dtype) if ctx.needs_input_grad[0] else None
+        return d_x, torch.cat(d_params[::-1]), None
+
+
+class Network(nn.Module):
+    """tinycudann.Network with otype FullyFusedMLP (model/decoder.py:26-37, 79-90; reachable only with
+    `decoder.tcnn_network: True`, which every shipped config sets False, configs/Replica/replica.yaml:60).  One flat fp32
+    `params` (the master copy the optimiser steps), layers in order, each [out, in] row-major with the input width and the
+    output width padded to multiples of 16 as FullyFusedMLP requires; Xavier-uniform init over the padded shapes (upstream
+    behaviour, recalled -- parity at this boundary is unpinned).  Output is fp16, sliced to n_output_dims."""
+
+    def __init__(self, n_input_dims, n_output_dims, network_config, seed=1337):
         super().__init__()
-        raise NotImplementedError('coslam_b200: tcnn.Network (FullyFusedMLP, decoder.tcnn_network: True) is not served; '
-                                  'use tcnn_network: False as every shipped Co-SLAM config does')
+        cfg = dict(network_config)
+        if cfg.get('otype', 'FullyFusedMLP') not in ('FullyFusedMLP', 'CutlassMLP'):
+            raise NotImplementedError('coslam_b200.tcnn.Network: otype %r' % cfg.get('otype'))
+        if cfg.get('activation', 'ReLU') != 'ReLU' or cfg.get('output_activation', 'None') != 'None':
+            raise NotImplementedError('coslam_b200.tcnn.Network serves ReLU hidden / linear output (model/decoder.py:30-31)')
+        pad16 = lambda n: (n + 15) // 16 * 16
+        width, hidden = int(cfg['n_neurons']), int(cfg['n_hidden_layers'])
+        dims = [pad16(n_input_dims)] + [width] * hidden + [pad16(n_output_dims)]
+        self.n_input_dims, self.n_output_dims = n_input_dims, n_output_dims
+        self.shapes = tuple((dims[k + 1], dims[k]) for k in range(len(dims) - 1))
+        g = torch.Generator().manual_seed(seed)
+        chunks = []
+        for o, i in self.shapes:
+            bound = (6.0 / (o + i)) ** 0.5
+            chunks.append((torch.rand(o * i, generator=g) * 2 - 1) * bound)
+        self.params = nn.Parameter(torch.cat(chunks))
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise RuntimeError('coslam_b200.tcnn.Network has no CPU path (input is on %s)' % x.device)
+        lead = x.shape[:-1]
+        out = _HalfMlpFunction.apply(x.reshape(-1, self.n_input_dims), self.params, self.shapes)
+        return out[:, :self.n_output_dims].reshape(*lead, self.n_output_dims)

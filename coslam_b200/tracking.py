@@ -30,9 +30,9 @@ from ._lib import check, ptr, stream
 class FrameTracker(object):
     def __init__(self, model, config, n_rays=None, device='cuda:0', use_graph=True, fused=None):
         t, tr = config['tracking'], config['training']
-        can_fuse = bool(config['grid']['oneGrid'])
+        can_fuse = bool(config['grid']['oneGrid']) and not config['decoder']['tcnn_network']
         if fused and not can_fuse:
-            raise NotImplementedError('FrameTracker(fused=True) serves oneGrid: True (every shipped config)')
+            raise NotImplementedError('FrameTracker(fused=True) serves oneGrid: True, tcnn_network: False (every shipped config)')
         self.n_imp = int(tr['n_importance'])
         self.fused = can_fuse if fused is None else bool(fused)
         self.model, self.config, self.device = model, config, torch.device(device)

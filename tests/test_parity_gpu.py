@@ -848,3 +848,54 @@ def test_mesh_lattice_query_matches_chunked_loop():
     with torch.no_grad():
         raw = [model.query_color(vf[i:i + chunk, None, :]).cpu() for i in range(0, vf.shape[0], chunk)]
     assert torch.equal(col.cpu(), torch.cat(raw, 0).reshape(-1, 3))
+
+
+def test_tcnn_network_variant_trains_in_half_precision_like_the_fp32_decoder():
+    """`decoder.tcnn_network: True` (model/decoder.py:23-37, 76-90): the decoder is two
+    tinycudann.Network FullyFusedMLPs -- fp16 weights and activations, fp32 accumulation, fp16 output, one flat fp32 `params`
+    each.  With the fp32 decoder's matrices copied in, the raw output agrees within half precision, and the gradients of a
+    training step agree with the fp32 step on the same batch within a few per cent."""
+    cfg = synth.room0_config()
+    cfg['training']['perturb'] = 0.0
+    weights = synth.decoder_init(seed=3)
+    probe = JointEncodingFor(cfg)
+    table = synth.table_init(probe.embed_fn.params.numel(), 'trained', seed=9)
+    ref = util.make_cuda_model(cfg, table, weights, DEV)
+    cfg_h = synth.room0_config()
+    cfg_h['training']['perturb'] = 0.0
+    cfg_h['decoder']['tcnn_network'] = True
+    half = JointEncodingFor(cfg_h).to(DEV)
+    sdf_p, col_p = half.decoder.sdf_net.model, half.decoder.color_net.model
+    assert sdf_p.params.dtype == torch.float32 and sdf_p.shapes == ((32, 80), (16, 32)) and col_p.shapes == ((32, 64), (16, 32))
+    fw = [w.detach() for w in ref._fused()]
+    with torch.no_grad():
+        half.embed_fn.params.copy_(fw[0])
+        w3 = torch.nn.functional.pad(fw[3], (0, 1))                       # 63 -> 64 input columns
+        w4 = torch.nn.functional.pad(fw[4], (0, 0, 0, 13))                # 3 -> 16 output rows
+        sdf_p.params.copy_(torch.cat([fw[1].reshape(-1), fw[2].reshape(-1)]))
+        col_p.params.copy_(torch.cat([w3.reshape(-1), w4.reshape(-1)]))
+    n = 512
+    rays_o, rays_d, rgb, depth = (t.to(DEV) for t in synth.ray_batch(cfg, n, seed=4))
+    with torch.no_grad():
+        z = ref._sample(depth)
+        raw_ref = ref.ray_points(rays_o, rays_d, z)
+        raw_half = half.ray_points(rays_o, rays_d, z)
+    assert raw_half.dtype == torch.float32
+    scale = float(raw_ref.abs().max())
+    assert float((raw_half - raw_ref).abs().max()) <= 2e-2 * scale, float((raw_half - raw_ref).abs().max()) / scale
+    ref.train(); half.train()
+    _weighted_loss(cfg, ref.forward(rays_o, rays_d, rgb, depth)).backward()
+    ret = half.forward(rays_o, rays_d, rgb, depth)
+    _weighted_loss(cfg, ret).backward()
+    g_ref = [p.grad for p in ref._fused()]
+    g_sdf, g_col = sdf_p.params.grad, col_p.params.grad
+    assert g_sdf.dtype == torch.float32
+    def rel(a, b):
+        return float((a - b).norm() / b.norm())
+    assert rel(g_sdf[:32 * 80].view(32, 80), g_ref[1]) < 0.1
+    assert rel(g_sdf[32 * 80:].view(16, 32), g_ref[2]) < 0.1
+    assert rel(g_col[:32 * 64].view(32, 64)[:, :63], g_ref[3]) < 0.1
+    assert rel(g_col[32 * 64:].view(16, 32)[:3], g_ref[4]) < 0.1
+    assert rel(half.embed_fn.params.grad, g_ref[0]) < 0.1
+    with pytest.raises(NotImplementedError):
+        half._fused()
