@@ -83,6 +83,11 @@ def test_no_cpu_fallback():
         m.forward(rays_o, rays_d, rgb, depth)
     with pytest.raises(RuntimeError, match='no CPU path'):
         m.embed_fn(torch.rand(4, 3))
+    from coslam_b200 import tcnn
     with pytest.raises(NotImplementedError):
-        from coslam_b200 import tcnn
-        tcnn.Network(3, 3, {})
+        tcnn.Network(3, 3, {'otype': 'FullyFusedMLP', 'activation': 'Sigmoid', 'n_neurons': 32, 'n_hidden_layers': 1})
+    net = tcnn.Network(3, 3, {'otype': 'FullyFusedMLP', 'activation': 'ReLU', 'output_activation': 'None', 'n_neurons': 32,
+                              'n_hidden_layers': 1})
+    assert net.params.numel() == 32 * 16 + 16 * 32
+    with pytest.raises(RuntimeError, match='no CPU path'):
+        net(torch.rand(4, 3))
