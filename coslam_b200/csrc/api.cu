@@ -205,7 +205,7 @@ int cb200_smooth_points(int64_t n_side, float voxel, const float* jitter, const 
 }
 
 int cb200_smooth_tv(const float* f, int64_t n_side, int64_t n_feat, float grad_scale, float* d_f, double* tv_sum, void* stream) {
-    CB_REQUIRE(n_side >= 1 && n_side <= 1024 && n_feat >= 1 && n_feat <= 1024, "smooth_tv: bad lattice shape");
+    CB_REQUIRE(n_side >= 1 && n_side <= 1024 && n_feat >= 4 && n_feat <= 1024 && n_feat % 4 == 0, "smooth_tv: bad lattice shape");
     CB_REQUIRE(f && d_f, "smooth_tv: NULL buffer");
     return cuda_result(cb200::launch_smooth_tv(f, (int)n_side, (int)n_feat, grad_scale, d_f, tv_sum, (cudaStream_t)stream), "smooth_tv");
 }

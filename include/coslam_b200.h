@@ -196,13 +196,15 @@ int cb200_pose_adam(float* rot, float* trans, float* exp_avg_rot, float* exp_avg
                     float lr_trans, int64_t step, int zero_grad, void* stream);
 
 /* lattice of CoSLAM.smoothness (coslam.py:258-266), normalised: x [n^3, 3] = (((coords + jitter) * voxel + lo + offset) - lo)
- * / ext with torch's operation order; jitter / offset / bb_lo / bb_ext are HOST arrays of 3 floats. */
+ * / ext with torch's operation order; jitter / offset / bb_lo / bb_ext are HOST arrays of 3 floats.  Row p of x is the lattice
+ * node (ix, iy, iz) with p = (iz * n + iy) * n + ix (x fastest: the term sums over the whole lattice, and this order makes
+ * neighbouring threads touch neighbouring table entries). */
 int cb200_smooth_points(int64_t n_side, float voxel, const float* jitter, const float* offset, const float* bb_lo,
                         const float* bb_ext, float* x, void* stream);
 
 /* total variation of the lattice features (coslam.py:268-270): f [n,n,n,F] (cb200_hash_fwd on the lattice) ->
  * tv_sum (double, +=, may be NULL) = tv_x + tv_y + tv_z,  d_f [n,n,n,F] (=) = grad_scale * d tv / d f.
- * The caller passes grad_scale = smooth_weight / smooth_pts^3 and feeds d_f to cb200_hash_bwd. */
+ * The caller passes grad_scale = smooth_weight / smooth_pts^3 and feeds d_f to cb200_hash_bwd.  F must be a multiple of 4. */
 int cb200_smooth_tv(const float* f, int64_t n_side, int64_t n_feat, float grad_scale, float* d_f, double* tv_sum,
                     void* stream);
 

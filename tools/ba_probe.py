@@ -1,5 +1,5 @@
 """One bundle-adjustment call (room0 / scene0000 shapes, synthetic keyframe store) for profiling.
-    python tools/ba_probe.py [room0|scannet0000] [time|ncu] [n_keyframes]
+    python tools/ba_probe.py [room0|scannet0000|tum_desk|tum_desk_imp] [time|ncu] [n_keyframes]
 time: ms per iteration of BundleAdjuster.run for 10 and 100 iterations per call (separates the per-call host work from the
 per-iteration cost); ncu: one call, for `ncu --metrics gpu__time_duration.sum`."""
 import os
@@ -18,7 +18,7 @@ DEV = 'cuda:0'
 name = sys.argv[1] if len(sys.argv) > 1 else 'room0'
 mode = sys.argv[2] if len(sys.argv) > 2 else 'time'
 n_kf = int(sys.argv[3]) if len(sys.argv) > 3 else 8
-cfg = synth.CONFIGS[name]()
+cfg = synth.tum_desk_config(n_importance=128) if name == 'tum_desk_imp' else synth.CONFIGS[name]()
 H, W = cfg['cam']['H'], cfg['cam']['W']
 R = int(H * W * cfg['mapping']['n_pixels'])
 every = cfg['mapping']['keyframe_every']
