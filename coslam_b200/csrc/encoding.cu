@@ -98,6 +98,54 @@ __global__ void __launch_bounds__(256) hash_bwd_kernel(SceneDev sc, const float*
     }
 }
 
+// table gradient only (the smoothness term, coslam.py:251-274: the lattice points are constants): thread (p, l) like the
+// forward.  Neighbouring lanes that sit in the same cell with the same y / z weights (a row of an axis-aligned lattice whose
+// fastest axis is x, cb200_smooth_points) are summed in the warp first -- sum_p wx wy wz g = wy wz sum_p wx g, so four values
+// per lane are reduced, and the first lane of each run issues the eight reductions.  Any other point set has no such runs and
+// takes the direct path.
+__global__ void __launch_bounds__(256) hash_bwd_table_kernel(SceneDev sc, const float* __restrict__ x, const float* __restrict__ dy,
+                                                             int64_t n_points, float2* dtable) {
+    // level is the FASTEST block coordinate: the CTAs in flight spread their reductions over all levels' slices of the table
+    // instead of all landing on the few thousand entries of one coarse level
+    const int l = blockIdx.x % sc.n_levels;
+    const int64_t p = (int64_t)(blockIdx.x / sc.n_levels) * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool live = p < n_points;
+    const int64_t pc = live ? p : n_points - 1;
+    const uint32_t size = sc.offset[l + 1] - sc.offset[l];
+    uint32_t cell[3];
+    float w[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) grid_pos(sc.scale[l], x[pc * 3 + d], cell[d], w[d]);
+    float2 g = reinterpret_cast<const float2*>(dy)[pc * sc.n_levels + l];
+    if (!live) g = make_float2(0.f, 0.f);
+    bool same = lane != 0;
+    same &= __shfl_up_sync(0xffffffffu, cell[0], 1) == cell[0];
+    same &= __shfl_up_sync(0xffffffffu, cell[1], 1) == cell[1];
+    same &= __shfl_up_sync(0xffffffffu, cell[2], 1) == cell[2];
+    same &= __float_as_uint(__shfl_up_sync(0xffffffffu, w[1], 1)) == __float_as_uint(w[1]);
+    same &= __float_as_uint(__shfl_up_sync(0xffffffffu, w[2], 1)) == __float_as_uint(w[2]);
+    const uint32_t heads = __ballot_sync(0xffffffffu, !same);
+    float a0 = (1.f - w[0]) * g.x, a1 = (1.f - w[0]) * g.y, b0 = w[0] * g.x, b1 = w[0] * g.y;
+    if (heads != 0xffffffffu) {
+        const uint32_t above = lane == 31 ? 0u : heads >> (lane + 1);
+        const int end = above ? lane + __ffs(above) : 32;             // first lane of the next run
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const float t0 = __shfl_down_sync(0xffffffffu, a0, s), t1 = __shfl_down_sync(0xffffffffu, a1, s);
+            const float t2 = __shfl_down_sync(0xffffffffu, b0, s), t3 = __shfl_down_sync(0xffffffffu, b1, s);
+            if (lane + s < end) { a0 += t0; a1 += t1; b0 += t2; b1 += t3; }
+        }
+    }
+    if (same || !live) return;          // lanes past the end repeat the last point with g = 0: they extend its run or head a run of zeros
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const uint32_t idx = sc.offset[l] + grid_index(sc.hashed[l] != 0, size, sc.res[l], cell[0] + (c & 1), cell[1] + ((c >> 1) & 1), cell[2] + (c >> 2));
+        const float wyz = ((c & 2) ? w[1] : 1.f - w[1]) * ((c & 4) ? w[2] : 1.f - w[2]);
+        red_add_f2(dtable + idx, wyz * ((c & 1) ? b0 : a0), wyz * ((c & 1) ? b1 : a1));
+    }
+}
+
 // OneBlob: thread per (point, dim)
 __global__ void __launch_bounds__(256) oneblob_fwd_kernel(const float* __restrict__ x, int64_t n, int n_bins, float* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // flat (point, dim)
@@ -144,6 +192,12 @@ cudaError_t launch_hash_indices(const SceneDev& sc, const float* x, int64_t n, u
 cudaError_t launch_hash_bwd(const SceneDev& sc, const float* x, const float* table, const float* dy, int64_t n, float* dtable, float* dx,
                             cudaStream_t st) {
     if (n == 0) return cudaSuccess;
+    if (dtable && !dx) {
+        const int64_t blocks = (n + 255) / 256 * sc.n_levels;
+        if (blocks > 0x7fffffffLL) return cudaErrorInvalidValue;
+        hash_bwd_table_kernel<<<(unsigned)blocks, 256, 0, st>>>(sc, x, dy, n, reinterpret_cast<float2*>(dtable));
+        return cudaGetLastError();
+    }
     hash_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sc, x, reinterpret_cast<const float2*>(table), dy, n,
                                                                 reinterpret_cast<float2*>(dtable), dx);
     return cudaGetLastError();

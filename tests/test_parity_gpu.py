@@ -899,3 +899,36 @@ def test_tcnn_network_variant_trains_in_half_precision_like_the_fp32_decoder():
     assert rel(half.embed_fn.params.grad, g_ref[0]) < 0.1
     with pytest.raises(NotImplementedError):
         half._fused()
+
+
+@pytest.mark.parametrize('order', ['x_fastest', 'z_fastest', 'random'])
+def test_hash_backward_table_only_kernel_matches_general_kernel(order):
+    """cb200_hash_bwd without dx (the smoothness term) takes the (point, level) kernel that sums runs of lanes in one cell of an
+    axis-aligned lattice row inside the warp before the table reductions; with dx it takes the per-point kernel.  Same table
+    gradient either way, for the lattice in both orders (63 is no multiple of 32: runs cross rows and the tail is ragged)
+    and for scattered points (no runs at all)."""
+    import ctypes
+    from coslam_b200 import _lib
+    from coslam_b200._lib import check, ptr, stream
+    cfg = synth.room0_config()
+    enc = JointEncodingFor(cfg).embed_fn
+    n = 21
+    g = torch.Generator().manual_seed(3)
+    idx = torch.arange(n, dtype=torch.float32)
+    lat = torch.stack(torch.meshgrid(idx, idx, idx, indexing='ij'), -1) * 0.013 + 0.31      # [ix, iy, iz, 3], z fastest
+    if order == 'x_fastest':
+        x = lat.permute(2, 1, 0, 3).reshape(-1, 3)
+    elif order == 'z_fastest':
+        x = lat.reshape(-1, 3)
+    else:
+        x = torch.rand(n ** 3, 3, generator=g)
+    x = x.contiguous().to(DEV)
+    P = x.shape[0]
+    dy = torch.randn(P, 32, generator=g).to(DEV)
+    lib, grid = _lib.load(), enc.grid()
+    d_a, d_b, dx = torch.zeros_like(enc.params), torch.zeros_like(enc.params), torch.empty_like(x)
+    check(lib.cb200_hash_bwd(ctypes.byref(grid), ptr(x), ptr(enc.params), ptr(dy), ctypes.c_int64(P), ptr(d_a), None, stream()), 'table only')
+    check(lib.cb200_hash_bwd(ctypes.byref(grid), ptr(x), ptr(enc.params), ptr(dy), ctypes.c_int64(P), ptr(d_b), ptr(dx), stream()), 'general')
+    torch.cuda.synchronize()
+    assert float(d_b.abs().max()) > 0
+    assert float((d_a - d_b).abs().max()) <= 2e-5 * float(d_b.abs().max())
