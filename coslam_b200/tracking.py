@@ -75,8 +75,13 @@ class FrameTracker(object):
             self.ray_idx = torch.arange(n, dtype=torch.int64, device=dev)
             self.pose_slot = torch.zeros(n, dtype=torch.int64, device=dev)
             self.rays_o, self.rays_d = torch.zeros((n, 3), **f32), torch.zeros((n, 3), **f32)
-            self.zbuf = torch.zeros(16, dtype=torch.float64, device=dev)           # step workspace (8) | dL/d c2w (16 floats)
+            # everything an iteration starts from zero, cleared by ONE fill: step workspace (8 doubles) | dL/d c2w (16 floats) |
+            # coarse-pass loss sums (4 doubles) | pad to 256 bytes | dL/d rays_o, dL/d rays_d [2, n, 3]
+            self.zbytes = torch.zeros(256 + 24 * n, dtype=torch.uint8, device=dev)
+            self.zbuf = self.zbytes[:128].view(torch.float64)
             self.d_c2w = self.zbuf[8:].view(torch.float32)
+            self.sums0 = self.zbytes[128:160].view(torch.float64)
+            self.d_rays = self.zbytes[256:].view(torch.float32).view(2, n, 3)
             self.loss_out = torch.zeros(8, **f32)                                   # 4 losses | 4 d loss / d sum
             self.w_dev = torch.tensor(self.loss_w, **f32).unbind(0)
             self.g_rot = torch.zeros(nr, **f32)
@@ -106,7 +111,7 @@ class FrameTracker(object):
         spec = m.spec
         fw = m._fused()
         tb, w = fw[0].detach(), tuple(x.detach() for x in fw[1:])
-        self.zbuf.zero_()
+        self.zbytes.zero_()
         ws = self.zbuf[:8]
         td = self.target_d.view(-1)
         check(lib.cb200_assemble_rays_fwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(self.c2w), ctypes.c_int64(n),
@@ -122,7 +127,7 @@ class FrameTracker(object):
             z0 = m._sample(td)
             rays0 = (self.rays_o, self.rays_d, z0)
             raw0, _, mask0 = ops.points_forward(spec.scene(), tb, w, rays=rays0)
-            sums0 = torch.zeros(4, dtype=torch.float64, device=z0.device)
+            sums0 = self.sums0
             _, _, _, weights0 = ops._render_forward(spec, raw0, z0, self.target_s, td, loss_sums=sums0, want_weights=True)
             u = draw_uniforms(n, self.n_imp, z0.device, det=(self.config['training']['perturb'] == 0.))
             z, _ = ops.importance_sample(spec, z0, weights0, u, target_d=td, counts=counts, want_std=False)
@@ -137,15 +142,14 @@ class FrameTracker(object):
         check(lib.cb200_loss_finish(ptr(ws[4:8]), ptr(counts), ctypes.c_int64(n), ctypes.c_int64(z.shape[1]),
                                     ptr(self.loss_out[:4]), ptr(self.loss_out[4:]), stream()), 'loss_finish')
         d_raw = ops._render_backward(spec, raw, z, self.target_s, td, self.w_dev, self.loss_out[4:], None, None)
-        _, _, d_od = ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, need_table=False, need_mlp=False)
+        into = (None, None, self.d_rays)                             # both passes add into the same ray-gradient buffer
+        ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, accumulate=into)
         if coarse is not None:
             rays0, raw0, mask0, _ = coarse
             d_raw0 = ops._render_backward(spec, raw0, rays0[2], self.target_s, td, (self.w_dev[0], self.w_dev[1], None, None),
                                           self.loss_out[4:], None, None)
-            _, _, d_od0 = ops.points_backward(spec.scene(), tb, w, mask0, d_raw0, rays=rays0, need_table=False, need_mlp=False)
-            d_od[0].add_(d_od0[0])
-            d_od[1].add_(d_od0[1])
-        d_o, d_d = d_od
+            ops.points_backward(spec.scene(), tb, w, mask0, d_raw0, rays=rays0, accumulate=into)
+        d_o, d_d = self.d_rays[0], self.d_rays[1]
         check(lib.cb200_assemble_rays_bwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(d_o), ptr(d_d), ctypes.c_int64(n),
                                           ctypes.c_int64(1), ptr(self.d_c2w), stream()), 'assemble_rays_bwd')
         check(lib.cb200_track_update(ctypes.byref(self._steps[0 if k == 0 else 1]), stream()), 'track_update')
