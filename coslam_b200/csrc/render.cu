@@ -374,12 +374,16 @@ __global__ void __launch_bounds__(kRayWarps * 32) importance_sample_kernel(Impor
         for (int k = lane; k < nb - 1; k += 32) part += a.weights[ray * S + k + 1] + 1e-5f;      // utils.py:44
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        // utils.py:45-47: pdf in parallel (staged in the cdf row), then the cumulative sum in index order by one lane -- from
+        // shared memory: the serial loop used to wait for a global load of weights[k + 1] per step
+        for (int k = lane; k < nb - 1; k += 32) cdf[k + 1] = __fdiv_rn(a.weights[ray * S + k + 1] + 1e-5f, part);
         __syncwarp();
-        if (lane == 0) {                                             // utils.py:45-47, cumulative sum in index order
+        if (lane == 0) {
             float c = 0.f;
             cdf[0] = 0.f;
+#pragma unroll 4
             for (int k = 0; k < nb - 1; ++k) {
-                c = __fadd_rn(c, __fdiv_rn(a.weights[ray * S + k + 1] + 1e-5f, part));
+                c = __fadd_rn(c, cdf[k + 1]);
                 cdf[k + 1] = c;
             }
         }
@@ -411,12 +415,14 @@ __global__ void __launch_bounds__(kRayWarps * 32) importance_sample_kernel(Impor
             if (e < S) {
                 v = zrow[e];
                 pos = e;
+#pragma unroll 8
                 for (int j = 0; j < I; ++j) pos += samp[j] < v;
             } else {
                 const int i = e - S;
                 v = samp[i];
                 mean += v;
                 pos = 0;
+#pragma unroll 8
                 for (int j = 0; j < I; ++j) pos += (samp[j] < v) || (samp[j] == v && j < i);
                 int lo = 0, hi = S;                                  // #{z <= v}
                 while (lo < hi) {
