@@ -101,8 +101,9 @@ __global__ void __launch_bounds__(256) hash_bwd_kernel(SceneDev sc, const float*
 // table gradient only (the smoothness term, coslam.py:251-274: the lattice points are constants): thread (p, l) like the
 // forward.  Neighbouring lanes that sit in the same cell with the same y / z weights (a row of an axis-aligned lattice whose
 // fastest axis is x, cb200_smooth_points) are summed in the warp first -- sum_p wx wy wz g = wy wz sum_p wx g, so four values
-// per lane are reduced, and the first lane of each run issues the eight reductions.  Any other point set has no such runs and
-// takes the direct path.
+// per lane are reduced, and the first lane of each run issues the eight reductions.  The same holds with z fastest (the
+// reference's own lattice order, CoSLAM.smoothness through autograd).  Any other point set has no such runs and takes the
+// direct path.
 __global__ void __launch_bounds__(256) hash_bwd_table_kernel(SceneDev sc, const float* __restrict__ x, const float* __restrict__ dy,
                                                              int64_t n_points, float2* dtable) {
     // level is the FASTEST block coordinate: the CTAs in flight spread their reductions over all levels' slices of the table
@@ -119,14 +120,22 @@ __global__ void __launch_bounds__(256) hash_bwd_table_kernel(SceneDev sc, const 
     for (int d = 0; d < 3; ++d) grid_pos(sc.scale[l], x[pc * 3 + d], cell[d], w[d]);
     float2 g = reinterpret_cast<const float2*>(dy)[pc * sc.n_levels + l];
     if (!live) g = make_float2(0.f, 0.f);
-    bool same = lane != 0;
-    same &= __shfl_up_sync(0xffffffffu, cell[0], 1) == cell[0];
-    same &= __shfl_up_sync(0xffffffffu, cell[1], 1) == cell[1];
-    same &= __shfl_up_sync(0xffffffffu, cell[2], 1) == cell[2];
-    same &= __float_as_uint(__shfl_up_sync(0xffffffffu, w[1], 1)) == __float_as_uint(w[1]);
-    same &= __float_as_uint(__shfl_up_sync(0xffffffffu, w[2], 1)) == __float_as_uint(w[2]);
-    const uint32_t heads = __ballot_sync(0xffffffffu, !same);
-    float a0 = (1.f - w[0]) * g.x, a1 = (1.f - w[0]) * g.y, b0 = w[0] * g.x, b1 = w[0] * g.y;
+    bool cell_same = lane != 0;
+    cell_same &= __shfl_up_sync(0xffffffffu, cell[0], 1) == cell[0];
+    cell_same &= __shfl_up_sync(0xffffffffu, cell[1], 1) == cell[1];
+    cell_same &= __shfl_up_sync(0xffffffffu, cell[2], 1) == cell[2];
+    bool eq[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) eq[d] = __float_as_uint(__shfl_up_sync(0xffffffffu, w[d], 1)) == __float_as_uint(w[d]);
+    // the lattice's fastest axis is the one whose weight changes along a run: x (cb200_smooth_points) or z (the reference's
+    // meshgrid order, CoSLAM.smoothness through autograd); the warp takes whichever gives it more merged lanes
+    const uint32_t run_x = __ballot_sync(0xffffffffu, cell_same && eq[1] && eq[2]);
+    const uint32_t run_z = __ballot_sync(0xffffffffu, cell_same && eq[0] && eq[1]);
+    const int axis = __popc(run_z) > __popc(run_x) ? 2 : 0;
+    const uint32_t heads = ~(axis == 2 ? run_z : run_x);
+    const bool same = !((heads >> lane) & 1u);
+    const float wa = axis == 2 ? w[2] : w[0];
+    float a0 = (1.f - wa) * g.x, a1 = (1.f - wa) * g.y, b0 = wa * g.x, b1 = wa * g.y;
     if (heads != 0xffffffffu) {
         const uint32_t above = lane == 31 ? 0u : heads >> (lane + 1);
         const int end = above ? lane + __ffs(above) : 32;             // first lane of the next run
@@ -141,8 +150,12 @@ __global__ void __launch_bounds__(256) hash_bwd_table_kernel(SceneDev sc, const 
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         const uint32_t idx = sc.offset[l] + grid_index(sc.hashed[l] != 0, size, sc.res[l], cell[0] + (c & 1), cell[1] + ((c >> 1) & 1), cell[2] + (c >> 2));
-        const float wyz = ((c & 2) ? w[1] : 1.f - w[1]) * ((c & 4) ? w[2] : 1.f - w[2]);
-        red_add_f2(dtable + idx, wyz * ((c & 1) ? b0 : a0), wyz * ((c & 1) ? b1 : a1));
+        float wo = 1.f;                 // the two weights that are constant along the run
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+            if (d != axis) wo *= ((c >> d) & 1) ? w[d] : 1.f - w[d];
+        const bool hi = (c >> axis) & 1;
+        red_add_f2(dtable + idx, wo * (hi ? b0 : a0), wo * (hi ? b1 : a1));
     }
 }
 
