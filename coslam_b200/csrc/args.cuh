@@ -83,6 +83,13 @@ struct RenderArgs {
     float* d_raw;              // [N,S,4]
 };
 
+cudaError_t launch_assemble_rays_fwd2(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, long long n_first,
+                                      const float* cur_rays, const long long* idx_cur, const long long* slot_cur, long long n_cur,
+                                      const float* poses, long long n_poses, float* rays_o, float* rays_d, float* target_rgb,
+                                      float* target_d, cudaStream_t st);
+cudaError_t launch_assemble_rays_bwd2(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, long long n_first,
+                                      const float* cur_rays, const long long* idx_cur, const long long* slot_cur, long long n_cur,
+                                      const float* d_rays_o, const float* d_rays_d, long long n_poses, float* d_poses, cudaStream_t st);
 cudaError_t launch_assemble_rays_fwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* poses,
                                      long long n, long long n_poses, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
                                      cudaStream_t st);

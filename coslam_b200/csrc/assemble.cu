@@ -21,14 +21,27 @@ struct AssembleArgs {
     const float* d_rays_o;       // backward
     const float* d_rays_d;
     float* d_poses;              // [K,4,4] +=
+    // optional second source: rays i >= n_first come from (kf_rays2, ray_idx2[i - n_first], pose_slot2[i - n_first]) -- the
+    // current frame's rays behind the keyframe rays of a bundle-adjustment batch (coslam.py:339-344) in ONE launch
+    long long n_first;
+    const float* kf_rays2;
+    const long long* ray_idx2;
+    const long long* pose_slot2;
 };
+
+__device__ __forceinline__ const float* assemble_source(const AssembleArgs& a, long long i, long long& slot) {
+    const bool second = i >= a.n_first;
+    const long long j = second ? i - a.n_first : i;
+    slot = (second ? a.pose_slot2 : a.pose_slot)[j];
+    if (slot < 0) slot += a.n_poses;
+    return (second ? a.kf_rays2 : a.kf_rays) + (second ? a.ray_idx2 : a.ray_idx)[j] * 7;
+}
 
 __global__ void __launch_bounds__(256) assemble_rays_fwd_kernel(AssembleArgs a) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.n) return;
-    const float* r = a.kf_rays + a.ray_idx[i] * 7;
-    long long slot = a.pose_slot[i];
-    if (slot < 0) slot += a.n_poses;
+    long long slot;
+    const float* r = assemble_source(a, i, slot);
     const float* T = a.poses + slot * 16;
     const float d0 = r[0], d1 = r[1], d2 = r[2];
 #pragma unroll
@@ -63,9 +76,8 @@ __global__ void __launch_bounds__(256) assemble_rays_bwd_kernel(AssembleArgs a, 
         for (int k = 0; k < 12; ++k) atomicAdd(dst + k, w[k]);           // rows of 4: [slot][row][0..3] is contiguous in both layouts
     };
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (long long)gridDim.x * blockDim.x) {
-        const float* r = a.kf_rays + a.ray_idx[i] * 7;
-        long long slot = a.pose_slot[i];
-        if (slot < 0) slot += a.n_poses;
+        long long slot;
+        const float* r = assemble_source(a, i, slot);
         if (slot != cur) {
             if (cur >= 0) emit(cur, v);
 #pragma unroll
@@ -104,28 +116,58 @@ __global__ void __launch_bounds__(256) assemble_rays_bwd_kernel(AssembleArgs a, 
     }
 }
 
-cudaError_t launch_assemble_rays_fwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* poses,
-                                     long long n, long long n_poses, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
-                                     cudaStream_t st) {
-    AssembleArgs a{kf_rays, ray_idx, pose_slot, poses, n, n_poses, rays_o, rays_d, target_rgb, target_d, nullptr, nullptr, nullptr};
-    assemble_rays_fwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a);
+static cudaError_t run_assemble_fwd(const AssembleArgs& a, cudaStream_t st) {
+    if (a.n <= 0) return cudaSuccess;
+    assemble_rays_fwd_kernel<<<(unsigned)((a.n + 255) / 256), 256, 0, st>>>(a);
     return cudaGetLastError();
 }
 
-cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* d_rays_o,
-                                     const float* d_rays_d, long long n, long long n_poses, float* d_poses, cudaStream_t st) {
-    AssembleArgs a{kf_rays, ray_idx, pose_slot, nullptr, n, n_poses, nullptr, nullptr, nullptr, nullptr, d_rays_o, d_rays_d, d_poses};
-    const int use_shared = n_poses <= kMaxSharedPoses;
-    const size_t smem = use_shared ? sizeof(float) * 12 * (size_t)n_poses : 0;
+static cudaError_t run_assemble_bwd(const AssembleArgs& a, cudaStream_t st) {
+    if (a.n <= 0) return cudaSuccess;
+    const int use_shared = a.n_poses <= kMaxSharedPoses;
+    const size_t smem = use_shared ? sizeof(float) * 12 * (size_t)a.n_poses : 0;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(assemble_rays_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    long long blocks = (n + 255) / 256;                        // one ray per thread up to 4 CTAs per SM, grid-stride beyond
+    long long blocks = (a.n + 255) / 256;                      // one ray per thread up to 4 CTAs per SM, grid-stride beyond
     if (blocks < 1) blocks = 1;
     if (blocks > 148 * 4) blocks = 148 * 4;
     assemble_rays_bwd_kernel<<<(unsigned)blocks, 256, smem, st>>>(a, use_shared);
     return cudaGetLastError();
+}
+
+cudaError_t launch_assemble_rays_fwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* poses,
+                                     long long n, long long n_poses, float* rays_o, float* rays_d, float* target_rgb, float* target_d,
+                                     cudaStream_t st) {
+    AssembleArgs a{kf_rays, ray_idx, pose_slot, poses, n, n_poses, rays_o, rays_d, target_rgb, target_d, nullptr, nullptr, nullptr,
+                   n, nullptr, nullptr, nullptr};
+    return run_assemble_fwd(a, st);
+}
+
+cudaError_t launch_assemble_rays_bwd(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, const float* d_rays_o,
+                                     const float* d_rays_d, long long n, long long n_poses, float* d_poses, cudaStream_t st) {
+    AssembleArgs a{kf_rays, ray_idx, pose_slot, nullptr, n, n_poses, nullptr, nullptr, nullptr, nullptr, d_rays_o, d_rays_d, d_poses,
+                   n, nullptr, nullptr, nullptr};
+    return run_assemble_bwd(a, st);
+}
+
+// keyframe rays [0, n_first) and current-frame rays [n_first, n) of one BA batch in one launch (csrc/runtime.cu)
+cudaError_t launch_assemble_rays_fwd2(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, long long n_first,
+                                      const float* cur_rays, const long long* idx_cur, const long long* slot_cur, long long n_cur,
+                                      const float* poses, long long n_poses, float* rays_o, float* rays_d, float* target_rgb,
+                                      float* target_d, cudaStream_t st) {
+    AssembleArgs a{kf_rays, ray_idx, pose_slot, poses, n_first + n_cur, n_poses, rays_o, rays_d, target_rgb, target_d, nullptr, nullptr,
+                   nullptr, n_first, cur_rays, idx_cur, slot_cur};
+    return run_assemble_fwd(a, st);
+}
+
+cudaError_t launch_assemble_rays_bwd2(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, long long n_first,
+                                      const float* cur_rays, const long long* idx_cur, const long long* slot_cur, long long n_cur,
+                                      const float* d_rays_o, const float* d_rays_d, long long n_poses, float* d_poses, cudaStream_t st) {
+    AssembleArgs a{kf_rays, ray_idx, pose_slot, nullptr, n_first + n_cur, n_poses, nullptr, nullptr, nullptr, nullptr, d_rays_o, d_rays_d,
+                   d_poses, n_first, cur_rays, idx_cur, slot_cur};
+    return run_assemble_bwd(a, st);
 }
 
 }  // namespace cb200

@@ -1,7 +1,8 @@
 // Native iteration runtime: one C call issues every launch of a bundle-adjustment iteration (coslam.py:336-390), so the
 // host pays ~30 cudaLaunchKernel calls instead of ~30 Python -> ctypes round trips with tensor bookkeeping in between
 // (1.5 ms -> the GPU time of the kernels at room0's 2048 + rays).  It only sequences the library's own public entry
-// points (include/coslam_b200.h) on the caller's stream; no allocation, no synchronisation.
+// points (include/coslam_b200.h) on the caller's stream -- plus the two-source ray assembly of assemble.cu, which gathers the
+// keyframe rays and the current frame's rays of a batch in one launch; no allocation, no synchronisation.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -9,6 +10,16 @@
 #include <vector>
 
 #include "../../include/coslam_b200.h"
+
+namespace cb200 {
+cudaError_t launch_assemble_rays_fwd2(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, long long n_first,
+                                      const float* cur_rays, const long long* idx_cur, const long long* slot_cur, long long n_cur,
+                                      const float* poses, long long n_poses, float* rays_o, float* rays_d, float* target_rgb,
+                                      float* target_d, cudaStream_t st);
+cudaError_t launch_assemble_rays_bwd2(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, long long n_first,
+                                      const float* cur_rays, const long long* idx_cur, const long long* slot_cur, long long n_cur,
+                                      const float* d_rays_o, const float* d_rays_d, long long n_poses, float* d_poses, cudaStream_t st);
+}  // namespace cb200
 
 namespace {
 
@@ -48,11 +59,11 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
     int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
     CB_TRY(cuda_rc(cudaMemsetAsync(p->ws, 0, 10 * sizeof(double), st)));
     if (p->d_rays) CB_TRY(cuda_rc(cudaMemsetAsync(p->d_rays, 0, sizeof(float) * 6 * n, st)));
-    if (g > 0)
-        CB_TRY(cb200_assemble_rays_fwd(p->kf_rays, p->idx_global + it * g, p->slot_global + it * g, p->poses_all, g, p->n_poses, p->rays_o,
-                                       p->rays_d, p->target_rgb, p->target_d, stream));
-    CB_TRY(cb200_assemble_rays_fwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->poses_all, p->n_cur, p->n_poses, p->rays_o + 3 * g,
-                                   p->rays_d + 3 * g, p->target_rgb + 3 * g, p->target_d + g, stream));
+    if (!p->cur_rays || !p->poses_all || !p->idx_cur || !p->slot_cur || (g > 0 && (!p->kf_rays || !p->idx_global || !p->slot_global))) return -1;
+    CB_TRY(cuda_rc(cb200::launch_assemble_rays_fwd2(
+        p->kf_rays, reinterpret_cast<const long long*>(p->idx_global) + it * g, reinterpret_cast<const long long*>(p->slot_global) + it * g, g,
+        p->cur_rays, reinterpret_cast<const long long*>(p->idx_cur) + it * p->n_cur, reinterpret_cast<const long long*>(p->slot_cur), p->n_cur,
+        p->poses_all, p->n_poses, p->rays_o, p->rays_d, p->target_rgb, p->target_d, st)));
     const float* noise = p->noise ? p->noise + it * n * S0 : nullptr;
     const uint64_t seed = p->seeds ? p->seeds[it] : 0;
     if (I > 0) {
@@ -115,11 +126,11 @@ int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
                                 stream));
     }
     if (p->d_rays) {
-        if (g > 0)
-            CB_TRY(cb200_assemble_rays_bwd(p->kf_rays, p->idx_global + it * g, p->slot_global + it * g, p->d_rays, p->d_rays + 3 * n, g, p->n_poses,
-                                           p->d_poses, stream));
-        CB_TRY(cb200_assemble_rays_bwd(p->cur_rays, p->idx_cur + it * p->n_cur, p->slot_cur, p->d_rays + 3 * g, p->d_rays + 3 * n + 3 * g, p->n_cur,
-                                       p->n_poses, p->d_poses, stream));
+        if (!p->d_poses) return -1;
+        CB_TRY(cuda_rc(cb200::launch_assemble_rays_bwd2(
+            p->kf_rays, reinterpret_cast<const long long*>(p->idx_global) + it * g, reinterpret_cast<const long long*>(p->slot_global) + it * g, g,
+            p->cur_rays, reinterpret_cast<const long long*>(p->idx_cur) + it * p->n_cur, reinterpret_cast<const long long*>(p->slot_cur), p->n_cur,
+            p->d_rays, p->d_rays + 3 * n, p->n_poses, p->d_poses, (cudaStream_t)stream)));
     }
     if (p->smooth_side > 0) {
         const int64_t m = p->smooth_side * p->smooth_side * p->smooth_side;
