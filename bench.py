@@ -25,6 +25,8 @@ if ROOT not in sys.path:
 
 import torch                                   # noqa: E402
 
+_STDOUT = sys.stdout                           # where the JSON line goes (see __main__)
+
 from coslam_b200 import synth                  # noqa: E402
 
 METRIC = 'rays_per_sec_render_fwd_bwd'
@@ -160,7 +162,7 @@ def run_reference(args):
                    'rays_per_step': args.cpu_rays, 'samples_per_ray': S},
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-        'gpu_launches': 0}))
+        'gpu_launches': 0}), file=_STDOUT, flush=True)
 
 
 def run_ours(args):
@@ -314,7 +316,7 @@ def run_ours(args):
             'cpu_baseline': cpu,
         }
         out.update(extra)
-        print(json.dumps(out))
+        print(json.dumps(out), file=_STDOUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -400,6 +402,9 @@ def time_mapping(model, cfg, dev, n_kf=8, calls=5):
 
 if __name__ == '__main__':
     a = parse()
+    # stdout carries the ONE JSON line only: the model's construction messages (the reference prints the same ones,
+    # model/scene_rep.py:36, encodings.py) and anything a library writes go to stderr
+    sys.stdout = sys.stderr
     if a.impl == 'reference':
         run_reference(a)
     else:
