@@ -404,6 +404,9 @@ if __name__ == '__main__':
     a = parse()
     # stdout carries the ONE JSON line only: the model's construction messages (the reference prints the same ones,
     # model/scene_rep.py:36, encodings.py) and anything a library writes go to stderr
+    sys.stdout.flush()
+    _STDOUT = os.fdopen(os.dup(1), 'w')      # keep the real stdout for the JSON line ...
+    os.dup2(2, 1)                            # ... and send file descriptor 1 to stderr too (NCCL prints its version banner there from C)
     sys.stdout = sys.stderr
     if a.impl == 'reference':
         run_reference(a)
