@@ -128,6 +128,16 @@ int cb200_hash_indices(const cb200_grid* grid, const float* x, int64_t n_points,
     return cuda_result(cb200::launch_hash_indices(cb200::make_scene_dev(*grid), x, n_points, idx, (cudaStream_t)stream), "hash_indices");
 }
 
+int cb200_debug_gather_peak(const cb200_grid* grid, const uint32_t* idx, int64_t n_points, const float* table, float* dtable, int mode,
+                            float* sink, void* stream) {
+    if (int rc = check_grid(grid)) return rc;
+    CB_REQUIRE(grid->n_levels == CB200_MAX_LEVELS, "gather_peak: expects %d levels", CB200_MAX_LEVELS);
+    CB_REQUIRE(mode >= 1 && mode <= 3, "gather_peak: mode must be 1 (gather), 2 (reduce) or 3 (both)");
+    CB_REQUIRE(n_points >= 0 && idx && sink && ((mode & 1) == 0 || table) && ((mode & 2) == 0 || dtable), "gather_peak: NULL buffer");
+    return cuda_result(cb200::launch_gather_peak(cb200::make_scene_dev(*grid), idx, n_points, table, dtable, mode, sink, (cudaStream_t)stream),
+                       "gather_peak");
+}
+
 int cb200_oneblob_fwd(const float* x, int64_t n_points, uint32_t n_dims, uint32_t n_bins, float* out, void* stream) {
     CB_REQUIRE(n_points >= 0 && n_dims >= 1 && n_bins >= 1, "oneblob_fwd: bad sizes");
     CB_REQUIRE(n_points == 0 || (x && out), "oneblob_fwd: NULL buffer");

@@ -123,6 +123,8 @@ cudaError_t launch_points_bwd(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_debug_positions(const PointsArgs& a, float* pts_out, float* x_out, cudaStream_t st);
 cudaError_t launch_hash_fwd(const SceneDev& sc, const float* x, const float* table, int64_t n, float* out, cudaStream_t st);
 cudaError_t launch_hash_indices(const SceneDev& sc, const float* x, int64_t n, uint32_t* idx, cudaStream_t st);
+cudaError_t launch_gather_peak(const SceneDev& sc, const uint32_t* idx, int64_t n_points, const float* table, float* dtable, int mode,
+                               float* sink, cudaStream_t st);
 cudaError_t launch_hash_bwd(const SceneDev& sc, const float* x, const float* table, const float* dy, int64_t n, float* dtable, float* dx,
                             cudaStream_t st);
 cudaError_t launch_oneblob_fwd(const float* x, int64_t n_flat, int n_bins, float* out, cudaStream_t st);

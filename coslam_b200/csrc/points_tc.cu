@@ -676,20 +676,26 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
             }
             if (a.d_rays_o) {
                 // segmented sum over the 16 consecutive points of this warp (even lanes; odd lanes mirror them)
+                // A run = adjacent slots of one ray.  The merge is bounded by the run's end (head-flag ballot), not by equal ray
+                // ids alone: the compacted list appends 1024-point blocks in arbitrary order, so a ray cut by a block boundary
+                // can reappear in the same warp window behind another block's points (X, Y, X) and must not be summed twice.
                 const int64_t ray = valid_g ? pg / a.n_samples : -1;
+                const int64_t rprev = __shfl_up_sync(0xffffffffu, ray, 2);
+                const bool head = lane < 2 || rprev != ray;
+                const uint32_t heads = __ballot_sync(0xffffffffu, head && xb == 0);
+                const uint32_t above = heads & ~((2u << (lane & ~1)) - 1u);
+                const int run_end = above ? __ffs(above) - 1 : 32;
                 float v6[6] = {dp[0], dp[1], dp[2], dp[0] * zray, dp[1] * zray, dp[2] * zray};
 #pragma unroll
                 for (int o = 2; o < 32; o <<= 1) {
-                    const int64_t r2 = __shfl_down_sync(0xffffffffu, ray, o);
-                    const bool take = (lane + o < 32) && (r2 == ray);
+                    const bool take = ((lane & ~1) + o < run_end);
 #pragma unroll
                     for (int i = 0; i < 6; ++i) {
                         const float t = __shfl_down_sync(0xffffffffu, v6[i], o);
                         if (take) v6[i] += t;
                     }
                 }
-                const int64_t rprev = __shfl_up_sync(0xffffffffu, ray, 2);
-                if (valid_g && xb == 0 && (lane < 2 || rprev != ray)) {
+                if (valid_g && xb == 0 && head) {
 #pragma unroll
                     for (int d = 0; d < 3; ++d) {
                         atomicAdd(a.d_rays_o + ray * 3 + d, v6[d]);

@@ -45,8 +45,9 @@ def scannet0000_config(hash_size=16):
     return c
 
 
-def tum_desk_config(n_importance=0):
-    """configs/Tum/tum.yaml + fr1_desk.yaml; this fork's tum.yaml:89 sets n_importance 128."""
+def tum_desk_config(n_importance=0, perturb=1):
+    """configs/Tum/tum.yaml + fr1_desk.yaml; this fork's tum.yaml:89 sets n_importance 128 (perturb 1, tum.yaml:90;
+    perturb 0 selects sample_pdf's deterministic uniforms, model/utils.py:50)."""
     c = room0_config()
     c['grid'].update({'hash_size': 16, 'voxel_sdf': 0.02, 'voxel_color': 0.04})
     c['cam'].update({'H': 480, 'W': 640, 'fx': 517.3, 'fy': 516.5, 'cx': 318.6, 'cy': 255.3, 'near': 0, 'far': 5,
@@ -54,7 +55,7 @@ def tum_desk_config(n_importance=0):
     c['training'].update({'rgb_weight': 1.0, 'depth_weight': 0.1, 'sdf_weight': 5000, 'fs_weight': 10,
                           'smooth_weight': 0.00000001, 'smooth_pts': 64, 'smooth_vox': 0.04, 'smooth_margin': 0.,
                           'n_samples_d': 64, 'range_d': 0.25, 'n_range_d': 21, 'n_importance': n_importance,
-                          'trunc': 0.05, 'rgb_missing': 1.0})
+                          'perturb': perturb, 'trunc': 0.05, 'rgb_missing': 1.0})
     c['mapping'].update({'bound': [[-3.5, 3], [-3, 3], [-3, 3]], 'iters': 20})
     return c
 

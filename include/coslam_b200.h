@@ -419,6 +419,12 @@ size_t cb200_sizeof(int which);
 int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals,
                           int64_t n_rays, int64_t n_samples, float* pts, float* x, void* stream);
 
+/* measurement hook (tools/l2_gather_peak.py): float2 gathers (mode 1), red.add.v2.f32 reductions (mode 2) or both (mode 3) over
+ * the corner list idx [P, L, 8] of cb200_hash_indices, lane pair per point like the fused kernels, no other arithmetic --
+ * the measured L2 gather / reduction ceiling the roofline fractions of points_fwd / points_bwd are quoted against */
+int cb200_debug_gather_peak(const cb200_grid* grid, const uint32_t* idx, int64_t n_points, const float* table, float* dtable,
+                            int mode, float* sink, void* stream);
+
 /* test hook for the tcgen05 decoder plumbing (one 128-row tile, bf16 hi/lo split, three MMAs per reduction step):
  *   mode 0: c[128,n] = a[128,k] * b[n,k]^T     mode 1: c[128,n] = a[128,128]^T * b[128,n]     (fp32 row-major) */
 int cb200_selftest_mma(const float* a, const float* b, int k, int n, int mode, float* c, void* stream);

@@ -5,7 +5,7 @@ oracle/tcnn_shim.py standing in for the un-vendored tinycudann) on the seeded sy
 coslam_b200/synth.py, checks that the restatement oracle/coslam_oracle.py reproduces it, and writes the fixtures under
 tests/golden/.  Works only where /root/reference exists (the build container); the fixtures travel with the repo.
 
-    python -m oracle.gen_golden
+    python -m oracle.gen_golden [case names ...]
 """
 import hashlib
 import os
@@ -29,7 +29,18 @@ CASES = [
     ('room0_trained', 'room0', {}, 128, 'trained', 1, {}),
     ('scannet0000_trained', 'scannet0000', {}, 64, 'trained', 2, {}),
     ('tum_desk_trained', 'tum_desk', {'n_importance': 0}, 64, 'trained', 3, {'over_trunc_frac': 0.05}),
+    # hierarchical pass (this fork's configs/Tum/tum.yaml:89 ships n_importance 128): the reference's
+    # own sample_pdf (model/utils.py:32-71) and second pass (scene_rep.py:262-295, 327-332), with the deterministic
+    # uniforms of perturb 0 and with the CPU generator's draws of perturb 1
+    ('tum_desk_imp128_det', 'tum_desk', {'n_importance': 128, 'perturb': 0}, 64, 'trained', 5, {'over_trunc_frac': 0.05}),
+    ('tum_desk_imp128', 'tum_desk', {'n_importance': 128, 'perturb': 1}, 64, 'trained', 6, {'over_trunc_frac': 0.05}),
+    ('tum_desk_imp8_det', 'tum_desk', {'n_importance': 8, 'perturb': 0}, 96, 'trained', 7, {'over_trunc_frac': 0.05}),
+    ('tum_desk_imp8', 'tum_desk', {'n_importance': 8, 'perturb': 1}, 96, 'trained', 8, {'over_trunc_frac': 0.05}),
+    # BASELINE config 1's size: the direct (no activation-pattern injection) 1e-3 gradient gate over ~176 k points.
+    # Per-point tensors are stored as checksums / strided samples to keep the fixture small.
+    ('room0_4096', 'room0', {}, 4096, 'trained', 4, {}),
 ]
+LARGE = {'room0_4096'}
 
 
 def checksum(t):
@@ -74,8 +85,12 @@ def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
     model.train()
 
     S = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
+    n_imp = cfg['training']['n_importance']
+    perturb = cfg['training']['perturb'] > 0.
+    # the CPU generator's draws in the reference's order: scene_rep.py:255 (jitter), then model/utils.py:53 (sample_pdf)
     torch.manual_seed(NOISE_SEED)
-    noise = torch.rand((n_rays, S))
+    noise = torch.rand((n_rays, S)) if perturb else None
+    u_imp = torch.rand((n_rays, n_imp)) if (n_imp > 0 and perturb) else None
 
     # ---- the reference, training mode: forward + backward of the weighted loss (coslam.py:140-160) -------------
     ro = rays_o.clone().requires_grad_(True)
@@ -98,7 +113,7 @@ def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
     orc.load_weights(table, *weights)
     o2 = rays_o.clone().requires_grad_(True)
     d2 = rays_d.clone().requires_grad_(True)
-    r2 = orc.forward(o2, d2, rgb, depth, noise=noise)
+    r2 = orc.forward(o2, d2, rgb, depth, noise=noise, noise_imp=u_imp)
     orc.total_loss(r2).backward()
 
     def close(a, b, what, rtol=1e-5, atol=1e-7):
@@ -130,16 +145,31 @@ def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
     n_idx = min(2048, x.shape[0])
     idx = torch.stack([tcnn_shim.hash_corner_indices(x[:n_idx], meta, l)[0] for l in range(16)], 1)   # [n,16,8]
 
+    if n_imp > 0:
+        # the merged samples, the coarse maps and the spread of the drawn depths (scene_rep.py:268-293), eval dictionary
+        assert ev['z_vals'].shape == (n_rays, S + n_imp)
+        for k in ('rgb0', 'depth0', 'depth_var0', 'acc0', 'z_std'):
+            close(r2[k], ev[k], k)
+    large = name in LARGE
+    stride = 16 if large else 1
+
     out = {
         'cfg_name': cfg_name, 'cfg_kw': repr(cfg_kw), 'n_rays': n_rays, 'table_kind': table_kind, 'seed': seed,
         'batch_kw': repr(batch_kw), 'noise_seed': NOISE_SEED,
         'chk_rays_o': checksum(rays_o), 'chk_rays_d': checksum(rays_d), 'chk_rgb': checksum(rgb), 'chk_depth': checksum(depth),
         'chk_table': checksum(table), 'chk_w': checksum(torch.cat([w.reshape(-1) for w in weights])),
-        'noise': noise.numpy(), 'z_vals': z.numpy(), 'pts': pts.reshape(-1, 3).numpy(), 'x': x.numpy(),
+        # `noise` [N,S] and `u_imp` [N,I] are torch.manual_seed(noise_seed); torch.rand((N,S)); torch.rand((N,I)) on the CPU
+        # generator (stored for the small cases; the large case regenerates them)
+        'noise': (noise.numpy() if (perturb and not large) else np.zeros((0, S), np.float32)),
+        'u_imp': (u_imp.numpy() if u_imp is not None else np.zeros((0, max(n_imp, 1)), np.float32)),
+        'chk_z_vals': checksum(z), 'chk_pts': checksum(pts.reshape(-1, 3)), 'chk_x': checksum(x),
+        'sample_stride': stride,
+        'z_vals': z[::stride].numpy(), 'pts': pts[::stride].reshape(-1, 3).numpy(),
+        'x': x.reshape(n_rays, -1, 3)[::stride].reshape(-1, 3).numpy(),
         'hash_idx': idx.numpy().astype(np.uint32),
         'grid_scale': np.asarray(meta['scale'], dtype=np.float32), 'grid_res': np.asarray(meta['res'], dtype=np.uint32),
         'grid_offset': np.asarray(meta['offset'], dtype=np.uint32),
-        'raw': ev['raw'].numpy(), 'rgb': ev['rgb'].numpy(), 'depth': ev['depth'].numpy(), 'depth_var': ev['depth_var'].numpy(),
+        'raw': ev['raw'][::stride].numpy(), 'rgb': ev['rgb'].numpy(), 'depth': ev['depth'].numpy(), 'depth_var': ev['depth_var'].numpy(),
         'disp_map': ev['disp_map'].numpy(), 'acc_map': ev['acc_map'].numpy(),
         'rgb_loss': ret['rgb_loss'].item(), 'depth_loss': ret['depth_loss'].item(), 'sdf_loss': ret['sdf_loss'].item(),
         'fs_loss': ret['fs_loss'].item(), 'psnr': ret['psnr'].detach().numpy(), 'loss': loss.item(),
@@ -148,6 +178,19 @@ def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
         'dW3': model.decoder.color_net.model[0].weight.grad.numpy(), 'dW4': model.decoder.color_net.model[2].weight.grad.numpy(),
         'state_dict_keys': np.array(sorted(model.state_dict().keys())),
     }
+    if n_imp > 0:
+        out.update({k: ev[k].numpy() for k in ('rgb0', 'depth0', 'depth_var0', 'acc0', 'disp0', 'z_std')})
+        # the coarse samples (before the merge), for the resampler's own test
+        model.eval()
+        cfg0 = dict(cfg, training=dict(cfg['training'], n_importance=0))
+        m0 = build_reference_model(cfg0, table, weights)
+        m0.eval()
+        with torch.no_grad():
+            torch.manual_seed(NOISE_SEED)
+            ev0 = m0.forward(rays_o, rays_d, rgb, depth)
+        w0 = m0.raw2outputs(ev0['raw'], ev0['z_vals'], False)[3]
+        out.update({'z_coarse': ev0['z_vals'].numpy(), 'w_coarse': w0.detach().numpy()})
+        close(ev0['rgb'], ev['rgb0'], 'coarse rgb of the one-pass model')
     out.update(table_grad_summary(model.embed_fn.params.grad, meta))
     path = os.path.join(GOLDEN_DIR, name + '.npz')
     np.savez_compressed(path, **out)
@@ -160,8 +203,10 @@ def main():
         raise SystemExit('reference tree not present; fixtures can only be regenerated in the build container')
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     torch.set_num_threads(max(1, os.cpu_count() or 1))
+    only = set(sys.argv[1:])
     for case in CASES:
-        run_case(*case)
+        if not only or case[0] in only:
+            run_case(*case)
 
 
 if __name__ == '__main__':

@@ -1,7 +1,8 @@
 """CPU tests (-m "not gpu"): pin the oracle.
 
  1. oracle/coslam_oracle.py (+ tcnn_shim) against the golden vectors that oracle/gen_golden.py produced by running the
-    reference's own, unmodified model/scene_rep.py in the build container;
+    reference's own, unmodified model/scene_rep.py in the build container -- including the hierarchical pass
+    (model/utils.py:32-71 sample_pdf, scene_rep.py:262-295, 327-332) at n_importance 128 / 8 and a 4096-ray room0 batch;
  2. oracle/hashgrid_ref.c (plain C, real fmaf) against the torch shim: bit-exact indices and sample positions;
  3. the tiny-cuda-nn level-size formula against the parameter counts written in the reference's YAML comments
     (configs/ScanNet/scene0000.yaml:8 "1.59M", scene0106.yaml:8 "0.48", scene0059.yaml:7 "0.13") -- the only in-tree
@@ -16,18 +17,30 @@ from oracle import c_oracle, coslam_oracle, ref_loader, tcnn_shim
 from tests import util
 
 
-@pytest.mark.parametrize('name', util.GOLDEN_CASES)
+@pytest.mark.parametrize('name', util.GOLDEN_CASES + util.IMPORTANCE_CASES + util.LARGE_CASES)
 def test_oracle_reproduces_reference_golden(name):
     g = util.load_golden(name)
     cfg, (rays_o, rays_d, rgb, depth), table, weights, noise = util.case_inputs(g)
+    u_imp = util.case_noise(g, cfg)[1]
     orc = util.make_oracle(cfg, table, weights)
     o = rays_o.clone().requires_grad_(True)
     d = rays_d.clone().requires_grad_(True)
-    r = orc.forward(o, d, rgb, depth, noise=noise)
+    r = orc.forward(o, d, rgb, depth, noise=noise, noise_imp=u_imp)
     orc.total_loss(r).backward()
-    assert np.array_equal(r['z_vals'].numpy(), g['z_vals'])                   # bit-exact sample depths
-    assert np.array_equal(r['pts'].reshape(-1, 3).detach().numpy(), g['pts'])    # bit-exact sample positions
-    util.assert_close(r['raw'], g['raw'], 'raw', 1e-5)
+    st = int(g['sample_stride']) if 'sample_stride' in g.files else 1
+    assert np.array_equal(r['z_vals'][::st].numpy(), g['z_vals'])             # bit-exact sample depths (merged, row a11)
+    assert np.array_equal(r['pts'][::st].reshape(-1, 3).detach().numpy(), g['pts'])    # bit-exact sample positions
+    if 'chk_z_vals' in g.files:
+        assert util.checksum(r['z_vals']) == str(g['chk_z_vals']) and util.checksum(r['pts'].reshape(-1, 3)) == str(g['chk_pts'])
+    if cfg['training']['n_importance'] > 0:                                    # coarse maps and the spread of the drawn depths
+        for k in ('rgb0', 'depth0', 'depth_var0', 'acc0', 'z_std'):
+            util.assert_close(r[k], g[k], k, 1e-5)
+        mid = .5 * (torch.from_numpy(g['z_coarse'])[..., 1:] + torch.from_numpy(g['z_coarse'])[..., :-1])
+        zi = coslam_oracle.sample_pdf(mid, torch.from_numpy(g['w_coarse'])[..., 1:-1], cfg['training']['n_importance'],
+                                      det=not cfg['training']['perturb'] > 0., u=u_imp)
+        merged = torch.sort(torch.cat([torch.from_numpy(g['z_coarse']), zi], -1), -1)[0]
+        assert np.array_equal(merged.numpy(), g['z_vals'])                     # sample_pdf alone, from the stored coarse weights
+    util.assert_close(r['raw'][::st], g['raw'], 'raw', 1e-5)
     util.assert_close(r['rgb'], g['rgb'], 'rgb', 1e-5)
     util.assert_close(r['depth'], g['depth'], 'depth', 1e-5)
     for k in ('rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):

@@ -11,6 +11,11 @@ from coslam_b200 import synth
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
 GOLDEN_CASES = ['room0_small', 'room0_trained', 'scannet0000_trained', 'tum_desk_trained']
+# hierarchical pass through the reference's own sample_pdf / second pass (row a11): 128 and 8 importance samples, with the
+# deterministic uniforms of perturb 0 (`_det`) and with the CPU generator's draws of perturb 1
+IMPORTANCE_CASES = ['tum_desk_imp128_det', 'tum_desk_imp128', 'tum_desk_imp8_det', 'tum_desk_imp8']
+# BASELINE config 1's size (4096 rays, ~176 k points); per-point tensors stored as checksums + every 16th ray
+LARGE_CASES = ['room0_4096']
 
 REL_TOL = 1e-3          # north_star: rendered depth/colour, SDF and gradients within 1e-3 relative (fp32 tables)
 
@@ -38,7 +43,24 @@ def case_inputs(g):
     assert checksum(rgb) == str(g['chk_rgb']) and checksum(depth) == str(g['chk_depth'])
     assert checksum(table) == str(g['chk_table'])
     assert checksum(torch.cat([w.reshape(-1) for w in weights])) == str(g['chk_w'])
-    return cfg, (rays_o, rays_d, rgb, depth), table, weights, torch.from_numpy(g['noise'])
+    return cfg, (rays_o, rays_d, rgb, depth), table, weights, case_noise(g, cfg)[0]
+
+
+def case_noise(g, cfg):
+    """(noise [N,S] or None, u_imp [N,I] or None): the CPU generator's draws of the reference's forward in its own order
+    (scene_rep.py:255, then model/utils.py:53).  Stored for the small cases, regenerated from the seed otherwise."""
+    t = cfg['training']
+    if not t['perturb'] > 0.:
+        return None, None
+    n, S, I = int(g['n_rays']), t['n_samples_d'] + t['n_range_d'], t['n_importance']
+    torch.manual_seed(int(g['noise_seed']))
+    noise = torch.rand((n, S))
+    u = torch.rand((n, I)) if I > 0 else None
+    if g['noise'].shape[0]:
+        assert np.array_equal(noise.numpy(), g['noise'])
+    if u is not None:
+        assert np.array_equal(u.numpy(), g['u_imp'])
+    return noise, u
 
 
 def make_oracle(cfg, table, weights):
