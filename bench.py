@@ -99,6 +99,48 @@ def build_oracle(cfg, table, weights):
     return orc
 
 
+class ReferenceCpuModel(object):
+    """The reference's OWN model/scene_rep.py:JointEncoding (unmodified copy under baseline/_ref, see
+    __graft_entry__.install_reference) with the pure-torch tinycudann stand-in, on the host cores: kind "reference"."""
+    kind = 'reference'
+
+    def __init__(self, cfg, table, weights):
+        from oracle import ref_loader
+        cls = ref_loader.load_reference_model_class()
+        self.cfg = cfg
+        self.model = cls(cfg, synth.bound_tensor(cfg))
+        with torch.no_grad():
+            self.model.embed_fn.params.copy_(table)
+            for dst, src in zip((self.model.decoder.sdf_net.model[0].weight, self.model.decoder.sdf_net.model[2].weight,
+                                 self.model.decoder.color_net.model[0].weight, self.model.decoder.color_net.model[2].weight), weights):
+                dst.copy_(src)
+        self.model.train()
+
+    def step(self, batch, noise):
+        rays_o, rays_d, rgb, depth = batch
+        for p in self.model.parameters():
+            p.grad = None
+        o = rays_o.clone().requires_grad_(True)
+        d = rays_d.clone().requires_grad_(True)
+        ret = self.model.forward(o, d, rgb, depth)                  # draws its own jitter (scene_rep.py:255)
+        t = self.cfg['training']                                    # coslam.py:140-160
+        loss = t['rgb_weight'] * ret['rgb_loss'] + t['depth_weight'] * ret['depth_loss'] + t['sdf_weight'] * ret['sdf_loss'] \
+            + t['fs_weight'] * ret['fs_loss']
+        loss.backward()
+        return float(ret['rgb_loss'].detach())
+
+
+class PortCpuModel(object):
+    """oracle/coslam_oracle.py (the restatement, asserted equal to the reference in the build container): kind "port"."""
+    kind = 'port'
+
+    def __init__(self, cfg, table, weights):
+        self.orc = build_oracle(cfg, table, weights)
+
+    def step(self, batch, noise):
+        return cpu_reference_step(self.orc, batch, noise)
+
+
 def cpu_reference_step(orc, batch, noise):
     """One fwd+bwd of the reference path's CPU restatement (oracle/coslam_oracle.py == the reference's own torch code
     plus the pure-torch tinycudann stand-in), all host threads."""
@@ -112,29 +154,36 @@ def cpu_reference_step(orc, batch, noise):
     return float(r['rgb_loss'].detach())
 
 
-def time_cpu(cfg, n_rays, steps, warmup, budget_s=25.0):
-    torch.set_num_threads(os.cpu_count() or 1)
+def time_cpu(cfg, n_rays, steps, warmup, budget_s=25.0, threads=None):
+    """Returns (step times, threads used, kind): the reference's own CPU code when baseline/_ref holds it, else the port."""
+    torch.set_num_threads(threads or os.cpu_count() or 1)
     weights = synth.decoder_init(seed=0)
-    from oracle import tcnn_shim
+    from oracle import ref_loader, tcnn_shim
     from oracle.coslam_oracle import hashgrid_encoding_config
     enc = hashgrid_encoding_config(cfg, synth.bound_tensor(cfg))
     meta = tcnn_shim.grid_meta(enc['n_levels'], enc['log2_hashmap_size'], enc['base_resolution'], enc['per_level_scale'])
     table = synth.table_init(meta['offset'][-1] * 2, 'trained')
-    orc = build_oracle(cfg, table, weights)
+    runner = (ReferenceCpuModel if ref_loader.available() else PortCpuModel)(cfg, table, weights)
     batch = synth.keyframe_ray_batch(cfg, n_rays, seed=0)[:4]
     S = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
     noise = torch.rand(n_rays, S)
     for _ in range(warmup):
-        cpu_reference_step(orc, batch, noise)
+        runner.step(batch, noise)
     times = []
     t_begin = time.perf_counter()
     for _ in range(steps):
         t0 = time.perf_counter()
-        cpu_reference_step(orc, batch, noise)
+        runner.step(batch, noise)
         times.append(time.perf_counter() - t0)
         if time.perf_counter() - t_begin > budget_s:
             break
-    return times, torch.get_num_threads()
+    used = torch.get_num_threads()
+    torch.set_num_threads(os.cpu_count() or 1)
+    return times, used, runner.kind
+
+
+CPU_KIND_TEXT = {'reference': "the reference's own model/scene_rep.py (unmodified copy in baseline/_ref) + pure-torch tinycudann shim",
+                 'port': 'oracle port (reference scene_rep.py restated + pure-torch tinycudann shim)'}
 
 
 def run_reference(args):
@@ -148,19 +197,18 @@ def run_reference(args):
     if args.n_importance >= 0:
         cfg['training']['n_importance'] = args.n_importance
     steps = max(1, args.steps)
-    times, cores = time_cpu(cfg, args.cpu_rays, steps, max(1, min(args.warmup, 3)), budget_s=120.0)
+    times, cores, kind = time_cpu(cfg, args.cpu_rays, steps, max(1, min(args.warmup, 3)), budget_s=120.0)
     total = sum(times)
     value = args.cpu_rays * len(times) / total
     S = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
-    sample = '%d steps of %d rays x %d samples, fwd+bwd, oracle port (reference scene_rep.py restated + pure-torch tinycudann shim)' % (
-        len(times), args.cpu_rays, S)
+    sample = '%d steps of %d rays x %d samples, fwd+bwd, %s' % (len(times), args.cpu_rays, S, CPU_KIND_TEXT[kind])
     print(json.dumps({
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': len(times),
         'warmup': args.warmup, 'ms_per_step': 1e3 * total / len(times), 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': {'workload': '%s mapping-BA render fwd+bwd, %d-ray CPU sample of the %d-ray/GPU batch' % (args.workload, args.cpu_rays, args.rays),
                    'rays_per_step': args.cpu_rays, 'samples_per_ray': S},
-        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': kind, 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0}), file=_STDOUT, flush=True)
 
@@ -276,9 +324,11 @@ def run_ours(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        times, cores = time_cpu(cfg, args.cpu_rays, steps=1000, warmup=1, budget_s=15.0)
-        cpu = {'value': args.cpu_rays * len(times) / sum(times), 'unit': UNIT, 'cores': cores, 'kind': 'port',
-               'sample': '%d steps of %d rays x %d samples fwd+bwd (oracle port, torch CPU, %d threads)' % (len(times), args.cpu_rays, S, cores)}
+        times, cores, kind = time_cpu(cfg, args.cpu_rays, steps=1000, warmup=1, budget_s=12.0)
+        cpu = {'value': args.cpu_rays * len(times) / sum(times), 'unit': UNIT, 'cores': cores, 'kind': kind,
+               'sample': '%d steps of %d rays x %d samples fwd+bwd (%s, torch CPU, %d threads)' % (len(times), args.cpu_rays, S, CPU_KIND_TEXT[kind], cores)}
+        t1, _, _ = time_cpu(cfg, args.cpu_rays, steps=1000, warmup=1, budget_s=8.0, threads=1)       # the per-core figure
+        cpu['one_thread'] = {'value': args.cpu_rays * len(t1) / sum(t1), 'unit': UNIT, 'cores': 1, 'steps': len(t1)}
 
     if rank == 0:
         peaks = {}

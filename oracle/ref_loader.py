@@ -1,11 +1,23 @@
-"""ORACLE tooling (test infrastructure) -- imports the UNMODIFIED reference model from /root/reference with
-oracle/tcnn_shim.py registered as `tinycudann`.  Works only in the build container: /root/reference does not
-exist on the GPU box, so nothing under tests/ (-m gpu), smoke() or bench.py may call this at run time.  It is
-used by oracle/gen_golden.py and by the CPU-only cross-check tests, which skip when the tree is absent."""
+"""ORACLE tooling (test infrastructure) -- imports the UNMODIFIED reference model from /root/reference (build container) or
+from baseline/_ref (the unmodified copy `__graft_entry__.build()` installs there; git-ignored, shipped to the GPU box by
+gpurun) with oracle/tcnn_shim.py registered as `tinycudann`.  Used by oracle/gen_golden.py, the CPU cross-check tests
+(skipped when no tree is present), bench.py's CPU arm (`--impl reference`, `cpu_baseline`: kind "reference") and the
+coslam.py drop-in test.  /root/reference itself is never read on the GPU box."""
 import os
 import sys
 
-REFERENCE_ROOT = os.environ.get('COSLAM_REFERENCE_ROOT', '/root/reference')
+_HERE = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _default_root():
+    # /root/reference in the build container; baseline/_ref (the unmodified copy __graft_entry__.build() installs, which
+    # travels with gpurun) on the GPU box
+    if os.path.isfile('/root/reference/model/scene_rep.py'):
+        return '/root/reference'
+    return os.path.join(_HERE, 'baseline', '_ref')
+
+
+REFERENCE_ROOT = os.environ.get('COSLAM_REFERENCE_ROOT') or _default_root()
 
 
 def available():
