@@ -47,6 +47,15 @@ int check_fused_scene(const cb200_scene* s) {
 
 }  // namespace
 
+// error reporting for entry points that live in other translation units (noalloc.cu)
+int cb200_set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
 extern "C" {
 
 int cb200_abi_version(void) { return CB200_ABI_VERSION; }

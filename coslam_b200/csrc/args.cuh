@@ -132,3 +132,6 @@ cudaError_t launch_tc_selftest(const float* A, const float* B, int K, int N, int
 cudaError_t launch_oneblob_bwd(const float* x, const float* dy, int64_t n_flat, int n_bins, float* dx, cudaStream_t st);
 
 }  // namespace cb200
+
+// sets cb200_last_error() of the calling thread and returns `code` (api.cu); for entry points in other translation units
+int cb200_set_error(int code, const char* fmt, ...);

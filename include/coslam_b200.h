@@ -414,6 +414,24 @@ int cb200_host_random_sample(uint32_t* state, int64_t n_draws, const int64_t* n,
  * 2 = cb200_adam_param */
 size_t cb200_sizeof(int which);
 
+/* ---- allocation-free variant (NO counterpart in the reference) ------------- */
+
+/* Largest n_rays * n_samples one cb200_points_bwd_noalloc call accepts: its scratch is a file-scope device array of
+ * 256 B + 4 B per point = 4 MiB + 256 B, held by every GPU that loads the library until exit. */
+#define CB200_NOALLOC_MAX_POINTS (1 << 20)
+int64_t cb200_points_bwd_noalloc_max_points(void);
+
+/* cb200_points_bwd in ray mode for callers that cannot allocate device memory (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc): same inputs, outputs (all caller-owned, accumulated into like cb200_points_bwd) and
+ * arithmetic, but the live-point compaction scratch is the library's static device array instead of a caller workspace.
+ * Calls no cudaMalloc / cudaFree / allocating routine.  Returns -1 with a message when n_rays * n_samples exceeds
+ * CB200_NOALLOC_MAX_POINTS.  The array is shared by every call on a device and keeps the last call's contents (the
+ * counter is cleared on `stream` at the start of each call): calls that overlap on the GPU race -- serialise them. */
+int cb200_points_bwd_noalloc(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* rays_o,
+                             const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
+                             const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_rays_o,
+                             float* d_rays_d, int sdf_only, void* stream);
+
 /* test hook for the bit-exact sample-position gate: pts [P,3] and normalised x [P,3] exactly as the fused
  * kernels compute them (model/scene_rep.py:258 and :186) */
 int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals,
