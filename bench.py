@@ -33,9 +33,8 @@ METRIC = 'rays_per_sec_render_fwd_bwd'
 UNIT = 'rays/s'
 BYTES_PER_POINT_FWD = 1024          # 16 levels x 8 corners x 8 B gathered           
 BYTES_PER_POINT_BWD = 2048          # the same gathers again for dL/dx + 1024 B of gradient scattered to the table
-# dram__bytes_read.sum + dram__bytes_write.sum of points_bwd_tc_kernel<wgrad> per point, from the ncu --set full capture in
-# profiles/r1/ncu_full_v9_tc.txt (51.32 MB + 0.30 MB over 1 409 024 points): the table is L2-resident, HBM sees the per-point streams.
-NCU_DRAM_BYTES_PER_POINT_BWD = 28.87     # (316.86 MB read + 8.59 MB written) / 11 272 192 points
+# roofline.traffic is read from the newest ncu --set full summary under profiles/ (ncu_traffic_per_point), scaled by live points
+NCU_V9_LIVE_POINTS = 6823377             # live points of the launch profiles/r1/ncu_full_v9_tc.txt captured (2^18 rays x 43 x 0.6053)
 
 
 def parse():
@@ -44,7 +43,8 @@ def parse():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--rays', type=int, default=1 << 18, help='rays per GPU per step')
+    ap.add_argument('--rays', type=int, default=1 << 22, help='rays per GPU per step (default: the top of BASELINE config 4\'s 2^16-2^22 sweep)')
+    ap.add_argument('--quick', action='store_true', help='headline numbers only: no sweep, other configs, pipelines, strong scaling or GPU baseline')
     ap.add_argument('--workload', default='room0', choices=sorted(synth.CONFIGS))
     ap.add_argument('--hash-size', type=int, default=0, help='override grid.hash_size (scannet base file: 19)')
     ap.add_argument('--n-importance', type=int, default=-1, help='override training.n_importance (tum.yaml: 128)')
@@ -317,10 +317,56 @@ def run_ours(args):
     h2d = sum(t.numel() * t.element_size() for t in host)
 
     extra = {}
+    full = not args.quick
+    if full:
+        # ---- the default mode of the drop-in (COSLAM_B200_NOISE=host): CPU torch.rand(N, S) + upload inside every step ------
+        model.noise_mode = 'host'
+        e2e_step()
+        k = min(3, args.steps)
+        ms_host = timed(e2e_step, k)
+        model.noise_mode = 'device'
+        extra['e2e_host_noise'] = {'value': world * n * k / (ms_host * 1e-3), 'unit': UNIT, 'ms_per_step': ms_host / k, 'steps': k,
+                                   'h2d_bytes_per_step': h2d + n * S * 4, 'd2h_bytes_per_step': 4,
+                                   'note': "the reference's own jitter: torch.rand(z_vals.shape) on the CPU generator + .to(device) every call (scene_rep.py:255)"}
+        # ---- BASELINE config 4's ray sweep, device-resident, same step -----------------------------------------------------
+        sweep = {}
+        for lg in (16, 18, 20, 22):
+            if (1 << lg) == n:
+                sweep['2^%d' % lg] = {'rays_per_gpu': n, 'ms_per_step': ms / args.steps, 'value': value, 'unit': UNIT}
+                continue
+            b = [t.to(dev) for t in synth.keyframe_ray_batch(cfg, 1 << lg, seed=100 + rank)[:4]]
+            for _ in range(3):
+                step(b)
+            k = 5 if lg >= 20 else 20
+            t_ms = timed(lambda: step(b), k)
+            sweep['2^%d' % lg] = {'rays_per_gpu': 1 << lg, 'ms_per_step': t_ms / k, 'value': world * (1 << lg) * k / (t_ms * 1e-3), 'unit': UNIT}
+            del b
+        extra['sweep'] = sweep
+        for p in model.parameters():
+            p.grad = None
+        torch.cuda.empty_cache()
+        group = dist.group.WORLD if world > 1 else None
+        try:
+            extra['strong_scaling'] = strong_scaling(dev, group, world, rank)
+        except Exception as e:
+            extra['strong_scaling'] = {'error': '%s: %s' % (type(e).__name__, e)}
+    gather_peak = None
+    if rank == 0 and full:
+        try:
+            gather_peak = measure_gather_peak(model, cfg, dev)
+        except Exception as e:
+            gather_peak = {'error': '%s: %s' % (type(e).__name__, e)}
     if rank == 0 and (args.tracking or world == 1) and not args.no_tracking:
         extra['tracking'] = time_tracking(model, cfg, dev)
-        if cfg['grid']['oneGrid'] and cfg['training']['n_importance'] == 0:
+        if cfg['grid']['oneGrid']:
             extra['mapping'] = time_mapping(model, cfg, dev)
+        if full:
+            extra['other_configs'] = other_config_loops(dev)
+            extra['pipelines'] = pipelines()
+            try:
+                extra['gpu_torch_baseline'] = gpu_torch_baseline(cfg, dev)
+            except Exception as e:
+                extra['gpu_torch_baseline'] = {'error': '%s: %s' % (type(e).__name__, e)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -342,6 +388,31 @@ def run_ours(args):
         # algorithmic bytes of the backward: gathers + scatter only for the points that carry a gradient
         bwd_bytes = P * live_frac * BYTES_PER_POINT_BWD
         achieved = bwd_bytes / (k_bwd * 1e-3) / 1e9
+        live_points = P * live_frac
+        traffic_src = ncu_traffic_per_point('points_bwd_tc_kernel') if tc else None
+        traffic = None
+        if traffic_src is not None:
+            # the capture's DRAM bytes scale with the live points of a launch (the table stays in L2; HBM sees the per-point streams)
+            per_point = traffic_src['dram_bytes_per_launch'] / (traffic_src['live_points'] or NCU_V9_LIVE_POINTS)
+            traffic = per_point * live_points
+        roofline = {'bound': 'hbm', 'kernel': 'points_bwd_tc_kernel<wgrad>' if tc else 'points_bwd_kernel<wgrad>', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                    'frac': achieved / peak, 'traffic': traffic,
+                    'traffic_source': ('%s: dram bytes per live point of that capture x live points of this launch' % traffic_src['file']) if traffic_src else None,
+                    'peak_source': 'measured (MEASURED_PEAKS.json hbm_gbs)' if peaks else 'fallback',
+                    'algorithmic_bytes_per_launch': bwd_bytes, 'live_point_fraction': live_frac, 'avg_launch_ms': k_bwd,
+                    'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
+                                   'evaluated_point_fraction': eval_frac,
+                                   'achieved': P * eval_frac * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
+                    'share_of_step': (k_fwd + k_bwd) / (ms / args.steps),
+                    'kernel_ms_per_step': {k: sum(v) / args.steps for k, v in kt.items()}}
+        if gather_peak is not None and 'gather_reduce_GBps' in gather_peak:
+            # the physical ceiling: the table is L2-resident, so the kernels are bounded by the L2 / L1TEX gather + reduction rate at
+            # this access pattern, measured live with no decoder at all (state both)
+            roofline['l2_gather_peak'] = gather_peak
+            roofline['frac_l2_gather'] = achieved / gather_peak['gather_reduce_GBps']
+            roofline['fwd_kernel']['frac_l2_gather'] = roofline['fwd_kernel']['achieved'] / gather_peak['gather_GBps']
+        elif gather_peak is not None:
+            roofline['l2_gather_peak'] = gather_peak
         out = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': max(3, args.warmup),
             'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
@@ -354,15 +425,7 @@ def run_ours(args):
             'clocks': clocks,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4, 'ms_per_step': ms_e2e / args.steps},
             'gpu_launches': launches,
-            'roofline': {'bound': 'hbm', 'kernel': 'points_bwd_tc_kernel<wgrad>' if tc else 'points_bwd_kernel<wgrad>', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                         'frac': achieved / peak, 'traffic': P * NCU_DRAM_BYTES_PER_POINT_BWD if tc else None,
-                         'traffic_source': 'ncu dram bytes per point (profiles/r1/ncu_full_v9_tc.txt) x points per launch', 'peak_source': 'measured' if peaks else 'fallback',
-                         'algorithmic_bytes_per_launch': bwd_bytes, 'live_point_fraction': live_frac, 'avg_launch_ms': k_bwd,
-                         'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
-                                        'evaluated_point_fraction': eval_frac,
-                                        'achieved': P * eval_frac * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
-                         'share_of_step': (k_fwd + k_bwd) / (ms / args.steps),
-                         'kernel_ms_per_step': {k: sum(v) / args.steps for k, v in kt.items()}},
+            'roofline': roofline,
             'cpu_baseline': cpu,
         }
         out.update(extra)
@@ -371,33 +434,264 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def time_tracking(model, cfg, dev, frames=20):
+# ------------------------------------------------------------------------------------------------------------------------
+# extra measurements of the line (VERDICT r1 "Next round" items 2 and 3)
+# ------------------------------------------------------------------------------------------------------------------------
+
+def measure_gather_peak(model, cfg, dev, n_rays=49152):
+    """Measured L2 gather / reduction ceiling at the fused kernels' access pattern for THIS table (tools/l2_gather_peak.py,
+    csrc/microbench.cu): GB/s of table bytes with no decoder and no index arithmetic -- the physical denominator next to the
+    HBM figure (the table is L2-resident, SURVEY.md 8d: "state both")."""
+    import ctypes
+    from coslam_b200 import _lib, ops
+    sys.path.insert(0, os.path.join(ROOT, 'tools'))
+    import l2_gather_peak as lg
+    lg.DEV = dev
+    rays_o, rays_d, _, depth = synth.ray_batch(cfg, n_rays, seed=0)
+    z = ops.sample_rays(model.spec, depth.to(dev), perturb=False)
+    n, s = z.shape
+    pts = torch.empty((n * s, 3), device=dev)
+    x = torch.empty((n * s, 3), device=dev)
+    o, d = rays_o.to(dev).contiguous(), rays_d.to(dev).contiguous()
+    _lib.check(_lib.load().cb200_debug_positions(ctypes.byref(model.spec.scene()), _lib.ptr(o), _lib.ptr(d), _lib.ptr(z), ctypes.c_int64(n),
+                                                 ctypes.c_int64(s), _lib.ptr(pts), _lib.ptr(x), _lib.stream()), 'debug_positions')
+    idx = lg.corner_list(model, x)
+    table = model.embed_fn.params.detach()
+    dtable = torch.zeros_like(table)
+    P = idx.shape[0]
+    out = {'points': P, 'pattern': 'corner list of %d rays x %d samples of this workload, lane pair per point, no other arithmetic' % (n, s)}
+    for mode, key, passes in ((1, 'gather', 1), (2, 'reduce', 1), (3, 'gather_reduce', 2)):
+        ms = lg.time_mode(model, idx, table, dtable, mode, iters=10, warmup=3)
+        out[key + '_GBps'] = P * 1024.0 * passes / (ms * 1e-3) / 1e9
+    return out
+
+
+def ncu_traffic_per_point(kernel='points_bwd_tc_kernel'):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the newest committed `ncu --set full` summary of `kernel` under
+    profiles/ (tools/ncu_summary.py format), per LIVE point of that capture when the file states it, else per launch."""
+    import glob
+    import re
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, 'profiles', 'r*', 'ncu_full_*.txt'))):
+        text = open(path).read()
+        if kernel not in text:
+            continue
+        rd = re.search(r'dram__bytes_read\.sum\s+([0-9.]+) (\w)byte', text)
+        wr = re.search(r'dram__bytes_write\.sum\s+([0-9.]+) (\w)byte', text)
+        pts = re.search(r'live_points:\s*([0-9]+)', text)
+        if not (rd and wr):
+            continue
+        unit = {'K': 1e3, 'M': 1e6, 'G': 1e9}
+        total = float(rd.group(1)) * unit[rd.group(2)] + float(wr.group(1)) * unit[wr.group(2)]
+        rnd = int(re.search(r'profiles/r(\d+)/', path.replace(os.sep, '/')).group(1))
+        ver = re.search(r'_v(\d+)', os.path.basename(path))
+        key = (rnd, int(ver.group(1)) if ver else 0)
+        if best is None or key > best[0]:
+            best = (key, path, total, int(pts.group(1)) if pts else None)
+    if best is None:
+        return None
+    _, path, total, live = best
+    return {'file': os.path.relpath(path, ROOT), 'dram_bytes_per_launch': total, 'live_points': live}
+
+
+def gpu_torch_baseline(cfg, dev, sizes=(4096, 65536)):
+    """The closest stand-in for the reference's GPU path this box allows (tinycudann is not installed): the reference's model
+    code restated (oracle/coslam_oracle.py == model/scene_rep.py + decoder.py, asserted equal in the build container) with the
+    pure-torch HashGrid / OneBlob shim, moved to the same B200 -- ATen + cuBLAS fp32, fwd + bwd of the weighted loss, CUDA-synced
+    median.  Checker code timed as a BASELINE only (like cpu_baseline); never on the product path."""
+    from oracle.coslam_oracle import OracleScene
+    from oracle import tcnn_shim
+    from oracle.coslam_oracle import hashgrid_encoding_config
+    enc = hashgrid_encoding_config(cfg, synth.bound_tensor(cfg))
+    meta = tcnn_shim.grid_meta(enc['n_levels'], enc['log2_hashmap_size'], enc['base_resolution'], enc['per_level_scale'])
+    orc = OracleScene(cfg, synth.bound_tensor(cfg))
+    orc.load_weights(synth.table_init(meta['offset'][-1] * 2, 'trained'), *synth.decoder_init(seed=0))
+    orc.to(dev)
+    S = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
+    out = {'what': 'oracle restatement of the reference model + pure-torch tinycudann shim on cuda (ATen / cuBLAS fp32), fwd+bwd, median',
+           'caveat': 'tinycudann itself is not installed on this box; its fused CUDA encodings are faster than this stand-in'}
+    for n in sizes:
+        batch = [t.to(dev) for t in synth.keyframe_ray_batch(cfg, n, seed=0)[:4]]
+        noise = torch.rand(n, S, device=dev)
+        times = []
+        for it in range(2 + 5):
+            for p in orc.parameters():
+                p.grad = None
+            o = batch[0].clone().requires_grad_(True)
+            d = batch[1].clone().requires_grad_(True)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = orc.forward(o, d, batch[2], batch[3], noise=noise)
+            orc.total_loss(r).backward()
+            torch.cuda.synchronize()
+            if it >= 2:
+                times.append(time.perf_counter() - t0)
+        med = sorted(times)[len(times) // 2]
+        out['rays_%d' % n] = {'ms_per_step': med * 1e3, 'value': n / med, 'unit': UNIT}
+        del batch, noise, r
+        torch.cuda.empty_cache()
+    return out
+
+
+
+def other_config_loops(dev):
+    """tracking ms/frame and mapping ms/iteration for BASELINE configs 3 and 5's shapes (scene0000: S = 117, quaternion poses,
+    lattice 63^3; fr1_desk: S = 85 + 128 importance samples, 20 BA iterations, lattice 63^3), random-init maps."""
+    from coslam_b200.scene_rep import JointEncoding
+    out = {}
+    for name, cfg in (('scannet0000', synth.scannet0000_config()), ('tum_desk', synth.tum_desk_config(n_importance=128))):
+        try:
+            if name == 'tum_desk':            # the frames fr1_desk.yaml:18-19 produces after resize + crop
+                cfg['cam'].update({'H': 368, 'W': 496, 'fx': 413.84, 'fy': 413.2, 'cx': 246.88, 'cy': 196.24})
+            model = JointEncoding(cfg, synth.bound_tensor(cfg).to(dev)).to(dev)
+            model.noise_mode = 'device'
+            with torch.no_grad():
+                model.embed_fn.params.copy_(synth.table_init(model.embed_fn.params.numel(), 'trained').to(dev))
+                for dst, src in zip(model.decoder.fused_weights(), synth.decoder_init(seed=0)):
+                    dst.copy_(src.to(dev))
+            model.train()
+            out[name] = {'tracking': time_tracking(model, cfg, dev, frames=10, full=False), 'mapping': time_mapping(model, cfg, dev, calls=3)}
+            del model
+        except Exception as e:                                   # a failure here must not take the headline line with it
+            out[name] = {'error': '%s: %s' % (type(e).__name__, e)}
+        torch.cuda.empty_cache()
+    return out
+
+
+def pipelines(frames=40):
+    """BASELINE configs 2, 3 and 5 in miniature (tools/slam_synth.py: sphere-traced synthetic RGB-D frames of the named
+    resolutions, first-frame mapping, per-frame tracking, BA every 5th frame, keyframe store): steady-state frames/s, tracking
+    ms/frame, mapping ms/iteration and the ATE against the generator's poses."""
+    sys.path.insert(0, os.path.join(ROOT, 'tools'))
+    import slam_synth
+    out = {}
+    for name in ('room0', 'scannet0000', 'tum_desk'):
+        try:
+            out[name] = slam_synth.run_workload(name, frames=frames)
+        except Exception as e:
+            out[name] = {'error': '%s: %s' % (type(e).__name__, e)}
+        torch.cuda.empty_cache()
+    return out
+
+
+def strong_scaling(dev, group, world, rank, log2s=(18, 22), iters=5, n_kf=401):
+    """BASELINE config 4 as worded: ONE batch of N rays per BA iteration sharded over the ranks (N / world each) through
+    coslam_b200.mapping.BundleAdjuster(group=...): ray assembly over a 401-keyframe device store, forward, losses, backward
+    (table, decoder, 400 poses), smoothness, Adam; counts / loss sums and the gradient bucket all-reduced over NCCL.  Device time,
+    max over ranks.  At world = 1 this is the denominator of the strong-scaling efficiency."""
+    import random
+    import torch.distributed as dist
+    from coslam_b200 import optim as cb_optim
+    from coslam_b200 import pose
+    from coslam_b200.keyframe import KeyFrameDatabase
+    from coslam_b200.mapping import BundleAdjuster
+    from coslam_b200.scene_rep import JointEncoding
+    cfg = synth.room0_config()
+    m, cam = cfg['mapping'], cfg['cam']
+    H, W = cam['H'], cam['W']
+    R = int(H * W * m['n_pixels'])
+    torch.manual_seed(0)
+    random.seed(0)
+    model = JointEncoding(cfg, synth.bound_tensor(cfg).to(dev)).to(dev)
+    with torch.no_grad():
+        model.embed_fn.params.copy_(synth.table_init(model.embed_fn.params.numel(), 'trained', seed=77).to(dev))
+        for dst, src in zip(model.decoder.fused_weights(), synth.decoder_init(seed=5)):
+            dst.copy_(src.to(dev))
+    model.noise_mode = 'device'
+    model.train()
+    db = KeyFrameDatabase(cfg, H, W, n_kf, R, dev)
+    g = torch.Generator(device=dev).manual_seed(1)
+    dirs = synth.camera_ray_dirs(H, W, cam['fx'], cam['fy'], cam['cx'], cam['cy']).reshape(-1, 3).to(dev)
+    pick = torch.randint(0, H * W, (n_kf, R), device=dev, generator=g)
+    db.rays[:n_kf, :, :3] = dirs[pick]
+    db.rays[:n_kf, :, 3:6] = torch.rand((n_kf, R, 3), device=dev, generator=g)
+    db.rays[:n_kf, :, 6] = torch.rand((n_kf, R), device=dev, generator=g) * 3.0 + 0.5
+    db.frame_ids = torch.arange(n_kf) * m['keyframe_every']
+    bound = synth.bound_tensor(cfg)
+    centre, ext = bound.mean(1), bound[:, 1] - bound[:, 0]
+    gh = torch.Generator().manual_seed(2)
+    poses = []
+    for k in range(n_kf + 1):
+        r = torch.randn(1, 3, generator=gh)
+        poses.append(pose.pose_matrix(r / r.norm() * (0.2 + 0.001 * k), (centre + 0.1 * ext * (torch.rand(3, generator=gh) - 0.5))[None])[0])
+    kf_poses, cur_pose = torch.stack(poses[:n_kf]).to(dev), poses[n_kf].to(dev)
+    current = torch.cat([dirs, torch.rand((H * W, 3), device=dev, generator=g), torch.rand((H * W, 1), device=dev, generator=g) * 3 + 0.5], -1)
+    opt = cb_optim.Adam([{'params': model.decoder.parameters(), 'weight_decay': 1e-6, 'lr': m['lr_decoder']},
+                         {'params': model.embed_fn.parameters(), 'eps': 1e-15, 'lr': m['lr_embed']}], betas=(0.9, 0.99))
+    ba = BundleAdjuster(model, cfg, db, opt, dev, group=group, device_sampler=True)
+    m['iters'] = iters
+    out = {'scaling': 'strong', 'keyframes': n_kf, 'iters_per_call': iters}
+    for lg in log2s:
+        m['sample'] = 1 << lg
+        m['min_pixels_cur'] = max(100, (1 << lg) // 64)
+        ba.run(kf_poses, cur_pose, current)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        reps = 3
+        for _ in range(reps):
+            ba.run(kf_poses, cur_pose, current)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / (reps * iters)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        n_rays = m['sample'] + max(m['sample'] // n_kf, m['min_pixels_cur'])
+        out['rays_2^%d' % lg] = {'rays_per_iteration': n_rays, 'ms_per_iteration': float(ms), 'value': n_rays / (float(ms) * 1e-3), 'unit': UNIT}
+    del ba, db, model
+    torch.cuda.empty_cache()
+    return out
+
+
+
+def time_tracking(model, cfg, dev, frames=20, full=True):
     """Tracking ms/frame (BASELINE.json metric 2): `tracking.iter` dependent iterations of pose -> rays -> fwd -> loss -> bwd to
     the pose -> pose Adam, with the best-pose bookkeeping (coslam.py:502-573), through coslam_b200.tracking.FrameTracker:
     the loop as ONE CUDA graph per frame, and the same loop launched eagerly for comparison.  Inputs start on the host
     (pinned), the estimated pose is read back every frame."""
     from coslam_b200 import pose
     from coslam_b200.tracking import FrameTracker
+    import random
+    from coslam_b200.keyframe import sample_range
     n_rays = int(cfg['tracking']['sample'])
     g = torch.Generator().manual_seed(5)
     bound = synth.bound_tensor(cfg)
-    dir_cam = torch.stack([(torch.rand(n_rays, generator=g) - 0.5) * 1.6, (torch.rand(n_rays, generator=g) - 0.5) * 1.0,
-                           -torch.ones(n_rays)], -1).pin_memory()
-    rgb = torch.rand(n_rays, 3, generator=g).pin_memory()
-    depth = (torch.rand(n_rays, 1, generator=g) * 3 + 0.5).pin_memory()
+    cam, trk = cfg['cam'], cfg['tracking']
+    H, W, iH, iW = cam['H'], cam['W'], trk['ignore_edge_H'], trk['ignore_edge_W']
+    # one synthetic RGB-D frame on the HOST, as the reference's DataLoader serves it (datasets/dataset.py:250-265)
+    frame_dirs = synth.camera_ray_dirs(H, W, cam['fx'], cam['fy'], cam['cx'], cam['cy'])[iH:H - iH, iW:W - iW, :].contiguous()
+    frame_rgb = torch.rand(H - 2 * iH, W - 2 * iW, 3, generator=g)
+    frame_depth = torch.rand(H - 2 * iH, W - 2 * iW, generator=g) * 3 + 0.5
+    Hh = H - 2 * iH
+    random.seed(11)
+
+    def draw():
+        """coslam.py:537-544: `tracking.sample` pixels by random.sample (bit-identical draws in C) and the CPU image gather."""
+        idx = torch.from_numpy(sample_range(Hh * (W - 2 * iW), n_rays))
+        ih, iw = idx % Hh, idx // Hh
+        return frame_dirs[ih, iw, :], frame_rgb[ih, iw, :], frame_depth[ih, iw].unsqueeze(-1)
+
     c2w0 = pose.pose_matrix(torch.tensor([[0.3, -0.5, 0.2]]), bound.mean(1)[None])[0]
-    out = {'rays': n_rays, 'iters': int(cfg['tracking']['iter'])}
+    out = {'rays': n_rays, 'iters': int(cfg['tracking']['iter']), 'frame': '%dx%d' % (W, H),
+           'timed_region': 'per frame: random.sample pixel draw + CPU gather of (direction, rgb, depth) + upload + %d iterations + pose read-back'
+                           % int(cfg['tracking']['iter'])}
     noise_state = (model.noise_mode, model._noise_counter)
     fusable = bool(cfg['grid']['oneGrid']) and cfg['training']['n_importance'] == 0
-    for name, use_graph, fused in (('graph', True, None), ('eager', False, None)) + ((('autograd_graph', True, False),) if fusable else ()):
+    for name, use_graph, fused in (('graph', True, None), ('eager', False, None)) + ((('autograd_graph', True, False),) if fusable and full else ()):
         tr = FrameTracker(model, cfg, device=dev, use_graph=use_graph, fused=fused)
         for _ in range(3):
-            tr.track(dir_cam, rgb, depth, c2w0)[0].cpu()
+            tr.track(*draw(), c2w0)[0].cpu()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for _ in range(frames):
-            tr.track(dir_cam, rgb, depth, c2w0)[0].cpu()          # the read-back is the per-frame sync
+            tr.track(*draw(), c2w0)[0].cpu()          # the read-back is the per-frame sync
         out['ms_per_frame_' + name] = (time.perf_counter() - t0) * 1e3 / frames
+    t0 = time.perf_counter()
+    for _ in range(frames):
+        draw()
+    out['ms_per_frame_pixel_draw_and_gather'] = (time.perf_counter() - t0) * 1e3 / frames
     model.noise_mode, model._noise_counter = noise_state
     out['ms_per_frame'] = out['ms_per_frame_graph']
     return out

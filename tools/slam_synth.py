@@ -337,6 +337,35 @@ def workload_config(workload, scale=1.0):
     return cfg
 
 
+def run_workload(workload='room0', frames=60, scale=1.0, first_iters=None, noise='device', dev='cuda:0'):
+    """One synthetic SLAM run (BASELINE.json configs 2 / 3 / 5 in miniature); returns the result dictionary `main` prints.
+    Re-entrant: the module-level room placement is reset first (bench.py runs the three workloads in one process)."""
+    SHIFT.zero_()
+    SCALE[0] = 1.0
+    seed_everything(0)
+    cfg = workload_config(workload, scale)
+    first_iters = cfg['mapping']['first_iters'] if first_iters is None else first_iters
+    frame_list = make_frames(cfg, frames, dev)
+    gt = torch.stack([f['c2w'] for f in frame_list])
+    slam = SynthSLAM(cfg, dev, frames, noise=noise)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    est = slam.run(frame_list, first_iters)
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    wall = t1 - t0
+    steady = (frames - 3) / (t1 - slam.t_steady) if getattr(slam, 't_steady', None) and frames > 3 else None
+    warm = slam.t_track[2:] if len(slam.t_track) > 4 else slam.t_track      # the first frame captures the graph
+    return {
+        'workload': '%s synthetic %dx%d RGB-D, %d frames, tracking %d rays x %d its, BA %d rays x %d its every %d frames' % (
+            workload, cfg['cam']['W'], cfg['cam']['H'], frames, cfg['tracking']['sample'], cfg['tracking']['iter'],
+            cfg['mapping']['sample'], cfg['mapping']['iters'], cfg['mapping']['map_every']),
+        'noise': noise, 'ate_rmse_cm': 100 * ate_rmse(est, gt), 'const_pose_ate_cm': 100 * ate_rmse(gt[:1].expand_as(gt), gt),
+        'tracking_ms_per_frame': 1e3 * sum(warm) / max(len(warm), 1),
+        'mapping_ms_per_iter': 1e3 * sum(slam.t_map) / max(slam.n_map_iters, 1),
+        'frames_per_s': (frames - 1) / wall, 'steady_frames_per_s': steady, 'first_frame_iters': first_iters}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--frames', type=int, default=60)
@@ -345,29 +374,7 @@ def main():
     ap.add_argument('--noise', default='device', choices=('device', 'host'))
     ap.add_argument('--workload', default='room0', choices=('room0', 'scannet0000', 'tum_desk'))
     a = ap.parse_args()
-    dev = 'cuda:0'
-    seed_everything(0)
-    cfg = workload_config(a.workload, a.scale)
-    first_iters = cfg['mapping']['first_iters'] if a.first_iters is None else a.first_iters
-    frames = make_frames(cfg, a.frames, dev)
-    gt = torch.stack([f['c2w'] for f in frames])
-    slam = SynthSLAM(cfg, dev, a.frames, noise=a.noise)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    est = slam.run(frames, first_iters)
-    torch.cuda.synchronize()
-    t1 = time.perf_counter()
-    wall = t1 - t0
-    steady = (a.frames - 3) / (t1 - slam.t_steady) if getattr(slam, 't_steady', None) and a.frames > 3 else None
-    warm = slam.t_track[2:] if len(slam.t_track) > 4 else slam.t_track      # the first frame captures the graph
-    print(json.dumps({
-        'workload': '%s synthetic %dx%d RGB-D, %d frames, tracking %d rays x %d its, BA %d rays x %d its every %d frames' % (
-            a.workload, cfg['cam']['W'], cfg['cam']['H'], a.frames, cfg['tracking']['sample'], cfg['tracking']['iter'],
-            cfg['mapping']['sample'], cfg['mapping']['iters'], cfg['mapping']['map_every']),
-        'noise': a.noise, 'ate_rmse_cm': 100 * ate_rmse(est, gt), 'const_pose_ate_cm': 100 * ate_rmse(gt[:1].expand_as(gt), gt),
-        'tracking_ms_per_frame': 1e3 * sum(warm) / max(len(warm), 1),
-        'mapping_ms_per_iter': 1e3 * sum(slam.t_map) / max(slam.n_map_iters, 1),
-        'frames_per_s': (a.frames - 1) / wall, 'steady_frames_per_s': steady, 'first_frame_iters': first_iters}))
+    print(json.dumps(run_workload(a.workload, a.frames, a.scale, a.first_iters, a.noise)))
 
 
 if __name__ == '__main__':
