@@ -60,7 +60,17 @@ def tum_desk_config(n_importance=0, perturb=1):
     return c
 
 
-CONFIGS = {'room0': room0_config, 'scannet0000': scannet0000_config, 'tum_desk': tum_desk_config}
+def room0_twogrid_config():
+    """room0 with `grid.oneGrid: False`: a second hash grid at voxel_color 0.08 for the colour net (model/scene_rep.py:56-58,
+    ColorSDFNet model/decoder.py:110-143).  Config-reachable, selected by no shipped YAML."""
+    c = room0_config()
+    c['grid']['oneGrid'] = False
+    c['mapping']['lr_embed_color'] = 0.01
+    return c
+
+
+CONFIGS = {'room0': room0_config, 'scannet0000': scannet0000_config, 'tum_desk': tum_desk_config,
+           'room0_twogrid': room0_twogrid_config}
 
 
 def bound_tensor(cfg):
@@ -118,15 +128,16 @@ def table_init(n_params, kind='small', seed=1337):
     return (torch.rand(n_params, generator=g) * 2.0 - 1.0) * scale
 
 
-def decoder_init(seed=0):
-    """nn.Linear default init U(-1/sqrt(in), 1/sqrt(in)) for the four bias-free matrices [out, in]."""
+def decoder_init(seed=0, col_in=63):
+    """nn.Linear default init U(-1/sqrt(in), 1/sqrt(in)) for the four bias-free matrices [out, in]; col_in = 63 for the
+    one-grid colour net (48 OneBlob + 15 geo), 95 with the colour grid's 32 features (two-grid variant)."""
     g = torch.Generator().manual_seed(seed)
 
     def lin(o, i):
         k = 1.0 / math.sqrt(i)
         return (torch.rand(o, i, generator=g) * 2 - 1) * k
 
-    return lin(32, 80), lin(16, 32), lin(32, 63), lin(3, 32)
+    return lin(32, 80), lin(16, 32), lin(32, col_in), lin(3, 32)
 
 
 def keyframe_ray_batch(cfg, n_rays, n_kf=64, seed=0, invalid_frac=0.05):

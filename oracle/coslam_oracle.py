@@ -75,16 +75,16 @@ def tum_desk_config(n_importance=0):
     return c
 
 
-def sdf_resolution(cfg, bound):
-    """model/scene_rep.py:23-31  get_resolution: int(dim_max / voxel_sdf) evaluated with a torch fp32 scalar."""
+def sdf_resolution(cfg, bound, voxel_key='voxel_sdf'):
+    """model/scene_rep.py:23-35  get_resolution: int(dim_max / voxel_sdf) (and / voxel_color) evaluated with a torch fp32 scalar."""
     dim_max = (bound[:, 1] - bound[:, 0]).max()
-    v = cfg['grid']['voxel_sdf']
+    v = cfg['grid'][voxel_key]
     return v if v > 10 else int(dim_max / v)
 
 
-def hashgrid_encoding_config(cfg, bound, n_levels=16, level_dim=2, base_resolution=16):
+def hashgrid_encoding_config(cfg, bound, n_levels=16, level_dim=2, base_resolution=16, voxel_key='voxel_sdf'):
     """model/encodings.py:31-46  (HashGrid branch of get_encoder)."""
-    desired = sdf_resolution(cfg, bound)
+    desired = sdf_resolution(cfg, bound, voxel_key)
     per_level_scale = np.exp2(np.log2(desired / base_resolution) / (n_levels - 1))
     return {'otype': 'HashGrid', 'n_levels': n_levels, 'n_features_per_level': level_dim,
             'log2_hashmap_size': cfg['grid']['hash_size'], 'base_resolution': base_resolution,
@@ -96,8 +96,9 @@ def hashgrid_encoding_config(cfg, bound, n_levels=16, level_dim=2, base_resoluti
 # --------------------------------------------------------------------------------------
 
 class OracleScene(object):
-    """Restatement of model/scene_rep.py:10-351 (JointEncoding) for the oneGrid / nn.Linear configuration,
-    with the decoder of model/decoder.py:145-180 (ColorSDFNet_v2), :57-108 (SDFNet), :7-55 (ColorNet)."""
+    """Restatement of model/scene_rep.py:10-351 (JointEncoding) for the nn.Linear configurations, with the decoders of
+    model/decoder.py:145-180 (ColorSDFNet_v2, `oneGrid: True`) and :110-143 (ColorSDFNet, `oneGrid: False`), :57-108 (SDFNet),
+    :7-55 (ColorNet)."""
 
     def __init__(self, cfg, bound, seed=0):
         self.cfg = cfg
@@ -107,6 +108,12 @@ class OracleScene(object):
         d = cfg['decoder']
         in_sdf = self.grid.n_output_dims + self.blob.n_output_dims
         in_col = self.blob.n_output_dims + d['geo_feat_dim']
+        # two-grid variant (`oneGrid: False`): a second hash grid at voxel_color (scene_rep.py:56-58, :32-33) whose feature
+        # joins the colour net's input (ColorSDFNet, decoder.py:110-143: cat([embed_pos, embed_color, geo_feat]))
+        self.grid_color = None
+        if not cfg['grid']['oneGrid']:
+            self.grid_color = tcnn_shim.Encoding(3, hashgrid_encoding_config(cfg, self.bound, voxel_key='voxel_color'))
+            in_col += self.grid_color.n_output_dims
         g = torch.Generator().manual_seed(seed)
 
         def lin(o, i):   # nn.Linear default init: U(-1/sqrt(in), 1/sqrt(in)), bias=False (decoder.py:51, 104)
@@ -124,20 +131,28 @@ class OracleScene(object):
     def table(self):
         return self.grid.params
 
+    @property
+    def table_color(self):
+        return self.grid_color.params
+
     def to(self, device):
         """The restatement is plain torch, so it also runs on a CUDA device (used by the trajectory test to keep it short)."""
         self.bound = self.bound.to(device)
         self.grid.to(device)
+        if self.grid_color is not None:
+            self.grid_color.to(device)
         for k in ('W1', 'W2', 'W3', 'W4'):
             setattr(self, k, getattr(self, k).detach().to(device).requires_grad_(True))
         return self
 
     def parameters(self):
-        return [self.grid.params, self.W1, self.W2, self.W3, self.W4]
+        return [self.grid.params, self.W1, self.W2, self.W3, self.W4] + ([self.grid_color.params] if self.grid_color is not None else [])
 
-    def load_weights(self, table, W1, W2, W3, W4):
+    def load_weights(self, table, W1, W2, W3, W4, table_color=None):
         with torch.no_grad():
             self.grid.params.copy_(torch.as_tensor(table))
+            if table_color is not None:
+                self.grid_color.params.copy_(torch.as_tensor(table_color))
             for dst, src in zip((self.W1, self.W2, self.W3, self.W4), (W1, W2, W3, W4)):
                 dst.copy_(torch.as_tensor(src))
 
@@ -153,7 +168,7 @@ class OracleScene(object):
     z_all_override = None
     last_z_all = None
 
-    def decode(self, embed, embed_pos):
+    def decode(self, embed, embed_pos, embed_color=None):
         ov = self.mask_override
         if isinstance(ov, list):
             ov = ov.pop(0)
@@ -161,7 +176,8 @@ class OracleScene(object):
         a1 = torch.relu(h1) if ov is None else torch.where(ov[0], h1, torch.zeros_like(h1))
         h = a1 @ self.W2.t()
         sdf, geo = h[..., :1], h[..., 1:]
-        h3 = torch.cat([embed_pos, geo], -1) @ self.W3.t()
+        col_in = [embed_pos, geo] if embed_color is None else [embed_pos, embed_color, geo]      # decoder.py:176 / :138
+        h3 = torch.cat(col_in, -1) @ self.W3.t()
         a3 = torch.relu(h3) if ov is None else torch.where(ov[1], h3, torch.zeros_like(h3))
         rgb = a3 @ self.W4.t()
         self.last_pre = (h1.detach(), h3.detach())
@@ -172,6 +188,8 @@ class OracleScene(object):
     # ---- scene_rep.py:155-171 -------------------------------------------------------
     def query_color_sdf(self, x):
         flat = x.reshape(-1, x.shape[-1])
+        if self.grid_color is not None:                            # scene_rep.py:168-170
+            return self.decode(self.grid(flat), self.blob(flat), self.grid_color(flat))
         return self.decode(self.grid(flat), self.blob(flat))
 
     # ---- scene_rep.py:126-153 -------------------------------------------------------

@@ -39,6 +39,8 @@ CASES = [
     # BASELINE config 1's size: the direct (no activation-pattern injection) 1e-3 gradient gate over ~176 k points.
     # Per-point tensors are stored as checksums / strided samples to keep the fixture small.
     ('room0_4096', 'room0', {}, 4096, 'trained', 4, {}),
+    # two-grid variant: `oneGrid: False`, second hash grid at voxel_color, ColorSDFNet (decoder.py:110-143)
+    ('room0_twogrid', 'room0_twogrid', {}, 128, 'trained', 9, {}),
 ]
 LARGE = {'room0_4096'}
 
@@ -47,11 +49,16 @@ def checksum(t):
     return hashlib.sha256(np.ascontiguousarray(t.detach().cpu().numpy()).tobytes()).hexdigest()[:16]
 
 
-def build_reference_model(cfg, table, weights):
+COLOR_TABLE_SEED = 1338
+
+
+def build_reference_model(cfg, table, weights, table_color=None):
     JointEncoding = ref_loader.load_reference_model_class()
     model = JointEncoding(cfg, synth.bound_tensor(cfg))
     with torch.no_grad():
         model.embed_fn.params.copy_(table)
+        if table_color is not None:
+            model.embed_fn_color.params.copy_(table_color)
         model.decoder.sdf_net.model[0].weight.copy_(weights[0])
         model.decoder.sdf_net.model[2].weight.copy_(weights[1])
         model.decoder.color_net.model[0].weight.copy_(weights[2])
@@ -75,13 +82,15 @@ def table_grad_summary(g, meta, n_pick=4096, seed=0):
 def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
     cfg = synth.CONFIGS[cfg_name](**cfg_kw)
     rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n_rays, seed=seed, **batch_kw)
-    weights = synth.decoder_init(seed=seed)
+    two_grid = not cfg['grid']['oneGrid']
+    weights = synth.decoder_init(seed=seed, col_in=95 if two_grid else 63)
     # table size comes from the reference model itself
     JointEncoding = ref_loader.load_reference_model_class()
     model = JointEncoding(cfg, synth.bound_tensor(cfg))
     n_params = model.embed_fn.params.numel()
     table = synth.table_init(n_params, table_kind)
-    model = build_reference_model(cfg, table, weights)
+    table_color = synth.table_init(model.embed_fn_color.params.numel(), table_kind, seed=COLOR_TABLE_SEED) if two_grid else None
+    model = build_reference_model(cfg, table, weights, table_color)
     model.train()
 
     S = cfg['training']['n_samples_d'] + cfg['training']['n_range_d']
@@ -110,7 +119,7 @@ def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
 
     # ---- cross-check the restatement against the reference ----------------------------------------------------
     orc = coslam_oracle.OracleScene(cfg, synth.bound_tensor(cfg))
-    orc.load_weights(table, *weights)
+    orc.load_weights(table, *weights, table_color=table_color)
     o2 = rays_o.clone().requires_grad_(True)
     d2 = rays_d.clone().requires_grad_(True)
     r2 = orc.forward(o2, d2, rgb, depth, noise=noise, noise_imp=u_imp)
@@ -135,6 +144,8 @@ def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
     close(orc.W2.grad, model.decoder.sdf_net.model[2].weight.grad, 'dW2', rtol=1e-4)
     close(orc.W3.grad, model.decoder.color_net.model[0].weight.grad, 'dW3', rtol=1e-4)
     close(orc.W4.grad, model.decoder.color_net.model[2].weight.grad, 'dW4', rtol=1e-4)
+    if two_grid:
+        close(orc.table_color.grad, model.embed_fn_color.params.grad, 'd colour table', rtol=1e-4)
 
     # ---- bit-exact gates: positions and hash indices from the reference's arithmetic --------------------------
     z = ev['z_vals']
@@ -192,10 +203,58 @@ def run_case(name, cfg_name, cfg_kw, n_rays, table_kind, seed, batch_kw):
         out.update({'z_coarse': ev0['z_vals'].numpy(), 'w_coarse': w0.detach().numpy()})
         close(ev0['rgb'], ev['rgb0'], 'coarse rgb of the one-pass model')
     out.update(table_grad_summary(model.embed_fn.params.grad, meta))
+    if two_grid:
+        cm = model.embed_fn_color.impl.meta
+        out.update({'c' + k: v for k, v in table_grad_summary(model.embed_fn_color.params.grad, cm).items()})
+        out.update({'chk_table_color': checksum(table_color), 'color_table_seed': COLOR_TABLE_SEED,
+                    'color_grid_offset': np.asarray(cm['offset'], dtype=np.uint32), 'color_grid_res': np.asarray(cm['res'], dtype=np.uint32)})
     path = os.path.join(GOLDEN_DIR, name + '.npz')
     np.savez_compressed(path, **out)
     print('%-22s N=%d S=%d loss=%.6f  -> %s (%.0f KB)' % (name, n_rays, S, loss.item(), os.path.relpath(path, ROOT),
                                                           os.path.getsize(path) / 1024))
+
+
+MESH_CASES = [
+    # name, config, voxel size (mesh.voxel_eval 0.05 of every shipped YAML; 0.1 as a second, coarser lattice)
+    ('room0_eval', 'room0', 0.05), ('scannet0000_eval', 'scannet0000', 0.05), ('tum_desk_eval', 'tum_desk', 0.05),
+    ('room0_coarse', 'room0', 0.1),
+]
+
+
+def reference_mesh_lattice(cfg, voxel_size):
+    """Runs the reference's OWN extract_mesh (utils.py:80-135, unmodified) with a recording query function and the stubbed
+    marching cubes: returns (tx, ty, tz, the normalised query points in the order of its 65 536-point chunk loop)."""
+    from oracle import ref_env
+    ref_utils = ref_env.import_reference('utils')
+    bound = synth.bound_tensor(cfg)
+    seen = []
+
+    def query_fn(pts):                                   # [chunk, 1, 3] -> [chunk, 1]
+        seen.append(pts.reshape(-1, 3).clone())
+        return torch.zeros(pts.shape[:-1])
+    mesh_cfg = dict(cfg, mesh={'render_color': False})
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        ref_utils.extract_mesh(query_fn, mesh_cfg, bound, marching_cube_bound=bound, voxel_size=voxel_size,
+                               mesh_savepath=os.path.join(tmp, 'm', 'mesh.ply'))
+    x_min, y_min, z_min = bound[:, 0]
+    x_max, y_max, z_max = bound[:, 1]
+    tx, ty, tz = ref_utils.getVoxels(x_max, x_min, y_max, y_min, z_max, z_min, voxel_size, None)
+    return tx, ty, tz, torch.cat(seen, 0)
+
+
+def write_mesh_golden():
+    import json
+    out = {}
+    for name, cfg_name, voxel in MESH_CASES:
+        cfg = synth.CONFIGS[cfg_name]()
+        tx, ty, tz, flat = reference_mesh_lattice(cfg, voxel)
+        out[name] = {'cfg_name': cfg_name, 'voxel_size': voxel, 'shape': [len(tx), len(ty), len(tz)],
+                     'chk_tx': checksum(tx), 'chk_ty': checksum(ty), 'chk_tz': checksum(tz), 'chk_points': checksum(flat),
+                     'first_point': [float(v) for v in flat[0]], 'last_point': [float(v) for v in flat[-1]]}
+        print('%-22s lattice %s, %d points' % (name, out[name]['shape'], flat.shape[0]))
+    with open(os.path.join(GOLDEN_DIR, 'mesh_lattice.json'), 'w') as f:
+        json.dump(out, f, indent=1)
 
 
 def main():
@@ -207,6 +266,8 @@ def main():
     for case in CASES:
         if not only or case[0] in only:
             run_case(*case)
+    if not only or 'mesh_lattice' in only:
+        write_mesh_golden()
 
 
 if __name__ == '__main__':

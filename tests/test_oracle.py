@@ -17,12 +17,12 @@ from oracle import c_oracle, coslam_oracle, ref_loader, tcnn_shim
 from tests import util
 
 
-@pytest.mark.parametrize('name', util.GOLDEN_CASES + util.IMPORTANCE_CASES + util.LARGE_CASES)
+@pytest.mark.parametrize('name', util.GOLDEN_CASES + util.IMPORTANCE_CASES + util.LARGE_CASES + util.TWOGRID_CASES)
 def test_oracle_reproduces_reference_golden(name):
     g = util.load_golden(name)
     cfg, (rays_o, rays_d, rgb, depth), table, weights, noise = util.case_inputs(g)
     u_imp = util.case_noise(g, cfg)[1]
-    orc = util.make_oracle(cfg, table, weights)
+    orc = util.make_oracle(cfg, table, weights, util.color_table(g, cfg) if name in util.TWOGRID_CASES else None)
     o = rays_o.clone().requires_grad_(True)
     d = rays_d.clone().requires_grad_(True)
     r = orc.forward(o, d, rgb, depth, noise=noise, noise_imp=u_imp)
@@ -52,6 +52,10 @@ def test_oracle_reproduces_reference_golden(name):
     tg = orc.table.grad
     util.assert_close(tg[torch.from_numpy(g['tg_pick_idx'])], g['tg_pick_val'], 'table grad (sampled)', 1e-4)
     assert int(torch.count_nonzero(tg)) == int(g['tg_nnz'])
+    if name in util.TWOGRID_CASES:                                             # decoder.py:110-143, scene_rep.py:56-58, 168-170
+        cg = orc.table_color.grad
+        util.assert_close(cg[torch.from_numpy(g['ctg_pick_idx'])], g['ctg_pick_val'], 'colour table grad (sampled)', 1e-4)
+        assert int(torch.count_nonzero(cg)) == int(g['ctg_nnz'])
 
 
 @pytest.mark.parametrize('name', util.GOLDEN_CASES)

@@ -1011,35 +1011,48 @@ def test_lazy_forward_is_exact(cfg_name, kind):
         assert bool((ev[:, 1:] <= ev[:, :-1]).all())        # what is evaluated is a prefix of every ray
 
 
-def test_two_grid_variant_runs_through_standalone_operators():
-    """`oneGrid: False` (model/scene_rep.py:56-58, 168-170): second hash grid for colour and the
-    ColorSDFNet decoder.  Not served by the fused kernels; the training step composes the stand-alone CUDA encodings, the torch
-    decoder and the rendering / loss kernels.  Checked against the same composition written out with the rendering oracle."""
-    cfg = synth.room0_config()
-    cfg['grid']['oneGrid'] = False
-    cfg['training']['perturb'] = 0.0
+def test_two_grid_variant_matches_reference_golden():
+    """`oneGrid: False` (model/scene_rep.py:56-58, 168-170; ColorSDFNet, model/decoder.py:110-143):
+    second hash grid for colour.  Not served by the fused kernels; the training step composes the stand-alone CUDA encodings, the
+    torch decoder and the rendering / loss kernels.  Compared DIRECTLY with the fixture the unmodified reference produced
+    (oracle/gen_golden.py, case room0_twogrid): values, ray / decoder / both tables' gradients, eval dictionary."""
+    g = util.load_golden('room0_twogrid')
+    cfg, (rays_o, rays_d, rgb, depth), table, weights, noise = util.case_inputs(g)
+    assert cfg['grid']['oneGrid'] is False
     model = JointEncodingFor(cfg)
     assert hasattr(model, 'embed_fn_color') and type(model.decoder).__name__ == 'ColorSDFNet'
+    assert sorted(model.state_dict().keys()) == [str(k) for k in g['state_dict_keys']]
     with torch.no_grad():
-        model.embed_fn.params.uniform_(-0.5, 0.5)
-        model.embed_fn_color.params.uniform_(-0.5, 0.5)
+        model.embed_fn.params.copy_(table.to(DEV))
+        model.embed_fn_color.params.copy_(util.color_table(g, cfg).to(DEV))
+        ws = (model.decoder.sdf_net.model[0].weight, model.decoder.sdf_net.model[2].weight,
+              model.decoder.color_net.model[0].weight, model.decoder.color_net.model[2].weight)
+        for dst, src in zip(ws, weights):
+            dst.copy_(src.to(DEV))
     model.train()
-    n = 300
-    rays_o, rays_d, rgb, depth = (t.to(DEV) for t in synth.ray_batch(cfg, n, seed=2))
-    o = rays_o.clone().requires_grad_(True)
-    ret = model.forward(o, rays_d, rgb, depth)
-    _weighted_loss(cfg, ret).backward()
-    assert model.embed_fn_color.params.grad is not None and float(model.embed_fn_color.params.grad.abs().max()) > 0
-    assert model.embed_fn.params.grad is not None and o.grad is not None
-    # same raw -> the oracle's sdf2weights / raw2outputs on the CPU
-    from oracle.coslam_oracle import OracleScene
-    orc = OracleScene(synth.room0_config(), synth.bound_tensor(cfg))
+    o = rays_o.to(DEV).requires_grad_(True)
+    d = rays_d.to(DEV).requires_grad_(True)
+    torch.manual_seed(int(g['noise_seed']))
+    ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
+    loss = _weighted_loss(cfg, ret)
+    loss.backward()
+    for k in ('rgb', 'depth', 'rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss', 'psnr'):
+        util.assert_close(ret[k], g[k], k)
+    util.assert_close(loss, float(g['loss']), 'loss')
+    util.assert_close(o.grad, g['d_rays_o'], 'd_rays_o')
+    util.assert_close(d.grad, g['d_rays_d'], 'd_rays_d')
+    for k, w in zip(('dW1', 'dW2', 'dW3', 'dW4'), ws):
+        util.assert_close(w.grad, g[k], k)
+    for prefix, p in (('', model.embed_fn.params), ('c', model.embed_fn_color.params)):
+        util.assert_close(p.grad[torch.from_numpy(g[prefix + 'tg_pick_idx']).to(DEV)], g[prefix + 'tg_pick_val'], prefix + 'table grad (sampled)')
+        assert int(torch.count_nonzero(p.grad)) == int(g[prefix + 'tg_nnz'])
+    model.eval()
     with torch.no_grad():
-        z = model._sample(depth)
-        raw = model.ray_points(rays_o, rays_d, z)
-        out = orc.raw2outputs(raw.cpu(), z.cpu())
-    util.assert_close(ret['rgb'], out['rgb'], 'rgb')
-    util.assert_close(ret['depth'], out['depth'], 'depth')
+        torch.manual_seed(int(g['noise_seed']))
+        ev = model.forward(rays_o.to(DEV), rays_d.to(DEV), rgb.to(DEV), depth.to(DEV))
+    assert np.array_equal(ev['z_vals'].cpu().numpy(), g['z_vals'])
+    for k in ('raw', 'rgb', 'depth', 'depth_var', 'acc_map'):
+        util.assert_close(ev[k], g[k], 'eval ' + k)
 
 
 def test_mesh_lattice_query_matches_chunked_loop():

@@ -16,6 +16,8 @@ GOLDEN_CASES = ['room0_small', 'room0_trained', 'scannet0000_trained', 'tum_desk
 IMPORTANCE_CASES = ['tum_desk_imp128_det', 'tum_desk_imp128', 'tum_desk_imp8_det', 'tum_desk_imp8']
 # BASELINE config 1's size (4096 rays, ~176 k points); per-point tensors stored as checksums + every 16th ray
 LARGE_CASES = ['room0_4096']
+# `oneGrid: False` (second hash grid for colour, ColorSDFNet): SURVEY 8(f) rank 4, through the unmodified reference
+TWOGRID_CASES = ['room0_twogrid']
 
 REL_TOL = 1e-3          # north_star: rendered depth/colour, SDF and gradients within 1e-3 relative (fp32 tables)
 
@@ -33,7 +35,8 @@ def case_inputs(g):
     cfg = synth.CONFIGS[str(g['cfg_name'])](**ast.literal_eval(str(g['cfg_kw'])))
     n = int(g['n_rays'])
     rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n, seed=int(g['seed']), **ast.literal_eval(str(g['batch_kw'])))
-    weights = synth.decoder_init(seed=int(g['seed']))
+    two_grid = not cfg['grid']['oneGrid']
+    weights = synth.decoder_init(seed=int(g['seed']), col_in=95 if two_grid else 63)
     from oracle import tcnn_shim
     from oracle.coslam_oracle import hashgrid_encoding_config
     enc = hashgrid_encoding_config(cfg, synth.bound_tensor(cfg))
@@ -63,10 +66,22 @@ def case_noise(g, cfg):
     return noise, u
 
 
-def make_oracle(cfg, table, weights):
+def color_table(g, cfg):
+    """The colour grid's table of a two-grid golden case (seeded, checksum verified)."""
+    from oracle import tcnn_shim
+    from oracle.coslam_oracle import hashgrid_encoding_config
+    enc = hashgrid_encoding_config(cfg, synth.bound_tensor(cfg), voxel_key='voxel_color')
+    meta = tcnn_shim.grid_meta(enc['n_levels'], enc['log2_hashmap_size'], enc['base_resolution'], enc['per_level_scale'])
+    assert np.array_equal(np.asarray(meta['offset'], dtype=np.uint32), g['color_grid_offset'])
+    t = synth.table_init(meta['offset'][-1] * 2, str(g['table_kind']), seed=int(g['color_table_seed']))
+    assert checksum(t) == str(g['chk_table_color'])
+    return t
+
+
+def make_oracle(cfg, table, weights, table_color=None):
     from oracle.coslam_oracle import OracleScene
     orc = OracleScene(cfg, synth.bound_tensor(cfg))
-    orc.load_weights(table, *weights)
+    orc.load_weights(table, *weights, table_color=table_color)
     return orc
 
 
