@@ -21,6 +21,8 @@ class _Inert(object):
     """Accepts any attribute access / call chain (matplotlib figures)."""
 
     def __getattr__(self, name):
+        if name.startswith('__'):
+            raise AttributeError(name)
         return _Inert()
 
     def __call__(self, *a, **k):
@@ -32,7 +34,12 @@ class _Inert(object):
 
 def _inert_module(name):
     m = types.ModuleType(name)
-    m.__getattr__ = lambda attr: _Inert()
+
+    def module_getattr(attr):
+        if attr.startswith('__'):                          # inspect / importlib probe __file__, __path__, ...
+            raise AttributeError(attr)
+        return _Inert()
+    m.__getattr__ = module_getattr
     return m
 
 
@@ -71,14 +78,48 @@ def install_stubs():
                     f.write('stub mesh: %d vertices\n' % (0 if self.vertices is None else len(self.vertices)))
         tm.Trimesh = Trimesh
         sys.modules['trimesh'] = tm
-    for name in ('matplotlib', 'matplotlib.pyplot', 'mathutils'):
+    for name in ('matplotlib', 'matplotlib.pyplot', 'matplotlib.pylab', 'matplotlib.patches'):
         if name not in sys.modules:
             try:
                 __import__(name)
             except ImportError:
                 sys.modules[name] = _inert_module(name)
     if isinstance(sys.modules.get('matplotlib'), types.ModuleType) and not hasattr(sys.modules['matplotlib'], '__file__'):
-        sys.modules['matplotlib'].pyplot = sys.modules['matplotlib.pyplot']
+        for sub in ('pyplot', 'pylab', 'patches'):
+            setattr(sys.modules['matplotlib'], sub, sys.modules['matplotlib.' + sub])
+    if 'mathutils' not in sys.modules:
+        try:
+            __import__('mathutils')
+        except ImportError:
+            mu = types.ModuleType('mathutils')
+
+            class Matrix(object):
+                """mathutils.Matrix(R).to_quaternion() as tools/eval_ate.py:22-26 uses it: (w, x, y, z) of a 3x3 rotation."""
+
+                def __init__(self, rows):
+                    self.m = np.asarray(rows, dtype=np.float64)
+
+                def to_quaternion(self):
+                    from scipy.spatial.transform import Rotation
+                    x, y, z, w = Rotation.from_matrix(self.m).as_quat()
+                    return np.array([w, x, y, z])
+            mu.Matrix = Matrix
+            sys.modules['mathutils'] = mu
+
+
+def register_reference_packages(root):
+    """The reference's top-level directories (`datasets`, `model`, `optimization`, `mp_slam`, `tools`) have no __init__.py, so a
+    regular package of the same name anywhere on sys.path (HuggingFace `datasets` is installed in this image) would win the
+    import.  Register them explicitly, as the packages they are in the reference's own environment."""
+    import os
+    for name in ('datasets', 'model', 'optimization', 'mp_slam', 'tools'):
+        d = os.path.join(root, name)
+        if os.path.isdir(d):
+            pkg = types.ModuleType(name)
+            pkg.__path__ = [d]
+            sys.modules[name] = pkg
+    if root not in sys.path:
+        sys.path.insert(0, root)
 
 
 def import_reference(name):
