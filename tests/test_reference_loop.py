@@ -43,3 +43,41 @@ def test_unmodified_coslam_py_runs_on_the_drop_in(tmp_path):
         assert r['ate_rmse_cm'] < 2.0, r                       # both track the 30-frame sequence (static-pose ATE is ~15 cm)
     assert abs(ours['ate_rmse_cm'] - ref['ate_rmse_cm']) < 0.2, (ours, ref)
     assert abs(ours['reference_pose_evaluation_ate_rmse_cm'] - ref['reference_pose_evaluation_ate_rmse_cm']) < 0.2, (ours, ref)
+
+
+def _run_mp(model, data, workdir, frames=30, timeout=600):
+    import signal
+    out = os.path.join(workdir, 'result.json')
+    os.makedirs(workdir, exist_ok=True)
+    cmd = [sys.executable, os.path.join(ROOT, 'tools', 'run_reference_coslam_mp.py'), '--model', model, '--frames', str(frames),
+           '--scale', '0.5', '--data', data, '--workdir', workdir, '--out', out]
+    log = open(os.path.join(workdir, 'log.txt'), 'w')
+    p = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, start_new_session=True)      # own process group: the workers die with it
+    try:
+        rc = p.wait(timeout=timeout)
+    except subprocess.TimeoutExpired:
+        os.killpg(p.pid, signal.SIGKILL)
+        p.wait()
+        rc = 'timeout after %d s' % timeout
+    finally:
+        try:
+            os.killpg(p.pid, signal.SIGKILL)                  # a worker that outlived the parent (one side crashed, the other spins)
+        except ProcessLookupError:
+            pass
+    log.close()
+    tail = open(os.path.join(workdir, 'log.txt')).read()[-4000:]
+    assert rc == 0, 'coslam_mp.py (%s) failed (%s):\n%s' % (model, rc, tail)
+    return json.load(open(out))
+
+
+def test_unmodified_coslam_mp_py_runs_on_the_drop_in(tmp_path):
+    """coslam_mp.py:295-320 unchanged: mapper process + tracker process (spawn) on ONE GPU, sharing the drop-in model through
+    `.share_memory()` / pickling / `copy.deepcopy` (mp_slam/tracker.py:27), the pose tensors and the two progress counters."""
+    data = str(tmp_path / 'room0_synth')
+    ours = _run_mp('ours', data, str(tmp_path / 'mp_ours'))
+    os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
+    with open(os.path.join(ROOT, 'gpurun_out', 'reference_coslam_mp_loop.json'), 'w') as f:
+        json.dump({'ours': ours}, f, indent=1)
+    assert ours['model_class'] == 'coslam_b200.scene_rep.JointEncoding'
+    assert ours['tracked_to'] == 29 and ours['all_poses_filled'], ours
+    assert ours['ate_rmse_cm'] < 2.0, ours
