@@ -34,14 +34,15 @@ def _build(cfg, dev):
     return model
 
 
-def _worker(rank, world, port, n_rays, out):
+def _worker(rank, world, port, n_rays, out, backend='nccl', one_gpu=False):
+    """one_gpu: every rank on cuda:0 over gloo (the host logic is backend-agnostic), so a 1-GPU box can run the shard parity."""
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
-    torch.cuda.set_device(rank)
-    dist.init_process_group('nccl', rank=rank, world_size=world)
+    torch.cuda.set_device(0 if one_gpu else rank)
+    dist.init_process_group(backend, rank=rank, world_size=world)
     try:
         from coslam_b200.dist import ShardedMapper, equal_shard
-        dev = 'cuda:%d' % rank
+        dev = 'cuda:0' if one_gpu else 'cuda:%d' % rank
         cfg = synth.room0_config()
         cfg['training']['perturb'] = 0.0
         model = _build(cfg, dev)
@@ -60,16 +61,21 @@ def _worker(rank, world, port, n_rays, out):
 
 
 def test_two_gpu_sharded_step_matches_single_gpu():
-    n_rays, world = 4096, 2
+    check_sharded_step('nccl', False)
+
+
+def check_sharded_step(backend, one_gpu, world=2):
+    n_rays = 4096
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_worker, args=(world, _free_port(), n_rays, out), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), n_rays, out, backend, one_gpu), nprocs=world, join=True)
 
     dev = 'cuda:0'
     cfg = synth.room0_config()
     cfg['training']['perturb'] = 0.0
     model = _build(cfg, dev)
-    batch = synth.keyframe_ray_batch(cfg, n_rays, n_kf=8, seed=3)
+    n_use = (n_rays // world) * world                    # equal_shard drops the remainder, like DistributedSampler(drop_last=True)
+    batch = [t[:n_use] for t in synth.keyframe_ray_batch(cfg, n_rays, n_kf=8, seed=3)[:4]]
     o = batch[0].to(dev).requires_grad_(True)
     d = batch[1].to(dev).requires_grad_(True)
     ret = model.forward(o, d, batch[2].to(dev), batch[3].to(dev))
@@ -86,21 +92,22 @@ def test_two_gpu_sharded_step_matches_single_gpu():
             assert abs(a - float(ret[k].detach())) <= 1e-5 * abs(float(ret[k].detach())) + 1e-9, k
         assert rel(out[r]['d_table'], model.embed_fn.params.grad.cpu()) <= 1e-3
         assert rel(out[r]['dW1'], model.decoder.fused_weights()[0].grad.cpu()) <= 1e-3
-    assert torch.equal(out[0]['d_table'], out[1]['d_table'])          # replicas stay identical after AR-2
-    got = torch.cat([out[0]['d_rays_o'], out[1]['d_rays_o']], 0)
+    for r in range(1, world):
+        assert torch.equal(out[0]['d_table'], out[r]['d_table'])      # replicas stay identical after AR-2
+    got = torch.cat([out[r]['d_rays_o'] for r in range(world)], 0)
     assert rel(got, o.grad.cpu()) <= 1e-3
 
 
-def _ba_worker(rank, world, port, out):
+def _ba_worker(rank, world, port, out, backend='nccl', one_gpu=False):
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
-    torch.cuda.set_device(rank)
-    dist.init_process_group('nccl', rank=rank, world_size=world)
+    torch.cuda.set_device(0 if one_gpu else rank)
+    dist.init_process_group(backend, rank=rank, world_size=world)
     try:
         import random
         from coslam_b200.mapping import BundleAdjuster
         from tests.test_mapping_gpu import _map_optimizer, _setup
-        dev = 'cuda:%d' % rank
+        dev = 'cuda:0' if one_gpu else 'cuda:%d' % rank
         cfg, model, db, kf_poses, cur_pose, current = _setup('room0', dev=dev)
         cfg['mapping'].update({'iters': 6, 'map_accum_step': 2, 'map_wait_step': 2, 'pose_accum_step': 3})
         random.seed(5 + 100 * rank); torch.manual_seed(5 + 100 * rank)        # rank 0's draws are the ones that count (broadcast)
@@ -117,14 +124,16 @@ def test_two_gpu_sharded_bundle_adjustment_matches_single_gpu():
     """BundleAdjuster with the rays of every iteration sharded over 2 ranks (AR-1 on the counts / loss sums, AR-2 on the flat
     gradient bucket and the pose gradients in front of the optimiser steps) against the single-GPU call on the same draws:
     replicas identical, poses and parameter updates equal up to the summation order."""
-    import copy
+    check_sharded_bundle_adjustment('nccl', False)
+
+
+def check_sharded_bundle_adjustment(backend, one_gpu, world=2):
     import random
     from coslam_b200.mapping import BundleAdjuster
     from tests.test_mapping_gpu import _map_optimizer, _setup
-    world = 2
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_ba_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    mp.spawn(_ba_worker, args=(world, _free_port(), out, backend, one_gpu), nprocs=world, join=True)
     cfg, model, db, kf_poses, cur_pose, current = _setup('room0', dev='cuda:0')
     cfg['mapping'].update({'iters': 6, 'map_accum_step': 2, 'map_wait_step': 2, 'pose_accum_step': 3})
     before = [p.detach().clone().cpu() for p in model._fused()]
