@@ -141,7 +141,7 @@ int cb200_debug_gather_peak(const cb200_grid* grid, const uint32_t* idx, int64_t
                             float* sink, void* stream) {
     if (int rc = check_grid(grid)) return rc;
     CB_REQUIRE(grid->n_levels == CB200_MAX_LEVELS, "gather_peak: expects %d levels", CB200_MAX_LEVELS);
-    CB_REQUIRE(mode >= 1 && mode <= 3, "gather_peak: mode must be 1 (gather), 2 (reduce) or 3 (both)");
+    CB_REQUIRE((mode & 3) >= 1, "gather_peak: mode bits 0-1 must be 1 (gather), 2 (reduce) or 3 (both)");
     CB_REQUIRE(n_points >= 0 && idx && sink && ((mode & 1) == 0 || table) && ((mode & 2) == 0 || dtable), "gather_peak: NULL buffer");
     return cuda_result(cb200::launch_gather_peak(cb200::make_scene_dev(*grid), idx, n_points, table, dtable, mode, sink, (cudaStream_t)stream),
                        "gather_peak");

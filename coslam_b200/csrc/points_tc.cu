@@ -491,6 +491,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
     const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     uint32_t parity = 0;
     bool first_tile = true;
+    float2* const dtab = a.dtable;
 
 #define TC_WAIT()                 \
     do {                          \
@@ -605,12 +606,16 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     idx[q][j] = hc.idx[j];
-                    v[q][j] = live ? ldg_f2(a.table + hc.idx[j]) : make_float2(0.f, 0.f);
+                    v[q][j] = ldg_f2(a.table + hc.idx[j]);
                 }
                 wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
             }
             tmem_ld_wait();
             float part[8];
+            // Dead and padding lanes have d_embed == 0 exactly (their d_raw is zero, so every product of the gradient chain is), hence
+            // their reductions would add zeros: the decision to reduce is taken per WARP (uniform branch, no divergence bookkeeping
+            // around every RED); on a compacted list only the last tile has such lanes.
+            const bool red_warp = dtab != nullptr && __any_sync(0xffffffffu, live);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const float de0 = __uint_as_float(__shfl_sync(0xffffffffu, de_raw[2 * q], src_lane));
@@ -629,14 +634,19 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
                 dx[0] = fmaf(scale, gx, dx[0]);
                 dx[1] = fmaf(scale, gy, dx[1]);
                 dx[2] = fmaf(scale, gz, dx[2]);
-                float f0 = 0.f, f1 = 0.f;
+                float wc[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
-                    if (a.dtable && live) red_add_f2(a.dtable + idx[q][j], wc * de0, wc * de1);
-                    if (kWgrad) {
-                        f0 = fmaf(wc, v[q][j].x, f0);
-                        f1 = fmaf(wc, v[q][j].y, f1);
+                for (int j = 0; j < 4; ++j) wc[j] = wx[q] * yz_weight(w1[q], w2[q], j);
+                if (red_warp) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) red_add_f2(dtab + idx[q][j], wc[j] * de0, wc[j] * de1);
+                }
+                float f0 = 0.f, f1 = 0.f;
+                if (kWgrad) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        f0 = fmaf(wc[j], v[q][j].x, f0);
+                        f1 = fmaf(wc[j], v[q][j].y, f1);
                     }
                 }
                 part[2 * q] = f0;

@@ -437,9 +437,12 @@ int cb200_points_bwd_noalloc(const cb200_scene* scene, const float* table, const
 int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals,
                           int64_t n_rays, int64_t n_samples, float* pts, float* x, void* stream);
 
-/* measurement hook (tools/l2_gather_peak.py): float2 gathers (mode 1), red.add.v2.f32 reductions (mode 2) or both (mode 3) over
+/* measurement hook (tools/l2_gather_peak.py): float2 gathers (mode bit 0), red.add.v2.f32 reductions (bit 1) or both over
  * the corner list idx [P, L, 8] of cb200_hash_indices, lane pair per point like the fused kernels, no other arithmetic --
- * the measured L2 gather / reduction ceiling the roofline fractions of points_fwd / points_bwd are quoted against */
+ * the measured L2 gather / reduction ceiling the roofline fractions of points_fwd / points_bwd are quoted against.
+ * Optional fields of `mode` (tools/level_probe.py): bits 4-19 level mask (0 = all levels); bits 20-23 log2(copies) and bits 24-28
+ * n of an experiment that sends the reductions of the first n levels to copy (SM id % copies) of those levels' rows, stored
+ * behind the table gradient (dtable then holds n_params + copies * 2 * offset[n] floats) */
 int cb200_debug_gather_peak(const cb200_grid* grid, const uint32_t* idx, int64_t n_points, const float* table, float* dtable,
                             int mode, float* sink, void* stream);
 
