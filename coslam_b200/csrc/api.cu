@@ -229,6 +229,13 @@ int cb200_smooth_tv(const float* f, int64_t n_side, int64_t n_feat, float grad_s
     return cuda_result(cb200::launch_smooth_tv(f, (int)n_side, (int)n_feat, grad_scale, d_f, tv_sum, (cudaStream_t)stream), "smooth_tv");
 }
 
+int cb200_track_init(const float* c2w_init, const cb200_track_step* s, void* stream) {
+    CB_REQUIRE(c2w_init != nullptr && s != nullptr, "track_init: NULL argument");
+    CB_REQUIRE(s->rot && s->trans && s->adam && s->step && s->c2w && s->patience && s->alive, "track_init: NULL buffer");
+    CB_REQUIRE(s->n_rot == 3 || s->n_rot == 4, "track_init: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    return cuda_result(cb200::launch_track_init(c2w_init, *s, (cudaStream_t)stream), "track_init");
+}
+
 int cb200_track_update(const cb200_track_step* s, void* stream) {
     CB_REQUIRE(s != nullptr, "track_update: NULL step");
     CB_REQUIRE(s->rot && s->trans && s->adam && s->step && s->losses && s->d_c2w && s->c2w && s->best_loss && s->best_c2w && s->last_loss &&
@@ -236,6 +243,93 @@ int cb200_track_update(const cb200_track_step* s, void* stream) {
                "track_update: NULL buffer");
     CB_REQUIRE(s->n_rot == 3 || s->n_rot == 4, "track_update: n_rot must be 3 (axis-angle) or 4 (quaternion)");
     return cuda_result(cb200::launch_track_update(*s, (cudaStream_t)stream), "track_update");
+}
+
+static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
+                            const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples);
+static int fill_render_args(cb200::RenderArgs& a, const cb200_render_cfg* cfg, const float* raw, const float* z_vals,
+                            const float* target_rgb, const float* target_d, int64_t n_rays, int64_t n_samples);
+
+// workspace of cb200_track_frame: 512-byte header (barrier, ticket, list count, mask counts, loss sums, dL/d c2w) + per-ray and
+// per-sample arrays, each starting on a 256-byte boundary
+namespace {
+struct TrackFrameLayout {
+    size_t rays_o, rays_d, target_rgb, target_d, d_rays_o, d_rays_d, z, raw, mask, d_raw, list, total;
+};
+TrackFrameLayout track_frame_layout(int64_t n, int64_t s) {
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    TrackFrameLayout l;
+    size_t off = 512;
+    const size_t N = (size_t)(n > 0 ? n : 0), P = N * (size_t)(s > 0 ? s : 0);
+    l.rays_o = off; off = up(off + 12 * N);
+    l.rays_d = off; off = up(off + 12 * N);
+    l.target_rgb = off; off = up(off + 12 * N);
+    l.target_d = off; off = up(off + 4 * N);
+    l.d_rays_o = off; off = up(off + 12 * N);
+    l.d_rays_d = off; off = up(off + 12 * N);
+    l.z = off; off = up(off + 4 * P);
+    l.raw = off; off = up(off + 16 * P);
+    l.mask = off; off = up(off + 8 * P);
+    l.d_raw = off; off = up(off + 16 * P);
+    l.list = off; off = up(off + 4 * P);
+    l.total = off;
+    return l;
+}
+}  // namespace
+
+size_t cb200_track_frame_workspace(int64_t n_rays, int64_t n_samples) { return track_frame_layout(n_rays, n_samples).total; }
+
+int cb200_track_frame(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const cb200_render_cfg* cfg, const float* lin_uniform,
+                      const float* lin_guided, const float* lin_nodepth, uint64_t seed, uint64_t* seed_dev, const float* kf_rays,
+                      const float* c2w_init, int64_t n_rays, int32_t n_iters, const cb200_track_step* step, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+    CB_REQUIRE(cfg != nullptr && step != nullptr, "track_frame: NULL cfg / step");
+    CB_REQUIRE(g_decoder == 1, "track_frame: needs the tensor-core decoder");
+    const int64_t S = (int64_t)cfg->n_uniform + cfg->n_guided;
+    CB_REQUIRE(cfg->n_guided >= 1 && S <= 256, "n_samples_d + n_range_d = %lld must be in [1,256] with n_range_d >= 1", (long long)S);
+    CB_REQUIRE(n_rays >= 1 && n_iters >= 1 && n_rays * S < (1ll << 31), "track_frame: bad sizes");
+    CB_REQUIRE(kf_rays && lin_guided && lin_nodepth && (cfg->n_uniform == 0 || lin_uniform), "track_frame: NULL buffer");
+    CB_REQUIRE(step->rot && step->trans && step->adam && step->step && step->losses && step->c2w && step->best_loss && step->best_c2w &&
+                   step->last_loss && step->last_c2w && step->patience && step->alive,
+               "track_frame: NULL buffer in the step block");
+    CB_REQUIRE(step->n_rot == 3 || step->n_rot == 4, "track_frame: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    const TrackFrameLayout l = track_frame_layout(n_rays, S);
+    CB_REQUIRE(workspace != nullptr && workspace_bytes >= l.total && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
+               "track_frame: workspace missing, not 256-byte aligned or smaller than cb200_track_frame_workspace (%zu bytes)", l.total);
+    char* w = static_cast<char*>(workspace);
+    auto f = [&](size_t off) { return reinterpret_cast<float*>(w + off); };
+    cb200::TrackFrameArgs t{};
+    if (int rc = fill_points_args(t.pts, scene, table, mlp, nullptr, f(l.rays_o), f(l.rays_d), f(l.z), n_rays, S)) return rc;
+    t.pts.raw = f(l.raw);
+    t.pts.act_mask = reinterpret_cast<uint32_t*>(w + l.mask);
+    t.pts.d_raw = f(l.d_raw);
+    t.pts.d_rays_o = f(l.d_rays_o);
+    t.pts.d_rays_d = f(l.d_rays_d);
+    t.smp.target_d = f(l.target_d); t.smp.lin_uniform = lin_uniform; t.smp.lin_guided = lin_guided; t.smp.lin_nodepth = lin_nodepth;
+    t.smp.seed = seed; t.smp.n_rays = n_rays; t.smp.z_vals = f(l.z);
+    t.smp.n_uniform = (int)cfg->n_uniform; t.smp.n_guided = (int)cfg->n_guided; t.smp.perturb = (int)cfg->perturb;
+    t.smp.trunc_sc = cfg->trunc_sc; t.smp.depth_trunc = cfg->depth_trunc;
+    if (int rc = fill_render_args(t.rnd, cfg, f(l.raw), f(l.z), f(l.target_rgb), f(l.target_d), n_rays, S)) return rc;
+    t.rnd.has_loss = 1;
+    t.rnd.d_raw = f(l.d_raw);
+    t.barrier = reinterpret_cast<unsigned*>(w);
+    t.ticket = reinterpret_cast<unsigned*>(w + 4);
+    t.live_count = reinterpret_cast<unsigned long long*>(w + 8);
+    t.counts = reinterpret_cast<unsigned long long*>(w + 16);
+    t.sums = reinterpret_cast<double*>(w + 64);
+    t.d_c2w = f(128);
+    t.losses = const_cast<float*>(step->losses);
+    t.live_list = reinterpret_cast<uint32_t*>(w + l.list);
+    t.kf_rays = kf_rays;
+    t.c2w_init = c2w_init;
+    t.seed_dev = reinterpret_cast<unsigned long long*>(seed_dev);
+    t.n_iters = n_iters;
+    t.step = *step;
+    t.step.d_c2w = t.d_c2w;
+    if (int rc = cuda_result(cudaMemsetAsync(w, 0, 512, (cudaStream_t)stream), "track_frame: clear header")) return rc;
+    const cudaError_t e = cb200::launch_track_frame(t, (cudaStream_t)stream);
+    CB_REQUIRE(e != cudaErrorNotSupported, "track_frame: no instantiation for this grid (dense levels) / samples-per-ray combination");
+    return cuda_result(e, "track_frame");
 }
 
 int cb200_adam_multi(const cb200_adam_param* params, int64_t n_params, int64_t step, int zero_grad, void* stream) {

@@ -83,6 +83,28 @@ struct RenderArgs {
     float* d_raw;              // [N,S,4]
 };
 
+// one tracked frame in one cooperative launch (track_frame.cu)
+struct TrackFrameArgs {
+    PointsArgs pts;              // scene, table, weights; the ray / sample / gradient buffers point into the workspace
+    SampleArgs smp;
+    RenderArgs rnd;
+    cb200_track_step step;
+    const float* kf_rays;        // [N,7] camera-frame direction, rgb, depth of the frame's sampled pixels
+    const float* c2w_init;       // [16] optional: start the frame from this matrix (track_init_state) instead of the state in `step`
+    uint32_t* live_list;         // [N*S]
+    unsigned long long* live_count;
+    unsigned long long* counts;  // [3] mask counts   } zero on entry, cleared again by the pose update
+    double* sums;                // [4] loss sums      }
+    float* d_c2w;                // [16]               }
+    float* losses;               // [4] out: the last iteration's four losses
+    unsigned* barrier;           // zero on entry
+    unsigned* ticket;            // zero on entry
+    unsigned long long* seed_dev;    // optional device noise counter: read at entry, advanced by the iterations run
+    int n_iters;
+};
+
+cudaError_t launch_track_frame(const TrackFrameArgs& t, cudaStream_t st);
+
 cudaError_t launch_assemble_rays_fwd2(const float* kf_rays, const long long* ray_idx, const long long* pose_slot, long long n_first,
                                       const float* cur_rays, const long long* idx_cur, const long long* slot_cur, long long n_cur,
                                       const float* poses, long long n_poses, float* rays_o, float* rays_d, float* target_rgb,
@@ -102,6 +124,7 @@ cudaError_t launch_smooth_tv(const float* f, int n, int n_feat, float scale, flo
 cudaError_t launch_smooth_points(int n, float vox, const float* jitter, const float* offset, const float* lo, const float* ext, float* x,
                                  cudaStream_t st);
 cudaError_t launch_track_update(const cb200_track_step& s, cudaStream_t st);
+cudaError_t launch_track_init(const float* c2w_init, const cb200_track_step& s, cudaStream_t st);
 cudaError_t launch_adam_multi(const cb200_adam_param* params, int n, int64_t step, int zero_grad, cudaStream_t st);
 cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
                              float weight_decay, const int64_t* step_dev, int64_t step, int zero_grad, cudaStream_t st);

@@ -16,6 +16,10 @@ Two implementations of one iteration:
     loss finish, render backward, live-point compaction, per-point backward (dL/d rays only), pose-gradient segment sum,
     and ONE single-thread kernel (`cb200_track_update`, csrc/track.cu) for the weighted loss, the best / last bookkeeping,
     the backward of the pose parametrisation, both Adam steps and the next c2w -- plus two memsets.
+  * `persistent=True` (default with `fused` and `use_graph` when there is no importance pass): the whole frame -- every iteration
+    of the list above -- is ONE cooperative launch (`cb200_track_frame`, csrc/track_frame.cu): CTAs stay resident, phases are
+    separated by grid-wide barriers, the decoder weights are staged once per frame and the loop leaves early when the patience
+    counter trips.  The graph-captured loop stays as its A/B twin (`persistent=False`).
   * `fused=False`: the same arithmetic through torch autograd (`pose.py`, `JointEncoding.forward`), ~100 graph nodes per
     iteration; kept as the A/B twin and for the two-grid / importance-sampling variants.
 """
@@ -28,7 +32,7 @@ from ._lib import check, ptr, stream
 
 
 class FrameTracker(object):
-    def __init__(self, model, config, n_rays=None, device='cuda:0', use_graph=True, fused=None):
+    def __init__(self, model, config, n_rays=None, device='cuda:0', use_graph=True, fused=None, persistent=None):
         t, tr = config['tracking'], config['training']
         can_fuse = bool(config['grid']['oneGrid']) and not config['decoder']['tcnn_network']
         if fused and not can_fuse:
@@ -85,7 +89,15 @@ class FrameTracker(object):
             self.loss_out = torch.zeros(8, **f32)                                   # 4 losses | 4 d loss / d sum
             self.w_dev = torch.tensor(self.loss_w, **f32).unbind(0)
             self.g_rot = torch.zeros(nr, **f32)
+            self.c2w_init = torch.zeros(16, **f32)
+            self._kf7_host = torch.zeros((n, 7), dtype=torch.float32).pin_memory()
             self._steps = [self._track_step(first) for first in (True, False)]
+        can_persist = self.fused and self.use_graph and self.n_imp == 0
+        if persistent and not can_persist:
+            raise NotImplementedError('FrameTracker(persistent=True) needs fused=True, use_graph=True (device noise) and n_importance 0')
+        self.persistent = can_persist if persistent is None else bool(persistent)
+        self._wsp = None
+        self._kf7_sent = None
 
     def _track_step(self, first):
         s = _lib.TrackStep()
@@ -101,10 +113,8 @@ class FrameTracker(object):
 
     # ---- one frame without autograd -----------------------------------------------------------------------------------
     def _reset_fused(self):
-        self.pstate.copy_(self.pinit)
-        self.istate.zero_()
-        self.alive.fill_(1)
-        check(_lib.load().cb200_track_pose(ptr(self.rot), ptr(self.trans), self.rot.shape[1], ptr(self.c2w), stream()), 'track_pose')
+        """Pose parameters of the initial matrix + a fresh Adam / patience state, on the device (cb200_track_init)."""
+        check(_lib.load().cb200_track_init(ptr(self.c2w_init), ctypes.byref(self._steps[0]), stream()), 'track_init')
 
     def _iteration_fused(self, k):
         lib, m, n = _lib.load(), self.model, self.n_rays
@@ -153,6 +163,26 @@ class FrameTracker(object):
         check(lib.cb200_assemble_rays_bwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(d_o), ptr(d_d), ctypes.c_int64(n),
                                           ctypes.c_int64(1), ptr(self.d_c2w), stream()), 'assemble_rays_bwd')
         check(lib.cb200_track_update(ctypes.byref(self._steps[0 if k == 0 else 1]), stream()), 'track_update')
+
+    def _frame_persistent(self):
+        """The whole frame in one cooperative launch (csrc/track_frame.cu)."""
+        lib, m, n = _lib.load(), self.model, self.n_rays
+        spec = m.spec
+        fw = m._fused()
+        tb, w = fw[0].detach(), tuple(x.detach() for x in fw[1:])
+        if self._wsp is None:
+            nbytes = int(lib.cb200_track_frame_workspace(ctypes.c_int64(n), ctypes.c_int64(spec.n_samples)))
+            self._wsp = torch.empty(nbytes + 256, dtype=torch.uint8, device=self.device)
+            self._wsp_off = (-self._wsp.data_ptr()) % 256
+            self._wsp_bytes = nbytes
+        lin_u, lin_g, lin_n = spec.linspaces(self.device)
+        mlp = ops._mlp_block(*w)
+        check(lib.cb200_track_frame(ctypes.byref(spec.scene()), ptr(tb), ctypes.byref(mlp), ctypes.byref(spec.render_cfg()), ptr(lin_u),
+                                    ptr(lin_g), ptr(lin_n), ctypes.c_uint64((int(m.noise_seed) << 32) & (2 ** 64 - 1)),
+                                    ptr(m._noise_counter), ptr(self.kf7), ptr(self.c2w_init), ctypes.c_int64(n), ctypes.c_int32(self.iters),
+                                    ctypes.byref(self._steps[0]), ctypes.c_void_p(self._wsp.data_ptr() + self._wsp_off),
+                                    ctypes.c_size_t(self._wsp_bytes), stream()), 'track_frame')
+        _lib.KERNEL_LAUNCHES += 1
 
     # ---- one frame, eager or under capture --------------------------------------------------------------------------
     def _adam(self, p, g, m, v, lr):
@@ -221,31 +251,58 @@ class FrameTracker(object):
     def track(self, dir_cam, target_s, target_d, c2w_init):
         """dir_cam [N,3] camera-frame ray directions of the sampled pixels, target_s [N,3], target_d [N,1] (any device),
         c2w_init [4,4].  Returns the estimated c2w [4,4] (best or last, `tracking.best`) and a dict of device scalars."""
-        c2w0 = torch.as_tensor(c2w_init, dtype=torch.float32).detach().cpu().reshape(1, 4, 4)
-        rot0 = pose.matrix_to_quaternion(c2w0[:, :3, :3]) if self.quat else pose.matrix_to_axis_angle(c2w0[:, :3, :3])
-        self.init_rot.copy_(rot0, non_blocking=True)
-        self.init_trans.copy_(c2w0[:, :3, 3], non_blocking=True)
-        if self.fused:                                               # the kernels read (direction, rgb, depth) rows: one upload
-            n = self.n_rays
-            self.kf7.copy_(torch.cat([dir_cam.reshape(n, 3), target_s.reshape(n, 3), target_d.reshape(n, 1)], -1).float(),
-                           non_blocking=True)
-        else:
-            self.dir_cam.copy_(dir_cam.reshape(self.n_rays, 3), non_blocking=True)
-            self.target_s.copy_(target_s.reshape(self.n_rays, 3), non_blocking=True)
-            self.target_d.copy_(target_d.reshape(self.n_rays, 1), non_blocking=True)
-        frozen = [p for p in self.model.parameters() if p.requires_grad]
-        for p in frozen:                                             # tracking needs dL/d rays only (no table scatter, no dW)
-            p.requires_grad_(False)
-        try:
-            if not self.use_graph:
-                self._frame()
+        n = self.n_rays
+        if self.fused:
+            # no host arithmetic and no synchronisation: the initial matrix goes to the device as it is (cb200_track_init derives
+            # the pose parameters there), the rays as ONE [N,7] upload (direction, rgb, depth rows -- what the kernels read)
+            c2w_src = torch.as_tensor(c2w_init, dtype=torch.float32).detach().reshape(16)
+            self.c2w_init.copy_(c2w_src, non_blocking=True)
+            parts = [dir_cam.reshape(n, 3), target_s.reshape(n, 3), target_d.reshape(n, 1)]
+            if all(p.device.type == 'cpu' for p in parts):
+                if self._kf7_sent is not None:
+                    self._kf7_sent.synchronize()                     # the previous frame's upload has left the staging buffer
+                torch.cat(parts, -1, out=self._kf7_host)
+                self.kf7.copy_(self._kf7_host, non_blocking=True)
+                self._kf7_sent = torch.cuda.Event()
+                self._kf7_sent.record()
             else:
-                if self._graph is None:
-                    self._capture()
-                self._graph.replay()
-        finally:
-            for p in frozen:
-                p.requires_grad_(True)
+                self.kf7.copy_(torch.cat([p.to(self.device, non_blocking=True).float() for p in parts], -1), non_blocking=True)
+            if self.persistent:
+                try:
+                    with torch.no_grad():
+                        self._frame_persistent()
+                except RuntimeError as e:                            # a grid / sample count the kernel is not instantiated for
+                    if 'no instantiation' not in str(e):
+                        raise
+                    self.persistent = False
+            if not self.persistent:
+                if not self.use_graph:
+                    self._frame()
+                else:
+                    if self._graph is None:
+                        self._capture()
+                    self._graph.replay()
+        else:
+            c2w0 = torch.as_tensor(c2w_init, dtype=torch.float32).detach().cpu().reshape(1, 4, 4)
+            rot0 = pose.matrix_to_quaternion(c2w0[:, :3, :3]) if self.quat else pose.matrix_to_axis_angle(c2w0[:, :3, :3])
+            self.init_rot.copy_(rot0, non_blocking=True)
+            self.init_trans.copy_(c2w0[:, :3, 3], non_blocking=True)
+            self.dir_cam.copy_(dir_cam.reshape(n, 3), non_blocking=True)
+            self.target_s.copy_(target_s.reshape(n, 3), non_blocking=True)
+            self.target_d.copy_(target_d.reshape(n, 1), non_blocking=True)
+            frozen = [p for p in self.model.parameters() if p.requires_grad]
+            for p in frozen:                                         # tracking needs dL/d rays only (no table scatter, no dW)
+                p.requires_grad_(False)
+            try:
+                if not self.use_graph:
+                    self._frame()
+                else:
+                    if self._graph is None:
+                        self._capture()
+                    self._graph.replay()
+            finally:
+                for p in frozen:
+                    p.requires_grad_(True)
         est = (self.best_c2w if self.use_best else self.last_c2w)[0]
         return est, {'best_loss': self.best_loss.reshape(()), 'last_loss': self.last_loss.reshape(()), 'psnr': self.psnr,
                      'last_c2w': self.last_c2w[0], 'best_c2w': self.best_c2w[0]}

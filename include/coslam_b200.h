@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 15
+#define CB200_ABI_VERSION 16
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -181,6 +181,27 @@ typedef struct cb200_track_step {
     int32_t wait_iters;
 } cb200_track_step;
 int cb200_track_update(const cb200_track_step* step, void* stream);
+
+/* Fresh per-frame tracking state from an initial camera-to-world matrix c2w_init [16] (device): the pose parameters the reference
+ * derives on the host with pytorch3d (optimization/utils.py:23-28 matrix_to_axis_angle = quaternion_to_axis_angle(matrix_to_quaternion),
+ * coslam.py:276-283; n_rot == 4: the quaternion with non-negative real part), zero Adam moments / step / patience, alive = 1, and
+ * c2w = the matrix of those parameters (coslam.py:508-526).  Uses rot, trans, adam, step, patience, alive, c2w, n_rot of `step`. */
+int cb200_track_init(const float* c2w_init, const cb200_track_step* step, void* stream);
+
+/* One tracked frame -- all `n_iters` iterations of coslam.py:523-573 (pose -> rays -> sampling -> render -> weighted loss -> backward
+ * to the pose -> Adam, with the best / last / patience bookkeeping of cb200_track_update) -- in ONE cooperative launch
+ * (csrc/track_frame.cu): phases separated by grid-wide barriers, decoder weights staged once, early exit when the patience counter
+ * trips.  kf_rays [N,7] = (camera-frame direction, rgb, depth) of the frame's sampled pixels (coslam.py:537-544); `step` as for
+ * cb200_track_update (first_iter is ignored, d_c2w is not used: the gradient lives in the workspace; losses [4] receives the last
+ * iteration's losses); seed / seed_dev as for cb200_sample_rays, *seed_dev is advanced by the iterations run.
+ * c2w_init [16] (device, may be NULL): start the frame from this matrix as cb200_track_init does; NULL = the state in `step`.
+ * workspace: cb200_track_frame_workspace(N, n_samples) bytes of device memory, 256-byte aligned; contents need not be preserved.
+ * Served: tensor-core decoder, 16-level grids with 5 or 6 dense levels, n_samples <= 64 (5 dense) / 97..128 (6 dense). */
+size_t cb200_track_frame_workspace(int64_t n_rays, int64_t n_samples);
+int cb200_track_frame(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const cb200_render_cfg* cfg,
+                      const float* lin_uniform, const float* lin_guided, const float* lin_nodepth, uint64_t seed,
+                      uint64_t* seed_dev, const float* kf_rays, const float* c2w_init, int64_t n_rays, int32_t n_iters,
+                      const cb200_track_step* step, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- bundle-adjustment glue (coslam.py:285-397 global_BA, :251-274 smoothness) -------------------------------------- */
 
