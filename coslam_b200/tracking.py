@@ -16,10 +16,12 @@ Two implementations of one iteration:
     loss finish, render backward, live-point compaction, per-point backward (dL/d rays only), pose-gradient segment sum,
     and ONE single-thread kernel (`cb200_track_update`, csrc/track.cu) for the weighted loss, the best / last bookkeeping,
     the backward of the pose parametrisation, both Adam steps and the next c2w -- plus two memsets.
-  * `persistent=True` (default with `fused` and `use_graph` when there is no importance pass): the whole frame -- every iteration
-    of the list above -- is ONE cooperative launch (`cb200_track_frame`, csrc/track_frame.cu): CTAs stay resident, phases are
-    separated by grid-wide barriers, the decoder weights are staged once per frame and the loop leaves early when the patience
-    counter trips.  The graph-captured loop stays as its A/B twin (`persistent=False`).
+  * `persistent=True` (opt-in; needs `fused`, `use_graph` and no importance pass): the whole frame -- every iteration of the list
+    above -- is ONE cooperative launch (`cb200_track_frame`, csrc/track_frame.cu): CTAs stay resident, phases are separated by
+    grid-wide barriers, the decoder weights are staged once per frame and the loop leaves early when the patience counter trips.
+    Bit-identical to the graph-captured loop at perturb 0; measured 0.86 ms against 0.82 ms of device time per room0 frame
+    (profiles/r2/NOTES.md: the two per-point phases are the same tile loops and take 52 of the 87 us of an iteration either way,
+    six grid barriers at ~2 us cost more than thirteen in-graph kernel boundaries at ~1 us), so the graph stays the default.
   * `fused=False`: the same arithmetic through torch autograd (`pose.py`, `JointEncoding.forward`), ~100 graph nodes per
     iteration; kept as the A/B twin and for the two-grid / importance-sampling variants.
 """
@@ -95,7 +97,7 @@ class FrameTracker(object):
         can_persist = self.fused and self.use_graph and self.n_imp == 0
         if persistent and not can_persist:
             raise NotImplementedError('FrameTracker(persistent=True) needs fused=True, use_graph=True (device noise) and n_importance 0')
-        self.persistent = can_persist if persistent is None else bool(persistent)
+        self.persistent = bool(persistent)
         self._wsp = None
         self._kf7_sent = None
 

@@ -782,6 +782,14 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
         assert abs(float(info_g['best_loss']) - best_e) <= 1e-4 * abs(best_e)
     assert all(p.requires_grad for p in model.parameters())
     assert float((info_g['last_c2w'].cpu() - c2w0).abs().max()) > 1e-4          # the pose did move
+    # the whole frame as ONE cooperative launch (cb200_track_frame): same phases, same arithmetic
+    one = FrameTracker(model, cfg, device=DEV, use_graph=True, persistent=True)
+    for _ in range(2):
+        est_p, info_p = one.track(dir_cam, rgb, depth, c2w0)
+        assert one.persistent
+        assert float((est_p - est_e).abs().max()) <= 2e-5
+        assert abs(float(info_p['best_loss']) - best_e) <= 1e-4 * abs(best_e)
+        assert float((info_p['last_c2w'] - info_e['last_c2w']).abs().max()) <= 2e-5
 
     # the reference loop on the oracle
     orc = util.make_oracle(cfg, table, weights)
