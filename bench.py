@@ -679,8 +679,13 @@ def time_tracking(model, cfg, dev, frames=20, full=True):
                            % int(cfg['tracking']['iter'])}
     noise_state = (model.noise_mode, model._noise_counter)
     fusable = bool(cfg['grid']['oneGrid']) and cfg['training']['n_importance'] == 0
-    for name, use_graph, fused in (('graph', True, None), ('eager', False, None)) + ((('autograd_graph', True, False),) if fusable and full else ()):
-        tr = FrameTracker(model, cfg, device=dev, use_graph=use_graph, fused=fused)
+    variants = (('graph', True, None, False), ('eager', False, None, False))
+    if fusable:
+        variants += (('one_launch', True, None, True),)        # cb200_track_frame: the whole frame as one cooperative launch
+    if fusable and full:
+        variants += (('autograd_graph', True, False, False),)
+    for name, use_graph, fused, persistent in variants:
+        tr = FrameTracker(model, cfg, device=dev, use_graph=use_graph, fused=fused, persistent=persistent)
         for _ in range(3):
             tr.track(*draw(), c2w0)[0].cpu()
         torch.cuda.synchronize()
@@ -688,6 +693,17 @@ def time_tracking(model, cfg, dev, frames=20, full=True):
         for _ in range(frames):
             tr.track(*draw(), c2w0)[0].cpu()          # the read-back is the per-frame sync
         out['ms_per_frame_' + name] = (time.perf_counter() - t0) * 1e3 / frames
+        if name == 'graph':
+            # the same loop with frame t+1's pixel draw + CPU gather done while the GPU tracks frame t (the draw does not depend
+            # on the pose; same random.sample stream, same order)
+            nxt = draw()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(frames):
+                est = tr.track(*nxt, c2w0)[0]
+                nxt = draw()
+                est.cpu()
+            out['ms_per_frame_graph_draw_overlapped'] = (time.perf_counter() - t0) * 1e3 / frames
     t0 = time.perf_counter()
     for _ in range(frames):
         draw()

@@ -229,6 +229,12 @@ int cb200_smooth_tv(const float* f, int64_t n_side, int64_t n_feat, float grad_s
     return cuda_result(cb200::launch_smooth_tv(f, (int)n_side, (int)n_feat, grad_scale, d_f, tv_sum, (cudaStream_t)stream), "smooth_tv");
 }
 
+int cb200_pose_params(const float* c2w, int64_t n_poses, int32_t n_rot, float* rot, float* trans, void* stream) {
+    CB_REQUIRE(n_poses >= 0 && (n_poses == 0 || (c2w && rot && trans)), "pose_params: NULL buffer");
+    CB_REQUIRE(n_rot == 3 || n_rot == 4, "pose_params: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    return cuda_result(cb200::launch_pose_params(c2w, n_poses, n_rot, rot, trans, (cudaStream_t)stream), "pose_params");
+}
+
 int cb200_track_init(const float* c2w_init, const cb200_track_step* s, void* stream) {
     CB_REQUIRE(c2w_init != nullptr && s != nullptr, "track_init: NULL argument");
     CB_REQUIRE(s->rot && s->trans && s->adam && s->step && s->c2w && s->patience && s->alive, "track_init: NULL buffer");

@@ -124,6 +124,7 @@ cudaError_t launch_smooth_tv(const float* f, int n, int n_feat, float scale, flo
 cudaError_t launch_smooth_points(int n, float vox, const float* jitter, const float* offset, const float* lo, const float* ext, float* x,
                                  cudaStream_t st);
 cudaError_t launch_track_update(const cb200_track_step& s, cudaStream_t st);
+cudaError_t launch_pose_params(const float* c2w, long long n, int n_rot, float* rot, float* trans, cudaStream_t st);
 cudaError_t launch_track_init(const float* c2w_init, const cb200_track_step& s, cudaStream_t st);
 cudaError_t launch_adam_multi(const cb200_adam_param* params, int n, int64_t step, int zero_grad, cudaStream_t st);
 cudaError_t launch_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,

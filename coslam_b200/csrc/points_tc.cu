@@ -115,10 +115,39 @@ cudaError_t launch_compact_live(const float* d_raw, int64_t n_points, unsigned l
     return cudaGetLastError();
 }
 
-static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
-    int dev = 0, sms = 148;
+// per-device host state looked up once: these launchers run ~20 times per bundle-adjustment iteration
+static int sm_count() {
+    static int sms_of[64] = {0};
+    int dev = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (sms_of[dev] == 0) {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        sms_of[dev] = sms;
+    }
+    return sms_of[dev];
+}
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel, device); kernels of one signature share a C++ type, so the
+// flag is keyed by the function's address
+static cudaError_t allow_dynamic_smem(const void* kernel, size_t smem) {
+    constexpr int kMax = 32;
+    static const void* seen[64][kMax];
+    static int n_seen[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64) {
+        for (int i = 0; i < n_seen[dev]; ++i)
+            if (seen[dev][i] == kernel) return cudaSuccess;
+    }
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess && dev >= 0 && dev < 64 && n_seen[dev] < kMax) seen[dev][n_seen[dev]++] = kernel;
+    return e;
+}
+
+static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
+    const int sms = sm_count();
     int64_t g = (int64_t)sms * ctas_per_sm;
     if (g > n_tiles) g = n_tiles;
     if (g < 1) g = 1;
@@ -129,7 +158,7 @@ template <bool kWgrad>
 static cudaError_t launch_points_bwd_tc_as(const PointsArgs& a, cudaStream_t st) {
     const size_t smem = tc::kBwdSmem;
     const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
-    cudaError_t e = cudaFuncSetAttribute(points_bwd_tc_kernel<kWgrad>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_bwd_tc_kernel<kWgrad>), smem);
     if (e != cudaSuccess) return e;
     points_bwd_tc_kernel<kWgrad><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     return cudaGetLastError();
@@ -152,7 +181,7 @@ static int dense_prefix(const SceneDev& sc) {
 template <int kDense>
 static cudaError_t launch_points_fwd_tc_as(const PointsArgs& a, cudaStream_t st) {
     const size_t smem = tc::kFwdSmem;
-    cudaError_t e = cudaFuncSetAttribute(points_fwd_tc_kernel<kDense>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_fwd_tc_kernel<kDense>), smem);
     if (e != cudaSuccess) return e;
     const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
     points_fwd_tc_kernel<kDense><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);

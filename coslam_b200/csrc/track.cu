@@ -160,6 +160,23 @@ cudaError_t launch_smooth_points(int n, float vox, const float* jitter, const fl
     return cudaGetLastError();
 }
 
+__global__ void pose_params_kernel(const float* c2w, long long n, int n_rot, float* rot, float* trans) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float m[16], r[4];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) m[k] = c2w[i * 16 + k];
+    rotation_params_from_matrix(m, n_rot, r);
+    for (int k = 0; k < n_rot; ++k) rot[i * n_rot + k] = r[k];
+    trans[i * 3 + 0] = m[3]; trans[i * 3 + 1] = m[7]; trans[i * 3 + 2] = m[11];
+}
+
+cudaError_t launch_pose_params(const float* c2w, long long n, int n_rot, float* rot, float* trans, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    pose_params_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(c2w, n, n_rot, rot, trans);
+    return cudaGetLastError();
+}
+
 __global__ void track_init_kernel(const float* c2w_init, cb200_track_step s) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     float c2w[16];

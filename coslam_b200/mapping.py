@@ -198,9 +198,9 @@ class BundleAdjuster(object):
             free = poses_all[1:] if optim_cur else poses_all[1:K]
             n_free = free.shape[0]
         if n_free > 0:
-            to_param = pose.matrix_to_axis_angle if nr == 3 else pose.matrix_to_quaternion
-            rot = to_param(free[:, :3, :3].cpu()).to(dev).contiguous()                  # matrix_to_tensor on the host, like coslam.py:279
-            trans = free[:, :3, 3].clone().contiguous()
+            # matrix_to_tensor (coslam.py:279) on the device: no host round trip of the poses, no synchronisation
+            rot, trans = torch.empty((n_free, nr), **f32), torch.empty((n_free, 3), **f32)
+            check(lib.cb200_pose_params(ptr(free.contiguous()), ctypes.c_int64(n_free), nr, ptr(rot), ptr(trans), stream()), 'pose_params')
             state = torch.zeros(2 * n_free * (nr + 3), **f32)
             m_rot, v_rot = state[:n_free * nr], state[n_free * nr:2 * n_free * nr]
             m_tr, v_tr = state[2 * n_free * nr:2 * n_free * nr + 3 * n_free], state[2 * n_free * nr + 3 * n_free:]

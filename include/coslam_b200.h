@@ -182,6 +182,10 @@ typedef struct cb200_track_step {
 } cb200_track_step;
 int cb200_track_update(const cb200_track_step* step, void* stream);
 
+/* matrix_to_tensor of the reference (optimization/utils.py:23-28 + pytorch3d, coslam.py:276-283) for n poses on the device:
+ * c2w [n,4,4] -> rot [n, n_rot] (axis-angle, or the quaternion with non-negative real part), trans [n,3] */
+int cb200_pose_params(const float* c2w, int64_t n_poses, int32_t n_rot, float* rot, float* trans, void* stream);
+
 /* Fresh per-frame tracking state from an initial camera-to-world matrix c2w_init [16] (device): the pose parameters the reference
  * derives on the host with pytorch3d (optimization/utils.py:23-28 matrix_to_axis_angle = quaternion_to_axis_angle(matrix_to_quaternion),
  * coslam.py:276-283; n_rot == 4: the quaternion with non-negative real part), zero Adam moments / step / patience, alive = 1, and

@@ -845,6 +845,45 @@ def test_frame_tracker_with_importance_samples_matches_autograd_loop():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize('n_rot', [3, 4])
+def test_pose_params_kernel_matches_matrix_to_tensor(n_rot):
+    """cb200_pose_params / cb200_track_init (device-side matrix_to_tensor, optimization/utils.py:23-28 + the pytorch3d conversions
+    restated in coslam_b200/pose.py and checked against the reference in tests/test_pose_math.py): rotations of every size
+    including ~0 and close to pi, where the largest-denominator candidate of matrix_to_quaternion changes."""
+    import ctypes
+    from coslam_b200 import _lib, pose
+    from coslam_b200._lib import check, ptr, stream
+    g = torch.Generator().manual_seed(11 + n_rot)
+    axis = torch.randn(64, 3, generator=g)
+    axis = axis / axis.norm(dim=-1, keepdim=True)
+    angle = torch.cat([torch.rand(40, generator=g) * 3.1, torch.tensor([1e-4, 1e-3, 3.13, 3.14, 3.1415]), torch.rand(19, generator=g) * 0.05])
+    rot_m = pose.axis_angle_to_matrix(axis * angle[:, None])
+    c2w = torch.eye(4)[None].repeat(64, 1, 1)
+    c2w[:, :3, :3] = rot_m
+    c2w[:, :3, 3] = torch.randn(64, 3, generator=g)
+    want = pose.matrix_to_axis_angle(rot_m) if n_rot == 3 else pose.matrix_to_quaternion(rot_m)
+    dev_c2w = c2w.to(DEV).contiguous()
+    rot, trans = torch.empty((64, n_rot), device=DEV), torch.empty((64, 3), device=DEV)
+    lib = _lib.load()
+    check(lib.cb200_pose_params(ptr(dev_c2w), ctypes.c_int64(64), n_rot, ptr(rot), ptr(trans), stream()), 'pose_params')
+    assert torch.equal(trans.cpu(), c2w[:, :3, 3])
+    assert float((rot.cpu() - want).abs().max()) <= 2e-6 * max(1.0, float(want.abs().max()))
+    # the per-frame state of the tracker from ONE matrix: same parameters, zeroed optimiser state, c2w = matrix of the parameters
+    f32 = dict(dtype=torch.float32, device=DEV)
+    pstate = torch.full((3 * n_rot + 9,), 7.0, **f32)
+    istate = torch.full((2,), 5, dtype=torch.int64, device=DEV)
+    alive = torch.zeros(1, dtype=torch.uint8, device=DEV)
+    out_c2w = torch.zeros(16, **f32)
+    s = _lib.TrackStep()
+    s.rot, s.trans, s.adam = pstate[:n_rot].data_ptr(), pstate[n_rot:n_rot + 3].data_ptr(), pstate[n_rot + 3:].data_ptr()
+    s.step, s.patience, s.alive, s.c2w, s.n_rot = istate[0:1].data_ptr(), istate[1:2].data_ptr(), alive.data_ptr(), out_c2w.data_ptr(), n_rot
+    check(lib.cb200_track_init(ptr(dev_c2w[3].reshape(16)), ctypes.byref(s), stream()), 'track_init')
+    assert torch.equal(pstate[:n_rot].cpu(), rot[3].cpu()) and torch.equal(pstate[n_rot:n_rot + 3].cpu(), c2w[3, :3, 3])
+    assert float(pstate[n_rot + 3:].abs().max()) == 0.0 and istate.tolist() == [0, 0] and int(alive) == 1
+    assert float((out_c2w.cpu().view(4, 4) - c2w[3]).abs().max()) <= 2e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('n_rot', [3, 4])
 def test_track_update_kernel_matches_autograd_and_adam(n_rot):
     """cb200_track_pose / cb200_track_update (csrc/track.cu) against torch: pose matrix, dL/d(rot, trans) from dL/d c2w
     (autograd through coslam_b200.pose, i.e. optimization/utils.py:5-55), torch.optim.Adam on both parameters, and the
