@@ -56,6 +56,7 @@ class BundleAdjuster(object):
         self.world = dist.get_world_size(group) if group is not None else 1
         self.rank = dist.get_rank(group) if group is not None else 0
         self._flat = None
+        self.phase_times = None                   # set to [] to collect CUDA events per sharded iteration: forward | AR-1 | backward | AR-2 | optimise
         bb = model.bounding_box.detach().float().cpu()
         self._lo = (ctypes.c_float * 3)(*bb[:, 0].tolist())
         self._ext = (ctypes.c_float * 3)(*(bb[:, 1] - bb[:, 0]).tolist())
@@ -328,20 +329,31 @@ class BundleAdjuster(object):
             if n_free > 0 and (it + 1) % int(m['pose_accum_step']) == 0:   # coslam.py:372-390
                 pose_step += 1
                 p_step = pose_step
-            if self.world == 1:
+            if self.world == 1 and self.phase_times is None:
                 check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 7, ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
                       'ba_iteration')
                 continue
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)] if self.phase_times is not None else None
+            mark = (lambda i: ev[i].record()) if ev else (lambda i: None)
+            mark(0)
             check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 1, ctypes.c_int64(0), 0, ctypes.c_int64(0), st), 'ba_iteration')
-            dist.all_reduce(ws[:4].view(torch.int64), group=self.group)        # AR-1: batch-global mask counts ...
-            dist.all_reduce(ws[4:8], group=self.group)                         #       ... and loss sums
+            mark(1)
+            if self.world > 1:
+                dist.all_reduce(ws[:4].view(torch.int64), group=self.group)    # AR-1: batch-global mask counts ...
+                dist.all_reduce(ws[4:8], group=self.group)                     #       ... and loss sums
+            mark(2)
             check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 2, ctypes.c_int64(0), 0, ctypes.c_int64(0), st), 'ba_iteration')
-            if map_step > 0:                                                   # AR-2, only in front of a step that consumes the sums
+            mark(3)
+            if map_step > 0 and self.world > 1:                                # AR-2, only in front of a step that consumes the sums
                 dist.all_reduce(self._flat, group=self.group)
-            if p_step > 0:
+            if p_step > 0 and self.world > 1:
                 dist.all_reduce(d_poses, group=self.group)
+            mark(4)
             check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 4, ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
                   'ba_iteration')
+            mark(5)
+            if ev:
+                self.phase_times.append(ev)
         _lib.KERNEL_LAUNCHES += iters * (17 + (3 if lazy else 0) + (4 if smooth_w > 0 else 0)) - iters
         del keep
         self.last_losses, self.last_tv, self.last_d_poses = loss_out[:4], ws[8:9], d_poses

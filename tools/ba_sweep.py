@@ -30,6 +30,7 @@ def main():
     ap.add_argument('--log2', type=int, nargs='+', default=[16, 18, 20, 22])
     ap.add_argument('--iters', type=int, default=5)
     ap.add_argument('--keyframes', type=int, default=401)
+    ap.add_argument('--phases', action='store_true', help='sharded runs: also print the device time of forward | AR-1 | backward | AR-2 | optimise per iteration')
     a = ap.parse_args()
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
@@ -90,6 +91,15 @@ def main():
             ba.run(kf_poses, cur_pose, current)
         e1.record()
         torch.cuda.synchronize()
+        if a.phases:
+            ba.phase_times = []
+            ba.run(kf_poses, cur_pose, current)
+            torch.cuda.synchronize()
+            names = ('forward', 'AR-1', 'backward', 'AR-2 (+ poses)', 'optimise')
+            tot = [sum(ev[i].elapsed_time(ev[i + 1]) for ev in ba.phase_times) / len(ba.phase_times) for i in range(5)]
+            if rank == 0:
+                print('   rank 0 phases, ms per iteration: ' + ', '.join('%s %.3f' % p_ for p_ in zip(names, tot)), flush=True)
+            ba.phase_times = None
         ms = torch.tensor([e0.elapsed_time(e1) / (reps * a.iters)], device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
