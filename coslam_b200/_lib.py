@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 16
+ABI_VERSION = 17
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p
@@ -51,7 +51,8 @@ class TrackStep(ctypes.Structure):
     _fields_ = [(n, ctypes.c_void_p) for n in ('rot', 'trans', 'adam', 'step', 'losses', 'd_c2w', 'c2w', 'best_loss', 'best_c2w',
                                                'last_loss', 'last_c2w', 'psnr', 'loss', 'g_rot_out', 'patience', 'alive')] + \
                [('loss_w', ctypes.c_float * 4), ('lr_rot', ctypes.c_float), ('lr_trans', ctypes.c_float), ('n_rot', ctypes.c_int32),
-                ('first_iter', ctypes.c_int32), ('may_stop', ctypes.c_int32), ('wait_iters', ctypes.c_int32)]
+                ('first_iter', ctypes.c_int32), ('may_stop', ctypes.c_int32), ('wait_iters', ctypes.c_int32),
+                ('sums', ctypes.c_void_p), ('counts', ctypes.c_void_p), ('n_rays_total', ctypes.c_int64), ('n_samples', ctypes.c_int64)]
 
 
 class MlpGrad(ctypes.Structure):
@@ -95,7 +96,7 @@ class BaPlan(ctypes.Structure):
 
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
            'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update', 'cb200_track_frame', 'cb200_track_init', 'cb200_pose_params', 'cb200_track_frame_workspace', 'cb200_pose_matrices', 'cb200_pose_adam', 'cb200_smooth_points', 'cb200_smooth_tv', 'cb200_ba_iteration', 'cb200_sizeof', 'cb200_host_random_sample', 'cb200_adam_multi',
-           'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd',
+           'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd', 'cb200_render_loss_bwd',
            'cb200_debug_positions', 'cb200_debug_gather_peak', 'cb200_points_bwd_noalloc', 'cb200_points_bwd_noalloc_max_points', 'cb200_selftest_mma', 'cb200_set_decoder',
            'cb200_get_decoder']
 

@@ -332,6 +332,10 @@ int cb200_track_frame(const cb200_scene* scene, const float* table, const cb200_
     t.n_iters = n_iters;
     t.step = *step;
     t.step.d_c2w = t.d_c2w;
+    t.step.sums = t.sums;                       // the pose update takes the losses from this iteration's sums and counts
+    t.step.counts = reinterpret_cast<const int64_t*>(t.counts);
+    t.step.n_rays_total = n_rays;
+    t.step.n_samples = S;
     if (int rc = cuda_result(cudaMemsetAsync(w, 0, 512, (cudaStream_t)stream), "track_frame: clear header")) return rc;
     const cudaError_t e = cb200::launch_track_frame(t, (cudaStream_t)stream);
     CB_REQUIRE(e != cudaErrorNotSupported, "track_frame: no instantiation for this grid (dense levels) / samples-per-ray combination");
@@ -482,7 +486,12 @@ int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_m
     }
     a.d_pts = d_pts; a.d_rays_o = d_rays_o; a.d_rays_d = d_rays_d;
     if (g_decoder == 1) {
-        if (workspace && rays_o && d_geo == nullptr && d_pts == nullptr) {
+        if (workspace && workspace_bytes == 0 && rays_o && d_geo == nullptr && d_pts == nullptr) {
+            // the list is there already (cb200_render_loss_bwd wrote it while it produced d_raw)
+            unsigned long long* count = reinterpret_cast<unsigned long long*>(workspace);
+            a.live_idx = reinterpret_cast<uint32_t*>(count + 2);
+            a.live_count = count;
+        } else if (workspace && rays_o && d_geo == nullptr && d_pts == nullptr) {
             CB_REQUIRE(workspace_bytes >= cb200_points_bwd_workspace(a.n_points), "points_bwd: workspace too small (%zu bytes)", workspace_bytes);
             CB_REQUIRE(a.n_points < (1ll << 32), "points_bwd: compaction indexes points with 32 bits");
             unsigned long long* count = reinterpret_cast<unsigned long long*>(workspace);
@@ -541,6 +550,31 @@ int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float*
     }
     a.coef = coef; a.g_rgb = g_rgb; a.g_depth = g_depth; a.d_raw = d_raw;
     return cuda_result(cb200::launch_render_bwd(a, (cudaStream_t)stream), "render_bwd");
+}
+
+int cb200_render_loss_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb, const float* target_d,
+                          int64_t n_rays, int64_t n_samples, const int64_t* counts, int64_t n_rays_total, const cb200_loss_grads* g_loss,
+                          double* loss_sums, float* coef, float* d_raw, void* list_workspace, size_t list_workspace_bytes, void* stream) {
+    cb200::RenderArgs a{};
+    if (int rc = fill_render_args(a, cfg, raw, z_vals, target_rgb, target_d, n_rays, n_samples)) return rc;
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(d_raw && counts && g_loss && target_rgb && target_d, "render_loss_bwd: NULL buffer");
+    CB_REQUIRE(n_rays_total >= n_rays, "render_loss_bwd: n_rays_total < n_rays");
+    a.g_loss[0] = g_loss->rgb; a.g_loss[1] = g_loss->depth; a.g_loss[2] = g_loss->sdf; a.g_loss[3] = g_loss->fs;
+    a.has_loss = 1;
+    a.loss_sums = loss_sums;
+    a.d_raw = d_raw;
+    uint32_t* list = nullptr;
+    unsigned long long* count = nullptr;
+    if (list_workspace) {
+        CB_REQUIRE(list_workspace_bytes >= cb200_points_bwd_workspace(n_rays * n_samples), "render_loss_bwd: list workspace too small");
+        CB_REQUIRE(n_rays * n_samples < (1ll << 32), "render_loss_bwd: the list indexes points with 32 bits");
+        count = reinterpret_cast<unsigned long long*>(list_workspace);
+        list = reinterpret_cast<uint32_t*>(count + 2);
+    }
+    return cuda_result(cb200::launch_render_loss_bwd(a, reinterpret_cast<const unsigned long long*>(counts), n_rays_total, list, count, coef,
+                                                     (cudaStream_t)stream),
+                       "render_loss_bwd");
 }
 
 int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,

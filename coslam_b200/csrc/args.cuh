@@ -137,6 +137,8 @@ cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st);
 cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st);
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st);
 cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st);
+cudaError_t launch_render_loss_bwd(const RenderArgs& r, const unsigned long long* counts, long long n_rays_total, uint32_t* list,
+                                   unsigned long long* list_count, float* coef_out, cudaStream_t st);
 cudaError_t launch_loss_finish(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
                                float* losses, float* coef, cudaStream_t st);
 cudaError_t launch_points_fwd(const PointsArgs& a, cudaStream_t st);

@@ -112,6 +112,55 @@ __global__ void __launch_bounds__(kRayWarps * 32) render_bwd_kernel(RenderArgs a
         ray_backward<kPerLane>(a, ray, lane, gl);
 }
 
+// Loss head forward AND backward of a ray in one pass (tracking / bundle-adjustment loops): the backward coefficients need only the
+// batch-global mask counts, which the sampling kernel has already produced, so a ray's d_raw can be written right after its
+// rendering -- no loss_finish launch and no second ray_forward in between.  Also accumulates the four squared-residual sums (for the
+// reported losses) and, when a list is given, appends the ray's samples with non-zero d_raw (the points the per-point backward must
+// visit) -- what compact_live_kernel would find.  gl = 2 * loss weight * d loss / d sum.
+struct RenderLossBwdArgs {
+    RenderArgs r;
+    const unsigned long long* counts;      // [3] batch-global n_front, n_sdf, n_valid
+    long long n_rays_total;
+    uint32_t* list;                        // may be NULL
+    unsigned long long* list_count;
+    float* coef_out;                       // [4] optional
+};
+
+template <int kPerLane>
+__global__ void __launch_bounds__(kRayWarps * 32) render_loss_bwd_kernel(RenderLossBwdArgs a) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float coef[4], gl[4];
+    {
+        long long counts[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) counts[i] = (long long)a.counts[i];
+        loss_coef_from_counts(counts, a.n_rays_total, a.r.n_samples, coef);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) gl[i] = a.r.g_loss[i] ? 2.0f * a.r.g_loss[i][0] * coef[i] : 0.f;
+        if (a.coef_out && blockIdx.x == 0 && threadIdx.x < 4) a.coef_out[threadIdx.x] = coef[threadIdx.x];
+    }
+    double part[4] = {0., 0., 0., 0.};
+    for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.r.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
+        RayState<kPerLane> st;
+        ray_forward<kPerLane>(a.r, ray, lane, st);
+        float rgb0 = st.rgb[0], rgb1 = st.rgb[1], rgb2 = st.rgb[2];
+        if (a.r.white_bkgd) { rgb0 += 1.f - st.acc; rgb1 += 1.f - st.acc; rgb2 += 1.f - st.acc; }
+        if (a.r.loss_sums) ray_loss_sums<kPerLane>(a.r, ray, lane, st, rgb0, rgb1, rgb2, part);
+        const unsigned live = ray_backward_from_state<kPerLane>(a.r, ray, lane, st, gl);
+        if (a.list) ray_append_live<kPerLane>(live, ray, a.r.n_samples, lane, a.list, a.list_count);
+    }
+    if (a.r.loss_sums) {
+        __shared__ double red[4][kRayWarps];
+        if (lane == 0) for (int i = 0; i < 4; ++i) red[i][warp] = part[i];
+        __syncthreads();
+        if (threadIdx.x < 4) {
+            double t = 0.;
+            for (int w = 0; w < kRayWarps; ++w) t += red[threadIdx.x][w];
+            atomicAdd(a.r.loss_sums + threadIdx.x, t);
+        }
+    }
+}
+
 static inline int ray_grid(int64_t n_rays) {
     int64_t blocks = (n_rays + kRayWarps - 1) / kRayWarps;
     const int64_t cap = 148 * 16;
@@ -362,12 +411,32 @@ cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st) {
         else kernel<kMaxPerLane><<<grid, kRayWarps * 32, 0, st>>>(a);                                      \
     } while (0)
 
+#define CB200_DISPATCH_PER_LANE_R(kernel, args, r)                                                         \
+    do {                                                                                                   \
+        const int per_lane = ((r).n_samples + 31) / 32;                                                    \
+        const int grid = ray_grid((r).n_rays);                                                             \
+        if (per_lane <= 1) kernel<1><<<grid, kRayWarps * 32, 0, st>>>(args);                               \
+        else if (per_lane == 2) kernel<2><<<grid, kRayWarps * 32, 0, st>>>(args);                          \
+        else if (per_lane <= 4) kernel<4><<<grid, kRayWarps * 32, 0, st>>>(args);                          \
+        else kernel<kMaxPerLane><<<grid, kRayWarps * 32, 0, st>>>(args);                                   \
+    } while (0)
+
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st) {
     CB200_DISPATCH_PER_LANE(render_fwd_kernel);
     return cudaGetLastError();
 }
 cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st) {
     CB200_DISPATCH_PER_LANE(render_bwd_kernel);
+    return cudaGetLastError();
+}
+cudaError_t launch_render_loss_bwd(const RenderArgs& r, const unsigned long long* counts, long long n_rays_total, uint32_t* list,
+                                   unsigned long long* list_count, float* coef_out, cudaStream_t st) {
+    if (list_count) {
+        cudaError_t e = cudaMemsetAsync(list_count, 0, sizeof(unsigned long long), st);
+        if (e != cudaSuccess) return e;
+    }
+    RenderLossBwdArgs a{r, counts, n_rays_total, list, list_count, coef_out};
+    CB200_DISPATCH_PER_LANE_R(render_loss_bwd_kernel, a, r);
     return cudaGetLastError();
 }
 cudaError_t launch_loss_finish(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,

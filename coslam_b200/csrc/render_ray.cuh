@@ -184,16 +184,33 @@ __device__ __forceinline__ void ray_loss_sums(const RenderArgs& a, int64_t ray, 
     }
 }
 
-// the four losses and d loss_k / d sum_k from the batch-global sums and mask counts (model/utils.py:111-161)
-__device__ __forceinline__ void loss_from_sums(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
-                                               float* losses, float* coef) {
-    // model/utils.py:111-115: int64 counts, true division in fp32
+// d loss_k / d sum_k: needs the batch-global mask counts only (model/utils.py:111-115: int64 counts, true division in fp32), not the sums,
+// so the backward of a ray can follow its forward without waiting for the other rays' residuals
+__device__ __forceinline__ void loss_coef_from_counts(const long long* counts, long long n_rays_total, long long n_samples, float* coef,
+                                                      float* sdf_w_out = nullptr, float* fs_w_out = nullptr) {
     const long long n_front = counts[0], n_sdf = counts[1], n_valid = counts[2];
     const float n_tot = (float)(n_front + n_sdf);
     const float fs_w = 1.0f - (float)n_front / n_tot;
     const float sdf_w = 1.0f - (float)n_sdf / n_tot;
     const double inv_rgb = 1.0 / (3.0 * (double)n_rays_total);
     const double inv_dep = 1.0 / (double)n_valid;                  // 0 valid rays -> NaN like mse_loss of empty
+    const double inv_smp = 1.0 / ((double)n_rays_total * (double)n_samples);
+    coef[0] = (float)inv_rgb;
+    coef[1] = n_valid > 0 ? (float)inv_dep : 0.f;
+    coef[2] = (float)inv_smp * sdf_w;
+    coef[3] = (float)inv_smp * fs_w;
+    if (sdf_w_out) *sdf_w_out = sdf_w;
+    if (fs_w_out) *fs_w_out = fs_w;
+}
+
+// the four losses and d loss_k / d sum_k from the batch-global sums and mask counts (model/utils.py:111-161)
+__device__ __forceinline__ void loss_from_sums(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
+                                               float* losses, float* coef) {
+    float sdf_w, fs_w;
+    loss_coef_from_counts(counts, n_rays_total, n_samples, coef, &sdf_w, &fs_w);
+    const long long n_valid = counts[2];
+    const double inv_rgb = 1.0 / (3.0 * (double)n_rays_total);
+    const double inv_dep = 1.0 / (double)n_valid;
     const double inv_smp = 1.0 / ((double)n_rays_total * (double)n_samples);
     const float mse_rgb = (float)(sums[0] * inv_rgb);
     const float mse_dep = n_valid > 0 ? (float)(sums[1] * inv_dep) : __int_as_float(0x7fc00000);
@@ -203,19 +220,14 @@ __device__ __forceinline__ void loss_from_sums(const double* sums, const long lo
     losses[1] = mse_dep;
     losses[2] = mse_sdf * sdf_w;
     losses[3] = mse_fs * fs_w;
-    coef[0] = (float)inv_rgb;
-    coef[1] = n_valid > 0 ? (float)inv_dep : 0.f;
-    coef[2] = (float)inv_smp * sdf_w;
-    coef[3] = (float)inv_smp * fs_w;
 }
 
 // backward of one ray: writes d_raw[ray, :, :]; gl[k] = 2 * upstream gradient of loss k * coef[k].  Returns the bit mask of this
 // lane's sample slots whose d_raw is not exactly zero (bit k = sample lane + 32 k).
 template <int kPerLane>
-__device__ __forceinline__ unsigned ray_backward(const RenderArgs& a, int64_t ray, int lane, const float (&gl)[4]) {
+__device__ __forceinline__ unsigned ray_backward_from_state(const RenderArgs& a, int64_t ray, int lane, const RayState<kPerLane>& st,
+                                                            const float (&gl)[4]) {
     const int S = a.n_samples;
-    RayState<kPerLane> st;
-    ray_forward<kPerLane>(a, ray, lane, st);
     float d = 0.f, rw = 0.f;
     bool valid = false;
     float g_map[3] = {0.f, 0.f, 0.f}, g_dep = 0.f;
@@ -277,6 +289,31 @@ __device__ __forceinline__ unsigned ray_backward(const RenderArgs& a, int64_t ra
         }
     }
     return live;
+}
+
+template <int kPerLane>
+__device__ __forceinline__ unsigned ray_backward(const RenderArgs& a, int64_t ray, int lane, const float (&gl)[4]) {
+    RayState<kPerLane> st;
+    ray_forward<kPerLane>(a, ray, lane, st);
+    return ray_backward_from_state<kPerLane>(a, ray, lane, st, gl);
+}
+
+// appends the ray's samples with non-zero d_raw (bit j of `live` = sample lane + 32 j) to a point list, ascending and adjacent
+template <int kPerLane>
+__device__ __forceinline__ void ray_append_live(unsigned live, int64_t ray, int n_samples, int lane, uint32_t* list, unsigned long long* count) {
+    unsigned total = 0, mine[kPerLane];
+#pragma unroll
+    for (int j = 0; j < kPerLane; ++j) {             // rank in ascending sample order s = lane + 32 j
+        const unsigned b = __ballot_sync(0xffffffffu, (live >> j) & 1u);
+        mine[j] = total + __popc(b & ((1u << lane) - 1u));
+        total += __popc(b);
+    }
+    unsigned long long base = 0;
+    if (lane == 0 && total) base = atomicAdd(count, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+    for (int j = 0; j < kPerLane; ++j)
+        if ((live >> j) & 1u) list[base + mine[j]] = (uint32_t)(ray * n_samples + lane + 32 * j);
 }
 
 }  // namespace cb200

@@ -53,10 +53,15 @@ __global__ void add_coarse_sums_kernel(double* sums, const double* sums0) {
 }
 
 // rays (coslam.py:336-355) -> JointEncoding.forward up to the loss sums (scene_rep.py:297-338)
-int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
+// without importance samples: rendering, loss sums, d_raw and the live-point list in one launch (cb200_render_loss_bwd), the losses
+// at the start of the optimise phase
+bool fused_loss_head(const cb200_ba_plan* p) { return p->n_importance == 0 && p->bwd_ws != nullptr; }
+
+int ba_forward(const cb200_ba_plan* p, int64_t it, bool do_rays, bool do_points, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t g = p->n_global, n = p->n_global + p->n_cur, S0 = p->n_samples, I = p->n_importance, S = S0 + I;
     int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
+    if (do_rays) {
     CB_TRY(cuda_rc(cudaMemsetAsync(p->ws, 0, 10 * sizeof(double), st)));
     if (p->d_rays) CB_TRY(cuda_rc(cudaMemsetAsync(p->d_rays, 0, sizeof(float) * 6 * n, st)));
     if (!p->cur_rays || !p->poses_all || !p->idx_cur || !p->slot_cur || (g > 0 && (!p->kf_rays || !p->idx_global || !p->slot_global))) return -1;
@@ -64,8 +69,17 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
         p->kf_rays, reinterpret_cast<const long long*>(p->idx_global) + it * g, reinterpret_cast<const long long*>(p->slot_global) + it * g, g,
         p->cur_rays, reinterpret_cast<const long long*>(p->idx_cur) + it * p->n_cur, reinterpret_cast<const long long*>(p->slot_cur), p->n_cur,
         p->poses_all, p->n_poses, p->rays_o, p->rays_d, p->target_rgb, p->target_d, st)));
+    }
     const float* noise = p->noise ? p->noise + it * n * S0 : nullptr;
     const uint64_t seed = p->seeds ? p->seeds[it] : 0;
+    if (I == 0) {
+        if (do_rays)
+            CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, noise, seed, p->seed_dev, n, p->z_vals,
+                                     counts, stream));
+        if (!do_points) return 0;
+    } else if (!do_points) {
+        return 0;                                 // with importance samples the counts come out of the coarse pass: nothing to split
+    }
     if (I > 0) {
         // coarse samples -> weights -> I extra depths per ray, merged and sorted; the mask counts belong to the merged samples
         CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, noise, seed, p->seed_dev, n, p->z0,
@@ -77,9 +91,6 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
                                 p->weights0, p->sums0, stream));
         CB_TRY(cb200_importance_sample(p->render, p->z0, p->weights0, p->u + (p->u_stride ? it * n * I : 0), p->u_stride, p->target_d, n, S0, I,
                                        p->z_vals, nullptr, counts, stream));
-    } else {
-        CB_TRY(cb200_sample_rays(p->render, p->target_d, p->lin_uniform, p->lin_guided, p->lin_nodepth, noise, seed, p->seed_dev, n, p->z_vals,
-                                 counts, stream));
     }
     if (p->lazy_ws) {
         CB_TRY(cuda_rc(cudaMemsetAsync(p->raw, 0, sizeof(float) * 4 * n * S, st)));
@@ -96,6 +107,7 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, void* stream) {
         CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0,
                                 nullptr, nullptr, stream));
     }
+    if (fused_loss_head(p)) return 0;             // the loss sums are taken by the backward phase's fused launch
     CB_TRY(cb200_render_fwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
                             p->ws + 4, stream));
     if (I > 0) {
@@ -110,11 +122,20 @@ int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
     const int64_t g = p->n_global, n = p->n_global + p->n_cur, S0 = p->n_samples, I = p->n_importance, S = S0 + I;
     int64_t* counts = reinterpret_cast<int64_t*>(p->ws);
     double* sums = p->ws + 4;
-    CB_TRY(cb200_loss_finish(sums, counts, p->n_rays_total > 0 ? p->n_rays_total : n, S, p->loss_out, p->loss_out + 4, stream));
-    CB_TRY(cb200_render_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, &p->loss_w, p->loss_out + 4, nullptr, nullptr, p->d_raw,
-                            stream));
-    CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask, p->g_table,
-                            &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes, stream));
+    const int64_t n_total = p->n_rays_total > 0 ? p->n_rays_total : n;
+    if (fused_loss_head(p)) {
+        CB_TRY(cb200_render_loss_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, counts, n_total, &p->loss_w, sums,
+                                     p->loss_out + 4, p->d_raw, p->bwd_ws, p->bwd_ws_bytes, stream));
+        CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask,
+                                p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, 0, stream));
+    } else {
+        CB_TRY(cb200_loss_finish(sums, counts, n_total, S, p->loss_out, p->loss_out + 4, stream));
+        CB_TRY(cb200_render_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, &p->loss_w, p->loss_out + 4, nullptr, nullptr,
+                                p->d_raw, stream));
+        CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask,
+                                p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes,
+                                stream));
+    }
     if (I > 0) {                                 // the coarse maps carry the colour and depth terms only
         cb200_loss_grads lw = p->loss_w;
         lw.sdf = nullptr;
@@ -146,6 +167,11 @@ int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
 // optimiser steps that are due (coslam.py:363-390)
 int ba_optimise(const cb200_ba_plan* p, int64_t map_step, int zero_map_grads, int64_t pose_step, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (fused_loss_head(p)) {                     // the reported losses, from the (by now batch-global) sums
+        const int64_t n = p->n_global + p->n_cur;
+        CB_TRY(cb200_loss_finish(p->ws + 4, reinterpret_cast<int64_t*>(p->ws), p->n_rays_total > 0 ? p->n_rays_total : n, p->n_samples,
+                                 p->loss_out, p->loss_out + 4, stream));
+    }
     if (map_step > 0) {
         CB_TRY(cb200_adam_multi(p->map_params, p->n_map_params, map_step, zero_map_grads ? 1 : 0, stream));
     } else if (zero_map_grads) {
@@ -170,7 +196,8 @@ int ba_optimise(const cb200_ba_plan* p, int64_t map_step, int zero_map_grads, in
 extern "C" int cb200_ba_iteration(const cb200_ba_plan* p, int64_t it, int phases, int64_t map_step, int zero_map_grads, int64_t pose_step,
                                   void* stream) {
     if (p == nullptr || it < 0) return -1;
-    if (phases & CB200_BA_FORWARD) CB_TRY(ba_forward(p, it, stream));
+    if (phases & CB200_BA_RAYS) CB_TRY(ba_forward(p, it, true, false, stream));
+    if (phases & CB200_BA_FORWARD) CB_TRY(ba_forward(p, it, !(phases & CB200_BA_AFTER_RAYS), true, stream));
     if (phases & CB200_BA_BACKWARD) CB_TRY(ba_backward(p, it, stream));
     if (phases & CB200_BA_OPTIMISE) CB_TRY(ba_optimise(p, map_step, zero_map_grads, pose_step, stream));
     return 0;

@@ -8,12 +8,12 @@
 //   P0  rays from the current pose (optimization/utils.py get_camera_rays equivalent of coslam.py:546-547), depth-guided
 //       sampling (scene_rep.py:227-255), mask counts                                                   warp per ray
 //   P1  per-point forward: encodings + decoder (points_tc.cuh fwd_tile_loop)                           128-point tiles
-//   P2  sdf2weights / raw2outputs / squared-residual sums of the four losses (render_ray.cuh)          warp per ray
-//   P3  losses + normalisers (every CTA, redundantly), rendering + loss backward -> d_raw, list of the points with non-zero
-//       d_raw (the ray's live samples stay adjacent and ascending)                                     warp per ray
+//   P2  sdf2weights / raw2outputs / squared-residual sums of the four losses, and -- d loss / d sum needs the mask counts only,
+//       not the sums -- the rendering + loss backward -> d_raw and the list of the points with non-zero d_raw (the ray's live
+//       samples stay adjacent and ascending)                                                           warp per ray
 //   P4  per-point backward to the ray gradients only (bwd_tile_loop<false>)                            tiles over the list
 //   P5  dL/d c2w = segment sum of the ray gradients; the LAST CTA to finish (ticket) runs the single-thread pose update
-//       (track_update.cuh: weighted loss, best / last bookkeeping, patience, dual-number pose Jacobian, Adam, next c2w)
+//       (track_update.cuh: losses from the sums, weighted loss, best / last bookkeeping, patience, dual-number pose Jacobian, Adam, next c2w)
 //       and clears the iteration's accumulators
 //
 // A ray is owned by the same warp in P0, P2, P3 and P5, so per-ray data (targets, z_vals) never needs a barrier of its own.
@@ -52,7 +52,6 @@ __global__ void __launch_bounds__(tc::kThreads, 2) track_frame_kernel(TrackFrame
     __shared__ double red_d[4][kRayWarps];
     __shared__ unsigned red_u[3][kRayWarps];
     __shared__ float red_f[12][kRayWarps];
-    __shared__ float sh_loss[8];                  // 4 losses | 4 d loss / d sum
     __shared__ float sh_c2w[16];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const unsigned n_ctas = gridDim.x;
@@ -146,8 +145,18 @@ __global__ void __launch_bounds__(tc::kThreads, 2) track_frame_kernel(TrackFrame
         TF_CLK(1);
         grid_sync(t.barrier, epoch, n_ctas);
         TF_CLK(7);
-        // ---- P2 ---------------------------------------------------------------------------------------------------------
+        // ---- P2 + P3: rendering, loss sums, d_raw and the live-point list of every ray (d loss / d sum needs the counts only) ------
         {
+            float gl[4];
+            {
+                long long counts[3];
+                float coef[4];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) counts[i] = (long long)__ldcg(t.counts + i);
+                loss_coef_from_counts(counts, N, S, coef);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) gl[i] = 2.0f * t.step.loss_w[i] * coef[i];
+            }
             double part[4] = {0., 0., 0., 0.};
             for (int64_t ray = ray_first; ray < N; ray += ray_step) {
                 RayState<kPerLane> st;
@@ -155,53 +164,20 @@ __global__ void __launch_bounds__(tc::kThreads, 2) track_frame_kernel(TrackFrame
                 float rgb0 = st.rgb[0], rgb1 = st.rgb[1], rgb2 = st.rgb[2];
                 if (t.rnd.white_bkgd) { rgb0 += 1.f - st.acc; rgb1 += 1.f - st.acc; rgb2 += 1.f - st.acc; }
                 ray_loss_sums<kPerLane>(t.rnd, ray, lane, st, rgb0, rgb1, rgb2, part);
+                const unsigned live = ray_backward_from_state<kPerLane>(t.rnd, ray, lane, st, gl);
+                ray_append_live<kPerLane>(live, ray, S, lane, t.live_list, t.live_count);
             }
             if (lane == 0) for (int i = 0; i < 4; ++i) red_d[i][warp] = part[i];
             __syncthreads();
             if (tid < 4) {
-                double s = 0.;
-                for (int w = 0; w < kRayWarps; ++w) s += red_d[tid][w];
-                if (s != 0.) atomicAdd(t.sums + tid, s);
+                double sum = 0.;
+                for (int w = 0; w < kRayWarps; ++w) sum += red_d[tid][w];
+                if (sum != 0.) atomicAdd(t.sums + tid, sum);
             }
         }
         TF_CLK(2);
         grid_sync(t.barrier, epoch, n_ctas);
         TF_CLK(8);
-        // ---- P3 ---------------------------------------------------------------------------------------------------------
-        if (tid == 0) {
-            double sums[4];
-            long long counts[3];
-            for (int i = 0; i < 4; ++i) sums[i] = __ldcg(t.sums + i);
-            for (int i = 0; i < 3; ++i) counts[i] = (long long)__ldcg(t.counts + i);
-            loss_from_sums(sums, counts, N, S, sh_loss, sh_loss + 4);
-            if (blockIdx.x == 0)
-                for (int i = 0; i < 4; ++i) t.losses[i] = sh_loss[i];
-        }
-        __syncthreads();
-        {
-            float gl[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) gl[i] = 2.0f * t.step.loss_w[i] * sh_loss[4 + i];
-            for (int64_t ray = ray_first; ray < N; ray += ray_step) {
-                const unsigned live = ray_backward<kPerLane>(t.rnd, ray, lane, gl);
-                unsigned total = 0, mine[kPerLane];
-#pragma unroll
-                for (int j = 0; j < kPerLane; ++j) {             // rank in ascending sample order s = lane + 32 j
-                    const unsigned b = __ballot_sync(0xffffffffu, (live >> j) & 1u);
-                    mine[j] = total + __popc(b & ((1u << lane) - 1u));
-                    total += __popc(b);
-                }
-                unsigned long long base = 0;
-                if (lane == 0 && total) base = atomicAdd(t.live_count, (unsigned long long)total);
-                base = __shfl_sync(0xffffffffu, base, 0);
-#pragma unroll
-                for (int j = 0; j < kPerLane; ++j)
-                    if ((live >> j) & 1u) t.live_list[base + mine[j]] = (uint32_t)(ray * S + lane + 32 * j);
-            }
-        }
-        TF_CLK(3);
-        grid_sync(t.barrier, epoch, n_ctas);
-        TF_CLK(9);
         // ---- P4 ---------------------------------------------------------------------------------------------------------
         {
             const int64_t n_live = (int64_t)__ldcg(t.live_count);

@@ -2,6 +2,7 @@
 // bundle-adjustment pose kernels (track.cu); also called from the one-launch tracking loop (track_frame.cu).
 #pragma once
 #include "args.cuh"
+#include "render_ray.cuh"
 
 namespace cb200 {
 
@@ -204,7 +205,19 @@ __device__ inline void track_init_state(const float* c2w_init, const cb200_track
 __device__ inline void track_update_step(const cb200_track_step& s, bool first_iter) {
     // every input first, into registers: the buffers may alias as far as the compiler knows, so loads interleaved with the
     // stores below would each wait for the previous store (a chain of ~20 dependent global round trips)
-    const float l0 = __ldcg(s.losses), l1 = __ldcg(s.losses + 1), l2 = __ldcg(s.losses + 2), l3 = __ldcg(s.losses + 3);
+    float l0, l1, l2, l3;
+    const bool own_losses = s.sums != nullptr;
+    if (own_losses) {                              // losses from this iteration's sums and counts (cb200_loss_finish arithmetic)
+        double sums[4];
+        long long counts[3];
+        for (int i = 0; i < 4; ++i) sums[i] = __ldcg(s.sums + i);
+        for (int i = 0; i < 3; ++i) counts[i] = (long long)__ldcg(s.counts + i);
+        float L[4], coef[4];
+        loss_from_sums(sums, counts, s.n_rays_total, s.n_samples, L, coef);
+        l0 = L[0]; l1 = L[1]; l2 = L[2]; l3 = L[3];
+    } else {
+        l0 = __ldcg(s.losses); l1 = __ldcg(s.losses + 1); l2 = __ldcg(s.losses + 2); l3 = __ldcg(s.losses + 3);
+    }
     bool alive = __ldcg(s.alive) != 0;
     const float best_in = __ldcg(s.best_loss);
     int64_t patience = __ldcg(s.patience);
@@ -273,6 +286,10 @@ __device__ inline void track_update_step(const cb200_track_step& s, bool first_i
         *s.last_loss = lv;
     }
     *s.patience = patience;
+    if (own_losses) {
+        float* lo = const_cast<float*>(s.losses);
+        lo[0] = l0; lo[1] = l1; lo[2] = l2; lo[3] = l3;
+    }
     if (s.may_stop) *s.alive = alive ? 1 : 0;
     if (s.psnr) *s.psnr = -10.f * logf(l0 + 1e-6f) / logf(10.f);      // mse2psnr, model/utils.py:8-12
     if (s.loss) *s.loss = lv;

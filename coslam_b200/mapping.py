@@ -335,22 +335,40 @@ class BundleAdjuster(object):
                 continue
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)] if self.phase_times is not None else None
             mark = (lambda i: ev[i].record()) if ev else (lambda i: None)
+            call = lambda phases, ms=0, z_=0, ps=0: check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), phases, ctypes.c_int64(ms), z_,
+                                                                                 ctypes.c_int64(ps), st), 'ba_iteration')
+            shard = self.world > 1
             mark(0)
-            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 1, ctypes.c_int64(0), 0, ctypes.c_int64(0), st), 'ba_iteration')
-            mark(1)
-            if self.world > 1:
-                dist.all_reduce(ws[:4].view(torch.int64), group=self.group)    # AR-1: batch-global mask counts ...
-                dist.all_reduce(ws[4:8], group=self.group)                     #       ... and loss sums
-            mark(2)
-            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 2, ctypes.c_int64(0), 0, ctypes.c_int64(0), st), 'ba_iteration')
+            if I == 0:
+                # the mask counts are complete after the sampling and are all the backward needs of the other ranks: their all-reduce
+                # (AR-1) runs behind the per-point forward; the loss sums only feed the reported losses and are reduced behind the backward
+                call(8)                                                        # CB200_BA_RAYS
+                h1 = dist.all_reduce(ws[:4].view(torch.int64), group=self.group, async_op=True) if shard else None
+                call(1 | 16)                                                   # FORWARD | AFTER_RAYS
+                mark(1)
+                if h1 is not None:
+                    h1.wait()
+                mark(2)
+                call(2)
+                h2 = dist.all_reduce(ws[4:8], group=self.group, async_op=True) if shard else None
+            else:
+                call(1)
+                mark(1)
+                if shard:
+                    dist.all_reduce(ws[:4].view(torch.int64), group=self.group)    # AR-1: batch-global mask counts ...
+                    dist.all_reduce(ws[4:8], group=self.group)                     #       ... and loss sums
+                mark(2)
+                call(2)
+                h2 = None
             mark(3)
-            if map_step > 0 and self.world > 1:                                # AR-2, only in front of a step that consumes the sums
+            if map_step > 0 and shard:                                         # AR-2, only in front of a step that consumes the sums
                 dist.all_reduce(self._flat, group=self.group)
-            if p_step > 0 and self.world > 1:
+            if p_step > 0 and shard:
                 dist.all_reduce(d_poses, group=self.group)
+            if h2 is not None:
+                h2.wait()
             mark(4)
-            check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 4, ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
-                  'ba_iteration')
+            call(4, map_step, zero, p_step)
             mark(5)
             if ev:
                 self.phase_times.append(ev)

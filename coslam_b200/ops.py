@@ -265,7 +265,7 @@ def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True):
 
 
 def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=None, need_table=True, need_mlp=True,
-                    need_pos=True, sdf_only=False, accumulate=None):
+                    need_pos=True, sdf_only=False, accumulate=None, ready_list=None):
     """Backward of points_forward.  Returns (d_table, (dW1..dW4), d_pts | (d_rays_o, d_rays_d)).
     accumulate = (d_table, (dW1..dW4), d_rays [2,N,3]): existing buffers the kernel adds into (any entry may be None = not
     needed) instead of fresh zero-filled ones -- the autograd-free loops (mapping.py) keep their gradient buffers."""
@@ -303,7 +303,9 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
     mlp = _mlp_block(*w)
     # scratch for the live-point compaction (ray mode): index list + counter, see cb200_points_bwd
     wsp, wsp_bytes = None, 0
-    if rays is not None and d_geo is None:
+    if ready_list is not None:                     # render_loss_backward has written the live-point list already
+        wsp = ready_list
+    elif rays is not None and d_geo is None:
         wsp_bytes = int(_lib.load().cb200_points_bwd_workspace(ctypes.c_int64(n * s)))
         wsp = torch.empty((wsp_bytes + 3) // 4, dtype=torch.int32, device=dev)
     _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd(
@@ -311,7 +313,7 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
         ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(d_table),
         ctypes.byref(gblock) if gblock is not None else None, ptr(d_pts), ptr(d_o), ptr(d_d), 1 if sdf_only else 0,
         ptr(wsp), ctypes.c_size_t(wsp_bytes), stream()), 'points_bwd'))
-    if wsp is not None and _lib.load().cb200_get_decoder() == 1:
+    if wsp is not None and ready_list is None and _lib.load().cb200_get_decoder() == 1:
         _lib.KERNEL_LAUNCHES += 1          # the compaction kernel in front of the per-point kernel
     return d_table, d_w, (d_pts if rays is None else (d_o, d_d))
 
@@ -421,6 +423,24 @@ def _render_backward(spec, raw, z, target_rgb, target_d, g_losses, coef, g_rgb, 
     check(_lib.load().cb200_render_bwd(ctypes.byref(spec.render_cfg()), ptr(raw), ptr(z), ptr(target_rgb), ptr(target_d),
                                        ctypes.c_int64(n), ctypes.c_int64(s), ctypes.byref(lg) if lg is not None else None,
                                        ptr(coef), ptr(g_rgb), ptr(g_depth), ptr(d_raw), stream()), 'render_bwd')
+    return d_raw
+
+
+def render_loss_backward(spec, raw, z, target_rgb, target_d, counts, loss_w, loss_sums, n_rays_total=None, list_ws=None, coef=None):
+    """cb200_render_loss_bwd: loss-head forward (sums) and backward (d_raw) of every ray in one launch, with the list of the points
+    whose d_raw is non-zero written into `list_ws` (int32 tensor of cb200_points_bwd_workspace bytes) for points_backward(ready_list=).
+    counts: the batch-global int64 [3] mask counts of the sampling; loss_w: four device scalars (or None)."""
+    n, s = z.shape
+    d_raw = torch.empty((n, s, 4), dtype=torch.float32, device=z.device)
+    lg = LossGrads()
+    for name, g in zip(('rgb', 'depth', 'sdf', 'fs'), loss_w):
+        if g is not None:
+            setattr(lg, name, g.data_ptr())
+    check(_lib.load().cb200_render_loss_bwd(ctypes.byref(spec.render_cfg()), ptr(raw), ptr(z), ptr(target_rgb), ptr(target_d),
+                                            ctypes.c_int64(n), ctypes.c_int64(s), ptr(counts), ctypes.c_int64(n_rays_total or n),
+                                            ctypes.byref(lg), ptr(loss_sums), ptr(coef), ptr(d_raw), ptr(list_ws),
+                                            ctypes.c_size_t(list_ws.numel() * list_ws.element_size() if list_ws is not None else 0),
+                                            stream()), 'render_loss_bwd')
     return d_raw
 
 

@@ -94,6 +94,8 @@ class FrameTracker(object):
             self.c2w_init = torch.zeros(16, **f32)
             self._kf7_host = torch.zeros((n, 7), dtype=torch.float32).pin_memory()
             self._steps = [self._track_step(first) for first in (True, False)]
+            self._steps_own = [self._track_step(first, own_losses=True) for first in (True, False)]
+            self._list_ws = None
         can_persist = self.fused and self.use_graph and self.n_imp == 0
         if persistent and not can_persist:
             raise NotImplementedError('FrameTracker(persistent=True) needs fused=True, use_graph=True (device noise) and n_importance 0')
@@ -101,8 +103,11 @@ class FrameTracker(object):
         self._wsp = None
         self._kf7_sent = None
 
-    def _track_step(self, first):
+    def _track_step(self, first, own_losses=False):
         s = _lib.TrackStep()
+        if own_losses:                                               # losses from the iteration's sums / counts inside the update kernel
+            s.sums, s.counts = self.zbuf[4:8].data_ptr(), self.zbuf[:4].data_ptr()
+            s.n_rays_total, s.n_samples = self.n_rays, self.model.spec.n_samples
         for name, t in (('rot', self.rot), ('trans', self.trans), ('adam', self.adam), ('step', self.step), ('losses', self.loss_out),
                         ('d_c2w', self.d_c2w), ('c2w', self.c2w), ('best_loss', self.best_loss), ('best_c2w', self.best_c2w),
                         ('last_loss', self.last_loss), ('last_c2w', self.last_c2w), ('psnr', self.psnr), ('loss', self.loss),
@@ -148,14 +153,25 @@ class FrameTracker(object):
             z = m._sample(td, counts=counts)
         rays = (self.rays_o, self.rays_d, z)
         raw, _, mask = ops.points_forward(spec.scene(), tb, w, rays=rays)
-        ops._render_forward(spec, raw, z, self.target_s, td, loss_sums=ws[4:8])
-        if coarse is not None:
-            ws[4:6].add_(coarse[3][:2])                              # colour and depth only: the coarse pass has no SDF / free-space terms
-        check(lib.cb200_loss_finish(ptr(ws[4:8]), ptr(counts), ctypes.c_int64(n), ctypes.c_int64(z.shape[1]),
-                                    ptr(self.loss_out[:4]), ptr(self.loss_out[4:]), stream()), 'loss_finish')
-        d_raw = ops._render_backward(spec, raw, z, self.target_s, td, self.w_dev, self.loss_out[4:], None, None)
         into = (None, None, self.d_rays)                             # both passes add into the same ray-gradient buffer
-        ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, accumulate=into)
+        if coarse is None and lib.cb200_get_decoder() == 1:
+            # rendering, loss sums, d_raw and the live-point list of every ray in ONE launch: d loss / d sum needs the mask counts only,
+            # which the sampling produced; the losses themselves are taken from the sums inside cb200_track_update
+            if self._list_ws is None or self._list_ws.numel() * 4 < lib.cb200_points_bwd_workspace(ctypes.c_int64(n * z.shape[1])):
+                self._list_ws = torch.empty((int(lib.cb200_points_bwd_workspace(ctypes.c_int64(n * z.shape[1]))) + 3) // 4,
+                                            dtype=torch.int32, device=self.device)
+            d_raw = ops.render_loss_backward(spec, raw, z, self.target_s, td, counts, self.w_dev, ws[4:8], list_ws=self._list_ws)
+            ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, accumulate=into, ready_list=self._list_ws)
+            step = self._steps_own[0 if k == 0 else 1]
+        else:
+            ops._render_forward(spec, raw, z, self.target_s, td, loss_sums=ws[4:8])
+            if coarse is not None:
+                ws[4:6].add_(coarse[3][:2])                          # colour and depth only: the coarse pass has no SDF / free-space terms
+            check(lib.cb200_loss_finish(ptr(ws[4:8]), ptr(counts), ctypes.c_int64(n), ctypes.c_int64(z.shape[1]),
+                                        ptr(self.loss_out[:4]), ptr(self.loss_out[4:]), stream()), 'loss_finish')
+            d_raw = ops._render_backward(spec, raw, z, self.target_s, td, self.w_dev, self.loss_out[4:], None, None)
+            ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, accumulate=into)
+            step = self._steps[0 if k == 0 else 1]
         if coarse is not None:
             rays0, raw0, mask0, _ = coarse
             d_raw0 = ops._render_backward(spec, raw0, rays0[2], self.target_s, td, (self.w_dev[0], self.w_dev[1], None, None),
@@ -164,7 +180,7 @@ class FrameTracker(object):
         d_o, d_d = self.d_rays[0], self.d_rays[1]
         check(lib.cb200_assemble_rays_bwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(d_o), ptr(d_d), ctypes.c_int64(n),
                                           ctypes.c_int64(1), ptr(self.d_c2w), stream()), 'assemble_rays_bwd')
-        check(lib.cb200_track_update(ctypes.byref(self._steps[0 if k == 0 else 1]), stream()), 'track_update')
+        check(lib.cb200_track_update(ctypes.byref(step), stream()), 'track_update')
 
     def _frame_persistent(self):
         """The whole frame in one cooperative launch (csrc/track_frame.cu)."""
@@ -281,7 +297,9 @@ class FrameTracker(object):
                 if not self.use_graph:
                     self._frame()
                 else:
-                    if self._graph is None:
+                    # the graph holds raw parameter addresses: model.to(), share_memory_(), load_state_dict(assign=True) or a
+                    # re-pointed parameter would make a replay read stale memory, so a moved parameter means a new capture
+                    if self._graph is None or self._graph_ptrs != self._param_ptrs():
                         self._capture()
                     self._graph.replay()
         else:
@@ -299,7 +317,7 @@ class FrameTracker(object):
                 if not self.use_graph:
                     self._frame()
                 else:
-                    if self._graph is None:
+                    if self._graph is None or self._graph_ptrs != self._param_ptrs():
                         self._capture()
                     self._graph.replay()
             finally:
@@ -321,3 +339,10 @@ class FrameTracker(object):
         with torch.cuda.graph(g):
             self._frame()
         self._graph = g
+        self._graph_ptrs = self._param_ptrs()
+
+    def _param_ptrs(self):
+        """Addresses the captured launches have baked in: the model's parameters and the noise counter."""
+        ptrs = tuple(p.data_ptr() for p in self.model.parameters())
+        c = self.model._noise_counter
+        return ptrs + ((c.data_ptr(),) if c is not None else ())

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 16
+#define CB200_ABI_VERSION 17
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -179,6 +179,12 @@ typedef struct cb200_track_step {
     int32_t first_iter;     /* != 0 for iteration 0 of a frame */
     int32_t may_stop;       /* wait_iters < iters */
     int32_t wait_iters;
+    /* optional (sums != NULL): take the four losses from the squared-residual sums [4] and mask counts [3] of this iteration
+     * (cb200_render_loss_bwd) instead of reading `losses`, which then RECEIVES them: the cb200_loss_finish arithmetic inside the update */
+    const double* sums;
+    const int64_t* counts;
+    int64_t n_rays_total;
+    int64_t n_samples;
 } cb200_track_step;
 int cb200_track_update(const cb200_track_step* step, void* stream);
 
@@ -291,7 +297,8 @@ int cb200_lazy_resolve(const cb200_render_cfg* cfg, const float* z_vals, const f
  * act_mask is the array written by cb200_points_fwd on the same inputs.
  * workspace: optional device scratch of at least cb200_points_bwd_workspace(P) bytes.  When given (ray mode, tensor-core
  * decoder) the points whose d_raw is exactly zero -- samples behind the truncation band carry no loss and no rendering
- * weight -- are compacted away before the per-point kernel runs (they contribute exact zeros to every output). */
+ * weight -- are compacted away before the per-point kernel runs (they contribute exact zeros to every output).
+ * workspace != NULL with workspace_bytes == 0: the workspace already holds that list (cb200_render_loss_bwd). */
 size_t cb200_points_bwd_workspace(int64_t n_points);
 int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
                      const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
@@ -329,6 +336,18 @@ typedef struct cb200_loss_grads {
 int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb,
                      const float* target_d, int64_t n_rays, int64_t n_samples, const cb200_loss_grads* g_loss,
                      const float* coef, const float* g_rgb, const float* g_depth, float* d_raw, void* stream);
+
+/* Loss head forward AND backward in one pass (the autograd-free loops): per ray the rendering, its terms of the four squared-residual
+ * sums (loss_sums [4] double, += ; may be NULL), and d_raw [N,S,4] (=) from the loss weights g_loss (device scalars) -- d loss / d sum
+ * depends only on the batch-global mask counts `counts` [3] (cb200_sample_rays / cb200_importance_sample), so no cb200_loss_finish
+ * has to run in between; coef [4] (may be NULL) receives those normalisers.  n_rays_total: rays of the whole batch (all ranks).
+ * list_workspace (may be NULL): cb200_points_bwd_workspace(N * S) bytes that receive the list of the points with non-zero d_raw;
+ * pass the same pointer to cb200_points_bwd with workspace_bytes = 0 and it skips its own compaction pass.
+ * Replaces cb200_render_fwd(loss_sums) + cb200_loss_finish + cb200_render_bwd (+ the compaction) of model/scene_rep.py:311-338 in those loops. */
+int cb200_render_loss_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb,
+                          const float* target_d, int64_t n_rays, int64_t n_samples, const int64_t* counts,
+                          int64_t n_rays_total, const cb200_loss_grads* g_loss, double* loss_sums, float* coef, float* d_raw,
+                          void* list_workspace, size_t list_workspace_bytes, void* stream);
 
 /* ---- native iteration runtime of global_BA (coslam.py:336-390) ------------------------------------------------------ */
 
@@ -421,11 +440,18 @@ typedef struct cb200_ba_plan {
  * model/utils.py:111-115), BACKWARD, then the caller all-reduces the gradient buffers that an optimiser step is about to
  * consume, OPTIMISE.
  * map_step / pose_step: 1-based optimiser step to take after this iteration's backward, 0 = none;
- * zero_map_grads != 0 clears the map gradients afterwards (map_optimizer.zero_grad(), coslam.py:370). */
+ * zero_map_grads != 0 clears the map gradients afterwards (map_optimizer.zero_grad(), coslam.py:370).
+ * Without importance samples the mask counts are complete after the SAMPLING, and the backward needs only them (the loss sums are
+ * for the reported losses): a sharded caller issues CB200_BA_RAYS (ray assembly + sampling), starts the all-reduce of ws[0..2]
+ * asynchronously, issues CB200_BA_FORWARD | CB200_BA_AFTER_RAYS (the per-point forward, which hides the collective), waits, issues
+ * BACKWARD (cb200_render_loss_bwd: sums, d_raw and the live-point list in one launch), all-reduces ws[4..7] and the gradients that are
+ * due, OPTIMISE (which starts with cb200_loss_finish). */
 #define CB200_BA_FORWARD 1
 #define CB200_BA_BACKWARD 2
 #define CB200_BA_OPTIMISE 4
 #define CB200_BA_ALL 7
+#define CB200_BA_RAYS 8        /* ray assembly + sampling only */
+#define CB200_BA_AFTER_RAYS 16 /* with FORWARD: the rays of this iteration were issued by an earlier CB200_BA_RAYS call */
 int cb200_ba_iteration(const cb200_ba_plan* plan, int64_t it, int phases, int64_t map_step, int zero_map_grads,
                        int64_t pose_step, void* stream);
 

@@ -778,7 +778,7 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
     for _ in range(2):                                   # second replay: the per-frame state reset is part of the graph
         est_g, info_g = graph.track(dir_cam, rgb, depth, c2w0)
         # not bit-identical: the ray-gradient atomics sum in a different order every run and Adam normalises the step
-        assert float((est_g - est_e).abs().max()) <= 2e-5
+        assert float((est_g - est_e).abs().max()) <= 5e-5
         assert abs(float(info_g['best_loss']) - best_e) <= 1e-4 * abs(best_e)
     assert all(p.requires_grad for p in model.parameters())
     assert float((info_g['last_c2w'].cpu() - c2w0).abs().max()) > 1e-4          # the pose did move
@@ -787,9 +787,10 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
     for _ in range(2):
         est_p, info_p = one.track(dir_cam, rgb, depth, c2w0)
         assert one.persistent
-        assert float((est_p - est_e).abs().max()) <= 2e-5
+        # the live-point list is appended ray by ray instead of block by block: another summation order of the ray-gradient atomics
+        assert float((est_p - est_e).abs().max()) <= 5e-5
         assert abs(float(info_p['best_loss']) - best_e) <= 1e-4 * abs(best_e)
-        assert float((info_p['last_c2w'] - info_e['last_c2w']).abs().max()) <= 2e-5
+        assert float((info_p['last_c2w'] - info_e['last_c2w']).abs().max()) <= 5e-5
 
     # the reference loop on the oracle
     orc = util.make_oracle(cfg, table, weights)
@@ -841,6 +842,66 @@ def test_frame_tracker_with_importance_samples_matches_autograd_loop():
     for _ in range(2):
         est_g, info_g = graph.track(dir_cam, rgb, depth, c2w0)
         assert float((est_g - est_f).abs().max()) <= 3e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('cfg_name', ['room0', 'scannet0000'])
+def test_render_loss_bwd_matches_separate_kernels(cfg_name):
+    """cb200_render_loss_bwd (loss sums + d_raw + live-point list in one launch, d loss / d sum from the mask counts alone) against
+    cb200_render_fwd(loss_sums) -> cb200_loss_finish -> cb200_render_bwd -> the compaction inside cb200_points_bwd."""
+    import ctypes
+    from coslam_b200 import _lib, ops
+    from coslam_b200._lib import check, ptr, stream
+    cfg = synth.CONFIGS[cfg_name]()
+    model = util.make_cuda_model(cfg, synth.table_init(JointEncodingFor(cfg).embed_fn.params.numel(), 'trained', seed=3),
+                                 synth.decoder_init(seed=4), DEV)
+    spec = model.spec
+    n = 777
+    rays_o, rays_d, rgb, depth = (t.to(DEV) for t in synth.ray_batch(cfg, n, seed=21))
+    depth = depth.clone()
+    depth[::13] = 0.0
+    counts = torch.zeros(4, dtype=torch.int64, device=DEV)
+    z = ops.sample_rays(spec, depth, perturb=False, counts=counts)
+    fw = model._fused()
+    raw, _, mask = ops.points_forward(spec.scene(), fw[0].detach(), tuple(x.detach() for x in fw[1:]), rays=(rays_o, rays_d, z))
+    S = z.shape[1]
+    raw = raw.view(n, S, 4)
+    w_dev = torch.tensor([5.0, 0.1, 1000.0, 10.0], device=DEV).unbind(0)
+    td = depth.reshape(-1).contiguous()
+    # separate kernels
+    sums = torch.zeros(4, dtype=torch.float64, device=DEV)
+    ops._render_forward(spec, raw, z, rgb, td, loss_sums=sums)
+    loss_out = torch.zeros(8, device=DEV)
+    check(_lib.load().cb200_loss_finish(ptr(sums), ptr(counts), ctypes.c_int64(n), ctypes.c_int64(S), ptr(loss_out[:4]), ptr(loss_out[4:]),
+                                        stream()), 'loss_finish')
+    d_raw_ref = ops._render_backward(spec, raw, z, rgb, td, w_dev, loss_out[4:], None, None)
+    # one launch
+    sums2 = torch.zeros(4, dtype=torch.float64, device=DEV)
+    coef2 = torch.zeros(4, device=DEV)
+    nbytes = int(_lib.load().cb200_points_bwd_workspace(ctypes.c_int64(n * S)))
+    ws = torch.full(((nbytes + 3) // 4,), -1, dtype=torch.int32, device=DEV)
+    d_raw = ops.render_loss_backward(spec, raw, z, rgb, td, counts, w_dev, sums2, list_ws=ws, coef=coef2)
+    assert torch.equal(d_raw, d_raw_ref)                            # same arithmetic, ray by ray
+    assert torch.equal(coef2, loss_out[4:])
+    assert float((sums2 - sums).abs().max()) <= 1e-9 * float(sums.abs().max())
+    count = int(ws[:2].view(torch.int64)[0])
+    live = (d_raw_ref.view(-1, 4) != 0).any(1)
+    assert count == int(live.sum())
+    lst = ws[4:4 + count].long()
+    assert torch.equal(torch.sort(lst).values, torch.nonzero(live).view(-1))
+    ray_of = lst // S                                               # a ray's points are adjacent and ascending
+    same = ray_of[1:] == ray_of[:-1]
+    assert bool((lst[1:][same] > lst[:-1][same]).all())
+    assert int((ray_of[1:] != ray_of[:-1]).sum()) + 1 == int(torch.unique(ray_of).numel())
+    # and the per-point backward takes that list as it is
+    tb, w = fw[0].detach(), tuple(x.detach() for x in fw[1:])
+    ref = ops.points_backward(spec.scene(), tb, w, mask, d_raw_ref.view(-1, 4), rays=(rays_o, rays_d, z))
+    got = ops.points_backward(spec.scene(), tb, w, mask, d_raw.view(-1, 4), rays=(rays_o, rays_d, z), ready_list=ws)
+    util.assert_close(got[0], ref[0], 'd_table', 1e-5)
+    for a_, b_ in zip(got[1], ref[1]):
+        util.assert_close(a_, b_, 'dW', 1e-5)
+    util.assert_close(got[2][0], ref[2][0], 'd_rays_o', 1e-5)
+    util.assert_close(got[2][1], ref[2][1], 'd_rays_d', 1e-5)
 
 
 @pytest.mark.gpu
