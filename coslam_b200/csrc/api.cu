@@ -235,6 +235,40 @@ int cb200_pose_params(const float* c2w, int64_t n_poses, int32_t n_rot, float* r
     return cuda_result(cb200::launch_pose_params(c2w, n_poses, n_rot, rot, trans, (cudaStream_t)stream), "pose_params");
 }
 
+int cb200_track_rays_sample(const cb200_render_cfg* cfg, const float* kf_rays, const float* c2w, const float* lin_uniform,
+                            const float* lin_guided, const float* lin_nodepth, const float* noise, uint64_t seed, const uint64_t* seed_dev,
+                            int64_t n_rays, float* rays_o, float* rays_d, float* target_rgb, float* target_d, float* z_vals, int64_t* counts,
+                            void* stream) {
+    CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
+    const int S = (int)(cfg->n_uniform + cfg->n_guided);
+    CB_REQUIRE(cfg->n_guided >= 1 && S <= 256, "n_samples_d + n_range_d = %d must be in [1,256] with n_range_d >= 1", S);
+    CB_REQUIRE(n_rays >= 0, "negative ray count");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(kf_rays && c2w && rays_o && rays_d && target_rgb && target_d && z_vals && lin_guided && lin_nodepth &&
+                   (cfg->n_uniform == 0 || lin_uniform),
+               "track_rays_sample: NULL buffer");
+    cb200::SampleArgs a{};
+    a.lin_uniform = lin_uniform; a.lin_guided = lin_guided; a.lin_nodepth = lin_nodepth;
+    a.noise = noise; a.seed = seed; a.seed_dev = reinterpret_cast<const unsigned long long*>(seed_dev); a.n_rays = n_rays; a.z_vals = z_vals;
+    a.counts = reinterpret_cast<unsigned long long*>(counts);
+    a.n_uniform = (int)cfg->n_uniform; a.n_guided = (int)cfg->n_guided; a.perturb = (int)cfg->perturb;
+    a.trunc_sc = cfg->trunc_sc; a.depth_trunc = cfg->depth_trunc;
+    return cuda_result(cb200::launch_track_rays_sample(a, kf_rays, c2w, rays_o, rays_d, target_rgb, target_d, (cudaStream_t)stream),
+                       "track_rays_sample");
+}
+
+int cb200_track_pose_update(const float* kf_rays, const float* d_rays_o, const float* d_rays_d, int64_t n_rays, const cb200_track_step* s,
+                            uint32_t* ticket, uint64_t* noise_counter, void* stream) {
+    CB_REQUIRE(s != nullptr && kf_rays && d_rays_o && d_rays_d && ticket && n_rays >= 1, "track_pose_update: NULL argument");
+    CB_REQUIRE(s->rot && s->trans && s->adam && s->step && s->losses && s->d_c2w && s->c2w && s->best_loss && s->best_c2w && s->last_loss &&
+                   s->last_c2w && s->patience && s->alive,
+               "track_pose_update: NULL buffer in the step block");
+    CB_REQUIRE(s->n_rot == 3 || s->n_rot == 4, "track_pose_update: n_rot must be 3 (axis-angle) or 4 (quaternion)");
+    return cuda_result(cb200::launch_track_pose_update(kf_rays, d_rays_o, d_rays_d, n_rays, *s, ticket,
+                                                       reinterpret_cast<unsigned long long*>(noise_counter), (cudaStream_t)stream),
+                       "track_pose_update");
+}
+
 int cb200_track_init(const float* c2w_init, const cb200_track_step* s, void* stream) {
     CB_REQUIRE(c2w_init != nullptr && s != nullptr, "track_init: NULL argument");
     CB_REQUIRE(s->rot && s->trans && s->adam && s->step && s->c2w && s->patience && s->alive, "track_init: NULL buffer");
@@ -554,7 +588,8 @@ int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float*
 
 int cb200_render_loss_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb, const float* target_d,
                           int64_t n_rays, int64_t n_samples, const int64_t* counts, int64_t n_rays_total, const cb200_loss_grads* g_loss,
-                          double* loss_sums, float* coef, float* d_raw, void* list_workspace, size_t list_workspace_bytes, void* stream) {
+                          double* loss_sums, float* coef, float* d_raw, void* list_workspace, size_t list_workspace_bytes,
+                          int list_count_is_zero, void* stream) {
     cb200::RenderArgs a{};
     if (int rc = fill_render_args(a, cfg, raw, z_vals, target_rgb, target_d, n_rays, n_samples)) return rc;
     if (n_rays == 0) return 0;
@@ -573,7 +608,7 @@ int cb200_render_loss_bwd(const cb200_render_cfg* cfg, const float* raw, const f
         list = reinterpret_cast<uint32_t*>(count + 2);
     }
     return cuda_result(cb200::launch_render_loss_bwd(a, reinterpret_cast<const unsigned long long*>(counts), n_rays_total, list, count, coef,
-                                                     (cudaStream_t)stream),
+                                                     list_count_is_zero, (cudaStream_t)stream),
                        "render_loss_bwd");
 }
 

@@ -138,7 +138,11 @@ cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st);
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st);
 cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st);
 cudaError_t launch_render_loss_bwd(const RenderArgs& r, const unsigned long long* counts, long long n_rays_total, uint32_t* list,
-                                   unsigned long long* list_count, float* coef_out, cudaStream_t st);
+                                   unsigned long long* list_count, float* coef_out, int count_is_zero, cudaStream_t st);
+cudaError_t launch_track_rays_sample(const SampleArgs& a, const float* kf_rays, const float* c2w, float* rays_o, float* rays_d, float* target_rgb,
+                                     float* target_d, cudaStream_t st);
+cudaError_t launch_track_pose_update(const float* kf_rays, const float* d_rays_o, const float* d_rays_d, long long n, const cb200_track_step& s,
+                                     unsigned* ticket, unsigned long long* noise_counter, cudaStream_t st);
 cudaError_t launch_loss_finish(const double* sums, const long long* counts, long long n_rays_total, long long n_samples,
                                float* losses, float* coef, cudaStream_t st);
 cudaError_t launch_points_fwd(const PointsArgs& a, cudaStream_t st);

@@ -49,6 +49,63 @@ __global__ void __launch_bounds__(kRayWarps * 32) sample_rays_kernel(SampleArgs 
     }
 }
 
+// Tracking iteration: rays of the frame's sampled pixels from the current pose (coslam.py:546-547; assemble.cu's arithmetic for one
+// pose) and their depth-guided samples in one launch -- the warp that samples a ray also rotates its direction.
+struct TrackSampleArgs {
+    SampleArgs s;                  // target_d = the [N] buffer written here
+    const float* kf_rays;          // [N,7] camera-frame direction, rgb, depth
+    const float* c2w;              // [16]
+    float *rays_o, *rays_d, *target_rgb, *target_d;
+};
+
+__global__ void __launch_bounds__(kRayWarps * 32) track_rays_sample_kernel(TrackSampleArgs t) {
+    extern __shared__ float smem[];
+    const SampleArgs& a = t.s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int S = a.n_uniform + a.n_guided;
+    float* row = smem + warp * S;
+    float* lin_u = smem + kRayWarps * S;
+    float* lin_g = lin_u + a.n_uniform;
+    float* lin_n = lin_g + a.n_guided;
+    for (int i = threadIdx.x; i < a.n_uniform; i += blockDim.x) lin_u[i] = a.lin_uniform[i];
+    for (int i = threadIdx.x; i < a.n_guided; i += blockDim.x) {
+        lin_g[i] = a.lin_guided[i];
+        lin_n[i] = a.lin_nodepth[i];
+    }
+    float T[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) T[i] = t.c2w[i];
+    __syncthreads();
+    unsigned n_front = 0, n_sdf = 0, n_valid = 0;
+    const uint64_t seed = a.seed + (a.seed_dev ? *a.seed_dev : 0ull);
+    for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
+        const float* r = t.kf_rays + ray * 7;
+        if (lane < 3) {
+            const float d0 = r[0], d1 = r[1], d2 = r[2];
+            // products rounded separately, summed left to right: what torch.sum over the last axis of 3 does
+            t.rays_d[ray * 3 + lane] = __fadd_rn(__fadd_rn(__fmul_rn(d0, T[lane * 4 + 0]), __fmul_rn(d1, T[lane * 4 + 1])), __fmul_rn(d2, T[lane * 4 + 2]));
+            t.rays_o[ray * 3 + lane] = T[lane * 4 + 3];
+            t.target_rgb[ray * 3 + lane] = r[3 + lane];
+        }
+        if (lane == 0) t.target_d[ray] = r[6];
+        __syncwarp();
+        sample_one_ray(a, ray, lane, row, lin_u, lin_g, lin_n, seed, n_front, n_sdf, n_valid);
+    }
+    if (a.counts) {
+        __shared__ unsigned red[3][kRayWarps];
+        n_front = __reduce_add_sync(0xffffffffu, n_front);
+        n_sdf = __reduce_add_sync(0xffffffffu, n_sdf);
+        n_valid = __reduce_add_sync(0xffffffffu, n_valid);
+        if (lane == 0) { red[0][warp] = n_front; red[1][warp] = n_sdf; red[2][warp] = n_valid; }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            unsigned long long c = 0;
+            for (int w = 0; w < kRayWarps; ++w) c += red[threadIdx.x][w];
+            if (c) atomicAdd(a.counts + threadIdx.x, c);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // rendering forward / backward (per-ray bodies: render_ray.cuh)
 // ------------------------------------------------------------------------------------------------------------------
@@ -395,6 +452,15 @@ cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st) {
     importance_sample_kernel<<<ray_grid(a.n_rays), kRayWarps * 32, smem, st>>>(a);
     return cudaGetLastError();
 }
+cudaError_t launch_track_rays_sample(const SampleArgs& a, const float* kf_rays, const float* c2w, float* rays_o, float* rays_d, float* target_rgb,
+                                     float* target_d, cudaStream_t st) {
+    const int S = a.n_uniform + a.n_guided;
+    const size_t smem = sizeof(float) * (size_t)(kRayWarps * S + a.n_uniform + 2 * a.n_guided);
+    TrackSampleArgs t{a, kf_rays, c2w, rays_o, rays_d, target_rgb, target_d};
+    t.s.target_d = target_d;
+    track_rays_sample_kernel<<<ray_grid(a.n_rays), kRayWarps * 32, smem, st>>>(t);
+    return cudaGetLastError();
+}
 cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st) {
     const int S = a.n_uniform + a.n_guided;
     const size_t smem = sizeof(float) * (size_t)(kRayWarps * S + a.n_uniform + 2 * a.n_guided);
@@ -430,8 +496,8 @@ cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st) {
     return cudaGetLastError();
 }
 cudaError_t launch_render_loss_bwd(const RenderArgs& r, const unsigned long long* counts, long long n_rays_total, uint32_t* list,
-                                   unsigned long long* list_count, float* coef_out, cudaStream_t st) {
-    if (list_count) {
+                                   unsigned long long* list_count, float* coef_out, int count_is_zero, cudaStream_t st) {
+    if (list_count && !count_is_zero) {
         cudaError_t e = cudaMemsetAsync(list_count, 0, sizeof(unsigned long long), st);
         if (e != cudaSuccess) return e;
     }

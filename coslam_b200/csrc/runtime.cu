@@ -125,7 +125,7 @@ int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
     const int64_t n_total = p->n_rays_total > 0 ? p->n_rays_total : n;
     if (fused_loss_head(p)) {
         CB_TRY(cb200_render_loss_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, counts, n_total, &p->loss_w, sums,
-                                     p->loss_out + 4, p->d_raw, p->bwd_ws, p->bwd_ws_bytes, stream));
+                                     p->loss_out + 4, p->d_raw, p->bwd_ws, p->bwd_ws_bytes, 0, stream));
         CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask,
                                 p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, 0, stream));
     } else {

@@ -160,6 +160,61 @@ cudaError_t launch_smooth_points(int n, float vox, const float* jitter, const fl
     return cudaGetLastError();
 }
 
+// Tracking iteration: dL/d c2w of the ONE pose all rays share (assemble.cu's segment sum for a single slot) and, in the CTA that
+// finishes last (ticket), the single-thread pose update -- two launches of the iteration in one.  s.d_c2w [16] and *ticket are
+// zero on entry; the noise counter of the device Philox stream (may be NULL) advances by one.
+__global__ void __launch_bounds__(256) track_pose_update_kernel(const float* kf_rays, const float* d_rays_o, const float* d_rays_d, long long n,
+                                                                cb200_track_step s, unsigned* ticket, unsigned long long* noise_counter) {
+    __shared__ float red[12][8];
+    __shared__ bool last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float v[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) v[k] = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float d[3] = {kf_rays[i * 7 + 0], kf_rays[i * 7 + 1], kf_rays[i * 7 + 2]};
+#pragma unroll
+        for (int row = 0; row < 3; ++row) {
+            const float gd = d_rays_d[i * 3 + row], go = d_rays_o[i * 3 + row];
+            v[row * 4 + 0] = fmaf(gd, d[0], v[row * 4 + 0]);
+            v[row * 4 + 1] = fmaf(gd, d[1], v[row * 4 + 1]);
+            v[row * 4 + 2] = fmaf(gd, d[2], v[row * 4 + 2]);
+            v[row * 4 + 3] += go;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+        if (lane == 0) red[k][warp] = v[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        float t = 0.f;
+        for (int w = 0; w < 8; ++w) t += red[threadIdx.x][w];
+        atomicAdd(const_cast<float*>(s.d_c2w) + threadIdx.x, t);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+        if (last) {
+            __threadfence();
+            track_update_step(s, s.first_iter != 0);
+            if (noise_counter) *noise_counter += 1ull;
+        }
+    }
+}
+
+cudaError_t launch_track_pose_update(const float* kf_rays, const float* d_rays_o, const float* d_rays_d, long long n, const cb200_track_step& s,
+                                     unsigned* ticket, unsigned long long* noise_counter, cudaStream_t st) {
+    long long blocks = (n + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 64) blocks = 64;
+    track_pose_update_kernel<<<(unsigned)blocks, 256, 0, st>>>(kf_rays, d_rays_o, d_rays_d, n, s, ticket, noise_counter);
+    return cudaGetLastError();
+}
+
 __global__ void pose_params_kernel(const float* c2w, long long n, int n_rot, float* rot, float* trans) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;

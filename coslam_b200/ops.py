@@ -426,12 +426,14 @@ def _render_backward(spec, raw, z, target_rgb, target_d, g_losses, coef, g_rgb, 
     return d_raw
 
 
-def render_loss_backward(spec, raw, z, target_rgb, target_d, counts, loss_w, loss_sums, n_rays_total=None, list_ws=None, coef=None):
+def render_loss_backward(spec, raw, z, target_rgb, target_d, counts, loss_w, loss_sums, n_rays_total=None, list_ws=None, coef=None,
+                         list_count_is_zero=False, d_raw=None):
     """cb200_render_loss_bwd: loss-head forward (sums) and backward (d_raw) of every ray in one launch, with the list of the points
     whose d_raw is non-zero written into `list_ws` (int32 tensor of cb200_points_bwd_workspace bytes) for points_backward(ready_list=).
     counts: the batch-global int64 [3] mask counts of the sampling; loss_w: four device scalars (or None)."""
     n, s = z.shape
-    d_raw = torch.empty((n, s, 4), dtype=torch.float32, device=z.device)
+    if d_raw is None:
+        d_raw = torch.empty((n, s, 4), dtype=torch.float32, device=z.device)
     lg = LossGrads()
     for name, g in zip(('rgb', 'depth', 'sdf', 'fs'), loss_w):
         if g is not None:
@@ -440,7 +442,7 @@ def render_loss_backward(spec, raw, z, target_rgb, target_d, counts, loss_w, los
                                             ctypes.c_int64(n), ctypes.c_int64(s), ptr(counts), ctypes.c_int64(n_rays_total or n),
                                             ctypes.byref(lg), ptr(loss_sums), ptr(coef), ptr(d_raw), ptr(list_ws),
                                             ctypes.c_size_t(list_ws.numel() * list_ws.element_size() if list_ws is not None else 0),
-                                            stream()), 'render_loss_bwd')
+                                            1 if list_count_is_zero else 0, stream()), 'render_loss_bwd')
     return d_raw
 
 

@@ -81,13 +81,24 @@ class FrameTracker(object):
             self.ray_idx = torch.arange(n, dtype=torch.int64, device=dev)
             self.pose_slot = torch.zeros(n, dtype=torch.int64, device=dev)
             self.rays_o, self.rays_d = torch.zeros((n, 3), **f32), torch.zeros((n, 3), **f32)
-            # everything an iteration starts from zero, cleared by ONE fill: step workspace (8 doubles) | dL/d c2w (16 floats) |
-            # coarse-pass loss sums (4 doubles) | pad to 256 bytes | dL/d rays_o, dL/d rays_d [2, n, 3]
-            self.zbytes = torch.zeros(256 + 24 * n, dtype=torch.uint8, device=dev)
-            self.zbuf = self.zbytes[:128].view(torch.float64)
+            # everything an iteration starts from zero, cleared by ONE fill: dL/d rays_o, dL/d rays_d [2, n, 3] (rounded up to 256 bytes) |
+            # a 256-byte header: step workspace (8 doubles: 4 counts, 4 loss sums) | dL/d c2w (16 floats) | coarse-pass loss sums
+            # (4 doubles) | ticket of cb200_track_pose_update | ... | count of the live-point list in its last 16 bytes.  The list
+            # itself follows the header (cb200_points_bwd_workspace layout: count, pad, indices) and is not cleared.
+            S_all = model.spec.n_samples + self.n_imp
+            R = (24 * n + 255) // 256 * 256
+            self.zbytes = torch.zeros(R + 256 + 4 * n * S_all, dtype=torch.uint8, device=dev)
+            self.zclear = self.zbytes[:R + 256]
+            hdr = self.zbytes[R:R + 256]
+            self.zbuf = hdr[:128].view(torch.float64)
             self.d_c2w = self.zbuf[8:].view(torch.float32)
-            self.sums0 = self.zbytes[128:160].view(torch.float64)
-            self.d_rays = self.zbytes[256:].view(torch.float32).view(2, n, 3)
+            self.sums0 = hdr[128:160].view(torch.float64)
+            self.ticket = hdr[160:164].view(torch.int32)
+            self.d_rays = self.zbytes[:24 * n].view(torch.float32).view(2, n, 3)
+            self._list_ws = self.zbytes[R + 240:].view(torch.int32)
+            self.z = torch.zeros((n, model.spec.n_samples), **f32)
+            self.raw, self.d_raw = torch.zeros((n * model.spec.n_samples, 4), **f32), torch.zeros((n, model.spec.n_samples, 4), **f32)
+            self.mask = torch.zeros((n * model.spec.n_samples, 2), dtype=torch.int32, device=dev)
             self.loss_out = torch.zeros(8, **f32)                                   # 4 losses | 4 d loss / d sum
             self.w_dev = torch.tensor(self.loss_w, **f32).unbind(0)
             self.g_rot = torch.zeros(nr, **f32)
@@ -95,7 +106,6 @@ class FrameTracker(object):
             self._kf7_host = torch.zeros((n, 7), dtype=torch.float32).pin_memory()
             self._steps = [self._track_step(first) for first in (True, False)]
             self._steps_own = [self._track_step(first, own_losses=True) for first in (True, False)]
-            self._list_ws = None
         can_persist = self.fused and self.use_graph and self.n_imp == 0
         if persistent and not can_persist:
             raise NotImplementedError('FrameTracker(persistent=True) needs fused=True, use_graph=True (device noise) and n_importance 0')
@@ -123,12 +133,42 @@ class FrameTracker(object):
         """Pose parameters of the initial matrix + a fresh Adam / patience state, on the device (cb200_track_init)."""
         check(_lib.load().cb200_track_init(ptr(self.c2w_init), ctypes.byref(self._steps[0]), stream()), 'track_init')
 
-    def _iteration_fused(self, k):
+    def _iteration_lean(self, k):
+        """Six launches: fill | rays from the pose + sampling | per-point forward | rendering, loss sums, d_raw and live-point list |
+        per-point backward over the list | pose-gradient sum + pose update (losses, bookkeeping, Adam, next c2w, noise counter)."""
         lib, m, n = _lib.load(), self.model, self.n_rays
         spec = m.spec
         fw = m._fused()
         tb, w = fw[0].detach(), tuple(x.detach() for x in fw[1:])
-        self.zbytes.zero_()
+        self.zclear.zero_()
+        ws = self.zbuf[:8]
+        counts = ws[:4].view(torch.int64)
+        td = self.target_d.view(-1)
+        seed = m._noise(n, spec.n_samples, self.device)[1] if spec.perturb else 0
+        counter = m._noise_counter
+        lin_u, lin_g, lin_n = spec.linspaces(self.device)
+        check(lib.cb200_track_rays_sample(ctypes.byref(spec.render_cfg()), ptr(self.kf7), ptr(self.c2w), ptr(lin_u), ptr(lin_g), ptr(lin_n),
+                                          None, ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ptr(counter), ctypes.c_int64(n), ptr(self.rays_o),
+                                          ptr(self.rays_d), ptr(self.target_s), ptr(td), ptr(self.z), ptr(counts), stream()),
+              'track_rays_sample')
+        rays = (self.rays_o, self.rays_d, self.z)
+        ops.points_forward(spec.scene(), tb, w, rays=rays, out=(self.raw, self.mask))
+        ops.render_loss_backward(spec, self.raw, self.z, self.target_s, td, counts, self.w_dev, ws[4:8], list_ws=self._list_ws,
+                                 list_count_is_zero=True, d_raw=self.d_raw)
+        ops.points_backward(spec.scene(), tb, w, self.mask, self.d_raw, rays=rays, accumulate=(None, None, self.d_rays),
+                            ready_list=self._list_ws)
+        check(lib.cb200_track_pose_update(ptr(self.kf7), ptr(self.d_rays[0]), ptr(self.d_rays[1]), ctypes.c_int64(n),
+                                          ctypes.byref(self._steps_own[0 if k == 0 else 1]), ptr(self.ticket), ptr(counter), stream()),
+              'track_pose_update')
+
+    def _iteration_fused(self, k):
+        lib, m, n = _lib.load(), self.model, self.n_rays
+        spec = m.spec
+        if self.n_imp == 0 and lib.cb200_get_decoder() == 1 and not (spec.perturb and m.noise_mode == 'host'):
+            return self._iteration_lean(k)
+        fw = m._fused()
+        tb, w = fw[0].detach(), tuple(x.detach() for x in fw[1:])
+        self.zclear.zero_()
         ws = self.zbuf[:8]
         td = self.target_d.view(-1)
         check(lib.cb200_assemble_rays_fwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(self.c2w), ctypes.c_int64(n),
@@ -157,10 +197,8 @@ class FrameTracker(object):
         if coarse is None and lib.cb200_get_decoder() == 1:
             # rendering, loss sums, d_raw and the live-point list of every ray in ONE launch: d loss / d sum needs the mask counts only,
             # which the sampling produced; the losses themselves are taken from the sums inside cb200_track_update
-            if self._list_ws is None or self._list_ws.numel() * 4 < lib.cb200_points_bwd_workspace(ctypes.c_int64(n * z.shape[1])):
-                self._list_ws = torch.empty((int(lib.cb200_points_bwd_workspace(ctypes.c_int64(n * z.shape[1]))) + 3) // 4,
-                                            dtype=torch.int32, device=self.device)
-            d_raw = ops.render_loss_backward(spec, raw, z, self.target_s, td, counts, self.w_dev, ws[4:8], list_ws=self._list_ws)
+            d_raw = ops.render_loss_backward(spec, raw, z, self.target_s, td, counts, self.w_dev, ws[4:8], list_ws=self._list_ws,
+                                             list_count_is_zero=True)
             ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, accumulate=into, ready_list=self._list_ws)
             step = self._steps_own[0 if k == 0 else 1]
         else:

@@ -192,6 +192,18 @@ int cb200_track_update(const cb200_track_step* step, void* stream);
  * c2w [n,4,4] -> rot [n, n_rot] (axis-angle, or the quaternion with non-negative real part), trans [n,3] */
 int cb200_pose_params(const float* c2w, int64_t n_poses, int32_t n_rot, float* rot, float* trans, void* stream);
 
+/* Two fusions of the tracking iteration (coslam.py:546-547 + model/scene_rep.py:227-255, and optimization/utils.py + coslam.py:552-573):
+ * cb200_track_rays_sample = cb200_assemble_rays_fwd for ONE pose c2w [16] over kf_rays [N,7] (rays_o, rays_d, target_rgb [N,3],
+ *   target_d [N] out) + cb200_sample_rays on those targets (z_vals, counts; noise / seed / seed_dev as there), one launch;
+ * cb200_track_pose_update = cb200_assemble_rays_bwd for that pose (step->d_c2w [16] +=, zero on entry) + cb200_track_update in the
+ *   CTA that finishes last (*ticket: uint32, zero on entry) + *noise_counter += 1 (may be NULL), one launch. */
+int cb200_track_rays_sample(const cb200_render_cfg* cfg, const float* kf_rays, const float* c2w, const float* lin_uniform,
+                            const float* lin_guided, const float* lin_nodepth, const float* noise, uint64_t seed,
+                            const uint64_t* seed_dev, int64_t n_rays, float* rays_o, float* rays_d, float* target_rgb,
+                            float* target_d, float* z_vals, int64_t* counts, void* stream);
+int cb200_track_pose_update(const float* kf_rays, const float* d_rays_o, const float* d_rays_d, int64_t n_rays,
+                            const cb200_track_step* step, uint32_t* ticket, uint64_t* noise_counter, void* stream);
+
 /* Fresh per-frame tracking state from an initial camera-to-world matrix c2w_init [16] (device): the pose parameters the reference
  * derives on the host with pytorch3d (optimization/utils.py:23-28 matrix_to_axis_angle = quaternion_to_axis_angle(matrix_to_quaternion),
  * coslam.py:276-283; n_rot == 4: the quaternion with non-negative real part), zero Adam moments / step / patience, alive = 1, and
@@ -342,12 +354,13 @@ int cb200_render_bwd(const cb200_render_cfg* cfg, const float* raw, const float*
  * depends only on the batch-global mask counts `counts` [3] (cb200_sample_rays / cb200_importance_sample), so no cb200_loss_finish
  * has to run in between; coef [4] (may be NULL) receives those normalisers.  n_rays_total: rays of the whole batch (all ranks).
  * list_workspace (may be NULL): cb200_points_bwd_workspace(N * S) bytes that receive the list of the points with non-zero d_raw;
- * pass the same pointer to cb200_points_bwd with workspace_bytes = 0 and it skips its own compaction pass.
+ * pass the same pointer to cb200_points_bwd with workspace_bytes = 0 and it skips its own compaction pass;
+ * list_count_is_zero != 0: the caller has cleared the first 8 bytes of the workspace already (no memset is issued).
  * Replaces cb200_render_fwd(loss_sums) + cb200_loss_finish + cb200_render_bwd (+ the compaction) of model/scene_rep.py:311-338 in those loops. */
 int cb200_render_loss_bwd(const cb200_render_cfg* cfg, const float* raw, const float* z_vals, const float* target_rgb,
                           const float* target_d, int64_t n_rays, int64_t n_samples, const int64_t* counts,
                           int64_t n_rays_total, const cb200_loss_grads* g_loss, double* loss_sums, float* coef, float* d_raw,
-                          void* list_workspace, size_t list_workspace_bytes, void* stream);
+                          void* list_workspace, size_t list_workspace_bytes, int list_count_is_zero, void* stream);
 
 /* ---- native iteration runtime of global_BA (coslam.py:336-390) ------------------------------------------------------ */
 
