@@ -56,6 +56,7 @@ class BundleAdjuster(object):
         self.world = dist.get_world_size(group) if group is not None else 1
         self.rank = dist.get_rank(group) if group is not None else 0
         self._flat = None
+        self._pin, self._pin_sent = None, None     # pinned staging block of a call's index draws, event of its upload
         self.phase_times = None                   # set to [] to collect CUDA events per sharded iteration: forward | AR-1 | backward | AR-2 | optimise
         bb = model.bounding_box.detach().float().cpu()
         self._lo = (ctypes.c_float * 3)(*bb[:, 0].tolist())
@@ -95,9 +96,24 @@ class BundleAdjuster(object):
                     smooth.append((torch.rand(3).to(offset_max) * offset_max + t['smooth_margin'], torch.rand((1, 1, 1, 3)).reshape(3)))
             return idx_g, slot_g, idx_c, (torch.stack(noise).to(dev, non_blocking=True) if host_noise else None), smooth
         draws = sample_ranges([(n_store, bs), (kf.H * kf.W, n_cur)] * iters)
-        idx_g = [torch.from_numpy(d) for d in draws[0::2]]
-        idx_c = [torch.from_numpy(d) for d in draws[1::2]]
-        slot_g = [(kf.frame_ids[i // kf.num_rays_to_save] // every).to(torch.int64) for i in idx_g]     # keyframe.py:103, coslam.py:345
+        # one pinned block [ray indices [iters, bs] | keyframe slots [iters, bs] | current-frame pixels [iters, n_cur]] filled with numpy
+        # over all iterations at once and sent in ONE copy (was ~60 small torch ops and three pageable uploads per call)
+        key = (iters, bs, n_cur)
+        if self._pin is None or self._pin[0] != key:
+            self._pin = (key, torch.empty(iters * (2 * bs + n_cur), dtype=torch.int64).pin_memory())
+        elif self._pin_sent is not None:
+            self._pin_sent.synchronize()                             # the previous call's upload has left the staging block
+        pin = self._pin[1].numpy()
+        pg, ps, pc = pin[:iters * bs].reshape(iters, bs), pin[iters * bs:2 * iters * bs].reshape(iters, bs), pin[2 * iters * bs:].reshape(iters, n_cur)
+        for it_ in range(iters):
+            pg[it_] = draws[2 * it_]
+            pc[it_] = draws[2 * it_ + 1]
+        ps[:] = kf.frame_ids.numpy()[pg // kf.num_rays_to_save] // every                                 # keyframe.py:103, coslam.py:345
+        all_dev = self._pin[1].to(self.device, non_blocking=True)
+        self._pin_sent = torch.cuda.Event()
+        self._pin_sent.record()
+        idx_g, slot_g = all_dev[:iters * bs].view(iters, bs), all_dev[iters * bs:2 * iters * bs].view(iters, bs)
+        idx_c = all_dev[2 * iters * bs:].view(iters, n_cur)
         for _ in range(iters):
             if host_noise:
                 noise.append(torch.rand((n_rays, n_samples)))                     # scene_rep.py:255
@@ -108,8 +124,7 @@ class BundleAdjuster(object):
                 offset = torch.rand(3).to(offset_max) * offset_max + t['smooth_margin']              # coslam.py:260
                 smooth.append((offset, torch.rand((1, 1, 1, 3)).reshape(3)))                         # coslam.py:262
         dev = self.device
-        up = lambda xs: torch.stack(xs).to(dev, non_blocking=True)
-        return up(idx_g), up(slot_g), up(idx_c), (up(noise) if host_noise else None), smooth
+        return idx_g, slot_g, idx_c, (torch.stack(noise).to(dev, non_blocking=True) if host_noise else None), smooth
 
     def _map_grads(self):
         """(table.grad, [dW1..dW4]) as zero-initialised persistent buffers of the caller's parameters."""
