@@ -814,6 +814,28 @@ def test_frame_tracker_graph_matches_eager_and_reference_loop(cfg_name):
     assert float((info_g['last_c2w'].cpu() - last_c2w[0]).abs().max()) <= 3e-4
 
 
+def test_one_launch_frame_kernel_matches_graph_loop_on_the_tum_shape():
+    """cb200_track_frame's third instantiation (5 dense levels, 85 samples per ray = 3 slots per lane: fr1_desk without importance samples)
+    against the graph-captured loop; the other two run in test_frame_tracker_graph_matches_eager_and_reference_loop."""
+    from coslam_b200.tracking import FrameTracker
+    cfg = synth.tum_desk_config(n_importance=0)
+    cfg['training']['perturb'] = 0.0
+    n_rays = 384
+    cfg['tracking']['sample'] = n_rays
+    probe = JointEncodingFor(cfg)
+    model = util.make_cuda_model(cfg, synth.table_init(probe.embed_fn.params.numel(), 'trained', seed=77), synth.decoder_init(seed=5), DEV)
+    dir_cam, rgb, depth, c2w0 = _tracking_case(cfg, n_rays)
+    graph = FrameTracker(model, cfg, device=DEV, use_graph=True)
+    est_g, info_g = graph.track(dir_cam, rgb, depth, c2w0)
+    est_g, best_g = est_g.clone(), float(info_g['best_loss'])
+    one = FrameTracker(model, cfg, device=DEV, use_graph=True, persistent=True)
+    est_p, info_p = one.track(dir_cam, rgb, depth, c2w0)
+    assert one.persistent and model.spec.n_samples == 85
+    assert float((est_p - est_g).abs().max()) <= 5e-5
+    assert abs(float(info_p['best_loss']) - best_g) <= 1e-4 * abs(best_g)
+    assert float((est_p.cpu() - c2w0).abs().max()) > 1e-4
+
+
 def test_frame_tracker_with_importance_samples_matches_autograd_loop():
     """This fork's TUM config (tum.yaml:89, n_importance 128): the autograd-free tracking iteration with the hierarchical pass
     (coarse render -> cb200_importance_sample -> fine render, coarse colour / depth terms added to the loss sums, two backward
