@@ -74,7 +74,7 @@ class BundleAdjuster(object):
             draws = sample_ranges([(kf.H * kf.W, n_cur)] * iters)
             idx_c = [torch.from_numpy((d % kf.H) * kf.W + d // kf.H) for d in draws]
             if host_noise:
-                noise = [torch.rand((n_rays, n_samples)) for _ in range(iters)]
+                noise = [ops.torch_rand_into(torch.empty((n_rays, n_samples))) for _ in range(iters)]
             dev = self.device
             empty = torch.zeros((iters, 0), dtype=torch.int64, device=dev)
             return empty, empty, torch.stack(idx_c).to(dev, non_blocking=True), \
@@ -89,7 +89,7 @@ class BundleAdjuster(object):
             slot_g = (kf.frame_ids.to(dev)[idx_g // kf.num_rays_to_save] // every).to(torch.int64)
             for _ in range(iters):
                 if host_noise:
-                    noise.append(torch.rand((n_rays, n_samples)))
+                    noise.append(ops.torch_rand_into(torch.empty((n_rays, n_samples))))
                 if self.smooth_w > 0 and smooth_on:
                     vol = self._bb[:, 1] - self._bb[:, 0]
                     offset_max = vol - (t['smooth_pts'] - 1) * t['smooth_vox'] - 2 * t['smooth_margin']
@@ -116,7 +116,7 @@ class BundleAdjuster(object):
         idx_c = all_dev[2 * iters * bs:].view(iters, n_cur)
         for _ in range(iters):
             if host_noise:
-                noise.append(torch.rand((n_rays, n_samples)))                     # scene_rep.py:255
+                noise.append(ops.torch_rand_into(torch.empty((n_rays, n_samples))))                     # scene_rep.py:255
             if self.smooth_w > 0 and smooth_on:
                 vol = self._bb[:, 1] - self._bb[:, 0]
                 n = t['smooth_pts']

@@ -155,6 +155,48 @@ class SceneSpec(object):
 
 
 # --------------------------------------------------------------------------------------------------------------------
+# host noise: torch.rand's CPU stream, bit for bit, from a tight loop (csrc/host_rng.cu)
+# --------------------------------------------------------------------------------------------------------------------
+
+def torch_rand_into(out):
+    """Fills the contiguous fp32 CPU tensor `out` with exactly the values `torch.rand(out.shape)` would draw from torch's default
+    CPU generator and leaves the generator in exactly the state that call would (model/scene_rep.py:255 draws its jitter this way)."""
+    if out.device.type != 'cpu' or out.dtype != torch.float32 or not out.is_contiguous():
+        raise ValueError('torch_rand_into: a contiguous fp32 CPU tensor')
+    st = torch.get_rng_state()
+    rc = _lib.load().cb200_host_torch_rand(ctypes.c_void_p(st.data_ptr()), ctypes.c_int64(out.numel()), ctypes.c_void_p(out.data_ptr()))
+    if rc != 0:                                    # a generator state the routine does not know: torch draws the same values itself
+        torch.rand(out.shape, out=out)
+        return out
+    torch.set_rng_state(st)
+    return out
+
+
+_PINNED = {}      # numel -> [[pinned buffer, event of its last upload] x 2, next]
+
+
+def host_uniform(shape, device):
+    """`torch.rand(shape).to(device)` (the reference's jitter, CPU generator + upload) through torch_rand_into and a pinned staging buffer."""
+    n = 1
+    for d in shape:
+        n *= int(d)
+    slot = _PINNED.get(n)
+    if slot is None:
+        slot = _PINNED[n] = [[torch.empty(n, dtype=torch.float32).pin_memory(), None], [torch.empty(n, dtype=torch.float32).pin_memory(), None], 0]
+        if len(_PINNED) > 8:                       # a handful of shapes in practice (tracking batch, mapping batch); do not hoard pinned memory
+            _PINNED.pop(next(iter(_PINNED)))
+    buf = slot[slot[2]]
+    slot[2] ^= 1
+    if buf[1] is not None:
+        buf[1].synchronize()                       # the upload that last used this buffer has finished
+    torch_rand_into(buf[0])
+    out = buf[0].view(shape).to(device, non_blocking=True)
+    buf[1] = torch.cuda.Event()
+    buf[1].record()
+    return out
+
+
+# --------------------------------------------------------------------------------------------------------------------
 # raw wrappers (no autograd)
 # --------------------------------------------------------------------------------------------------------------------
 

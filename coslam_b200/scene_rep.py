@@ -119,7 +119,7 @@ class JointEncoding(nn.Module):
 
     def _noise(self, n_rays, n_samples, device):
         if self.noise_mode == 'host':
-            return torch.rand((n_rays, n_samples)).to(device), 0       # CPU generator, model/scene_rep.py:255
+            return ops.host_uniform((n_rays, n_samples), device), 0    # torch.rand((N, S)).to(device): CPU generator, model/scene_rep.py:255
         if self._noise_counter is not None:                               # graph-captured loops: the step lives on the device
             return None, int(self.noise_seed) << 32
         self._step += 1

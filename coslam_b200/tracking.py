@@ -144,11 +144,11 @@ class FrameTracker(object):
         ws = self.zbuf[:8]
         counts = ws[:4].view(torch.int64)
         td = self.target_d.view(-1)
-        seed = m._noise(n, spec.n_samples, self.device)[1] if spec.perturb else 0
-        counter = m._noise_counter
+        noise, seed = m._noise(n, spec.n_samples, self.device) if spec.perturb else (None, 0)      # host mode: torch.rand's CPU stream, uploaded
+        counter = m._noise_counter if noise is None else None
         lin_u, lin_g, lin_n = spec.linspaces(self.device)
         check(lib.cb200_track_rays_sample(ctypes.byref(spec.render_cfg()), ptr(self.kf7), ptr(self.c2w), ptr(lin_u), ptr(lin_g), ptr(lin_n),
-                                          None, ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ptr(counter), ctypes.c_int64(n), ptr(self.rays_o),
+                                          ptr(noise), ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ptr(counter), ctypes.c_int64(n), ptr(self.rays_o),
                                           ptr(self.rays_d), ptr(self.target_s), ptr(td), ptr(self.z), ptr(counts), stream()),
               'track_rays_sample')
         rays = (self.rays_o, self.rays_d, self.z)
@@ -164,7 +164,7 @@ class FrameTracker(object):
     def _iteration_fused(self, k):
         lib, m, n = _lib.load(), self.model, self.n_rays
         spec = m.spec
-        if self.n_imp == 0 and lib.cb200_get_decoder() == 1 and not (spec.perturb and m.noise_mode == 'host'):
+        if self.n_imp == 0 and lib.cb200_get_decoder() == 1:
             return self._iteration_lean(k)
         fw = m._fused()
         tb, w = fw[0].detach(), tuple(x.detach() for x in fw[1:])

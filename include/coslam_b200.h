@@ -496,6 +496,12 @@ int cb200_points_bwd_noalloc(const cb200_scene* scene, const float* table, const
                              const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_rays_o,
                              float* d_rays_d, int sdf_only, void* stream);
 
+/* HOST routine: `n` fp32 uniforms exactly as `torch.rand(n)` draws them from torch's default CPU generator (model/scene_rep.py:255
+ * `torch.rand(z_vals.shape)`), on the caller's copy of the generator state: `state` = the 5 056 bytes of torch.get_rng_state(),
+ * updated in place (write it back with torch.set_rng_state and every later draw is unchanged).  at::mt19937 + the 24-bit
+ * uniform_real transformation in a tight loop instead of one virtual call per element.  Returns 0, or -1 for a state it does not understand. */
+int cb200_host_torch_rand(uint8_t* state, int64_t n, float* out);
+
 /* test hook for the bit-exact sample-position gate: pts [P,3] and normalised x [P,3] exactly as the fused
  * kernels compute them (model/scene_rep.py:258 and :186) */
 int cb200_debug_positions(const cb200_scene* scene, const float* rays_o, const float* rays_d, const float* z_vals,

@@ -141,3 +141,26 @@ def test_restatement_matches_unmodified_reference_live():
     for k in ('rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):
         util.assert_close(r[k], ret[k], k, 1e-5)
     util.assert_close(r['rgb'], ret['rgb'], 'rgb', 1e-5)
+
+
+def test_host_torch_rand_is_the_cpu_generators_stream():
+    """cb200_host_torch_rand (csrc/host_rng.cu) against torch.rand on torch's default CPU generator -- the stream the reference draws
+    its stratified jitter from (model/scene_rep.py:255): same values for any split into calls, same generator state afterwards (so
+    every later draw, uniform or normal, is unchanged), across block boundaries of the 624-word Mersenne-Twister state."""
+    import torch
+    from coslam_b200 import ops
+    for seed in (0, 1, 12345):
+        for sizes in ([1, 5, 623, 624, 625, 1000, 2304 * 43, 3], [1024 * 43] * 3, [624, 624, 1], [0, 7]):
+            torch.manual_seed(seed)
+            ref = [torch.rand(k) for k in sizes]
+            tail_ref, state_ref = torch.randn(9), torch.get_rng_state()
+            torch.manual_seed(seed)
+            got = [ops.torch_rand_into(torch.empty(k)) for k in sizes]
+            tail, state = torch.randn(9), torch.get_rng_state()
+            assert all(torch.equal(a, b) for a, b in zip(ref, got)), (seed, sizes)
+            assert torch.equal(tail, tail_ref) and torch.equal(state, state_ref)
+    torch.manual_seed(3)                                   # interleaved with normal draws (their cache lives in the same state block)
+    a, b, c = torch.randn(5), torch.rand(4, 25), torch.randn(3)
+    torch.manual_seed(3)
+    a2, b2, c2 = torch.randn(5), ops.torch_rand_into(torch.empty(4, 25)), torch.randn(3)
+    assert torch.equal(a, a2) and torch.equal(b, b2) and torch.equal(c, c2)
