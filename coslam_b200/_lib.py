@@ -177,6 +177,11 @@ def ptr(t):
 
 
 def stream():
+    """The current CUDA stream of the current device as a raw handle (called ~10 times per forward + backward: the raw query is
+    ~10x cheaper than building a torch.cuda.Stream object)."""
+    raw = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+    if raw is not None:
+        return ctypes.c_void_p(raw(torch.cuda.current_device()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
