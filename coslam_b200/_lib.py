@@ -91,11 +91,12 @@ class BaPlan(ctypes.Structure):
                 ('smooth_x', ctypes.c_void_p), ('smooth_f', ctypes.c_void_p), ('smooth_df', ctypes.c_void_p),
                 ('map_params', ctypes.c_void_p), ('n_map_params', ctypes.c_int64),
                 ('rot', ctypes.c_void_p), ('trans', ctypes.c_void_p), ('pose_adam', ctypes.c_void_p), ('n_free', ctypes.c_int64),
-                ('n_rot', ctypes.c_int32), ('lr_rot', ctypes.c_float), ('lr_trans', ctypes.c_float)]
+                ('n_rot', ctypes.c_int32), ('lr_rot', ctypes.c_float), ('lr_trans', ctypes.c_float),
+                ('rank', ctypes.c_void_p), ('new_list', ctypes.c_void_p), ('new_count', ctypes.c_void_p)]
 
 
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
-           'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update', 'cb200_track_frame', 'cb200_track_init', 'cb200_track_rays_sample', 'cb200_track_pose_update', 'cb200_pose_params', 'cb200_track_frame_workspace', 'cb200_pose_matrices', 'cb200_pose_adam', 'cb200_smooth_points', 'cb200_smooth_tv', 'cb200_ba_iteration', 'cb200_sizeof', 'cb200_host_random_sample', 'cb200_host_torch_rand', 'cb200_adam_multi',
+           'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_importance_sample_merge', 'cb200_merge_coarse', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update', 'cb200_track_frame', 'cb200_track_init', 'cb200_track_rays_sample', 'cb200_track_pose_update', 'cb200_pose_params', 'cb200_track_frame_workspace', 'cb200_pose_matrices', 'cb200_pose_adam', 'cb200_smooth_points', 'cb200_smooth_tv', 'cb200_ba_iteration', 'cb200_sizeof', 'cb200_host_random_sample', 'cb200_host_torch_rand', 'cb200_adam_multi',
            'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd', 'cb200_render_loss_bwd',
            'cb200_debug_positions', 'cb200_debug_gather_peak', 'cb200_points_bwd_noalloc', 'cb200_points_bwd_noalloc_max_points', 'cb200_selftest_mma', 'cb200_set_decoder',
            'cb200_get_decoder']

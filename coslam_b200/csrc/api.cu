@@ -406,9 +406,9 @@ int cb200_sample_rays(const cb200_render_cfg* cfg, const float* target_d, const 
     return cuda_result(cb200::launch_sample_rays(a, (cudaStream_t)stream), "sample_rays");
 }
 
-int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, const float* weights, const float* u, int64_t u_stride,
-                            const float* target_d, int64_t n_rays, int64_t n_samples, int64_t n_importance, float* z_out, float* z_std,
-                            int64_t* counts, void* stream) {
+static int importance_sample_impl(const cb200_render_cfg* cfg, const float* z_vals, const float* weights, const float* u, int64_t u_stride,
+                                  const float* target_d, int64_t n_rays, int64_t n_samples, int64_t n_importance, float* z_out, float* z_std,
+                                  int64_t* counts, int32_t* rank, uint32_t* new_list, uint64_t* new_count, void* stream) {
     CB_REQUIRE(cfg != nullptr, "render cfg is NULL");
     CB_REQUIRE(n_samples >= 3 && n_importance >= 1 && n_samples + n_importance <= 256,
                "importance_sample: need 3 <= n_samples, 1 <= n_importance, n_samples + n_importance <= 256 (got %lld + %lld)",
@@ -416,6 +416,8 @@ int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, co
     CB_REQUIRE(n_rays >= 0, "negative ray count");
     CB_REQUIRE(u_stride == 0 || u_stride == n_importance, "importance_sample: u_stride must be 0 or n_importance");
     CB_REQUIRE(counts == nullptr || target_d != nullptr, "importance_sample: counts need target_d");
+    CB_REQUIRE((new_list == nullptr) == (new_count == nullptr), "importance_sample: new_list and new_count go together");
+    CB_REQUIRE(new_list == nullptr || n_rays * (n_samples + n_importance) < (1ll << 32), "importance_sample: the point list indexes with 32 bits");
     if (n_rays == 0) return 0;
     CB_REQUIRE(z_vals && weights && u && z_out, "importance_sample: NULL buffer");
     cb200::ImportanceArgs a{};
@@ -423,7 +425,34 @@ int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, co
     a.n_samples = (int)n_samples; a.n_importance = (int)n_importance; a.z_out = z_out; a.z_std = z_std;
     a.counts = reinterpret_cast<unsigned long long*>(counts);
     a.trunc_sc = cfg->trunc_sc; a.depth_trunc = cfg->depth_trunc;
+    a.rank = rank; a.new_list = new_list; a.new_count = reinterpret_cast<unsigned long long*>(new_count);
     return cuda_result(cb200::launch_importance_sample(a, (cudaStream_t)stream), "importance_sample");
+}
+
+int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, const float* weights, const float* u, int64_t u_stride,
+                            const float* target_d, int64_t n_rays, int64_t n_samples, int64_t n_importance, float* z_out, float* z_std,
+                            int64_t* counts, void* stream) {
+    return importance_sample_impl(cfg, z_vals, weights, u, u_stride, target_d, n_rays, n_samples, n_importance, z_out, z_std, counts, nullptr,
+                                  nullptr, nullptr, stream);
+}
+
+int cb200_importance_sample_merge(const cb200_render_cfg* cfg, const float* z_vals, const float* weights, const float* u, int64_t u_stride,
+                                  const float* target_d, int64_t n_rays, int64_t n_samples, int64_t n_importance, float* z_out, float* z_std,
+                                  int64_t* counts, int32_t* rank, uint32_t* new_list, uint64_t* new_count, void* stream) {
+    CB_REQUIRE(rank != nullptr, "importance_sample_merge: rank is NULL");
+    return importance_sample_impl(cfg, z_vals, weights, u, u_stride, target_d, n_rays, n_samples, n_importance, z_out, z_std, counts, rank,
+                                  new_list, new_count, stream);
+}
+
+int cb200_merge_coarse(const int32_t* rank, int64_t n_rays, int64_t n_coarse, int64_t n_fine, const float* src, float* dst,
+                       const uint32_t* src_mask, uint32_t* dst_mask, int accumulate, void* stream) {
+    CB_REQUIRE(n_rays >= 0 && n_coarse >= 1 && n_fine >= n_coarse && n_fine <= 256, "merge_coarse: bad sizes");
+    if (n_rays == 0) return 0;
+    CB_REQUIRE(rank && src && dst, "merge_coarse: NULL buffer");
+    CB_REQUIRE((src_mask == nullptr) == (dst_mask == nullptr), "merge_coarse: the two masks go together");
+    return cuda_result(cb200::launch_merge_coarse(rank, n_rays, (int)n_coarse, (int)n_fine, src, dst, src_mask, dst_mask, accumulate,
+                                                  (cudaStream_t)stream),
+                       "merge_coarse");
 }
 
 static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,

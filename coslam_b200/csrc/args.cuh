@@ -60,6 +60,12 @@ struct ImportanceArgs {
     float* z_std;              // [N] or NULL
     unsigned long long* counts;
     float trunc_sc, depth_trunc;
+    // optional: where the samples went in the merged row.  The coarse samples keep their positions in space, so the fine pass need not
+    // evaluate them again: rank [N,S] = position of coarse sample s in z_out's row; new_list [N*I] = flat indices (ray * (S+I) + position)
+    // of the I new samples of every ray, new_count (device) = N * I -- a point list for the per-point forward
+    int32_t* rank;
+    uint32_t* new_list;
+    unsigned long long* new_count;
 };
 
 struct RenderArgs {
@@ -134,6 +140,8 @@ cudaError_t launch_lazy_prefix(const float* z_vals, const float* target_d, int64
 cudaError_t launch_lazy_resolve(const float* z_vals, const float* target_d, const float* raw, int64_t n_rays, int n_samples, float trunc_sc,
                                 int* k_done, uint32_t* list, unsigned long long* count, cudaStream_t st);
 cudaError_t launch_importance_sample(const ImportanceArgs& a, cudaStream_t st);
+cudaError_t launch_merge_coarse(const int32_t* rank, int64_t n_rays, int n_coarse, int n_fine, const float* src4, float* dst4, const uint32_t* src_mask,
+                                uint32_t* dst_mask, int accumulate, cudaStream_t st);
 cudaError_t launch_sample_rays(const SampleArgs& a, cudaStream_t st);
 cudaError_t launch_render_fwd(const RenderArgs& a, cudaStream_t st);
 cudaError_t launch_render_bwd(const RenderArgs& a, cudaStream_t st);

@@ -239,6 +239,7 @@ __global__ void __launch_bounds__(kRayWarps * 32) importance_sample_kernel(Impor
     float* cdf = zrow + S;                                           // [nb]
     float* samp = cdf + S;                                           // [I]  (one float of padding after cdf)
     unsigned n_front = 0, n_sdf = 0, n_valid = 0;
+    if (a.new_count && blockIdx.x == 0 && threadIdx.x == 0) *a.new_count = (unsigned long long)a.n_rays * (unsigned long long)I;
     for (int64_t ray = (int64_t)blockIdx.x * kRayWarps + warp; ray < a.n_rays; ray += (int64_t)gridDim.x * kRayWarps) {
         for (int s = lane; s < S; s += 32) zrow[s] = a.z_vals[ray * S + s];
         float part = 0.f;
@@ -288,6 +289,7 @@ __global__ void __launch_bounds__(kRayWarps * 32) importance_sample_kernel(Impor
                 pos = e;
 #pragma unroll 8
                 for (int j = 0; j < I; ++j) pos += samp[j] < v;
+                if (a.rank) a.rank[ray * S + e] = pos;
             } else {
                 const int i = e - S;
                 v = samp[i];
@@ -303,6 +305,7 @@ __global__ void __launch_bounds__(kRayWarps * 32) importance_sample_kernel(Impor
                 pos += lo;
             }
             a.z_out[ray * (S + I) + pos] = v;
+            if (a.new_list && e >= S) a.new_list[ray * I + (e - S)] = (uint32_t)(ray * (S + I) + pos);
             if (a.target_d) {
                 const bool front = v < front_edge, back = v > back_edge;
                 n_front += front;
@@ -444,6 +447,36 @@ cudaError_t launch_lazy_resolve(const float* z_vals, const float* target_d, cons
     if (e != cudaSuccess) return e;
     LazyArgs a{z_vals, target_d, raw, n_rays, n_samples, trunc_sc, k_done, list, count};
     lazy_resolve_kernel<<<ray_grid(n_rays), kRayWarps * 32, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+// The coarse samples of the hierarchical pass are a subset of the merged samples (same positions, hence the same network outputs):
+// copies (accumulate = 0) their raw / activation masks into the merged rows, or adds (accumulate = 1) the coarse pass's d_raw to the
+// merged rows' d_raw so that ONE per-point backward serves both passes.  Thread per coarse sample.
+__global__ void __launch_bounds__(256) merge_coarse_kernel(const int32_t* __restrict__ rank, int64_t n_rays, int S, int F, const float4* __restrict__ src,
+                                                           float4* dst, const uint2* __restrict__ src_mask, uint2* dst_mask, int accumulate) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rays * S) return;
+    const int64_t ray = i / S;
+    const int64_t j = ray * F + rank[i];
+    if (accumulate) {
+        const float4 a = src[i];
+        float4 b = dst[j];
+        b.x += a.x; b.y += a.y; b.z += a.z; b.w += a.w;
+        dst[j] = b;
+    } else {
+        dst[j] = src[i];
+        if (src_mask) dst_mask[j] = src_mask[i];
+    }
+}
+
+cudaError_t launch_merge_coarse(const int32_t* rank, int64_t n_rays, int n_coarse, int n_fine, const float* src4, float* dst4, const uint32_t* src_mask,
+                                uint32_t* dst_mask, int accumulate, cudaStream_t st) {
+    const int64_t total = n_rays * n_coarse;
+    if (total <= 0) return cudaSuccess;
+    merge_coarse_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(rank, n_rays, n_coarse, n_fine, reinterpret_cast<const float4*>(src4),
+                                                                         reinterpret_cast<float4*>(dst4), reinterpret_cast<const uint2*>(src_mask),
+                                                                         reinterpret_cast<uint2*>(dst_mask), accumulate);
     return cudaGetLastError();
 }
 

@@ -89,10 +89,22 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, bool do_rays, bool do_points,
         CB_TRY(cuda_rc(cudaMemsetAsync(p->sums0, 0, 4 * sizeof(double), st)));
         CB_TRY(cb200_render_fwd(p->render, p->raw0, p->z0, p->target_rgb, p->target_d, n, S0, nullptr, nullptr, nullptr, nullptr, nullptr,
                                 p->weights0, p->sums0, stream));
-        CB_TRY(cb200_importance_sample(p->render, p->z0, p->weights0, p->u + (p->u_stride ? it * n * I : 0), p->u_stride, p->target_d, n, S0, I,
-                                       p->z_vals, nullptr, counts, stream));
+        if (p->rank) {
+            // the coarse samples sit in the merged rows with the same positions, i.e. the same network outputs: evaluate the new
+            // samples only and take the coarse rows over
+            CB_TRY(cb200_importance_sample_merge(p->render, p->z0, p->weights0, p->u + (p->u_stride ? it * n * I : 0), p->u_stride, p->target_d, n,
+                                                 S0, I, p->z_vals, nullptr, counts, p->rank, p->new_list, p->new_count, stream));
+            CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0,
+                                    p->new_list, p->new_count, stream));
+            CB_TRY(cb200_merge_coarse(p->rank, n, S0, S, p->raw0, p->raw, p->act_mask0, p->act_mask, 0, stream));
+        } else {
+            CB_TRY(cb200_importance_sample(p->render, p->z0, p->weights0, p->u + (p->u_stride ? it * n * I : 0), p->u_stride, p->target_d, n, S0, I,
+                                           p->z_vals, nullptr, counts, stream));
+        }
     }
-    if (p->lazy_ws) {
+    if (I > 0 && p->rank) {
+        // (fine forward done above)
+    } else if (p->lazy_ws) {
         CB_TRY(cuda_rc(cudaMemsetAsync(p->raw, 0, sizeof(float) * 4 * n * S, st)));
         unsigned char* base = static_cast<unsigned char*>(p->lazy_ws);
         const uint64_t* count = reinterpret_cast<const uint64_t*>(base);
@@ -132,19 +144,22 @@ int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
         CB_TRY(cb200_loss_finish(sums, counts, n_total, S, p->loss_out, p->loss_out + 4, stream));
         CB_TRY(cb200_render_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, &p->loss_w, p->loss_out + 4, nullptr, nullptr,
                                 p->d_raw, stream));
+        if (I > 0) {                             // the coarse maps carry the colour and depth terms only
+            cb200_loss_grads lw = p->loss_w;
+            lw.sdf = nullptr;
+            lw.fs = nullptr;
+            CB_TRY(cb200_render_bwd(p->render, p->raw0, p->z0, p->target_rgb, p->target_d, n, S0, &lw, p->loss_out + 4, nullptr, nullptr, p->d_raw0,
+                                    stream));
+            if (p->rank)                         // ... on points the merged rows contain: one backward for both passes
+                CB_TRY(cb200_merge_coarse(p->rank, n, S0, S, p->d_raw0, p->d_raw, nullptr, nullptr, 1, stream));
+        }
         CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask,
                                 p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes,
                                 stream));
-    }
-    if (I > 0) {                                 // the coarse maps carry the colour and depth terms only
-        cb200_loss_grads lw = p->loss_w;
-        lw.sdf = nullptr;
-        lw.fs = nullptr;
-        CB_TRY(cb200_render_bwd(p->render, p->raw0, p->z0, p->target_rgb, p->target_d, n, S0, &lw, p->loss_out + 4, nullptr, nullptr, p->d_raw0,
-                                stream));
-        CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z0, n, S0, p->d_raw0, nullptr, p->act_mask0,
-                                p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, p->bwd_ws_bytes,
-                                stream));
+        if (I > 0 && !p->rank)
+            CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z0, n, S0, p->d_raw0, nullptr, p->act_mask0,
+                                    p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws,
+                                    p->bwd_ws_bytes, stream));
     }
     if (p->d_rays) {
         if (!p->d_poses) return -1;

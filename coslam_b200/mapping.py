@@ -305,6 +305,13 @@ class BundleAdjuster(object):
             P.n_importance, P.z0, P.raw0, P.act_mask0, P.weights0, P.d_raw0 = I, dp(z0), dp(raw0), dp(mask0), dp(w0), dp(d_raw0)
             P.u, P.u_stride, P.sums0 = dp(u), (0 if det else I), dp(sums0)
             keep += [u, z0, w0, raw0, d_raw0, mask0, sums0]
+            if lib.cb200_get_decoder() == 1 and n * Sf < 2 ** 32:
+                # the fine pass evaluates the I new samples per ray only (the coarse ones are taken over) and one backward serves both passes
+                rank = torch.empty((n, S), dtype=torch.int32, device=dev)
+                new_list = torch.empty((n * I,), dtype=torch.int32, device=dev)
+                new_count = torch.empty((1,), dtype=torch.int64, device=dev)
+                P.rank, P.new_list, P.new_count = dp(rank), dp(new_list), dp(new_count)
+                keep += [rank, new_list, new_count]
         P.ws, P.loss_out = dp(ws), dp(loss_out)
         P.loss_w.rgb, P.loss_w.depth, P.loss_w.sdf, P.loss_w.fs = (t_.data_ptr() for t_ in self.w_dev)
         P.g_table = dp(g_table)

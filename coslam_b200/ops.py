@@ -217,9 +217,11 @@ def sample_rays(spec, target_d, noise=None, seed=0, counts=None, perturb=None, s
     return z
 
 
-def importance_sample(spec, z_vals, weights, u, target_d=None, counts=None, want_std=True):
+def importance_sample(spec, z_vals, weights, u, target_d=None, counts=None, want_std=True, merge=False):
     """sample_pdf + sorted merge (model/scene_rep.py:265-272, model/utils.py:32-71).  u is [N,I] or one shared row [I].
-    Returns (z [N,S+I], z_std [N] | None); accumulates the mask counts of the merged samples into counts when given."""
+    Returns (z [N,S+I], z_std [N] | None); accumulates the mask counts of the merged samples into counts when given.
+    merge=True: also returns (rank [N,S] int32, new_list [N*I] int32 storage of uint32 indices, new_count int64 [1]) -- where the coarse
+    samples sit in the merged rows and the point list of the new samples (cb200_importance_sample_merge)."""
     z, w = _f32c(z_vals), _f32c(weights)
     n, s = z.shape
     u = _f32c(u)
@@ -230,10 +232,27 @@ def importance_sample(spec, z_vals, weights, u, target_d=None, counts=None, want
     z_out = torch.empty((n, s + n_imp), dtype=torch.float32, device=z.device)
     z_std = torch.empty((n,), dtype=torch.float32, device=z.device) if want_std else None
     d = _f32c(target_d.reshape(-1)) if target_d is not None else None
+    if merge:
+        rank = torch.empty((n, s), dtype=torch.int32, device=z.device)
+        new_list = torch.empty((n * n_imp,), dtype=torch.int32, device=z.device)
+        new_count = torch.empty((1,), dtype=torch.int64, device=z.device)
+        check(_lib.load().cb200_importance_sample_merge(ctypes.byref(spec.render_cfg()), ptr(z), ptr(w), ptr(u), ctypes.c_int64(stride), ptr(d),
+                                                        ctypes.c_int64(n), ctypes.c_int64(s), ctypes.c_int64(n_imp), ptr(z_out), ptr(z_std),
+                                                        ptr(counts), ptr(rank), ptr(new_list), ptr(new_count), stream()), 'importance_sample_merge')
+        return z_out, z_std, (rank, new_list, new_count)
     check(_lib.load().cb200_importance_sample(ctypes.byref(spec.render_cfg()), ptr(z), ptr(w), ptr(u), ctypes.c_int64(stride), ptr(d),
                                               ctypes.c_int64(n), ctypes.c_int64(s), ctypes.c_int64(n_imp), ptr(z_out), ptr(z_std),
                                               ptr(counts), stream()), 'importance_sample')
     return z_out, z_std
+
+
+def merge_coarse(rank, src, dst, src_mask=None, dst_mask=None, accumulate=False):
+    """dst[ray, rank[ray, s]] (=, or += with accumulate) src[ray, s] over float4 rows ([N,S,4] into [N,S+I,4]); optionally the [.,2]
+    uint32 activation masks as well (cb200_merge_coarse)."""
+    n, s = rank.shape
+    f = dst.numel() // (4 * n)
+    check(_lib.load().cb200_merge_coarse(ptr(rank), ctypes.c_int64(n), ctypes.c_int64(s), ctypes.c_int64(f), ptr(src), ptr(dst), ptr(src_mask),
+                                         ptr(dst_mask), 1 if accumulate else 0, stream()), 'merge_coarse')
 
 
 def _mlp_block(w1, w2, w3, w4):

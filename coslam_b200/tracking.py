@@ -187,12 +187,21 @@ class FrameTracker(object):
             sums0 = self.sums0
             _, _, _, weights0 = ops._render_forward(spec, raw0, z0, self.target_s, td, loss_sums=sums0, want_weights=True)
             u = draw_uniforms(n, self.n_imp, z0.device, det=(self.config['training']['perturb'] == 0.))
-            z, _ = ops.importance_sample(spec, z0, weights0, u, target_d=td, counts=counts, want_std=False)
-            coarse = (rays0, raw0, mask0, sums0)
+            z, _, (rank, new_list, new_count) = ops.importance_sample(spec, z0, weights0, u, target_d=td, counts=counts, want_std=False, merge=True)
+            coarse = (rays0, raw0, mask0, sums0, rank)
         else:
             z = m._sample(td, counts=counts)
         rays = (self.rays_o, self.rays_d, z)
-        raw, _, mask = ops.points_forward(spec.scene(), tb, w, rays=rays)
+        if coarse is not None and lib.cb200_get_decoder() == 1:
+            # the coarse samples are part of the merged rows with the same positions, i.e. the same network outputs: evaluate the NEW
+            # samples only and take the coarse rows over
+            P_f = n * z.shape[1]
+            raw = torch.empty((P_f, 4), dtype=torch.float32, device=self.device)
+            mask = torch.empty((P_f, 2), dtype=torch.int32, device=self.device)
+            ops.points_forward(spec.scene(), tb, w, rays=rays, out=(raw, mask), point_list=(ptr(new_list), ptr(new_count)))
+            ops.merge_coarse(rank, raw0, raw, mask0, mask)
+        else:
+            raw, _, mask = ops.points_forward(spec.scene(), tb, w, rays=rays)
         into = (None, None, self.d_rays)                             # both passes add into the same ray-gradient buffer
         if coarse is None and lib.cb200_get_decoder() == 1:
             # rendering, loss sums, d_raw and the live-point list of every ray in ONE launch: d loss / d sum needs the mask counts only,
@@ -208,13 +217,15 @@ class FrameTracker(object):
             check(lib.cb200_loss_finish(ptr(ws[4:8]), ptr(counts), ctypes.c_int64(n), ctypes.c_int64(z.shape[1]),
                                         ptr(self.loss_out[:4]), ptr(self.loss_out[4:]), stream()), 'loss_finish')
             d_raw = ops._render_backward(spec, raw, z, self.target_s, td, self.w_dev, self.loss_out[4:], None, None)
+            if coarse is not None:
+                # the coarse maps' gradient (colour and depth terms only) lands on the same points: add it to the merged rows' d_raw and
+                # run ONE per-point backward
+                rays0, raw0, mask0, _, rank = coarse
+                d_raw0 = ops._render_backward(spec, raw0, rays0[2], self.target_s, td, (self.w_dev[0], self.w_dev[1], None, None),
+                                              self.loss_out[4:], None, None)
+                ops.merge_coarse(rank, d_raw0, d_raw, accumulate=True)
             ops.points_backward(spec.scene(), tb, w, mask, d_raw, rays=rays, accumulate=into)
             step = self._steps[0 if k == 0 else 1]
-        if coarse is not None:
-            rays0, raw0, mask0, _ = coarse
-            d_raw0 = ops._render_backward(spec, raw0, rays0[2], self.target_s, td, (self.w_dev[0], self.w_dev[1], None, None),
-                                          self.loss_out[4:], None, None)
-            ops.points_backward(spec.scene(), tb, w, mask0, d_raw0, rays=rays0, accumulate=into)
         d_o, d_d = self.d_rays[0], self.d_rays[1]
         check(lib.cb200_assemble_rays_bwd(ptr(self.kf7), ptr(self.ray_idx), ptr(self.pose_slot), ptr(d_o), ptr(d_d), ctypes.c_int64(n),
                                           ctypes.c_int64(1), ptr(self.d_c2w), stream()), 'assemble_rays_bwd')

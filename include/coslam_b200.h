@@ -275,6 +275,19 @@ int cb200_importance_sample(const cb200_render_cfg* cfg, const float* z_vals, co
                             int64_t u_stride, const float* target_d, int64_t n_rays, int64_t n_samples,
                             int64_t n_importance, float* z_out, float* z_std, int64_t* counts, void* stream);
 
+/* The same, plus where the samples went: rank [N,S] int32 = position of coarse sample s in its merged row; new_list [N*I] uint32 =
+ * flat indices (ray * (S+I) + position) of the NEW samples, *new_count = N * I (both may be NULL) -- a point list for cb200_points_fwd.
+ * The coarse samples keep their positions in space, hence their network outputs: the fine pass of the autograd-free loops evaluates
+ * only the new points and takes the coarse ones over with cb200_merge_coarse (accumulate = 0: dst[ray, rank[ray, s]] = src[ray, s] for
+ * raw [.,4] and, when given, the activation masks [.,2]); in the backward the coarse pass's d_raw is ADDED to the merged rows'
+ * (accumulate = 1), so one cb200_points_bwd over the merged samples serves both passes (model/scene_rep.py:262-295, :327-329). */
+int cb200_importance_sample_merge(const cb200_render_cfg* cfg, const float* z_vals, const float* weights, const float* u,
+                                  int64_t u_stride, const float* target_d, int64_t n_rays, int64_t n_samples,
+                                  int64_t n_importance, float* z_out, float* z_std, int64_t* counts, int32_t* rank,
+                                  uint32_t* new_list, uint64_t* new_count, void* stream);
+int cb200_merge_coarse(const int32_t* rank, int64_t n_rays, int64_t n_coarse, int64_t n_fine, const float* src, float* dst,
+                       const uint32_t* src_mask, uint32_t* dst_mask, int accumulate, void* stream);
+
 /* run_network / query_color_sdf / query_sdf forward (model/scene_rep.py:126-191 + model/decoder.py:165-180):
  * positions are either explicit (pts [P,3], rays_o == NULL) or pts = rays_o + rays_d * z (scene_rep.py:258,
  * separate multiply and add) with P = n_rays * n_samples.
@@ -446,6 +459,11 @@ typedef struct cb200_ba_plan {
     int64_t n_free;
     int32_t n_rot;
     float lr_rot, lr_trans;
+    /* hierarchical pass, optional (rank != NULL): scratch of cb200_importance_sample_merge -- rank [N,S] int32, new_list [N*I] uint32,
+     * new_count [1] -- so that the fine pass evaluates the new samples only and ONE per-point backward serves both passes */
+    int32_t* rank;
+    uint32_t* new_list;
+    uint64_t* new_count;
 } cb200_ba_plan;
 
 /* phases: which part of iteration `it` to issue.  One GPU: all three in one call.  Rays sharded over several GPUs
