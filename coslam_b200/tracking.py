@@ -11,11 +11,13 @@ coslam.py stays unchanged by design; this class is the op
 (`batch['direction']` pixels, rgb, depth, initial c2w) and the same result (`est_c2w_data[frame_id]`).
 
 Two implementations of one iteration:
-  * `fused=True` (default for the shipped single-grid configs without importance samples): no autograd graph at all.  The
-    iteration is 11 library launches -- ray assembly from the device c2w, sampling, per-point forward, render + loss sums,
-    loss finish, render backward, live-point compaction, per-point backward (dL/d rays only), pose-gradient segment sum,
-    and ONE single-thread kernel (`cb200_track_update`, csrc/track.cu) for the weighted loss, the best / last bookkeeping,
-    the backward of the pose parametrisation, both Adam steps and the next c2w -- plus two memsets.
+  * `fused=True` (default for the shipped single-grid configs): no autograd graph at all.  Without importance samples an iteration is
+    SIX launches (`_iteration_lean`): one fill | `cb200_track_rays_sample` (rays from the device c2w + depth-guided samples) |
+    per-point forward | `cb200_render_loss_bwd` (rendering, loss sums, d_raw and the live-point list: the loss head's backward needs the
+    mask counts only) | per-point backward (dL/d rays only) | `cb200_track_pose_update` (pose-gradient segment sum and, in its last
+    CTA, the weighted loss, the best / last bookkeeping, the backward of the pose parametrisation, both Adam steps, the next c2w and
+    the noise counter).  With importance samples (this fork's TUM config) the coarse pass, `cb200_importance_sample_merge` and the
+    separate loss-head kernels run; the fine pass evaluates only the new samples and one backward serves both passes.
   * `persistent=True` (opt-in; needs `fused`, `use_graph` and no importance pass): the whole frame -- every iteration of the list
     above -- is ONE cooperative launch (`cb200_track_frame`, csrc/track_frame.cu): CTAs stay resident, phases are separated by
     grid-wide barriers, the decoder weights are staged once per frame and the loop leaves early when the patience counter trips.
