@@ -342,6 +342,26 @@ def run_ours(args):
             sweep['2^%d' % lg] = {'rays_per_gpu': 1 << lg, 'ms_per_step': t_ms / k, 'value': world * (1 << lg) * k / (t_ms * 1e-3), 'unit': UNIT}
             del b
         extra['sweep'] = sweep
+        # ---- the same step with FIXED rays (no pose is optimised: first-frame mapping, mapping on given poses): NOT the headline ----
+        # the backward then reads the forward's kept hash-grid features instead of gathering the table again (cb200_points_bwd_kept)
+        from coslam_b200 import ops
+        lg = min(20, n.bit_length() - 1)
+        b = [t.to(dev) for t in synth.keyframe_ray_batch(cfg, 1 << lg, seed=100 + rank)[:4]]
+
+        def fixed_step():
+            for p in model.parameters():
+                p.grad = None
+            return mapper.step(b[0], b[1], b[2], b[3])[0]
+        mo = {'rays_per_gpu': 1 << lg, 'unit': UNIT, 'note': 'rays without gradient; the headline step also produces the ray (pose) gradients'}
+        for keep in (True, False):
+            ops.KEEP_FEATURES = keep
+            for _ in range(3):
+                fixed_step()
+            t_ms = timed(fixed_step, 5)
+            mo['kept_features' if keep else 'gathering_backward'] = {'ms_per_step': t_ms / 5, 'value': world * (1 << lg) * 5 / (t_ms * 1e-3)}
+        ops.KEEP_FEATURES = True
+        extra['map_only'] = mo
+        del b
         for p in model.parameters():
             p.grad = None
         torch.cuda.empty_cache()

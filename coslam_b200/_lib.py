@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 17
+ABI_VERSION = 18
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p
@@ -97,7 +97,7 @@ class BaPlan(ctypes.Structure):
 
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',
            'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_importance_sample_merge', 'cb200_merge_coarse', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update', 'cb200_track_frame', 'cb200_track_init', 'cb200_track_rays_sample', 'cb200_track_pose_update', 'cb200_pose_params', 'cb200_track_frame_workspace', 'cb200_pose_matrices', 'cb200_pose_adam', 'cb200_smooth_points', 'cb200_smooth_tv', 'cb200_ba_iteration', 'cb200_sizeof', 'cb200_host_random_sample', 'cb200_host_torch_rand', 'cb200_adam_multi',
-           'cb200_points_fwd', 'cb200_points_bwd', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd', 'cb200_render_loss_bwd',
+           'cb200_points_fwd', 'cb200_points_bwd', 'cb200_points_fwd_keep', 'cb200_points_bwd_kept', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd', 'cb200_render_loss_bwd',
            'cb200_debug_positions', 'cb200_debug_gather_peak', 'cb200_points_bwd_noalloc', 'cb200_points_bwd_noalloc_max_points', 'cb200_selftest_mma', 'cb200_set_decoder',
            'cb200_get_decoder']
 

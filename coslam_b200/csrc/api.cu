@@ -474,13 +474,16 @@ static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, cons
     return 0;
 }
 
-int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
-                     const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
-                     uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, void* stream) {
+static int points_fwd_impl(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                           const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
+                           uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, float* feat,
+                           void* stream) {
     cb200::PointsArgs a{};
     if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
     if (a.n_points == 0) return 0;
     a.raw = raw; a.geo = geo; a.act_mask = act_mask; a.sdf_only = sdf_only;
+    CB_REQUIRE(feat == nullptr || g_decoder == 1, "points_fwd_keep: the kept features need the tensor-core decoder");
+    a.feat = feat;
     CB_REQUIRE((point_list == nullptr) == (point_count == nullptr), "points_fwd: point_list and point_count go together");
     CB_REQUIRE(point_list == nullptr || g_decoder == 1, "points_fwd: point lists need the tensor-core decoder");
     CB_REQUIRE(point_list == nullptr || a.n_points < (1ll << 32), "points_fwd: point lists index with 32 bits");
@@ -488,6 +491,22 @@ int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_m
     a.live_count = reinterpret_cast<const unsigned long long*>(point_count);
     if (g_decoder == 1) return cuda_result(cb200::launch_points_fwd_tc(a, (cudaStream_t)stream), "points_fwd_tc");
     return cuda_result(cb200::launch_points_fwd(a, (cudaStream_t)stream), "points_fwd");
+}
+
+int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                     const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
+                     uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, void* stream) {
+    return points_fwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, raw, geo, act_mask, sdf_only, point_list,
+                           point_count, nullptr, stream);
+}
+
+int cb200_points_fwd_keep(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                          const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
+                          uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, float* feat,
+                          void* stream) {
+    CB_REQUIRE(feat != nullptr || n_rays == 0, "points_fwd_keep: feat is NULL");
+    return points_fwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, raw, geo, act_mask, sdf_only, point_list,
+                           point_count, feat, stream);
 }
 
 size_t cb200_lazy_workspace(int64_t n_rays, int64_t n_samples) {
@@ -531,13 +550,15 @@ int cb200_lazy_resolve(const cb200_render_cfg* cfg, const float* z_vals, const f
 
 size_t cb200_points_bwd_workspace(int64_t n_points) { return 16 + sizeof(uint32_t) * (size_t)(n_points > 0 ? n_points : 0); }
 
-int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
-                     const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
-                     const float* d_geo, const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
-                     float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace, size_t workspace_bytes, void* stream) {
+static int points_bwd_impl(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                           const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
+                           const float* d_geo, const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
+                           float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace, size_t workspace_bytes, const float* feat,
+                           void* stream) {
     cb200::PointsArgs a{};
     if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
     if (a.n_points == 0) return 0;
+    a.feat = const_cast<float*>(feat);
     CB_REQUIRE(d_raw && act_mask, "points_bwd: d_raw / act_mask is NULL");
     CB_REQUIRE((d_rays_o == nullptr) == (d_rays_d == nullptr), "points_bwd: d_rays_o and d_rays_d go together");
     CB_REQUIRE(d_rays_o == nullptr || rays_o != nullptr, "points_bwd: ray gradients need ray mode");
@@ -566,6 +587,25 @@ int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_m
         return cuda_result(cb200::launch_points_bwd_tc(a, (cudaStream_t)stream), "points_bwd_tc");
     }
     return cuda_result(cb200::launch_points_bwd(a, (cudaStream_t)stream), "points_bwd");
+}
+
+int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                     const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
+                     const float* d_geo, const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
+                     float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace, size_t workspace_bytes, void* stream) {
+    return points_bwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, d_raw, d_geo, act_mask, dtable, d_mlp, d_pts,
+                           d_rays_o, d_rays_d, sdf_only, workspace, workspace_bytes, nullptr, stream);
+}
+
+int cb200_points_bwd_kept(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
+                          const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
+                          const float* d_geo, const uint32_t* act_mask, const float* feat, float* dtable,
+                          const cb200_mlp_grad* d_mlp, int sdf_only, void* workspace, size_t workspace_bytes, void* stream) {
+    CB_REQUIRE(feat != nullptr || n_rays == 0, "points_bwd_kept: feat is NULL");
+    CB_REQUIRE(g_decoder == 1, "points_bwd_kept: the kept features need the tensor-core decoder");
+    CB_REQUIRE(d_mlp != nullptr, "points_bwd_kept: the kept features serve the weight-gradient backward (d_mlp is NULL)");
+    return points_bwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, d_raw, d_geo, act_mask, dtable, d_mlp, nullptr,
+                           nullptr, nullptr, sdf_only, workspace, workspace_bytes, feat, stream);
 }
 
 static int fill_render_args(cb200::RenderArgs& a, const cb200_render_cfg* cfg, const float* raw, const float* z_vals,

@@ -22,6 +22,9 @@ struct PointsArgs {
     float* raw;
     float* geo;
     uint32_t* act_mask;
+    // tensor-core decoder, optional: the 32 hash-grid features of every evaluated point [P, 32] fp32, written by the forward and read
+    // back by the weight-gradient backward INSTEAD of gathering the table again (no position gradient in that mode)
+    float* feat;
     // backward
     const float* d_raw;
     const float* d_geo;

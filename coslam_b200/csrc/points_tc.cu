@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
 }
 
 
-template <bool kWgrad>
+template <bool kWgrad, bool kSaved>
 __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsArgs a) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smem[];
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
     uint32_t parity = 0;
     bool first_tile = true;
     const int64_t n_slots = a.live_count ? (int64_t)*a.live_count : a.n_points;
-    bwd_tile_loop<kWgrad>(a, smem, bar, tmem, parity, first_tile, a.live_idx, n_slots, blockIdx.x, gridDim.x);
+    bwd_tile_loop<kWgrad, kSaved>(a, smem, bar, tmem, parity, first_tile, a.live_idx, n_slots, blockIdx.x, gridDim.x);
 
     if (kWgrad && !first_tile && half == 0) {
         // lane = row of the transposed weight gradients: dW1^T [80 x 32], dW3^T [63 x 32], dW2^T [32 x 16], dW4^T [32 x 3]
@@ -154,18 +154,21 @@ static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
     return (int)g;
 }
 
-template <bool kWgrad>
+template <bool kWgrad, bool kSaved>
 static cudaError_t launch_points_bwd_tc_as(const PointsArgs& a, cudaStream_t st) {
     const size_t smem = tc::kBwdSmem;
     const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
-    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_bwd_tc_kernel<kWgrad>), smem);
+    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_bwd_tc_kernel<kWgrad, kSaved>), smem);
     if (e != cudaSuccess) return e;
-    points_bwd_tc_kernel<kWgrad><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
+    points_bwd_tc_kernel<kWgrad, kSaved><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
 cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st) {
-    return a.dw1 != nullptr ? launch_points_bwd_tc_as<true>(a, st) : launch_points_bwd_tc_as<false>(a, st);
+    if (a.dw1 == nullptr) return launch_points_bwd_tc_as<false, false>(a, st);
+    // kept features replace the second gather when no position gradient is asked for (it needs the corner values)
+    const bool saved = a.feat != nullptr && a.d_pts == nullptr && a.d_rays_o == nullptr;
+    return saved ? launch_points_bwd_tc_as<true, true>(a, st) : launch_points_bwd_tc_as<true, false>(a, st);
 }
 
 // number of leading dense levels when the scene is "dense levels first, hashed levels after" over all 16 levels, else -1

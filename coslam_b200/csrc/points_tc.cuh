@@ -117,7 +117,9 @@ __device__ __forceinline__ void tile_store4(uint32_t hi_base, uint32_t lo_base, 
 }
 
 // the pair's per-corner partial features of one chunk (4 levels x 2) -> complete features; thread xb keeps columns 4 xb .. 4 xb + 3
-__device__ __forceinline__ void pair_combine_store(const float (&part)[8], int xb, uint32_t a_hi, uint32_t a_lo, int row, int c) {
+// keep (optional): the point's row of PointsArgs::feat -- the fp32 features are streamed out for the backward as well
+__device__ __forceinline__ void pair_combine_store(const float (&part)[8], int xb, uint32_t a_hi, uint32_t a_lo, int row, int c,
+                                                   float* keep = nullptr) {
     float mine[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -126,11 +128,13 @@ __device__ __forceinline__ void pair_combine_store(const float (&part)[8], int x
         mine[i] = (xb ? part[4 + i] : part[i]) + recv;
     }
     tile_store4(a_hi, a_lo, kAGS, row, c, xb, mine);
+    if (keep) __stcs(reinterpret_cast<float4*>(keep + 8 * c + 4 * xb), make_float4(mine[0], mine[1], mine[2], mine[3]));
 }
 
 // one chunk (4 levels, 8 features) of hash-grid features -> A tile; 16 gathers in flight per thread
 template <int kDense>
-__device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row
+__device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row,
+                                                  float* keep
 #ifdef CB200_PHASE_CLOCKS
                                                   , long long* sub
 #endif
@@ -169,7 +173,7 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
         part[2 * q] = f0;
         part[2 * q + 1] = f1;
     }
-    pair_combine_store(part, xb, a_hi, a_lo, row, c);
+    pair_combine_store(part, xb, a_hi, a_lo, row, c, keep);
 #ifdef CB200_PHASE_CLOCKS
     long long t3 = clock64();
     sub[0] += t1 - t0; sub[1] += t2 - t1; sub[2] += t3 - t2;
@@ -295,11 +299,12 @@ __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char
             const int64_t pg = list ? (int64_t)list[pg_slot] : pg_slot;
             float x[3], zdummy;
             point_position(a, pg, x, zdummy);
+            float* const keep = a.feat ? a.feat + pg * kGridFeats : nullptr;      // padding slots repeat the last point: same values
 #pragma unroll
 #ifdef CB200_PHASE_CLOCKS
-            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g, sub);
+            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g, keep, sub);
 #else
-            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g);
+            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g, keep);
 #endif
             PH(0);
 #pragma unroll
@@ -454,7 +459,9 @@ constexpr int kBwdTmemCols = 256;
 
 // The persistent tile loop of the backward (same contract as fwd_tile_loop; kBwdTmemCols columns; additionally expects the fp32
 // copy of W4 at kBOffW4f).  first_tile: no weight-gradient product has been accumulated in TMEM yet (kWgrad).
-template <bool kWgrad>
+// kSaved (with kWgrad): the hash-grid features come from PointsArgs::feat (kept by the forward) instead of a second gather of the table;
+// no position gradient in that mode (it needs the corner values).
+template <bool kWgrad, bool kSaved = false>
 __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char* smem, uint64_t& bar, uint32_t tmem, uint32_t& parity,
                                               bool& first_tile, const uint32_t* list, int64_t n_slots, int64_t tile_begin,
                                               int64_t tile_step) {
@@ -575,6 +582,35 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
         for (int c = 0; c < 4; ++c) {
             uint32_t de_raw[8];
             tmem_ld_x8(trow + kColDin1 + 8 * c, de_raw);        // d embed of levels 4c .. 4c+3, row = this lane's TMEM lane
+            if (kSaved) {
+                // table scatter only: thread xb takes columns 8c + 4xb .. + 3 of the point's kept feature row
+                float4 kept = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (live) kept = __ldcs(reinterpret_cast<const float4*>(a.feat + pg * kGridFeats + 8 * c + 4 * xb));
+                uint32_t idx[4][4];
+                float wx[4], w1[4], w2[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    HalfCorners hc;
+                    level_corners_x<-1>(a.scene, 4 * c + q, x, xb, hc);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) idx[q][j] = hc.idx[j];
+                    wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
+                }
+                tmem_ld_wait();
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float de0 = __uint_as_float(__shfl_sync(0xffffffffu, de_raw[2 * q], src_lane));
+                    const float de1 = __uint_as_float(__shfl_sync(0xffffffffu, de_raw[2 * q + 1], src_lane));
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
+                        if (dtab && live) red_add_f2(dtab + idx[q][j], wc * de0, wc * de1);
+                    }
+                }
+                const float mine[4] = {kept.x, kept.y, kept.z, kept.w};
+                tile_store4(a_hi, a_lo, kAGS, row_g, c, xb, mine);
+                continue;
+            }
             float2 v[4][4];
             uint32_t idx[4][4];
             float wx[4], w1[4], w2[4];
@@ -640,9 +676,14 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
         // OneBlob: thread xb owns bins 8 xb .. 8 xb + 7 of every coordinate (gradient columns 32 + 16 d + 8 xb .. of d_in1)
 #pragma unroll
         for (int d = 0; d < 3; ++d) {
+            float val[8], dval[8];
+            if (kSaved) {
+                blob_half<false>(x[d], xb, val, dval);
+                tile_store8(a_hi, a_lo, kAGS, row_g, 4 + 2 * d + xb, val);
+                continue;
+            }
             uint32_t gb[16];
             tmem_ld_x16(trow + kColDin1 + 32 + 16 * d, gb);
-            float val[8], dval[8];
             blob_half<true>(x[d], xb, val, dval);
             tmem_ld_wait();
             float acc = 0.f;
@@ -659,7 +700,7 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
         for (int d = 0; d < 3; ++d) dx[d] += __shfl_xor_sync(0xffffffffu, dx[d], 1);      // both threads of the pair: full dL/dx
 
         // ---- position gradient (pair leader) ----------------------------------------------------------------------------------
-        {
+        if (!kSaved) {
             float dp[3];
 #pragma unroll
             for (int d = 0; d < 3; ++d) dp[d] = valid_g ? (a.scene.normalise ? dx[d] / a.scene.bb_ext[d] : dx[d]) : 0.f;

@@ -13,6 +13,7 @@ from . import _lib
 from ._lib import check, ptr, stream
 
 N_GEO = 15
+N_GRID_FEATS = 32      # 16 levels x 2 hash-grid features (CB200_GRID_FEATS)
 
 # tests set KEEP_LAST_MASK to read back the ReLU sign bits the last ray forward saved for its backward
 KEEP_LAST_MASK = False
@@ -268,14 +269,16 @@ def _check_weights(w1, w2, w3, w4):
                            [tuple(w.shape) for w in (w1, w2, w3, w4)])
 
 
+KEEP_FEATURES = True     # map-only steps keep the hash-grid features of the forward for the backward (RayPointsFunction)
 LAZY_FORWARD = True      # training forward evaluates only the sample points the step can depend on (lazy_ray_forward)
 LAZY_MIN_POINTS = 1 << 18   # below ~7 waves of tiles (tracking / BA batches) the three extra launches cost more than the skipped points save
 
 
 def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo=False, want_mask=True, sdf_only=False,
-                   out=None, point_list=None):
+                   out=None, point_list=None, feat=None):
     """query_color_sdf / run_network forward through the fused kernel.  rays = (rays_o [N,3], rays_d [N,3], z [N,S]).
-    out = (raw, mask) to write into existing buffers; point_list = (list ptr, count ptr) restricts the launch to them."""
+    out = (raw, mask) to write into existing buffers; point_list = (list ptr, count ptr) restricts the launch to them;
+    feat [P,32]: also keep the hash-grid features of the evaluated points for points_backward(feat=) (cb200_points_fwd_keep)."""
     _check_weights(*w)
     if rays is not None:
         o, d, z = rays
@@ -294,13 +297,18 @@ def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo
     geo = torch.empty((P, N_GEO), dtype=torch.float32, device=dev) if want_geo else None
     mlp = _mlp_block(*w)
     lst, cnt = point_list if point_list is not None else (None, None)
+    if feat is not None:
+        _timed('points_fwd', lambda: check(_lib.load().cb200_points_fwd_keep(
+            ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
+            ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask), 1 if sdf_only else 0, lst, cnt, ptr(feat), stream()), 'points_fwd_keep'))
+        return raw, geo, mask
     _timed('points_fwd', lambda: check(_lib.load().cb200_points_fwd(
         ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
         ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask), 1 if sdf_only else 0, lst, cnt, stream()), 'points_fwd'))
     return raw, geo, mask
 
 
-def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True):
+def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True, feat=None):
     """Training forward over the sample points the step can depend on (cb200_lazy_prefix / cb200_lazy_resolve): the loss
     prefix of every ray first, then whatever the first sign change found there still exposes.  Points never listed keep
     raw = 0; the rendering mask gives them zero weight and the loss masks exclude them, as in the reference."""
@@ -318,18 +326,20 @@ def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True):
     cfg = spec.render_cfg()
     check(lib.cb200_lazy_prefix(ctypes.byref(cfg), ptr(z), ptr(td), ctypes.c_int64(n), ctypes.c_int64(s), ptr(wsp),
                                 ctypes.c_size_t(nbytes), stream()), 'lazy_prefix')
-    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist)
+    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist, feat=feat)
     check(lib.cb200_lazy_resolve(ctypes.byref(cfg), ptr(z), ptr(td), ptr(raw), ctypes.c_int64(n), ctypes.c_int64(s), ptr(wsp),
                                  ctypes.c_size_t(nbytes), stream()), 'lazy_resolve')
-    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist)
+    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist, feat=feat)
     return raw, mask
 
 
 def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=None, need_table=True, need_mlp=True,
-                    need_pos=True, sdf_only=False, accumulate=None, ready_list=None):
+                    need_pos=True, sdf_only=False, accumulate=None, ready_list=None, feat=None):
     """Backward of points_forward.  Returns (d_table, (dW1..dW4), d_pts | (d_rays_o, d_rays_d)).
     accumulate = (d_table, (dW1..dW4), d_rays [2,N,3]): existing buffers the kernel adds into (any entry may be None = not
-    needed) instead of fresh zero-filled ones -- the autograd-free loops (mapping.py) keep their gradient buffers."""
+    needed) instead of fresh zero-filled ones -- the autograd-free loops (mapping.py) keep their gradient buffers.
+    feat: the features kept by points_forward(feat=); used (cb200_points_bwd_kept) when the decoder gradients are wanted and no
+    position gradient is."""
     if rays is not None:
         o, d, z = rays
         n, s = z.shape
@@ -369,11 +379,17 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
     elif rays is not None and d_geo is None:
         wsp_bytes = int(_lib.load().cb200_points_bwd_workspace(ctypes.c_int64(n * s)))
         wsp = torch.empty((wsp_bytes + 3) // 4, dtype=torch.int32, device=dev)
-    _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd(
-        ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
-        ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(d_table),
-        ctypes.byref(gblock) if gblock is not None else None, ptr(d_pts), ptr(d_o), ptr(d_d), 1 if sdf_only else 0,
-        ptr(wsp), ctypes.c_size_t(wsp_bytes), stream()), 'points_bwd'))
+    if feat is not None and gblock is not None and d_pts is None and d_o is None:
+        _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd_kept(
+            ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
+            ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(feat), ptr(d_table), ctypes.byref(gblock),
+            1 if sdf_only else 0, ptr(wsp), ctypes.c_size_t(wsp_bytes), stream()), 'points_bwd_kept'))
+    else:
+        _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd(
+            ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
+            ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(d_table),
+            ctypes.byref(gblock) if gblock is not None else None, ptr(d_pts), ptr(d_o), ptr(d_d), 1 if sdf_only else 0,
+            ptr(wsp), ctypes.c_size_t(wsp_bytes), stream()), 'points_bwd'))
     if wsp is not None and ready_list is None and _lib.load().cb200_get_decoder() == 1:
         _lib.KERNEL_LAUNCHES += 1          # the compaction kernel in front of the per-point kernel
     return d_table, d_w, (d_pts if rays is None else (d_o, d_d))
@@ -392,29 +408,41 @@ class RayPointsFunction(torch.autograd.Function):
         tb, w = _f32c(table), tuple(_f32c(x) for x in (w1, w2, w3, w4))
         need_grad = any(ctx.needs_input_grad)
         ctx.set_materialize_grads(False)
-        lazy = target_d is not None and LAZY_FORWARD and _lib.load().cb200_get_decoder() == 1 and LAZY_MIN_POINTS <= z.numel() < 2 ** 32
+        tc = _lib.load().cb200_get_decoder() == 1
+        lazy = target_d is not None and LAZY_FORWARD and tc and LAZY_MIN_POINTS <= z.numel() < 2 ** 32
+        # a map-only step (decoder gradients wanted, rays fixed): keep the hash-grid features for the backward, which then does not
+        # gather the table a second time (128 B per point of scratch; without the memory the step runs as before)
+        feat = None
+        need = ctx.needs_input_grad
+        if KEEP_FEATURES and tc and z.numel() > 0 and any(need[4:8]) and not (need[0] or need[1]):
+            try:
+                feat = torch.empty((z.numel(), N_GRID_FEATS), dtype=torch.float32, device=z.device)
+            except torch.cuda.OutOfMemoryError:
+                feat = None
         if lazy:
             _check_weights(*w)
-            raw, mask = lazy_ray_forward(spec, tb, w, (o, d, z), target_d, want_mask=need_grad)
+            raw, mask = lazy_ray_forward(spec, tb, w, (o, d, z), target_d, want_mask=need_grad, feat=feat)
         else:
-            raw, _, mask = points_forward(spec.scene(), tb, w, rays=(o, d, z), want_mask=need_grad)
+            raw, _, mask = points_forward(spec.scene(), tb, w, rays=(o, d, z), want_mask=need_grad, feat=feat)
         if KEEP_LAST_MASK:
             global LAST_MASK, LAST_EVALUATED
             LAST_MASK = mask
             LAST_EVALUATED = (raw != 0).any(-1) if lazy else None
             MASK_LOG.append(mask)
         ctx.spec = spec
-        ctx.save_for_backward(o, d, z, tb, *w, mask if mask is not None else torch.empty(0))
+        ctx.kept = feat is not None
+        ctx.save_for_backward(o, d, z, tb, *w, mask if mask is not None else torch.empty(0), *((feat,) if feat is not None else ()))
         return raw.view(z.shape[0], z.shape[1], 4)
 
     @staticmethod
     def backward(ctx, g_raw):
         if g_raw is None:
             return (None,) * 10
-        o, d, z, tb, w1, w2, w3, w4, mask = ctx.saved_tensors
+        o, d, z, tb, w1, w2, w3, w4, mask = ctx.saved_tensors[:9]
+        feat = ctx.saved_tensors[9] if ctx.kept else None
         need = ctx.needs_input_grad
         d_table, d_w, d_ray = points_backward(ctx.spec.scene(), tb, (w1, w2, w3, w4), mask, _f32c(g_raw), rays=(o, d, z),
-                                              need_table=need[3], need_mlp=any(need[4:8]), need_pos=need[0] or need[1])
+                                              need_table=need[3], need_mlp=any(need[4:8]), need_pos=need[0] or need[1], feat=feat)
         d_o, d_d = d_ray if d_ray is not None else (None, None)
         d_w = d_w or (None, None, None, None)
         return d_o, d_d, None, d_table, d_w[0], d_w[1], d_w[2], d_w[3], None, None

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 17
+#define CB200_ABI_VERSION 18
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -330,6 +330,22 @@ int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_m
                      int64_t n_samples, const float* d_raw, const float* d_geo, const uint32_t* act_mask,
                      float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts, float* d_rays_o, float* d_rays_d,
                      int sdf_only, void* workspace, size_t workspace_bytes, void* stream);
+
+/* The pair for a step that optimises the map but no pose (the batch of model/scene_rep.py:297-351 with fixed rays): the forward
+ * also keeps the 32 hash-grid features of every point it evaluates, feat [P,32] fp32 (tcnn.Encoding(HashGrid) output order:
+ * level-major, 2 per level; rows of points it does not evaluate are left untouched), and the backward reads them back instead of
+ * gathering 128 table entries per point a second time -- 128 B of streamed HBM traffic per point for 1 KB of L2 gathers.  No position
+ * gradient (it needs the corner values: use cb200_points_bwd).  Tensor-core decoder only; d_mlp must be given; every point with
+ * non-zero d_raw must have been evaluated by the forward that wrote `feat`.  Same results as cb200_points_fwd / cb200_points_bwd. */
+int cb200_points_fwd_keep(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
+                          const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
+                          int64_t n_samples, float* raw, float* geo, uint32_t* act_mask, int sdf_only,
+                          const uint32_t* point_list, const uint64_t* point_count, float* feat, void* stream);
+int cb200_points_bwd_kept(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
+                          const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
+                          int64_t n_samples, const float* d_raw, const float* d_geo, const uint32_t* act_mask,
+                          const float* feat, float* dtable, const cb200_mlp_grad* d_mlp, int sdf_only, void* workspace,
+                          size_t workspace_bytes, void* stream);
 
 /* raw2outputs + sdf2weights (model/scene_rep.py:77-124) and, when loss_sums != NULL, the loss head
  * (model/scene_rep.py:319-338, model/utils.py:138-161).

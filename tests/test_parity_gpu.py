@@ -1141,6 +1141,68 @@ def test_lazy_forward_is_exact(cfg_name, kind):
         assert bool((ev[:, 1:] <= ev[:, :-1]).all())        # what is evaluated is a prefix of every ray
 
 
+@pytest.mark.parametrize('cfg_name,lazy', [('room0', True), ('room0', False), ('scannet0000', True)])
+def test_map_only_step_with_kept_features_matches_the_gathering_backward(cfg_name, lazy):
+    """A step whose rays carry no gradient (fixed poses) keeps the hash-grid features of the forward and its backward reads them back
+    instead of gathering the table again (cb200_points_fwd_keep / cb200_points_bwd_kept).  Same outputs; gradients equal up to the
+    summation order of their atomics; and the weight / table gradients are the ones of the step WITH ray gradients."""
+    cfg = synth.CONFIGS[cfg_name]()
+    n_rays = 3000
+    rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n_rays, seed=21)
+    weights = [w.clone() for w in synth.decoder_init(seed=6)]
+    table = synth.table_init(JointEncodingFor(cfg).embed_fn.params.numel(), 'trained', seed=78)
+    res = {}
+    min_points, ops.LAZY_MIN_POINTS = ops.LAZY_MIN_POINTS, (1 if lazy else 1 << 62)
+    try:
+        for mode in ('kept', 'gathered', 'with_ray_grads'):
+            model = util.make_cuda_model(cfg, table, weights, DEV)
+            ops.KEEP_FEATURES = mode != 'gathered'
+            o, d = rays_o.to(DEV), rays_d.to(DEV)
+            if mode == 'with_ray_grads':
+                o, d = o.requires_grad_(True), d.requires_grad_(True)
+            torch.manual_seed(3)
+            ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
+            _weighted_loss(cfg, ret).backward()
+            res[mode] = (ret, model.embed_fn.params.grad, [w.grad for w in model.decoder.fused_weights()])
+    finally:
+        ops.KEEP_FEATURES = True
+        ops.LAZY_MIN_POINTS = min_points
+    a = res['kept']
+    for other in ('gathered', 'with_ray_grads'):
+        b = res[other]
+        for k in ('rgb', 'depth', 'rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):
+            assert torch.equal(a[0][k], b[0][k]), (other, k)
+        util.assert_close(a[1], b[1], 'd_table vs ' + other, tol=2e-5)
+        for x, y in zip(a[2], b[2]):
+            util.assert_close(x, y, 'dW vs ' + other, tol=2e-5)
+    assert float(a[1].abs().max()) > 0 and all(float(x.abs().max()) > 0 for x in a[2])
+
+
+def test_kept_feature_rows_are_the_hash_encoding():
+    """cb200_points_fwd_keep's feat [P,32] is tcnn.Encoding(HashGrid)'s output for the same points (level-major, 2 per level), i.e.
+    cb200_hash_fwd on the normalised positions."""
+    cfg = synth.CONFIGS['room0']()
+    n_rays = 500
+    rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n_rays, seed=4)
+    model = util.make_cuda_model(cfg, synth.table_init(JointEncodingFor(cfg).embed_fn.params.numel(), 'trained', seed=2),
+                                 synth.decoder_init(seed=1), DEV)
+    spec = model.spec
+    z = ops.sample_rays(spec, depth.to(DEV), seed=5, perturb=True)
+    o, d = rays_o.to(DEV).contiguous(), rays_d.to(DEV).contiguous()
+    P = z.numel()
+    feat = torch.full((P, 32), float('nan'), device=DEV)
+    w = tuple(x.detach().contiguous() for x in model.decoder.fused_weights())
+    ops.points_forward(spec.scene(), model.embed_fn.params.detach(), w, rays=(o, d, z.contiguous()), feat=feat)
+    pts = torch.empty((P, 3), device=DEV)
+    x = torch.empty((P, 3), device=DEV)
+    _lib.check(_lib.load().cb200_debug_positions(ctypes.byref(spec.scene()), _lib.ptr(o), _lib.ptr(d), _lib.ptr(z), ctypes.c_int64(n_rays),
+                                                 ctypes.c_int64(z.shape[1]), _lib.ptr(pts), _lib.ptr(x), _lib.stream()), 'debug_positions')
+    with torch.no_grad():
+        want = model.embed_fn(x)
+    assert not torch.isnan(feat).any()
+    util.assert_close(feat, want.float(), 'kept features', tol=1e-6)
+
+
 def test_two_grid_variant_matches_reference_golden():
     """`oneGrid: False` (model/scene_rep.py:56-58, 168-170; ColorSDFNet, model/decoder.py:110-143):
     second hash grid for colour.  Not served by the fused kernels; the training step composes the stand-alone CUDA encodings, the

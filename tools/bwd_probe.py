@@ -79,6 +79,21 @@ def main():
         k.update(over)
         ms = timed(lambda: real_bwd(*a, **k), args.reps)
         print('%-26s %.3f ms   %.1f M live points/s   %.0f GB/s of 2 048 B/pt' % (name, ms, P * live / ms / 1e3, P * live * 2048 / ms / 1e6), flush=True)
+    if 'fwd' in captured:
+        # kept features (cb200_points_fwd_keep / cb200_points_bwd_kept): the forward streams 128 B per evaluated point out, the
+        # backward reads them back instead of gathering the table a second time (no position gradient)
+        feat = torch.empty((P, 32), dtype=torch.float32, device=DEV)
+        fa, fkw = captured['fwd']
+        print('fwd keeping the features   %.3f ms' % timed(lambda: real_fwd(*fa, **dict(fkw, feat=feat)), args.reps), flush=True)
+        k = dict(kw)
+        k.update(need_pos=False, feat=feat)
+        ms = timed(lambda: real_bwd(*a, **k), args.reps)
+        print('%-26s %.3f ms   %.1f M live points/s' % ('bwd from kept features', ms, P * live / ms / 1e3), flush=True)
+        ref = real_bwd(*a, **dict(kw, need_pos=False))
+        got = real_bwd(*a, **k)
+        torch.cuda.synchronize()
+        for n_, x, y in [('d_table', ref[0], got[0])] + [('dW%d' % (i + 1), ref[1][i], got[1][i]) for i in range(4)]:
+            print('kept vs gathered %-8s max |diff| %.3e of max %.3e' % (n_, float((x - y).abs().max()), float(x.abs().max())), flush=True)
     if args.check:
         d_table, d_w, (d_o, d_d) = real_bwd(*a, **kw)
         torch.cuda.synchronize()
