@@ -477,13 +477,14 @@ static int fill_points_args(cb200::PointsArgs& a, const cb200_scene* scene, cons
 static int points_fwd_impl(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
                            const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
                            uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, float* feat,
-                           void* stream) {
+                           int feat_stride, void* stream) {
     cb200::PointsArgs a{};
     if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
     if (a.n_points == 0) return 0;
     a.raw = raw; a.geo = geo; a.act_mask = act_mask; a.sdf_only = sdf_only;
     CB_REQUIRE(feat == nullptr || g_decoder == 1, "points_fwd_keep: the kept features need the tensor-core decoder");
     a.feat = feat;
+    a.feat_stride = feat_stride;
     CB_REQUIRE((point_list == nullptr) == (point_count == nullptr), "points_fwd: point_list and point_count go together");
     CB_REQUIRE(point_list == nullptr || g_decoder == 1, "points_fwd: point lists need the tensor-core decoder");
     CB_REQUIRE(point_list == nullptr || a.n_points < (1ll << 32), "points_fwd: point lists index with 32 bits");
@@ -497,16 +498,16 @@ int cb200_points_fwd(const cb200_scene* scene, const float* table, const cb200_m
                      const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
                      uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, void* stream) {
     return points_fwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, raw, geo, act_mask, sdf_only, point_list,
-                           point_count, nullptr, stream);
+                           point_count, nullptr, 0, stream);
 }
 
 int cb200_points_fwd_keep(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
                           const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, float* raw, float* geo,
                           uint32_t* act_mask, int sdf_only, const uint32_t* point_list, const uint64_t* point_count, float* feat,
-                          void* stream) {
+                          int with_derivatives, void* stream) {
     CB_REQUIRE(feat != nullptr || n_rays == 0, "points_fwd_keep: feat is NULL");
     return points_fwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, raw, geo, act_mask, sdf_only, point_list,
-                           point_count, feat, stream);
+                           point_count, feat, with_derivatives ? 4 * CB200_GRID_FEATS : CB200_GRID_FEATS, stream);
 }
 
 size_t cb200_lazy_workspace(int64_t n_rays, int64_t n_samples) {
@@ -554,11 +555,12 @@ static int points_bwd_impl(const cb200_scene* scene, const float* table, const c
                            const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
                            const float* d_geo, const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
                            float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace, size_t workspace_bytes, const float* feat,
-                           void* stream) {
+                           int feat_stride, void* stream) {
     cb200::PointsArgs a{};
     if (int rc = fill_points_args(a, scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples)) return rc;
     if (a.n_points == 0) return 0;
     a.feat = const_cast<float*>(feat);
+    a.feat_stride = feat_stride;
     CB_REQUIRE(d_raw && act_mask, "points_bwd: d_raw / act_mask is NULL");
     CB_REQUIRE((d_rays_o == nullptr) == (d_rays_d == nullptr), "points_bwd: d_rays_o and d_rays_d go together");
     CB_REQUIRE(d_rays_o == nullptr || rays_o != nullptr, "points_bwd: ray gradients need ray mode");
@@ -594,18 +596,22 @@ int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_m
                      const float* d_geo, const uint32_t* act_mask, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
                      float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace, size_t workspace_bytes, void* stream) {
     return points_bwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, d_raw, d_geo, act_mask, dtable, d_mlp, d_pts,
-                           d_rays_o, d_rays_d, sdf_only, workspace, workspace_bytes, nullptr, stream);
+                           d_rays_o, d_rays_d, sdf_only, workspace, workspace_bytes, nullptr, 0, stream);
 }
 
 int cb200_points_bwd_kept(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts, const float* rays_o,
                           const float* rays_d, const float* z_vals, int64_t n_rays, int64_t n_samples, const float* d_raw,
-                          const float* d_geo, const uint32_t* act_mask, const float* feat, float* dtable,
-                          const cb200_mlp_grad* d_mlp, int sdf_only, void* workspace, size_t workspace_bytes, void* stream) {
+                          const float* d_geo, const uint32_t* act_mask, const float* feat, int with_derivatives, float* dtable,
+                          const cb200_mlp_grad* d_mlp, float* d_pts, float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace,
+                          size_t workspace_bytes, void* stream) {
     CB_REQUIRE(feat != nullptr || n_rays == 0, "points_bwd_kept: feat is NULL");
-    CB_REQUIRE(g_decoder == 1, "points_bwd_kept: the kept features need the tensor-core decoder");
-    CB_REQUIRE(d_mlp != nullptr, "points_bwd_kept: the kept features serve the weight-gradient backward (d_mlp is NULL)");
-    return points_bwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, d_raw, d_geo, act_mask, dtable, d_mlp, nullptr,
-                           nullptr, nullptr, sdf_only, workspace, workspace_bytes, feat, stream);
+    CB_REQUIRE(g_decoder == 1, "points_bwd_kept: the kept rows need the tensor-core decoder");
+    CB_REQUIRE(d_mlp != nullptr, "points_bwd_kept: the kept rows serve the weight-gradient backward (d_mlp is NULL)");
+    CB_REQUIRE(with_derivatives || (d_pts == nullptr && d_rays_o == nullptr),
+               "points_bwd_kept: a position gradient needs rows kept with_derivatives (or cb200_points_bwd)");
+    return points_bwd_impl(scene, table, mlp, pts, rays_o, rays_d, z_vals, n_rays, n_samples, d_raw, d_geo, act_mask, dtable, d_mlp, d_pts,
+                           d_rays_o, d_rays_d, sdf_only, workspace, workspace_bytes, feat,
+                           with_derivatives ? 4 * CB200_GRID_FEATS : CB200_GRID_FEATS, stream);
 }
 
 static int fill_render_args(cb200::RenderArgs& a, const cb200_render_cfg* cfg, const float* raw, const float* z_vals,

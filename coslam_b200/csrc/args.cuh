@@ -22,9 +22,11 @@ struct PointsArgs {
     float* raw;
     float* geo;
     uint32_t* act_mask;
-    // tensor-core decoder, optional: the 32 hash-grid features of every evaluated point [P, 32] fp32, written by the forward and read
-    // back by the weight-gradient backward INSTEAD of gathering the table again (no position gradient in that mode)
+    // tensor-core decoder, optional: rows kept by the forward for every point it evaluates and read back by the weight-gradient backward
+    // INSTEAD of gathering the table again.  feat_stride 32: the hash-grid features (no position gradient in that mode);
+    // feat_stride 128: [features | d/dx | d/dy | d/dz of them] (x = normalised position), which also serve the position gradient
     float* feat;
+    int feat_stride;
     // backward
     const float* d_raw;
     const float* d_geo;

@@ -3,7 +3,7 @@
 
 namespace cb200 {
 
-template <int kDense>
+template <int kDense, bool kJac>
 __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsArgs a) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smem[];
@@ -20,12 +20,12 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_fwd_tc_kernel(PointsAr
     const uint32_t tmem = tmem_slot;
     uint32_t parity = 0;
     const int64_t n_slots = a.live_count ? (int64_t)*a.live_count : a.n_points;
-    fwd_tile_loop<kDense>(a, smem, bar, tmem, parity, a.live_idx, n_slots, blockIdx.x, gridDim.x);
+    fwd_tile_loop<kDense, kJac>(a, smem, bar, tmem, parity, a.live_idx, n_slots, blockIdx.x, gridDim.x);
     if (warp == 0) tmem_dealloc<tc::kTmemCols>(tmem);
 }
 
 
-template <bool kWgrad, bool kSaved>
+template <bool kWgrad, int kKept>
 __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsArgs a) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smem[];
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(tc::kThreads, 2) points_bwd_tc_kernel(PointsAr
     uint32_t parity = 0;
     bool first_tile = true;
     const int64_t n_slots = a.live_count ? (int64_t)*a.live_count : a.n_points;
-    bwd_tile_loop<kWgrad, kSaved>(a, smem, bar, tmem, parity, first_tile, a.live_idx, n_slots, blockIdx.x, gridDim.x);
+    bwd_tile_loop<kWgrad, kKept>(a, smem, bar, tmem, parity, first_tile, a.live_idx, n_slots, blockIdx.x, gridDim.x);
 
     if (kWgrad && !first_tile && half == 0) {
         // lane = row of the transposed weight gradients: dW1^T [80 x 32], dW3^T [63 x 32], dW2^T [32 x 16], dW4^T [32 x 3]
@@ -154,21 +154,23 @@ static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
     return (int)g;
 }
 
-template <bool kWgrad, bool kSaved>
+template <bool kWgrad, int kKept>
 static cudaError_t launch_points_bwd_tc_as(const PointsArgs& a, cudaStream_t st) {
     const size_t smem = tc::kBwdSmem;
     const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
-    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_bwd_tc_kernel<kWgrad, kSaved>), smem);
+    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_bwd_tc_kernel<kWgrad, kKept>), smem);
     if (e != cudaSuccess) return e;
-    points_bwd_tc_kernel<kWgrad, kSaved><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
+    points_bwd_tc_kernel<kWgrad, kKept><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
 cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st) {
-    if (a.dw1 == nullptr) return launch_points_bwd_tc_as<false, false>(a, st);
-    // kept features replace the second gather when no position gradient is asked for (it needs the corner values)
-    const bool saved = a.feat != nullptr && a.d_pts == nullptr && a.d_rays_o == nullptr;
-    return saved ? launch_points_bwd_tc_as<true, true>(a, st) : launch_points_bwd_tc_as<true, false>(a, st);
+    if (a.dw1 == nullptr) return launch_points_bwd_tc_as<false, 0>(a, st);
+    // kept rows replace the second gather: features alone when no position gradient is asked for, features + their derivatives else
+    const bool want_pos = a.d_pts != nullptr || a.d_rays_o != nullptr;
+    if (a.feat != nullptr && !want_pos) return launch_points_bwd_tc_as<true, 1>(a, st);
+    if (a.feat != nullptr && a.feat_stride == 4 * kGridFeats) return launch_points_bwd_tc_as<true, 2>(a, st);
+    return launch_points_bwd_tc_as<true, 0>(a, st);
 }
 
 // number of leading dense levels when the scene is "dense levels first, hashed levels after" over all 16 levels, else -1
@@ -181,22 +183,27 @@ static int dense_prefix(const SceneDev& sc) {
     return k;
 }
 
-template <int kDense>
+template <int kDense, bool kJac>
 static cudaError_t launch_points_fwd_tc_as(const PointsArgs& a, cudaStream_t st) {
     const size_t smem = tc::kFwdSmem;
-    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_fwd_tc_kernel<kDense>), smem);
+    cudaError_t e = allow_dynamic_smem(reinterpret_cast<const void*>(points_fwd_tc_kernel<kDense, kJac>), smem);
     if (e != cudaSuccess) return e;
     const int64_t n_tiles = (a.n_points + tc::kTile - 1) / tc::kTile;
-    points_fwd_tc_kernel<kDense><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
+    points_fwd_tc_kernel<kDense, kJac><<<tc_persistent_grid(n_tiles, 2), tc::kThreads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
-cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st) {
+template <bool kJac>
+static cudaError_t launch_points_fwd_tc_jac(const PointsArgs& a, cudaStream_t st) {
     switch (dense_prefix(a.scene)) {          // 5: room0 / fr1_desk (and every Replica / TUM scene), 6: scene0000
-        case 5: return launch_points_fwd_tc_as<5>(a, st);
-        case 6: return launch_points_fwd_tc_as<6>(a, st);
-        default: return launch_points_fwd_tc_as<-1>(a, st);
+        case 5: return launch_points_fwd_tc_as<5, kJac>(a, st);
+        case 6: return launch_points_fwd_tc_as<6, kJac>(a, st);
+        default: return launch_points_fwd_tc_as<-1, kJac>(a, st);
     }
+}
+
+cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st) {
+    return (a.feat != nullptr && a.feat_stride == 4 * kGridFeats) ? launch_points_fwd_tc_jac<true>(a, st) : launch_points_fwd_tc_jac<false>(a, st);
 }
 
 }  // namespace cb200

@@ -117,7 +117,7 @@ __device__ __forceinline__ void tile_store4(uint32_t hi_base, uint32_t lo_base, 
 }
 
 // the pair's per-corner partial features of one chunk (4 levels x 2) -> complete features; thread xb keeps columns 4 xb .. 4 xb + 3
-// keep (optional): the point's row of PointsArgs::feat -- the fp32 features are streamed out for the backward as well
+// keep (optional): where this thread's four fp32 features go in the point's row of PointsArgs::feat (streamed out for the backward)
 __device__ __forceinline__ void pair_combine_store(const float (&part)[8], int xb, uint32_t a_hi, uint32_t a_lo, int row, int c,
                                                    float* keep = nullptr) {
     float mine[4];
@@ -128,11 +128,29 @@ __device__ __forceinline__ void pair_combine_store(const float (&part)[8], int x
         mine[i] = (xb ? part[4 + i] : part[i]) + recv;
     }
     tile_store4(a_hi, a_lo, kAGS, row, c, xb, mine);
-    if (keep) __stcs(reinterpret_cast<float4*>(keep + 8 * c + 4 * xb), make_float4(mine[0], mine[1], mine[2], mine[3]));
+    if (keep) __stcs(reinterpret_cast<float4*>(keep), make_float4(mine[0], mine[1], mine[2], mine[3]));
 }
 
-// one chunk (4 levels, 8 features) of hash-grid features -> A tile; 16 gathers in flight per thread
-template <int kDense>
+// where thread xb's four columns of chunk c start in a kept row of `stride` floats (32: features only; 128: see encode_grid_chunk)
+__device__ __forceinline__ int kept_offset(int stride, int c, int xb) { return stride == kGridFeats ? 8 * c + 4 * xb : 32 * c + 4 * xb; }
+
+// the same exchange for one derivative of the chunk's features: thread xb streams columns 4 xb .. 4 xb + 3 to dst[8 c + 4 xb ..]
+__device__ __forceinline__ void pair_combine_keep(const float (&part)[8], int xb, float* dst) {
+    float mine[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float send = xb ? part[i] : part[4 + i];
+        const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+        mine[i] = (xb ? part[4 + i] : part[i]) + recv;
+    }
+    __stcs(reinterpret_cast<float4*>(dst), make_float4(mine[0], mine[1], mine[2], mine[3]));
+}
+
+// one chunk (4 levels, 8 features) of hash-grid features -> A tile; 16 gathers in flight per thread.
+// kJac: the kept row holds the features' derivatives along the normalised position as well, one 128-byte line per chunk --
+// [chunk c][feat | d/dx | d/dy | d/dz][thread xb][columns 8c + 4xb .. + 3] -- so that every store (and every load of the backward) of a
+// lane pair is one whole 32-byte sector; they come from the corner values that are in registers anyway.
+template <int kDense, bool kJac>
 __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row,
                                                   float* keep
 #ifdef CB200_PHASE_CLOCKS
@@ -161,6 +179,7 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
     long long t2 = clock64();
 #endif
     float part[8];
+    float jx[8], jy[8], jz[8];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         float f0 = 0.f, f1 = 0.f;
@@ -172,8 +191,31 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
         }
         part[2 * q] = f0;
         part[2 * q + 1] = f1;
+        if (kJac) {
+            // d/dx: (value at x+1) - (value at x), bilinear in (y, z): this thread contributes its side with its sign;
+            // d/dy, d/dz: this thread's x weight times the differences along y / z
+            const float scale = a.scene.scale[4 * c + q];
+            const float sx = xb ? scale : -scale, sw = scale * wx[q];
+            // y-interpolated values at z0 / z1 (lo, hi) and the y differences there; value at this x = lo + w2 (hi - lo)
+            const float dy0x = v[q][1].x - v[q][0].x, dy1x = v[q][3].x - v[q][2].x;
+            const float dy0y = v[q][1].y - v[q][0].y, dy1y = v[q][3].y - v[q][2].y;
+            const float lox = fmaf(w1[q], dy0x, v[q][0].x), hix = fmaf(w1[q], dy1x, v[q][2].x);
+            const float loy = fmaf(w1[q], dy0y, v[q][0].y), hiy = fmaf(w1[q], dy1y, v[q][2].y);
+            jx[2 * q] = sx * fmaf(w2[q], hix - lox, lox);
+            jx[2 * q + 1] = sx * fmaf(w2[q], hiy - loy, loy);
+            jy[2 * q] = sw * fmaf(w2[q], dy1x - dy0x, dy0x);
+            jy[2 * q + 1] = sw * fmaf(w2[q], dy1y - dy0y, dy0y);
+            jz[2 * q] = sw * (hix - lox);
+            jz[2 * q + 1] = sw * (hiy - loy);
+        }
     }
-    pair_combine_store(part, xb, a_hi, a_lo, row, c, keep);
+    float* const mine_at = keep ? keep + kept_offset(kJac ? 4 * kGridFeats : kGridFeats, c, xb) : nullptr;
+    pair_combine_store(part, xb, a_hi, a_lo, row, c, mine_at);
+    if (kJac) {
+        pair_combine_keep(jx, xb, mine_at + 8);
+        pair_combine_keep(jy, xb, mine_at + 16);
+        pair_combine_keep(jz, xb, mine_at + 24);
+    }
 #ifdef CB200_PHASE_CLOCKS
     long long t3 = clock64();
     sub[0] += t1 - t0; sub[1] += t2 - t1; sub[2] += t3 - t2;
@@ -259,7 +301,7 @@ __device__ __forceinline__ void mask16_to_tile(const uint32_t (&r)[16], uint32_t
 // Expects the weights staged (stage_all_weights), `bar` initialised with count 1, at least kTmemCols TMEM columns at `tmem`;
 // `parity` is the phase the next wait on `bar` expects and is left up to date.  Called by points_fwd_tc_kernel and by the
 // one-launch tracking loop (track_frame_kernel).
-template <int kDense>
+template <int kDense, bool kJac = false>
 __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char* smem, uint64_t& bar, uint32_t tmem, uint32_t& parity,
                                               const uint32_t* list, int64_t n_slots, int64_t tile_begin, int64_t tile_step) {
     using namespace tc;
@@ -299,12 +341,13 @@ __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char
             const int64_t pg = list ? (int64_t)list[pg_slot] : pg_slot;
             float x[3], zdummy;
             point_position(a, pg, x, zdummy);
-            float* const keep = a.feat ? a.feat + pg * kGridFeats : nullptr;      // padding slots repeat the last point: same values
+            // padding slots repeat the last point: same values
+            float* const keep = (kJac || a.feat) ? a.feat + pg * a.feat_stride : nullptr;
 #pragma unroll
 #ifdef CB200_PHASE_CLOCKS
-            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g, keep, sub);
+            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense, kJac>(a, x, xb, c, a_hi, a_lo, row_g, keep, sub);
 #else
-            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense>(a, x, xb, c, a_hi, a_lo, row_g, keep);
+            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense, kJac>(a, x, xb, c, a_hi, a_lo, row_g, keep);
 #endif
             PH(0);
 #pragma unroll
@@ -459,9 +502,10 @@ constexpr int kBwdTmemCols = 256;
 
 // The persistent tile loop of the backward (same contract as fwd_tile_loop; kBwdTmemCols columns; additionally expects the fp32
 // copy of W4 at kBOffW4f).  first_tile: no weight-gradient product has been accumulated in TMEM yet (kWgrad).
-// kSaved (with kWgrad): the hash-grid features come from PointsArgs::feat (kept by the forward) instead of a second gather of the table;
-// no position gradient in that mode (it needs the corner values).
-template <bool kWgrad, bool kSaved = false>
+// kKept (with kWgrad): the hash-grid features come from PointsArgs::feat (kept by the forward) instead of a second gather of the table.
+// 1: rows of 32 features, no position gradient (it needs the corner values); 2: rows of [feat | d feat/dx | d feat/dy | d feat/dz],
+// position gradient = d embed . those derivatives.
+template <bool kWgrad, int kKept = 0>
 __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char* smem, uint64_t& bar, uint32_t tmem, uint32_t& parity,
                                               bool& first_tile, const uint32_t* list, int64_t n_slots, int64_t tile_begin,
                                               int64_t tile_step) {
@@ -582,10 +626,19 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
         for (int c = 0; c < 4; ++c) {
             uint32_t de_raw[8];
             tmem_ld_x8(trow + kColDin1 + 8 * c, de_raw);        // d embed of levels 4c .. 4c+3, row = this lane's TMEM lane
-            if (kSaved) {
-                // table scatter only: thread xb takes columns 8c + 4xb .. + 3 of the point's kept feature row
-                float4 kept = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (live) kept = __ldcs(reinterpret_cast<const float4*>(a.feat + pg * kGridFeats + 8 * c + 4 * xb));
+            if (kKept) {
+                // table scatter only: thread xb takes columns 8c + 4xb .. + 3 of the point's kept row
+                const float* const krow = a.feat + pg * a.feat_stride + kept_offset(kKept == 2 ? 4 * kGridFeats : a.feat_stride, c, xb);
+                float4 kept = make_float4(0.f, 0.f, 0.f, 0.f), jac[3];
+                if (live) kept = __ldcs(reinterpret_cast<const float4*>(krow));
+                if (kKept == 2) {
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) {
+                        jac[d] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (live) jac[d] = __ldcs(reinterpret_cast<const float4*>(krow + 8 * (d + 1)));
+                    }
+                }
+                float dm[4] = {0.f, 0.f, 0.f, 0.f};      // d embed of this thread's columns (levels 4c + 2xb, 4c + 2xb + 1)
                 uint32_t idx[4][4];
                 float wx[4], w1[4], w2[4];
 #pragma unroll
@@ -606,6 +659,15 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
                         const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
                         if (dtab && live) red_add_f2(dtab + idx[q][j], wc * de0, wc * de1);
                     }
+                    if (kKept == 2 && (q >> 1) == xb) {
+                        dm[2 * (q & 1)] = de0;
+                        dm[2 * (q & 1) + 1] = de1;
+                    }
+                }
+                if (kKept == 2) {
+#pragma unroll
+                    for (int d = 0; d < 3; ++d)
+                        dx[d] = fmaf(dm[0], jac[d].x, fmaf(dm[1], jac[d].y, fmaf(dm[2], jac[d].z, fmaf(dm[3], jac[d].w, dx[d]))));
                 }
                 const float mine[4] = {kept.x, kept.y, kept.z, kept.w};
                 tile_store4(a_hi, a_lo, kAGS, row_g, c, xb, mine);
@@ -677,7 +739,7 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
 #pragma unroll
         for (int d = 0; d < 3; ++d) {
             float val[8], dval[8];
-            if (kSaved) {
+            if (kKept == 1) {
                 blob_half<false>(x[d], xb, val, dval);
                 tile_store8(a_hi, a_lo, kAGS, row_g, 4 + 2 * d + xb, val);
                 continue;
@@ -700,7 +762,7 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
         for (int d = 0; d < 3; ++d) dx[d] += __shfl_xor_sync(0xffffffffu, dx[d], 1);      // both threads of the pair: full dL/dx
 
         // ---- position gradient (pair leader) ----------------------------------------------------------------------------------
-        if (!kSaved) {
+        if (kKept != 1) {
             float dp[3];
 #pragma unroll
             for (int d = 0; d < 3; ++d) dp[d] = valid_g ? (a.scene.normalise ? dx[d] / a.scene.bb_ext[d] : dx[d]) : 0.f;

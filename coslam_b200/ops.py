@@ -269,9 +269,18 @@ def _check_weights(w1, w2, w3, w4):
                            [tuple(w.shape) for w in (w1, w2, w3, w4)])
 
 
-KEEP_FEATURES = True     # map-only steps keep the hash-grid features of the forward for the backward (RayPointsFunction)
+KEEP_FEATURES = True     # training steps keep the hash-grid features of the forward for the backward (RayPointsFunction) ...
+KEEP_DERIVATIVES = True  # ... and, when the rays carry a gradient, the features' position derivatives as well
 LAZY_FORWARD = True      # training forward evaluates only the sample points the step can depend on (lazy_ray_forward)
 LAZY_MIN_POINTS = 1 << 18   # below ~7 waves of tiles (tracking / BA batches) the three extra launches cost more than the skipped points save
+
+
+def _kept_width(feat):
+    """with_derivatives of cb200_points_fwd_keep / cb200_points_bwd_kept from the shape of the kept rows: [P,32] features, [P,128]
+    features and their three position derivatives."""
+    if feat.dim() != 2 or feat.shape[1] not in (N_GRID_FEATS, 4 * N_GRID_FEATS) or not feat.is_contiguous() or feat.dtype != torch.float32:
+        raise ValueError('kept rows must be a contiguous fp32 [P,32] or [P,128] tensor')
+    return 1 if feat.shape[1] == 4 * N_GRID_FEATS else 0
 
 
 def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo=False, want_mask=True, sdf_only=False,
@@ -300,7 +309,8 @@ def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo
     if feat is not None:
         _timed('points_fwd', lambda: check(_lib.load().cb200_points_fwd_keep(
             ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
-            ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask), 1 if sdf_only else 0, lst, cnt, ptr(feat), stream()), 'points_fwd_keep'))
+            ctypes.c_int64(s), ptr(raw), ptr(geo), ptr(mask), 1 if sdf_only else 0, lst, cnt, ptr(feat), _kept_width(feat), stream()),
+            'points_fwd_keep'))
         return raw, geo, mask
     _timed('points_fwd', lambda: check(_lib.load().cb200_points_fwd(
         ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
@@ -379,11 +389,11 @@ def points_backward(scene, table, w, mask, d_raw, d_geo=None, pts=None, rays=Non
     elif rays is not None and d_geo is None:
         wsp_bytes = int(_lib.load().cb200_points_bwd_workspace(ctypes.c_int64(n * s)))
         wsp = torch.empty((wsp_bytes + 3) // 4, dtype=torch.int32, device=dev)
-    if feat is not None and gblock is not None and d_pts is None and d_o is None:
+    if feat is not None and gblock is not None and (_kept_width(feat) or (d_pts is None and d_o is None)):
         _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd_kept(
             ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
-            ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(feat), ptr(d_table), ctypes.byref(gblock),
-            1 if sdf_only else 0, ptr(wsp), ctypes.c_size_t(wsp_bytes), stream()), 'points_bwd_kept'))
+            ctypes.c_int64(s), ptr(d_raw), ptr(d_geo), ptr(mask), ptr(feat), _kept_width(feat), ptr(d_table), ctypes.byref(gblock),
+            ptr(d_pts), ptr(d_o), ptr(d_d), 1 if sdf_only else 0, ptr(wsp), ctypes.c_size_t(wsp_bytes), stream()), 'points_bwd_kept'))
     else:
         _timed('points_bwd', lambda: check(_lib.load().cb200_points_bwd(
             ctypes.byref(scene), ptr(table), ctypes.byref(mlp), ptr(pts), ptr(o), ptr(d), ptr(z), ctypes.c_int64(n),
@@ -414,11 +424,14 @@ class RayPointsFunction(torch.autograd.Function):
         # gather the table a second time (128 B per point of scratch; without the memory the step runs as before)
         feat = None
         need = ctx.needs_input_grad
-        if KEEP_FEATURES and tc and z.numel() > 0 and any(need[4:8]) and not (need[0] or need[1]):
-            try:
-                feat = torch.empty((z.numel(), N_GRID_FEATS), dtype=torch.float32, device=z.device)
-            except torch.cuda.OutOfMemoryError:
-                feat = None
+        if KEEP_FEATURES and tc and z.numel() > 0 and any(need[4:8]):
+            # with ray gradients the rows also hold d feature / d position (512 B per point instead of 128)
+            width = 4 * N_GRID_FEATS if (need[0] or need[1]) else N_GRID_FEATS
+            if width == N_GRID_FEATS or KEEP_DERIVATIVES:
+                try:
+                    feat = torch.empty((z.numel(), width), dtype=torch.float32, device=z.device)
+                except torch.cuda.OutOfMemoryError:
+                    feat = None
         if lazy:
             _check_weights(*w)
             raw, mask = lazy_ray_forward(spec, tb, w, (o, d, z), target_d, want_mask=need_grad, feat=feat)

@@ -331,21 +331,28 @@ int cb200_points_bwd(const cb200_scene* scene, const float* table, const cb200_m
                      float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts, float* d_rays_o, float* d_rays_d,
                      int sdf_only, void* workspace, size_t workspace_bytes, void* stream);
 
-/* The pair for a step that optimises the map but no pose (the batch of model/scene_rep.py:297-351 with fixed rays): the forward
- * also keeps the 32 hash-grid features of every point it evaluates, feat [P,32] fp32 (tcnn.Encoding(HashGrid) output order:
- * level-major, 2 per level; rows of points it does not evaluate are left untouched), and the backward reads them back instead of
- * gathering 128 table entries per point a second time -- 128 B of streamed HBM traffic per point for 1 KB of L2 gathers.  No position
- * gradient (it needs the corner values: use cb200_points_bwd).  Tensor-core decoder only; d_mlp must be given; every point with
- * non-zero d_raw must have been evaluated by the forward that wrote `feat`.  Same results as cb200_points_fwd / cb200_points_bwd. */
+/* The pair that does not gather twice (tensor-core decoder, weight-gradient backward: d_mlp must be given).  cb200_points_bwd reads
+ * the 128 table entries of every point a second time, for the features (operand of the weight-gradient products) and for the position
+ * gradient (d feature / dx is a combination of the corner values).  Here the forward keeps what the backward needs, per point it
+ * evaluates (rows of other points are left untouched), and the backward's level loop is index arithmetic + red.v2 only:
+ *   with_derivatives == 0: feat [P,32] fp32, the tcnn.Encoding(HashGrid) output (level-major, 2 per level) -- 128 B per point of
+ *       streamed HBM traffic instead of 1 KB of L2 gathers.  No position gradient (d_pts, d_rays_o, d_rays_d must be NULL): the step
+ *       of model/scene_rep.py:297-351 on fixed rays (first-frame mapping, mapping on given poses).
+ *   with_derivatives != 0: feat [P,128] = [features | d/dx | d/dy | d/dz of them] (x = the normalised position the encoding sees);
+ *       the position gradient is d embed . those rows, so d_pts / d_rays_o / d_rays_d work as in cb200_points_bwd (512 B per point).
+ * Every point with non-zero d_raw must have been evaluated by the forward that wrote `feat`.  Results equal cb200_points_fwd /
+ * cb200_points_bwd up to fp32 summation order. */
 int cb200_points_fwd_keep(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
                           const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
                           int64_t n_samples, float* raw, float* geo, uint32_t* act_mask, int sdf_only,
-                          const uint32_t* point_list, const uint64_t* point_count, float* feat, void* stream);
+                          const uint32_t* point_list, const uint64_t* point_count, float* feat, int with_derivatives,
+                          void* stream);
 int cb200_points_bwd_kept(const cb200_scene* scene, const float* table, const cb200_mlp* mlp, const float* pts,
                           const float* rays_o, const float* rays_d, const float* z_vals, int64_t n_rays,
                           int64_t n_samples, const float* d_raw, const float* d_geo, const uint32_t* act_mask,
-                          const float* feat, float* dtable, const cb200_mlp_grad* d_mlp, int sdf_only, void* workspace,
-                          size_t workspace_bytes, void* stream);
+                          const float* feat, int with_derivatives, float* dtable, const cb200_mlp_grad* d_mlp, float* d_pts,
+                          float* d_rays_o, float* d_rays_d, int sdf_only, void* workspace, size_t workspace_bytes,
+                          void* stream);
 
 /* raw2outputs + sdf2weights (model/scene_rep.py:77-124) and, when loss_sums != NULL, the loss head
  * (model/scene_rep.py:319-338, model/utils.py:138-161).

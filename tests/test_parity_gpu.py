@@ -1142,10 +1142,10 @@ def test_lazy_forward_is_exact(cfg_name, kind):
 
 
 @pytest.mark.parametrize('cfg_name,lazy', [('room0', True), ('room0', False), ('scannet0000', True)])
-def test_map_only_step_with_kept_features_matches_the_gathering_backward(cfg_name, lazy):
-    """A step whose rays carry no gradient (fixed poses) keeps the hash-grid features of the forward and its backward reads them back
-    instead of gathering the table again (cb200_points_fwd_keep / cb200_points_bwd_kept).  Same outputs; gradients equal up to the
-    summation order of their atomics; and the weight / table gradients are the ones of the step WITH ray gradients."""
+def test_step_with_kept_rows_matches_the_gathering_backward(cfg_name, lazy):
+    """The training forward keeps, per evaluated point, the hash-grid features (rays without gradient: 128 B) or the features and
+    their position derivatives (rays with gradient: 512 B), and the backward reads them back instead of gathering the table again
+    (cb200_points_fwd_keep / cb200_points_bwd_kept).  Same outputs, bit for bit; gradients equal up to fp32 summation order."""
     cfg = synth.CONFIGS[cfg_name]()
     n_rays = 3000
     rays_o, rays_d, rgb, depth = synth.ray_batch(cfg, n_rays, seed=21)
@@ -1153,22 +1153,32 @@ def test_map_only_step_with_kept_features_matches_the_gathering_backward(cfg_nam
     table = synth.table_init(JointEncodingFor(cfg).embed_fn.params.numel(), 'trained', seed=78)
     res = {}
     min_points, ops.LAZY_MIN_POINTS = ops.LAZY_MIN_POINTS, (1 if lazy else 1 << 62)
+    seen = []
+    real = ops.points_backward
+
+    def spy(*a, **kw):
+        seen.append(None if kw.get('feat') is None else int(kw['feat'].shape[1]))
+        return real(*a, **kw)
+    ops.points_backward = spy
     try:
-        for mode in ('kept', 'gathered', 'with_ray_grads'):
+        for mode, keep, ray_grads in (('fixed rays, kept', True, False), ('fixed rays, gathered', False, False),
+                                      ('ray gradients, kept', True, True), ('ray gradients, gathered', False, True)):
             model = util.make_cuda_model(cfg, table, weights, DEV)
-            ops.KEEP_FEATURES = mode != 'gathered'
+            ops.KEEP_FEATURES = keep
             o, d = rays_o.to(DEV), rays_d.to(DEV)
-            if mode == 'with_ray_grads':
+            if ray_grads:
                 o, d = o.requires_grad_(True), d.requires_grad_(True)
             torch.manual_seed(3)
             ret = model.forward(o, d, rgb.to(DEV), depth.to(DEV))
             _weighted_loss(cfg, ret).backward()
-            res[mode] = (ret, model.embed_fn.params.grad, [w.grad for w in model.decoder.fused_weights()])
+            res[mode] = (ret, model.embed_fn.params.grad, [w.grad for w in model.decoder.fused_weights()], o.grad, d.grad)
     finally:
         ops.KEEP_FEATURES = True
         ops.LAZY_MIN_POINTS = min_points
-    a = res['kept']
-    for other in ('gathered', 'with_ray_grads'):
+        ops.points_backward = real
+    assert seen == [32, None, 128, None]                     # the kept rows were what the backward ran on
+    a = res['fixed rays, kept']
+    for other in list(res)[1:]:
         b = res[other]
         for k in ('rgb', 'depth', 'rgb_loss', 'depth_loss', 'sdf_loss', 'fs_loss'):
             assert torch.equal(a[0][k], b[0][k]), (other, k)
@@ -1176,6 +1186,10 @@ def test_map_only_step_with_kept_features_matches_the_gathering_backward(cfg_nam
         for x, y in zip(a[2], b[2]):
             util.assert_close(x, y, 'dW vs ' + other, tol=2e-5)
     assert float(a[1].abs().max()) > 0 and all(float(x.abs().max()) > 0 for x in a[2])
+    k, g = res['ray gradients, kept'], res['ray gradients, gathered']
+    assert float(g[3].abs().max()) > 0 and float(g[4].abs().max()) > 0
+    util.assert_close(k[3], g[3], 'd_rays_o from the kept derivatives', tol=2e-5)
+    util.assert_close(k[4], g[4], 'd_rays_d from the kept derivatives', tol=2e-5)
 
 
 def test_kept_feature_rows_are_the_hash_encoding():

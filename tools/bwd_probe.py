@@ -70,8 +70,10 @@ def main():
     live = float((d_raw.reshape(-1, 4) != 0).any(1).float().mean())
     P = d_raw.numel() // 4
     print('workload %s rays %d points %d live %.4f' % (args.workload, args.rays, P, live), flush=True)
+    kw = dict(kw, feat=None)                       # the step above may have kept rows: the lines below time the gathering backward
     if 'fwd' in captured:
         fa, fkw = captured['fwd']
+        fkw = dict(fkw, feat=None)
         print('fwd (lazy, two launches)   %.3f ms' % timed(lambda: real_fwd(*fa, **fkw), args.reps), flush=True)
     for name, over in (('bwd full', {}), ('bwd no table grad', dict(need_table=False)), ('bwd no mlp grad', dict(need_mlp=False)),
                        ('bwd no pos grad', dict(need_pos=False)), ('bwd pos only', dict(need_table=False, need_mlp=False))):
@@ -93,6 +95,20 @@ def main():
         got = real_bwd(*a, **k)
         torch.cuda.synchronize()
         for n_, x, y in [('d_table', ref[0], got[0])] + [('dW%d' % (i + 1), ref[1][i], got[1][i]) for i in range(4)]:
+            print('kept vs gathered %-8s max |diff| %.3e of max %.3e' % (n_, float((x - y).abs().max()), float(x.abs().max())), flush=True)
+    if 'fwd' in captured:
+        # the same with the derivatives kept as well (512 B per point): the full backward, ray gradients included, without a gather
+        feat4 = torch.empty((P, 128), dtype=torch.float32, device=DEV)
+        print('fwd keeping feat + d/dx    %.3f ms' % timed(lambda: real_fwd(*fa, **dict(fkw, feat=feat4)), args.reps), flush=True)
+        k = dict(kw)
+        k.update(feat=feat4)
+        ms = timed(lambda: real_bwd(*a, **k), args.reps)
+        print('%-26s %.3f ms   %.1f M live points/s' % ('bwd full from kept rows', ms, P * live / ms / 1e3), flush=True)
+        ref = real_bwd(*a, **kw)
+        got = real_bwd(*a, **k)
+        torch.cuda.synchronize()
+        for n_, x, y in [('d_table', ref[0], got[0])] + [('dW%d' % (i + 1), ref[1][i], got[1][i]) for i in range(4)] + \
+                [('d_rays_o', ref[2][0], got[2][0]), ('d_rays_d', ref[2][1], got[2][1])]:
             print('kept vs gathered %-8s max |diff| %.3e of max %.3e' % (n_, float((x - y).abs().max()), float(x.abs().max())), flush=True)
     if args.check:
         d_table, d_w, (d_o, d_d) = real_bwd(*a, **kw)
