@@ -415,6 +415,7 @@ def run_ours(args):
             # the capture's DRAM bytes scale with the live points of a launch (the table stays in L2; HBM sees the per-point streams)
             per_point = traffic_src['dram_bytes_per_launch'] / (traffic_src['live_points'] or NCU_V9_LIVE_POINTS)
             traffic = per_point * live_points
+        from coslam_b200 import ops as ops_mod
         roofline = {'bound': 'hbm', 'kernel': 'points_bwd_tc_kernel<wgrad>' if tc else 'points_bwd_kernel<wgrad>', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                     'frac': achieved / peak, 'traffic': traffic,
                     'traffic_source': ('%s: dram bytes per live point of that capture x live points of this launch' % traffic_src['file']) if traffic_src else None,
@@ -423,6 +424,13 @@ def run_ours(args):
                     'fwd_kernel': {'kernel': 'points_fwd_tc_kernel' if tc else 'points_fwd_kernel', 'avg_launch_ms': k_fwd,
                                    'evaluated_point_fraction': eval_frac,
                                    'achieved': P * eval_frac * BYTES_PER_POINT_FWD / (k_fwd * 1e-3) / 1e9},
+                    # the training step keeps rows in the forward so that the backward does not gather twice (ops.KEEP_FEATURES /
+                    # KEEP_DERIVATIVES): the backward's fraction rose at the forward's expense, so the pair is stated as well
+                    'kept_rows': {'enabled': bool(tc and ops_mod.KEEP_FEATURES and ops_mod.KEEP_DERIVATIVES), 'bytes_per_point': 512,
+                                  'note': 'same algorithmic bytes (SURVEY 8d: 1 024 B/pt forward, 2 048 B/pt backward); the backward streams 512 B/pt '
+                                          'written by the forward instead of gathering 1 024 B/pt again'},
+                    'fwd_bwd_pair': {'achieved': (bwd_bytes + P * eval_frac * BYTES_PER_POINT_FWD) / ((k_fwd + k_bwd) * 1e-3) / 1e9,
+                                     'frac': (bwd_bytes + P * eval_frac * BYTES_PER_POINT_FWD) / ((k_fwd + k_bwd) * 1e-3) / 1e9 / peak},
                     'share_of_step': (k_fwd + k_bwd) / (ms / args.steps),
                     'kernel_ms_per_step': {k: sum(v) / args.steps for k, v in kt.items()}}
         if gather_peak is not None and 'gather_reduce_GBps' in gather_peak:
@@ -496,9 +504,14 @@ def ncu_traffic_per_point(kernel='points_bwd_tc_kernel'):
         text = open(path).read()
         if kernel not in text:
             continue
+        pts = re.search(r'live_points:\s*([0-9]+)', text)
+        # the summary may hold several kernels: read the section of the first launch of `kernel`
+        sec = [b for b in text.split('\nkernel: ')[1:] if kernel in b.split('\n', 1)[0]]
+        if not sec:
+            continue
+        text = sec[0]
         rd = re.search(r'dram__bytes_read\.sum\s+([0-9.]+) (\w)byte', text)
         wr = re.search(r'dram__bytes_write\.sum\s+([0-9.]+) (\w)byte', text)
-        pts = re.search(r'live_points:\s*([0-9]+)', text)
         if not (rd and wr):
             continue
         unit = {'K': 1e3, 'M': 1e6, 'G': 1e9}
