@@ -275,6 +275,16 @@ LAZY_FORWARD = True      # training forward evaluates only the sample points the
 LAZY_MIN_POINTS = 1 << 18   # below ~7 waves of tiles (tracking / BA batches) the three extra launches cost more than the skipped points save
 
 
+def _kept_rows_fit(nbytes, device, fraction=0.6):
+    """Kept rows are an optimisation, never a reason to run out of memory: large ones (> 1 GB) are only allocated when they take at
+    most `fraction` of what the device still has (driver-free memory + the caching allocator's unused reserve)."""
+    if nbytes <= (1 << 30):
+        return True
+    free, _ = torch.cuda.mem_get_info(device)
+    free += torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
+    return nbytes <= fraction * free
+
+
 def _kept_width(feat):
     """with_derivatives of cb200_points_fwd_keep / cb200_points_bwd_kept from the shape of the kept rows: [P,32] features, [P,128]
     features and their three position derivatives."""
@@ -427,7 +437,7 @@ class RayPointsFunction(torch.autograd.Function):
         if KEEP_FEATURES and tc and z.numel() > 0 and any(need[4:8]):
             # with ray gradients the rows also hold d feature / d position (512 B per point instead of 128)
             width = 4 * N_GRID_FEATS if (need[0] or need[1]) else N_GRID_FEATS
-            if width == N_GRID_FEATS or KEEP_DERIVATIVES:
+            if (width == N_GRID_FEATS or KEEP_DERIVATIVES) and _kept_rows_fit(z.numel() * width * 4, z.device):
                 try:
                     feat = torch.empty((z.numel(), width), dtype=torch.float32, device=z.device)
                 except torch.cuda.OutOfMemoryError:
