@@ -92,7 +92,8 @@ class BaPlan(ctypes.Structure):
                 ('map_params', ctypes.c_void_p), ('n_map_params', ctypes.c_int64),
                 ('rot', ctypes.c_void_p), ('trans', ctypes.c_void_p), ('pose_adam', ctypes.c_void_p), ('n_free', ctypes.c_int64),
                 ('n_rot', ctypes.c_int32), ('lr_rot', ctypes.c_float), ('lr_trans', ctypes.c_float),
-                ('rank', ctypes.c_void_p), ('new_list', ctypes.c_void_p), ('new_count', ctypes.c_void_p)]
+                ('rank', ctypes.c_void_p), ('new_list', ctypes.c_void_p), ('new_count', ctypes.c_void_p),
+                ('kept', ctypes.c_void_p), ('kept_derivatives', ctypes.c_int64)]
 
 
 EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb200_grid_meta', 'cb200_hash_fwd',

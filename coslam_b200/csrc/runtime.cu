@@ -57,6 +57,22 @@ __global__ void add_coarse_sums_kernel(double* sums, const double* sums0) {
 // at the start of the optimise phase
 bool fused_loss_head(const cb200_ba_plan* p) { return p->n_importance == 0 && p->bwd_ws != nullptr; }
 
+// kept rows (cb200_points_fwd_keep / cb200_points_bwd_kept): the single-pass iteration with the fused loss head, on the tensor-core
+// decoder, with rows wide enough for the ray gradients when poses are optimised
+bool kept_rows(const cb200_ba_plan* p) {
+    return p->kept != nullptr && fused_loss_head(p) && cb200_get_decoder() == 1 && (p->kept_derivatives != 0 || p->d_rays == nullptr);
+}
+
+// per-point forward of the merged / only sample set over an optional point list
+int points_fwd(const cb200_ba_plan* p, const uint32_t* list, const uint64_t* count, void* stream) {
+    const int64_t n = p->n_global + p->n_cur, S = p->n_samples + p->n_importance;
+    if (kept_rows(p))
+        return cb200_points_fwd_keep(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0,
+                                     list, count, p->kept, (int)p->kept_derivatives, stream);
+    return cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0, list,
+                            count, stream);
+}
+
 int ba_forward(const cb200_ba_plan* p, int64_t it, bool do_rays, bool do_points, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t g = p->n_global, n = p->n_global + p->n_cur, S0 = p->n_samples, I = p->n_importance, S = S0 + I;
@@ -110,14 +126,11 @@ int ba_forward(const cb200_ba_plan* p, int64_t it, bool do_rays, bool do_points,
         const uint64_t* count = reinterpret_cast<const uint64_t*>(base);
         const uint32_t* list = reinterpret_cast<const uint32_t*>(base + 16 + 4 * n);      // layout of cb200_lazy_workspace
         CB_TRY(cb200_lazy_prefix(p->render, p->z_vals, p->target_d, n, S, p->lazy_ws, p->lazy_ws_bytes, stream));
-        CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0, list,
-                                count, stream));
+        CB_TRY(points_fwd(p, list, count, stream));
         CB_TRY(cb200_lazy_resolve(p->render, p->z_vals, p->target_d, p->raw, n, S, p->lazy_ws, p->lazy_ws_bytes, stream));
-        CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0, list,
-                                count, stream));
+        CB_TRY(points_fwd(p, list, count, stream));
     } else {
-        CB_TRY(cb200_points_fwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->raw, nullptr, p->act_mask, 0,
-                                nullptr, nullptr, stream));
+        CB_TRY(points_fwd(p, nullptr, nullptr, stream));
     }
     if (fused_loss_head(p)) return 0;             // the loss sums are taken by the backward phase's fused launch
     CB_TRY(cb200_render_fwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
@@ -138,8 +151,13 @@ int ba_backward(const cb200_ba_plan* p, int64_t it, void* stream) {
     if (fused_loss_head(p)) {
         CB_TRY(cb200_render_loss_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, counts, n_total, &p->loss_w, sums,
                                      p->loss_out + 4, p->d_raw, p->bwd_ws, p->bwd_ws_bytes, 0, stream));
-        CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask,
-                                p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, 0, stream));
+        if (kept_rows(p))
+            CB_TRY(cb200_points_bwd_kept(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask,
+                                         p->kept, (int)p->kept_derivatives, p->g_table, &p->g_mlp, nullptr, p->d_rays,
+                                         p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, 0, stream));
+        else
+            CB_TRY(cb200_points_bwd(p->scene, p->table, &p->mlp, nullptr, p->rays_o, p->rays_d, p->z_vals, n, S, p->d_raw, nullptr, p->act_mask,
+                                    p->g_table, &p->g_mlp, nullptr, p->d_rays, p->d_rays ? p->d_rays + 3 * n : nullptr, 0, p->bwd_ws, 0, stream));
     } else {
         CB_TRY(cb200_loss_finish(sums, counts, n_total, S, p->loss_out, p->loss_out + 4, stream));
         CB_TRY(cb200_render_bwd(p->render, p->raw, p->z_vals, p->target_rgb, p->target_d, n, S, &p->loss_w, p->loss_out + 4, nullptr, nullptr,

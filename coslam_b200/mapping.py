@@ -46,6 +46,7 @@ class BundleAdjuster(object):
         self.last_losses = None                   # device [4] of the last iteration (rgb, depth, sdf, fs)
         self.last_tv = None                       # device double [1]: raw TV sum of the last iteration
         self.last_d_poses = None                  # [K+1,4,4] pose gradient accumulated since the last pose step
+        self.last_kept_width = 0                  # floats per point the last call's forward kept for its backward (0, 32 or 128)
         self._noise_calls = 0
         # non-parity index draws on the device (uniform, with replacement) for the large sweeps of BASELINE.json config 4:
         # `random.sample` of 2^22 out of 16 M rays is host-bound even in C
@@ -291,6 +292,16 @@ class BundleAdjuster(object):
             nbytes = int(lib.cb200_lazy_workspace(ctypes.c_int64(n), ctypes.c_int64(Sf)))
             lazy_ws = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
             P.lazy_ws, P.lazy_ws_bytes = dp(lazy_ws), nbytes
+        if lazy and I == 0 and ops.KEEP_FEATURES and lib.cb200_get_decoder() == 1:
+            # large batches: the forward keeps rows for the backward (features, + their position derivatives when poses are optimised)
+            width = 4 * ops.N_GRID_FEATS if d_rays is not None else ops.N_GRID_FEATS
+            if (width == ops.N_GRID_FEATS or ops.KEEP_DERIVATIVES) and ops._kept_rows_fit(n * Sf * width * 4, dev):
+                try:
+                    kept = torch.empty((n * Sf, width), **f32)
+                    P.kept, P.kept_derivatives = dp(kept), int(width != ops.N_GRID_FEATS)
+                    keep.append(kept)
+                except torch.cuda.OutOfMemoryError:
+                    pass
         bbytes = int(lib.cb200_points_bwd_workspace(ctypes.c_int64(n * Sf)))
         bwd_ws = torch.empty((bbytes + 3) // 4, dtype=torch.int32, device=dev)
         P.bwd_ws, P.bwd_ws_bytes = dp(bwd_ws), bbytes
@@ -397,6 +408,7 @@ class BundleAdjuster(object):
         _lib.KERNEL_LAUNCHES += iters * (17 + (3 if lazy else 0) + (4 if smooth_w > 0 else 0)) - iters
         del keep
         self.last_losses, self.last_tv, self.last_d_poses = loss_out[:4], ws[8:9], d_poses
+        self.last_kept_width = (4 * ops.N_GRID_FEATS if P.kept_derivatives else ops.N_GRID_FEATS) if P.kept else 0
         # ---- coslam.py:392-397 --------------------------------------------------------------------------------------------
         if n_free == 0:
             return kf_poses, cur_pose

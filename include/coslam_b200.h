@@ -487,6 +487,10 @@ typedef struct cb200_ba_plan {
     int32_t* rank;
     uint32_t* new_list;
     uint64_t* new_count;
+    /* kept rows, optional (n_importance == 0): [N*S, 32] fp32, or [N*S, 128] when kept_derivatives != 0 (required when d_rays != NULL);
+     * the iteration then runs cb200_points_fwd_keep / cb200_points_bwd_kept */
+    float* kept;
+    int64_t kept_derivatives;
 } cb200_ba_plan;
 
 /* phases: which part of iteration `it` to issue.  One GPU: all three in one call.  Rays sharded over several GPUs

@@ -147,6 +147,34 @@ def test_one_iteration_gradients_match_autograd(cfg_name):
         assert ba.last_d_poses.shape[0] == K + 1
 
 
+def test_large_batch_iteration_with_kept_rows_matches_autograd():
+    """Above ops.LAZY_MIN_POINTS points the native iteration runs the lazy forward and keeps rows for its backward
+    (cb200_points_fwd_keep / cb200_points_bwd_kept: features and their position derivatives, since poses are optimised).
+    Gradients against the autograd loop on the gathering kernels."""
+    from coslam_b200 import ops
+    cfg, model, db, kf_poses, cur_pose, current = _setup('room0')
+    cfg['mapping'].update({'iters': 1, 'map_accum_step': 2, 'pose_accum_step': 2})
+    ref_model = copy.deepcopy(model)
+    min_points, ops.LAZY_MIN_POINTS = ops.LAZY_MIN_POINTS, 1
+    try:
+        random.seed(11); torch.manual_seed(11)
+        ba = BundleAdjuster(model, cfg, db, _map_optimizer(cfg, model), DEV)
+        ba.run(kf_poses, cur_pose, current)
+        assert ba.last_kept_width == 128
+        ops.KEEP_FEATURES = False
+        random.seed(11); torch.manual_seed(11)
+        _, _, d_poses = _autograd_ba(cfg, ref_model, db, _map_optimizer(cfg, ref_model), kf_poses, cur_pose, current, keep_grads=True)
+    finally:
+        ops.LAZY_MIN_POINTS = min_points
+        ops.KEEP_FEATURES = True
+    torch.cuda.synchronize()
+    for (name, p), (_, q) in zip(model.named_parameters(), ref_model.named_parameters()):
+        if q.grad is None:
+            continue
+        assert _rel(p.grad, q.grad) <= 1e-3, name
+    assert _rel(ba.last_d_poses[1:, :3, :], d_poses[1:, :3, :]) <= 1e-3
+
+
 @pytest.mark.parametrize('cfg_name', ['room0', 'scannet0000'])
 def test_ba_call_matches_autograd_loop(cfg_name):
     """Six iterations with the reference's schedule exercised: decoder / table steps only after `map_wait_step`, gradient
