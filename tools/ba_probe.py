@@ -1,5 +1,5 @@
 """One bundle-adjustment call (room0 / scene0000 shapes, synthetic keyframe store) for profiling.
-    python tools/ba_probe.py [room0|scannet0000|tum_desk|tum_desk_imp] [time|ncu] [n_keyframes]
+    python tools/ba_probe.py [room0|scannet0000|tum_desk|tum_desk_imp] [time|ncu|profile] [n_keyframes]
 time: ms per iteration of BundleAdjuster.run for 10 and 100 iterations per call (separates the per-call host work from the
 per-iteration cost); ncu: one call, for `ncu --metrics gpu__time_duration.sum`."""
 import os
@@ -53,6 +53,25 @@ ba = BundleAdjuster(model, cfg, db, opt, DEV)
 ba.run(kf_poses, cur_pose, current)
 torch.cuda.synchronize()
 if mode == 'ncu':
+    sys.exit(0)
+if mode == 'profile':          # host side of a call: cProfile over 300 calls with a device sync after each (as bench.py's mapping line)
+    import cProfile
+    import pstats
+    for _ in range(20):
+        ba.run(kf_poses, cur_pose, current)
+        torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(300):
+        ba.run(kf_poses, cur_pose, current)
+        torch.cuda.synchronize()
+    print('%.3f ms per call of %d iterations without the profiler' % ((time.perf_counter() - t0) / 300 * 1e3, m['iters']))
+    pr = cProfile.Profile()
+    pr.enable()
+    for _ in range(300):
+        ba.run(kf_poses, cur_pose, current)
+        torch.cuda.synchronize()
+    pr.disable()
+    pstats.Stats(pr).sort_stats('cumulative').print_stats(28)
     sys.exit(0)
 for iters in (10, 100):
     m['iters'] = iters
