@@ -47,6 +47,11 @@ class BundleAdjuster(object):
         self.last_tv = None                       # device double [1]: raw TV sum of the last iteration
         self.last_d_poses = None                  # [K+1,4,4] pose gradient accumulated since the last pose step
         self.last_kept_width = 0                  # floats per point the last call's forward kept for its backward (0, 32 or 128)
+        self._kept_buf = None                     # those rows (large batches only), reused across calls
+        # Opt-in here: the rows pay for themselves when the forward evaluates little more than the points that end up with a gradient
+        # (a depth-consistent batch: +3 % on the autograd step); over a store whose depths the map does not explain yet the lazy forward
+        # evaluates every sample, writes rows for all of them and the call comes out even (tools/ba_sweep.py, profiles/r2/NOTES.md 13)
+        self.keep_rows = False
         self._noise_calls = 0
         # non-parity index draws on the device (uniform, with replacement) for the large sweeps of BASELINE.json config 4:
         # `random.sample` of 2^22 out of 16 M rays is host-bound even in C
@@ -292,16 +297,22 @@ class BundleAdjuster(object):
             nbytes = int(lib.cb200_lazy_workspace(ctypes.c_int64(n), ctypes.c_int64(Sf)))
             lazy_ws = torch.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
             P.lazy_ws, P.lazy_ws_bytes = dp(lazy_ws), nbytes
-        if lazy and I == 0 and ops.KEEP_FEATURES and lib.cb200_get_decoder() == 1:
+        if lazy and I == 0 and self.keep_rows and ops.KEEP_FEATURES and lib.cb200_get_decoder() == 1:
             # large batches: the forward keeps rows for the backward (features, + their position derivatives when poses are optimised)
             width = 4 * ops.N_GRID_FEATS if d_rays is not None else ops.N_GRID_FEATS
-            if (width == ops.N_GRID_FEATS or ops.KEEP_DERIVATIVES) and ops._kept_rows_fit(n * Sf * width * 4, dev):
-                try:
-                    kept = torch.empty((n * Sf, width), **f32)
-                    P.kept, P.kept_derivatives = dp(kept), int(width != ops.N_GRID_FEATS)
-                    keep.append(kept)
-                except torch.cuda.OutOfMemoryError:
-                    pass
+            if width == ops.N_GRID_FEATS or ops.KEEP_DERIVATIVES:
+                # one buffer per adjuster, grown when a call needs more: allocated per call next to the other scratch, a block of this
+                # size does not find its way back through the caching allocator (94 GB at 2^22 rays: a cudaMalloc + cudaFree per call)
+                need = n * Sf * width
+                if self._kept_buf is None or self._kept_buf.numel() < need:
+                    self._kept_buf = None
+                    if ops._kept_rows_fit(need * 4, dev):
+                        try:
+                            self._kept_buf = torch.empty(need, **f32)
+                        except torch.cuda.OutOfMemoryError:
+                            self._kept_buf = None
+                if self._kept_buf is not None:
+                    P.kept, P.kept_derivatives = dp(self._kept_buf), int(width != ops.N_GRID_FEATS)
         bbytes = int(lib.cb200_points_bwd_workspace(ctypes.c_int64(n * Sf)))
         bwd_ws = torch.empty((bbytes + 3) // 4, dtype=torch.int32, device=dev)
         P.bwd_ws, P.bwd_ws_bytes = dp(bwd_ws), bbytes

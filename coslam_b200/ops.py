@@ -4,6 +4,7 @@ Every compute call goes through libcoslam_b200.so (coslam_b200/_lib.py); torch o
 the autograd graph.  Reference lines each piece stands in for are cited at the wrappers.
 """
 import ctypes
+import os
 import math
 
 import numpy as np
@@ -269,16 +270,18 @@ def _check_weights(w1, w2, w3, w4):
                            [tuple(w.shape) for w in (w1, w2, w3, w4)])
 
 
-KEEP_FEATURES = True     # training steps keep the hash-grid features of the forward for the backward (RayPointsFunction) ...
-KEEP_DERIVATIVES = True  # ... and, when the rays carry a gradient, the features' position derivatives as well
+# training steps keep the hash-grid features of the forward for the backward (RayPointsFunction, BundleAdjuster) ...
+KEEP_FEATURES = os.environ.get('COSLAM_B200_KEEP_ROWS', '1') != '0'
+# ... and, when the rays carry a gradient, the features' position derivatives as well
+KEEP_DERIVATIVES = os.environ.get('COSLAM_B200_KEEP_ROWS', '2') not in ('0', '1')
 LAZY_FORWARD = True      # training forward evaluates only the sample points the step can depend on (lazy_ray_forward)
 LAZY_MIN_POINTS = 1 << 18   # below ~7 waves of tiles (tracking / BA batches) the three extra launches cost more than the skipped points save
 
 
 def _kept_rows_fit(nbytes, device, fraction=0.6):
-    """Kept rows are an optimisation, never a reason to run out of memory: large ones (> 1 GB) are only allocated when they take at
+    """Kept rows are an optimisation, never a reason to run out of memory: large ones (> 8 GB) are only allocated when they take at
     most `fraction` of what the device still has (driver-free memory + the caching allocator's unused reserve)."""
-    if nbytes <= (1 << 30):
+    if nbytes <= (8 << 30):                      # (the driver query costs ~40 us: not worth asking for a few GB on a 180 GB device)
         return True
     free, _ = torch.cuda.mem_get_info(device)
     free += torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)

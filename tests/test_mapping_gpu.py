@@ -148,7 +148,7 @@ def test_one_iteration_gradients_match_autograd(cfg_name):
 
 
 def test_large_batch_iteration_with_kept_rows_matches_autograd():
-    """Above ops.LAZY_MIN_POINTS points the native iteration runs the lazy forward and keeps rows for its backward
+    """Above ops.LAZY_MIN_POINTS points the native iteration runs the lazy forward and, with `keep_rows`, keeps rows for its backward
     (cb200_points_fwd_keep / cb200_points_bwd_kept: features and their position derivatives, since poses are optimised).
     Gradients against the autograd loop on the gathering kernels."""
     from coslam_b200 import ops
@@ -159,6 +159,7 @@ def test_large_batch_iteration_with_kept_rows_matches_autograd():
     try:
         random.seed(11); torch.manual_seed(11)
         ba = BundleAdjuster(model, cfg, db, _map_optimizer(cfg, model), DEV)
+        ba.keep_rows = True
         ba.run(kf_poses, cur_pose, current)
         assert ba.last_kept_width == 128
         ops.KEEP_FEATURES = False
