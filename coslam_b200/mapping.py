@@ -31,6 +31,78 @@ from ._lib import check, ptr, stream
 from .keyframe import sample_ranges
 
 
+class _StagedDraws(object):
+    """The `random.sample` index draws of a BA call (model/keyframe.py:100, coslam.py:339-341), made iteration by iteration in
+    front of each iteration's launches instead of all at once in front of the first: the GPU starts after one iteration's draws
+    (~0.05 ms) instead of the call's (~0.9 ms for 10 iterations), and the host stays ahead of it (an iteration's draws + launches
+    take less host time than its kernels take).  Same values, same order, same state of Python's generator afterwards as
+    keyframe.sample_ranges on the whole list: the Mersenne-Twister state lives in one numpy array for the duration of the call.
+    Layout per iteration, identical in the pinned block and on the device: [ray indices (bs) | current-frame pixels (n_cur) |
+    keyframe slots (bs)], one upload per iteration."""
+
+    def __init__(self, adj, iters, bs, n_cur):
+        import numpy as np
+        kf = adj.kfdb
+        n_store, n_pix = len(kf) * kf.num_rays_to_save, kf.H * kf.W
+        if not (0 <= bs <= n_store and 0 <= n_cur <= n_pix):
+            raise ValueError('Sample larger than population or is negative')
+        self.bs, self.n_cur, self.T = bs, n_cur, 2 * bs + n_cur
+        # two pinned blocks used in turn: a call only waits for the uploads of the call before the previous one, so back-to-back
+        # calls do not make the host wait for the GPU to reach the previous call's last iteration
+        key = (iters, bs, n_cur)
+        st = adj._pin_staged
+        if st is None or st['key'] != key:
+            st = adj._pin_staged = {'key': key, 'bufs': [torch.empty(iters * self.T, dtype=torch.int64).pin_memory() for _ in range(2)],
+                                    'sent': [None, None], 'turn': 0}
+        self.slot = st['turn']
+        st['turn'] ^= 1
+        if st['sent'][self.slot] is not None:
+            st['sent'][self.slot].synchronize()
+        self.adj = adj
+        pin = st['bufs'][self.slot]
+        self.pin_rows = pin.view(iters, self.T)
+        self.pin_np = pin.numpy().reshape(iters, self.T)
+        self.pin_base = pin.data_ptr()
+        self.smooth = None                                               # (jitter, offset ctypes arrays, offset_max, margin) when staged too
+        self.dev = torch.empty(iters * self.T, dtype=torch.int64, device=adj.device)
+        self.dev_rows = self.dev.view(iters, self.T)
+        self.version, mt, self.gauss = random.getstate()
+        self.state = np.array(mt, dtype=np.uint32)
+        self.ns = np.array([n_store, n_pix], dtype=np.int64)
+        self.ks = np.array([bs, n_cur], dtype=np.int64)
+        self.args = (ctypes.c_void_p(self.state.ctypes.data), ctypes.c_int64(2), ctypes.c_void_p(self.ns.ctypes.data),
+                     ctypes.c_void_p(self.ks.ctypes.data))
+        self.fn = _lib.load().cb200_host_random_sample
+        self.frame_ids = kf.frame_ids.numpy()
+        self.R, self.every = kf.num_rays_to_save, adj.config['mapping']['keyframe_every']
+
+    def stage(self, it, plan):
+        """draws of iteration `it` -> pinned row -> device row; points the plan's index arrays at that row"""
+        row = self.pin_np[it]
+        if self.fn(*self.args, ctypes.c_void_p(self.pin_base + 8 * it * self.T)) != 0:
+            raise RuntimeError('cb200_host_random_sample failed')
+        bs, n_cur, T = self.bs, self.n_cur, self.T
+        row[bs + n_cur:] = self.frame_ids[row[:bs] // self.R] // self.every                   # keyframe.py:103, coslam.py:345
+        self.dev_rows[it].copy_(self.pin_rows[it], non_blocking=True)
+        base = self.dev.data_ptr() + 8 * it * T
+        # the runtime addresses iteration `it` as array + it * length: bias the three bases accordingly
+        plan.idx_global = base - 8 * it * bs
+        plan.idx_cur = base + 8 * bs - 8 * it * n_cur
+        plan.slot_global = base + 8 * (bs + n_cur) - 8 * it * bs
+        if self.smooth is not None:                                     # coslam.py:260, :262 -- the call's only draws from torch's CPU generator
+            jit, off, offset_max, margin = self.smooth
+            o = (torch.rand(3).to(offset_max) * offset_max + margin).tolist()
+            j = torch.rand((1, 1, 1, 3)).reshape(3).tolist()
+            off[3 * it], off[3 * it + 1], off[3 * it + 2] = o
+            jit[3 * it], jit[3 * it + 1], jit[3 * it + 2] = j
+
+    def finish(self):
+        random.setstate((self.version, tuple(self.state.tolist()), self.gauss))
+        ev = torch.cuda.Event()
+        ev.record()
+        self.adj._pin_staged['sent'][self.slot] = ev
+
+
 class BundleAdjuster(object):
     def __init__(self, model, config, kfdb, map_optimizer, device='cuda:0', group=None, device_sampler=False):
         if not config['grid']['oneGrid'] or config['decoder']['tcnn_network']:
@@ -63,6 +135,8 @@ class BundleAdjuster(object):
         self.rank = dist.get_rank(group) if group is not None else 0
         self._flat = None
         self._pin, self._pin_sent = None, None     # pinned staging block of a call's index draws, event of its upload
+        self.staged_draws = True                   # one GPU, host sampler: draw iteration by iteration in front of each launch (_StagedDraws)
+        self._pin_staged = None
         self.phase_times = None                   # set to [] to collect CUDA events per sharded iteration: forward | AR-1 | backward | AR-2 | optimise
         bb = model.bounding_box.detach().float().cpu()
         self._lo = (ctypes.c_float * 3)(*bb[:, 0].tolist())
@@ -70,7 +144,7 @@ class BundleAdjuster(object):
         self._bb = bb
 
     # ---- host-side draws of one BA call, in the reference's order ------------------------------------------------------
-    def _draw(self, iters, bs, n_cur, n_rays, n_samples, smooth_on=True):
+    def _draw(self, iters, bs, n_cur, n_rays, n_samples, smooth_on=True, staged=False):
         kf, every = self.kfdb, self.config['mapping']['keyframe_every']
         t = self.config['training']
         host_noise = self.model.spec.perturb and self.model.noise_mode == 'host'
@@ -101,6 +175,17 @@ class BundleAdjuster(object):
                     offset_max = vol - (t['smooth_pts'] - 1) * t['smooth_vox'] - 2 * t['smooth_margin']
                     smooth.append((torch.rand(3).to(offset_max) * offset_max + t['smooth_margin'], torch.rand((1, 1, 1, 3)).reshape(3)))
             return idx_g, slot_g, idx_c, (torch.stack(noise).to(dev, non_blocking=True) if host_noise else None), smooth
+        if staged:
+            idx_g = slot_g = idx_c = None            # made per iteration by _StagedDraws (the torch-generator draws below are a separate stream)
+            if not host_noise:
+                return idx_g, slot_g, idx_c, None, None      # smoothness draws per iteration as well (no other user of that generator)
+            for _ in range(iters):                           # host jitter and smoothness draws alternate on torch's CPU generator
+                noise.append(ops.torch_rand_into(torch.empty((n_rays, n_samples))))                         # scene_rep.py:255
+                if self.smooth_w > 0 and smooth_on:
+                    vol = self._bb[:, 1] - self._bb[:, 0]
+                    offset_max = vol - (t['smooth_pts'] - 1) * t['smooth_vox'] - 2 * t['smooth_margin']
+                    smooth.append((torch.rand(3).to(offset_max) * offset_max + t['smooth_margin'], torch.rand((1, 1, 1, 3)).reshape(3)))
+            return idx_g, slot_g, idx_c, torch.stack(noise).to(self.device, non_blocking=True), smooth
         draws = sample_ranges([(n_store, bs), (kf.H * kf.W, n_cur)] * iters)
         # one pinned block [ray indices [iters, bs] | keyframe slots [iters, bs] | current-frame pixels [iters, n_cur]] filled with numpy
         # over all iterations at once and sent in ONE copy (was ~60 small torch ops and three pageable uploads per call)
@@ -231,7 +316,9 @@ class BundleAdjuster(object):
         d_poses = torch.zeros((K + 1, 4, 4), **f32)
         pose_step = 0
         # ---- buffers and the plan of the native iteration runtime (csrc/runtime.cu) ---------------------------------------
-        idx_g, slot_g, idx_c, noise, smooth = self._draw(iters, bs, n_cur, n, S, smooth_on=not first)
+        staged = self.staged_draws and self.world == 1 and not self.device_sampler and bs > 0 and self.phase_times is None
+        idx_g, slot_g, idx_c, noise, smooth = self._draw(iters, bs, n_cur, n, S, smooth_on=not first, staged=staged)
+        stager = _StagedDraws(self, iters, bs, n_cur) if staged else None
         n_total = n
         if self.world > 1:
             for t_ in (idx_g, slot_g, idx_c) + ((noise,) if noise is not None else ()):
@@ -269,7 +356,7 @@ class BundleAdjuster(object):
         scene, render = spec.scene(), spec.render_cfg()
         lin_u, lin_g, lin_n = spec.linspaces(dev)
         lazy = ops.LAZY_FORWARD and lib.cb200_get_decoder() == 1 and ops.LAZY_MIN_POINTS <= n * Sf < 2 ** 32
-        keep = [idx_g, slot_g, idx_c, slot_c, noise, cur]               # referenced by raw pointer below
+        keep = [idx_g, slot_g, idx_c, slot_c, noise, cur, stager]       # referenced by raw pointer below
         P = _lib.BaPlan()
         dp = lambda t: t.data_ptr() if t is not None else None
         P.scene, P.render = ctypes.addressof(scene), ctypes.addressof(render)
@@ -347,8 +434,13 @@ class BundleAdjuster(object):
             sx = torch.empty((n_side ** 3, 3), **f32)
             sf = torch.empty((n_side ** 3, n_feat), **f32)
             sdf_ = torch.empty_like(sf)
-            jit = (ctypes.c_float * (3 * iters))(*[v for _, j in smooth for v in j.tolist()])
-            off = (ctypes.c_float * (3 * iters))(*[v for o, _ in smooth for v in o.tolist()])
+            if smooth is None:                                           # staged: filled iteration by iteration
+                jit, off = (ctypes.c_float * (3 * iters))(), (ctypes.c_float * (3 * iters))()
+                vol = self._bb[:, 1] - self._bb[:, 0]
+                stager.smooth = (jit, off, vol - (t['smooth_pts'] - 1) * t['smooth_vox'] - 2 * t['smooth_margin'], t['smooth_margin'])
+            else:
+                jit = (ctypes.c_float * (3 * iters))(*[v for _, j in smooth for v in j.tolist()])
+                off = (ctypes.c_float * (3 * iters))(*[v for o, _ in smooth for v in o.tolist()])
             P.grid = ctypes.addressof(grid)
             P.smooth_side, P.smooth_feat, P.smooth_voxel = n_side, n_feat, float(t['smooth_vox'])
             P.smooth_grad_scale = smooth_w / float(int(t['smooth_pts']) ** 3)
@@ -373,6 +465,8 @@ class BundleAdjuster(object):
             if n_free > 0 and (it + 1) % int(m['pose_accum_step']) == 0:   # coslam.py:372-390
                 pose_step += 1
                 p_step = pose_step
+            if stager is not None:
+                stager.stage(it, P)
             if self.world == 1 and self.phase_times is None:
                 check(lib.cb200_ba_iteration(ctypes.byref(P), ctypes.c_int64(it), 7, ctypes.c_int64(map_step), zero, ctypes.c_int64(p_step), st),
                       'ba_iteration')
@@ -416,6 +510,8 @@ class BundleAdjuster(object):
             mark(5)
             if ev:
                 self.phase_times.append(ev)
+        if stager is not None:
+            stager.finish()
         _lib.KERNEL_LAUNCHES += iters * (17 + (3 if lazy else 0) + (4 if smooth_w > 0 else 0)) - iters
         del keep
         self.last_losses, self.last_tv, self.last_d_poses = loss_out[:4], ws[8:9], d_poses
