@@ -12,7 +12,7 @@ import torch
 from . import build as _build
 
 MAX_LEVELS = 16
-ABI_VERSION = 18
+ABI_VERSION = 19
 
 c_f32p = ctypes.c_void_p
 c_stream = ctypes.c_void_p
@@ -32,7 +32,7 @@ class Grid(ctypes.Structure):
 
 class Scene(ctypes.Structure):
     _fields_ = [('grid', Grid), ('bb_lo', ctypes.c_float * 3), ('bb_ext', ctypes.c_float * 3),
-                ('normalise', ctypes.c_uint32), ('n_bins', ctypes.c_uint32)]
+                ('normalise', ctypes.c_uint32), ('n_bins', ctypes.c_uint32), ('cells', ctypes.c_void_p), ('dcells', ctypes.c_void_p)]
 
 
 class RenderCfg(ctypes.Structure):
@@ -100,7 +100,8 @@ EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb
            'cb200_hash_bwd', 'cb200_hash_indices', 'cb200_oneblob_fwd', 'cb200_oneblob_bwd', 'cb200_sample_rays', 'cb200_importance_sample', 'cb200_importance_sample_merge', 'cb200_merge_coarse', 'cb200_points_bwd_workspace', 'cb200_lazy_workspace', 'cb200_lazy_prefix', 'cb200_lazy_resolve', 'cb200_adam_step', 'cb200_assemble_rays_fwd', 'cb200_assemble_rays_bwd', 'cb200_track_pose', 'cb200_track_update', 'cb200_track_frame', 'cb200_track_init', 'cb200_track_rays_sample', 'cb200_track_pose_update', 'cb200_pose_params', 'cb200_track_frame_workspace', 'cb200_pose_matrices', 'cb200_pose_adam', 'cb200_smooth_points', 'cb200_smooth_tv', 'cb200_ba_iteration', 'cb200_sizeof', 'cb200_host_random_sample', 'cb200_host_torch_rand', 'cb200_adam_multi',
            'cb200_points_fwd', 'cb200_points_bwd', 'cb200_points_fwd_keep', 'cb200_points_bwd_kept', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd', 'cb200_render_loss_bwd',
            'cb200_debug_positions', 'cb200_debug_gather_peak', 'cb200_points_bwd_noalloc', 'cb200_points_bwd_noalloc_max_points', 'cb200_selftest_mma', 'cb200_set_decoder',
-           'cb200_get_decoder']
+           'cb200_get_decoder', 'cb200_set_forward_pipeline', 'cb200_get_forward_pipeline', 'cb200_cell_table_bytes', 'cb200_cell_table_build',
+           'cb200_cell_table_fold']
 
 _lib = None
 
@@ -139,6 +140,8 @@ def load():
         raise RuntimeError('coslam_b200: ABI version mismatch (library %d, binding %d); rebuild with '
                            '`python -m coslam_b200.build --force`' % (lib.cb200_abi_version(), ABI_VERSION))
     lib.cb200_sizeof.restype = ctypes.c_size_t
+    lib.cb200_get_forward_pipeline.restype = ctypes.c_longlong
+    lib.cb200_cell_table_bytes.restype = ctypes.c_size_t
     for which, cls in ((0, BaPlan), (1, TrackStep), (2, AdamParam)):
         if lib.cb200_sizeof(which) != ctypes.sizeof(cls):
             raise RuntimeError('coslam_b200: %s layout differs from the library (%d vs %d bytes)'
@@ -157,6 +160,15 @@ def set_decoder(kind):
     rc = load().cb200_set_decoder({'simt': 0, 'tc': 1}[kind])
     if rc != 0:
         raise RuntimeError('cb200_set_decoder failed')
+
+
+def set_forward_pipeline(min_points):
+    """< 0 / None: one-role tensor-core forward; >= 0: warp-specialised forward for batches of at least that many points."""
+    load().cb200_set_forward_pipeline(ctypes.c_longlong(-1 if min_points is None else int(min_points)))
+
+
+def get_forward_pipeline():
+    return int(load().cb200_get_forward_pipeline())
 
 
 def check(rc, what):

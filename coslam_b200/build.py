@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, 'csrc')
 INCLUDE = os.path.join(os.path.dirname(HERE), 'include')
 OBJ_DIR = os.path.join(HERE, 'build')
 LIB_PATH = os.path.join(HERE, 'libcoslam_b200.so')
-SOURCES = ['api.cu', 'render.cu', 'points.cu', 'encoding.cu', 'tc_selftest.cu', 'points_tc.cu', 'optim.cu', 'assemble.cu', 'track.cu', 'runtime.cu', 'microbench.cu', 'noalloc.cu', 'track_frame.cu', 'host_rng.cu']
+SOURCES = ['api.cu', 'render.cu', 'points.cu', 'encoding.cu', 'tc_selftest.cu', 'points_tc.cu', 'points_ws.cu', 'cells.cu', 'optim.cu', 'assemble.cu', 'track.cu', 'runtime.cu', 'microbench.cu', 'noalloc.cu', 'track_frame.cu', 'host_rng.cu']
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr',

@@ -70,6 +70,13 @@ int cb200_set_decoder(int kind) {
 
 int cb200_get_decoder(void) { return g_decoder; }
 
+int cb200_set_forward_pipeline(long long min_points) {
+    cb200::set_fwd_ws_min_points(min_points);
+    return 0;
+}
+
+long long cb200_get_forward_pipeline(void) { return cb200::fwd_ws_min_points(); }
+
 int cb200_device_sm_count(void) {
     int dev = 0, sms = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return -1;

@@ -162,6 +162,8 @@ cudaError_t launch_points_fwd(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_compact_live(const float* d_raw, int64_t n_points, unsigned long long* count, uint32_t* idx, cudaStream_t st);
 cudaError_t launch_points_bwd_tc(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st);
+long long fwd_ws_min_points();
+void set_fwd_ws_min_points(long long v);
 cudaError_t launch_points_bwd(const PointsArgs& a, cudaStream_t st);
 cudaError_t launch_debug_positions(const PointsArgs& a, float* pts_out, float* x_out, cudaStream_t st);
 cudaError_t launch_hash_fwd(const SceneDev& sc, const float* x, const float* table, int64_t n, float* out, cudaStream_t st);

@@ -35,7 +35,20 @@ struct SceneDev {
     float bb_lo[3];
     float bb_ext[3];
     uint32_t normalise;
+    // optional cell-major copies of the dense levels (cb200_cell_table_build): block of cell (cx, cy, cz) of dense level l =
+    // cells + 4 * (cell_offset[l] + cx + res * (cy + res * cz)), 4 float4 = [corner x][corner (y, z)][2 features]
+    const float4* cells;
+    float4* dcells;
+    uint32_t cell_offset[kLevels];
 };
+
+// number of cells (one per vertex, so that edge cells exist) of the dense levels in front of level l
+__host__ inline uint32_t cell_table_cells(const cb200_grid& g, int upto) {
+    uint32_t n = 0;
+    for (int l = 0; l < upto && l < (int)g.n_levels; ++l)
+        if (!g.hashed[l]) n += g.res[l] * g.res[l] * g.res[l];
+    return n;
+}
 
 __host__ inline SceneDev make_scene_dev(const cb200_scene& s) {
     SceneDev d;
@@ -51,6 +64,9 @@ __host__ inline SceneDev make_scene_dev(const cb200_scene& s) {
         d.bb_ext[i] = s.bb_ext[i];
     }
     d.normalise = s.normalise;
+    d.cells = reinterpret_cast<const float4*>(s.cells);
+    d.dcells = reinterpret_cast<float4*>(s.dcells);
+    for (int l = 0; l < kLevels; ++l) d.cell_offset[l] = cell_table_cells(s.grid, l);
     return d;
 }
 

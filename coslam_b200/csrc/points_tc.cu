@@ -1,4 +1,6 @@
 // Kernels and launchers of the per-point tensor-core path; the tile loops live in points_tc.cuh.
+#include <cstdlib>
+
 #include "points_tc.cuh"
 
 namespace cb200 {
@@ -146,6 +148,11 @@ static cudaError_t allow_dynamic_smem(const void* kernel, size_t smem) {
     return e;
 }
 
+// for the other translation units of the tensor-core path (points_ws.cu)
+int cb200_sm_count() { return sm_count(); }
+cudaError_t cb200_allow_dynamic_smem(const void* kernel, size_t smem) { return allow_dynamic_smem(kernel, smem); }
+cudaError_t launch_points_fwd_ws(const PointsArgs& a, int dense, cudaStream_t st);      // points_ws.cu
+
 static int tc_persistent_grid(int64_t n_tiles, int ctas_per_sm) {
     const int sms = sm_count();
     int64_t g = (int64_t)sms * ctas_per_sm;
@@ -202,7 +209,22 @@ static cudaError_t launch_points_fwd_tc_jac(const PointsArgs& a, cudaStream_t st
     }
 }
 
+// Which forward runs: < 0 the one-role kernel above, >= 0 the warp-specialised kernel (points_ws.cu) for batches of at least that many
+// points.  Process-wide (cb200_set_forward_pipeline); the first query takes COSLAM_B200_FWD_WS / COSLAM_B200_FWD_WS_MIN from the environment.
+static long long g_fwd_ws_min = -2;
+long long fwd_ws_min_points() {
+    if (g_fwd_ws_min == -2) {
+        const char* on = getenv("COSLAM_B200_FWD_WS");
+        const char* mn = getenv("COSLAM_B200_FWD_WS_MIN");
+        g_fwd_ws_min = (on && atoi(on) > 0) ? (mn ? atoll(mn) : 0) : -1;
+    }
+    return g_fwd_ws_min;
+}
+void set_fwd_ws_min_points(long long v) { g_fwd_ws_min = v < 0 ? -1 : v; }
+
 cudaError_t launch_points_fwd_tc(const PointsArgs& a, cudaStream_t st) {
+    const long long ws_min = fwd_ws_min_points();
+    if (ws_min >= 0 && a.n_points >= ws_min) return launch_points_fwd_ws(a, dense_prefix(a.scene), st);
     return (a.feat != nullptr && a.feat_stride == 4 * kGridFeats) ? launch_points_fwd_tc_jac<true>(a, st) : launch_points_fwd_tc_jac<false>(a, st);
 }
 

@@ -106,6 +106,53 @@ __device__ __forceinline__ void level_corners_x(const SceneDev& sc, int l, const
 
 __device__ __forceinline__ float yz_weight(float w1, float w2, int j) { return ((j & 1) ? w1 : 1.f - w1) * ((j & 2) ? w2 : 1.f - w2); }
 
+// 32 bytes = this thread's four (y, z) corners of a cell block of the cell-major copy (cells.cu): one 256-bit load
+__device__ __forceinline__ void ldg_corners4(const float4* p, float2 (&v)[4]) {
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(v[0].x), "=f"(v[0].y), "=f"(v[1].x), "=f"(v[1].y), "=f"(v[2].x), "=f"(v[2].y), "=f"(v[3].x), "=f"(v[3].y)
+                 : "l"(p));
+}
+__device__ __forceinline__ void red_add_f4(float4* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+// index (in float4) of thread xb's half of the block of cell (cx, cy, cz) of dense level l; false: the cell lies outside the level
+__device__ __forceinline__ bool cell_block(const SceneDev& sc, int l, const uint32_t (&cell)[3], int xb, uint32_t& at) {
+    const uint32_t res = sc.res[l];
+    at = (sc.cell_offset[l] + cell[0] + res * (cell[1] + res * cell[2])) * 4u + 2u * (uint32_t)xb;
+    return cell[0] < res && cell[1] < res && cell[2] < res;
+}
+
+// the four corner values at this thread's x of level l, and the interpolation weights: dense levels come from the cell-major copy
+// when the scene carries one (identical values), everything else from the table
+template <int kDense>
+__device__ __forceinline__ void gather_level_x(const PointsArgs& a, int l, const float x[3], int xb, float2 (&v)[4], float& wx, float& w1,
+                                               float& w2) {
+    const bool dense = kDense >= 0 ? (l < kDense) : (a.scene.hashed[l] == 0);
+    if (dense && a.scene.cells != nullptr) {
+        const float scale = a.scene.scale[l];
+        uint32_t cell[3], at;
+        float w0;
+        grid_pos(scale, x[0], cell[0], w0);
+        grid_pos(scale, x[1], cell[1], w1);
+        grid_pos(scale, x[2], cell[2], w2);
+        wx = xb ? w0 : 1.f - w0;
+        if (cell_block(a.scene, l, cell, xb, at)) {
+            ldg_corners4(a.scene.cells + at, v);
+        } else {                                  // outside the unit cube: the table's wrapped indices
+            const uint32_t res = a.scene.res[l], size = a.scene.offset[l + 1] - a.scene.offset[l];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                v[j] = ldg_f2(a.table + a.scene.offset[l] + grid_index(false, size, res, cell[0] + xb, cell[1] + (j & 1), cell[2] + (j >> 1)));
+        }
+        return;
+    }
+    HalfCorners hc;
+    level_corners_x<kDense>(a.scene, l, x, xb, hc);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = ldg_f2(a.table + hc.idx[j]);
+    wx = hc.wx; w1 = hc.w1; w2 = hc.w2;
+}
+
 // 4 consecutive columns (sub = 0 / 1: first / second half of a chunk) of row r into the hi and lo tiles
 __device__ __forceinline__ void tile_store4(uint32_t hi_base, uint32_t lo_base, uint32_t group_stride, int r, int chunk, int sub, const float (&v)[4]) {
     uint32_t h[2], l[2];
@@ -118,6 +165,7 @@ __device__ __forceinline__ void tile_store4(uint32_t hi_base, uint32_t lo_base, 
 
 // the pair's per-corner partial features of one chunk (4 levels x 2) -> complete features; thread xb keeps columns 4 xb .. 4 xb + 3
 // keep (optional): where this thread's four fp32 features go in the point's row of PointsArgs::feat (streamed out for the backward)
+template <uint32_t kGS = kAGS>
 __device__ __forceinline__ void pair_combine_store(const float (&part)[8], int xb, uint32_t a_hi, uint32_t a_lo, int row, int c,
                                                    float* keep = nullptr) {
     float mine[4];
@@ -127,7 +175,7 @@ __device__ __forceinline__ void pair_combine_store(const float (&part)[8], int x
         const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
         mine[i] = (xb ? part[4 + i] : part[i]) + recv;
     }
-    tile_store4(a_hi, a_lo, kAGS, row, c, xb, mine);
+    tile_store4(a_hi, a_lo, kGS, row, c, xb, mine);
     if (keep) __stcs(reinterpret_cast<float4*>(keep), make_float4(mine[0], mine[1], mine[2], mine[3]));
 }
 
@@ -150,7 +198,8 @@ __device__ __forceinline__ void pair_combine_keep(const float (&part)[8], int xb
 // kJac: the kept row holds the features' derivatives along the normalised position as well, one 128-byte line per chunk --
 // [chunk c][feat | d/dx | d/dy | d/dz][thread xb][columns 8c + 4xb .. + 3] -- so that every store (and every load of the backward) of a
 // lane pair is one whole 32-byte sector; they come from the corner values that are in registers anyway.
-template <int kDense, bool kJac>
+// kGS: group stride of the tile the features go to (the warp-specialised forward keeps them in a [128 x 32] tile of its own)
+template <int kDense, bool kJac, uint32_t kGS = kAGS>
 __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row,
                                                   float* keep
 #ifdef CB200_PHASE_CLOCKS
@@ -163,13 +212,7 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
     float2 v[4][4];
     float wx[4], w1[4], w2[4];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        HalfCorners hc;
-        level_corners_x<kDense>(a.scene, 4 * c + q, x, xb, hc);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) v[q][j] = ldg_f2(a.table + hc.idx[j]);
-        wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
-    }
+    for (int q = 0; q < 4; ++q) gather_level_x<kDense>(a, 4 * c + q, x, xb, v[q], wx[q], w1[q], w2[q]);
 #ifdef CB200_PHASE_CLOCKS
     long long t1 = clock64();
     {
@@ -210,7 +253,7 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
         }
     }
     float* const mine_at = keep ? keep + kept_offset(kJac ? 4 * kGridFeats : kGridFeats, c, xb) : nullptr;
-    pair_combine_store(part, xb, a_hi, a_lo, row, c, mine_at);
+    pair_combine_store<kGS>(part, xb, a_hi, a_lo, row, c, mine_at);
     if (kJac) {
         pair_combine_keep(jx, xb, mine_at + 8);
         pair_combine_keep(jy, xb, mine_at + 16);
@@ -641,6 +684,7 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
                 float dm[4] = {0.f, 0.f, 0.f, 0.f};      // d embed of this thread's columns (levels 4c + 2xb, 4c + 2xb + 1)
                 uint32_t idx[4][4];
                 float wx[4], w1[4], w2[4];
+                uint32_t in_cells = 0;      // bit q: level 4c + q reduces into the cell-major gradient block idx[q][0] (dense level, copy present)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     HalfCorners hc;
@@ -648,16 +692,36 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
 #pragma unroll
                     for (int j = 0; j < 4; ++j) idx[q][j] = hc.idx[j];
                     wx[q] = hc.wx; w1[q] = hc.w1; w2[q] = hc.w2;
+                    if (a.scene.dcells != nullptr && a.scene.hashed[4 * c + q] == 0) {
+                        const float scale = a.scene.scale[4 * c + q];
+                        uint32_t cell[3], at;
+                        float unused;
+#pragma unroll
+                        for (int d = 0; d < 3; ++d) grid_pos(scale, x[d], cell[d], unused);
+                        if (cell_block(a.scene, 4 * c + q, cell, xb, at)) {
+                            idx[q][0] = at;
+                            in_cells |= 1u << q;
+                        }
+                    }
                 }
                 tmem_ld_wait();
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const float de0 = __uint_as_float(__shfl_sync(0xffffffffu, de_raw[2 * q], src_lane));
                     const float de1 = __uint_as_float(__shfl_sync(0xffffffffu, de_raw[2 * q + 1], src_lane));
+                    if ((in_cells >> q) & 1u) {
+                        if (dtab && live) {
+                            const float c0 = wx[q] * yz_weight(w1[q], w2[q], 0), c1 = wx[q] * yz_weight(w1[q], w2[q], 1);
+                            const float c2 = wx[q] * yz_weight(w1[q], w2[q], 2), c3 = wx[q] * yz_weight(w1[q], w2[q], 3);
+                            red_add_f4(a.scene.dcells + idx[q][0], c0 * de0, c0 * de1, c1 * de0, c1 * de1);
+                            red_add_f4(a.scene.dcells + idx[q][0] + 1, c2 * de0, c2 * de1, c3 * de0, c3 * de1);
+                        }
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
-                        if (dtab && live) red_add_f2(dtab + idx[q][j], wc * de0, wc * de1);
+                        for (int j = 0; j < 4; ++j) {
+                            const float wc = wx[q] * yz_weight(w1[q], w2[q], j);
+                            if (dtab && live) red_add_f2(dtab + idx[q][j], wc * de0, wc * de1);
+                        }
                     }
                     if (kKept == 2 && (q >> 1) == xb) {
                         dm[2 * (q & 1)] = de0;

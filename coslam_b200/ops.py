@@ -274,6 +274,12 @@ def _check_weights(w1, w2, w3, w4):
 KEEP_FEATURES = os.environ.get('COSLAM_B200_KEEP_ROWS', '1') != '0'
 # ... and, when the rays carry a gradient, the features' position derivatives as well
 KEEP_DERIVATIVES = os.environ.get('COSLAM_B200_KEEP_ROWS', '2') not in ('0', '1')
+# opt-in (COSLAM_B200_CELL_TABLES=1): large training steps read / reduce the dense levels through cell-major copies
+# (cb200_cell_table_build / _fold, csrc/cells.cu).  Measured SLOWER on B200 (profiles/r2/NOTES.md section 15: forward +14 %, backward +1 %
+# at 2^20 rays -- adjacent cells no longer share their corners' lines in L1), so it is off by default and kept as the A/B twin.
+CELL_TABLES = os.environ.get('COSLAM_B200_CELL_TABLES', '0') == '1'
+CELL_MIN_POINTS = 1 << 20   # below this the build / clear / fold launches (~25 us together) are not worth it
+_CELL_BUFFERS = {}          # (device, bytes) -> [cells, dcells or None]: reused across steps, rebuilt from the table in front of every forward
 LAZY_FORWARD = True      # training forward evaluates only the sample points the step can depend on (lazy_ray_forward)
 LAZY_MIN_POINTS = 1 << 18   # below ~7 waves of tiles (tracking / BA batches) the three extra launches cost more than the skipped points save
 
@@ -286,6 +292,26 @@ def _kept_rows_fit(nbytes, device, fraction=0.6):
     free, _ = torch.cuda.mem_get_info(device)
     free += torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
     return nbytes <= fraction * free
+
+
+def cell_tables(scene, table, want_grad=False):
+    """Scene copy whose `cells` points at a fresh cell-major copy of `table`'s dense levels (None if the grid has no leading dense
+    level).  Returns (scene_with_cells, buffers); buffers[1] is the gradient block buffer when want_grad (allocated, not cleared)."""
+    lib = _lib.load()
+    nbytes = int(lib.cb200_cell_table_bytes(ctypes.byref(scene)))
+    if nbytes == 0:
+        return None, None
+    key = (table.device.index, nbytes)
+    buf = _CELL_BUFFERS.get(key)
+    if buf is None:
+        buf = [torch.empty(nbytes // 4, dtype=torch.float32, device=table.device), None]
+        _CELL_BUFFERS[key] = buf
+    if want_grad and buf[1] is None:
+        buf[1] = torch.empty(nbytes // 4, dtype=torch.float32, device=table.device)
+    check(lib.cb200_cell_table_build(ctypes.byref(scene), ptr(table), ptr(buf[0]), stream()), 'cell_table_build')
+    s2 = _lib.Scene.from_buffer_copy(scene)
+    s2.cells = buf[0].data_ptr()
+    return s2, buf
 
 
 def _kept_width(feat):
@@ -331,7 +357,7 @@ def points_forward(scene, table, w, pts=None, rays=None, want_raw=True, want_geo
     return raw, geo, mask
 
 
-def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True, feat=None):
+def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True, feat=None, scene=None):
     """Training forward over the sample points the step can depend on (cb200_lazy_prefix / cb200_lazy_resolve): the loss
     prefix of every ray first, then whatever the first sign change found there still exposes.  Points never listed keep
     raw = 0; the rendering mask gives them zero weight and the loss masks exclude them, as in the reference."""
@@ -349,10 +375,11 @@ def lazy_ray_forward(spec, table, w, rays, target_d, want_mask=True, feat=None):
     cfg = spec.render_cfg()
     check(lib.cb200_lazy_prefix(ctypes.byref(cfg), ptr(z), ptr(td), ctypes.c_int64(n), ctypes.c_int64(s), ptr(wsp),
                                 ctypes.c_size_t(nbytes), stream()), 'lazy_prefix')
-    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist, feat=feat)
+    scene = scene if scene is not None else spec.scene()
+    points_forward(scene, table, w, rays=rays, out=(raw, mask), point_list=plist, feat=feat)
     check(lib.cb200_lazy_resolve(ctypes.byref(cfg), ptr(z), ptr(td), ptr(raw), ctypes.c_int64(n), ctypes.c_int64(s), ptr(wsp),
                                  ctypes.c_size_t(nbytes), stream()), 'lazy_resolve')
-    points_forward(spec.scene(), table, w, rays=rays, out=(raw, mask), point_list=plist, feat=feat)
+    points_forward(scene, table, w, rays=rays, out=(raw, mask), point_list=plist, feat=feat)
     return raw, mask
 
 
@@ -445,11 +472,16 @@ class RayPointsFunction(torch.autograd.Function):
                     feat = torch.empty((z.numel(), width), dtype=torch.float32, device=z.device)
                 except torch.cuda.OutOfMemoryError:
                     feat = None
+        scene, cellbuf = spec.scene(), None
+        if CELL_TABLES and tc and z.numel() >= CELL_MIN_POINTS:
+            # the backward reduces into gradient blocks of the same layout when it runs on kept rows and a table gradient is wanted
+            with_cells, cellbuf = cell_tables(scene, tb, want_grad=feat is not None and need[3])
+            scene = with_cells if with_cells is not None else scene
         if lazy:
             _check_weights(*w)
-            raw, mask = lazy_ray_forward(spec, tb, w, (o, d, z), target_d, want_mask=need_grad, feat=feat)
+            raw, mask = lazy_ray_forward(spec, tb, w, (o, d, z), target_d, want_mask=need_grad, feat=feat, scene=scene)
         else:
-            raw, _, mask = points_forward(spec.scene(), tb, w, rays=(o, d, z), want_mask=need_grad, feat=feat)
+            raw, _, mask = points_forward(scene, tb, w, rays=(o, d, z), want_mask=need_grad, feat=feat)
         if KEEP_LAST_MASK:
             global LAST_MASK, LAST_EVALUATED
             LAST_MASK = mask
@@ -457,6 +489,7 @@ class RayPointsFunction(torch.autograd.Function):
             MASK_LOG.append(mask)
         ctx.spec = spec
         ctx.kept = feat is not None
+        ctx.dcells = cellbuf[1] if (cellbuf is not None and feat is not None and need[3]) else None
         ctx.save_for_backward(o, d, z, tb, *w, mask if mask is not None else torch.empty(0), *((feat,) if feat is not None else ()))
         return raw.view(z.shape[0], z.shape[1], 4)
 
@@ -467,8 +500,14 @@ class RayPointsFunction(torch.autograd.Function):
         o, d, z, tb, w1, w2, w3, w4, mask = ctx.saved_tensors[:9]
         feat = ctx.saved_tensors[9] if ctx.kept else None
         need = ctx.needs_input_grad
-        d_table, d_w, d_ray = points_backward(ctx.spec.scene(), tb, (w1, w2, w3, w4), mask, _f32c(g_raw), rays=(o, d, z),
+        scene = ctx.spec.scene()
+        if ctx.dcells is not None:
+            scene = _lib.Scene.from_buffer_copy(scene)
+            scene.dcells = ctx.dcells.zero_().data_ptr()
+        d_table, d_w, d_ray = points_backward(scene, tb, (w1, w2, w3, w4), mask, _f32c(g_raw), rays=(o, d, z),
                                               need_table=need[3], need_mlp=any(need[4:8]), need_pos=need[0] or need[1], feat=feat)
+        if ctx.dcells is not None:
+            check(_lib.load().cb200_cell_table_fold(ctypes.byref(scene), ptr(ctx.dcells), ptr(d_table), stream()), 'cell_table_fold')
         d_o, d_d = d_ray if d_ray is not None else (None, None)
         d_w = d_w or (None, None, None, None)
         return d_o, d_d, None, d_table, d_w[0], d_w[1], d_w[2], d_w[3], None, None

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CB200_ABI_VERSION 18
+#define CB200_ABI_VERSION 19
 #define CB200_MAX_LEVELS 16
 
 /* decoder geometry served by the fused kernels (model/decoder.py:145-180 with every shipped YAML:
@@ -62,6 +62,12 @@ typedef struct cb200_scene {
     float bb_ext[3];    /* bound[:,1] - bound[:,0], subtracted in fp32 by the caller */
     uint32_t normalise; /* config['grid']['tcnn_encoding']: 1 = apply (p - lo) / ext */
     uint32_t n_bins;    /* OneBlob bins per dimension; the fused kernels require 16 */
+    /* optional (NULL = absent), DEVICE: cell-major copies of the DENSE levels, see cb200_cell_table_build.  cells: the 8 corner
+     * values of every cell in one 64-byte block, read by the tensor-core forward instead of 8 separate table entries; dcells: a
+     * gradient accumulator of the same layout, added to by cb200_points_bwd_kept instead of d_table's dense levels and folded
+     * into d_table afterwards (cb200_cell_table_fold) */
+    const void* cells;
+    void* dcells;
 } cb200_scene;
 
 /* ray sampling + loss head parameters (model/scene_rep.py:220-255, 311-338; model/utils.py:89-161) */
@@ -97,6 +103,24 @@ const char* cb200_last_error(void);
  * 0 = SIMT fp32 decoder (kept as the A/B reference of the tensor-core path).  Process-wide, not thread-safe. */
 int cb200_set_decoder(int kind);
 int cb200_get_decoder(void);
+/* which tensor-core forward cb200_points_fwd / cb200_points_fwd_keep launch: min_points < 0 = the one-role kernel (every warp gathers,
+ * then runs the decoder rounds), min_points >= 0 = the warp-specialised kernel (gather warps and decoder warps coupled by mbarriers,
+ * csrc/points_ws.cu) for batches of at least min_points points.  Same outputs bit for bit.  Process-wide, not thread-safe; the
+ * initial value comes from COSLAM_B200_FWD_WS (0 / 1) and COSLAM_B200_FWD_WS_MIN.  No counterpart in the reference (the decoder there
+ * is model/decoder.py:145-180 on torch / tinycudann); an A/B switch like cb200_set_decoder. */
+/* Cell-major copies of the dense hash-grid levels (tensor-core per-point kernels, optional).  The dense levels index their vertices
+ * x + y*res + z*res^2 (tiny-cuda-nn grid.h, model/encodings.py:34-43), so the 8 corners of a cell lie in 4 different places of the
+ * table and cost a lane pair 4 requests per level; in the copy a cell's corners are ONE 64-byte block
+ * [cell = x + res*(y + res*z)][corner x][corner (y, z)][2 features], a lane pair reads it with one request (32 bytes per lane) and the
+ * backward reduces into a gradient block of the same layout with two 16-byte reductions per lane.  Values are copies: the forward's
+ * outputs do not change by a bit.  cb200_cell_table_bytes: size of either buffer (0 if no level is dense); _build: fills `cells` from
+ * `table` (call again after every optimiser step on the table); _fold: adds the non-zero entries of `dcells` to d_table (the caller
+ * zero-fills dcells in front of the backward).  No counterpart in the reference (tinycudann keeps one layout). */
+size_t cb200_cell_table_bytes(const cb200_scene* scene);
+int cb200_cell_table_build(const cb200_scene* scene, const float* table, void* cells, void* stream);
+int cb200_cell_table_fold(const cb200_scene* scene, const void* dcells, float* d_table, void* stream);
+int cb200_set_forward_pipeline(long long min_points);
+long long cb200_get_forward_pipeline(void);
 /* number of SMs of the current device (host query), used by callers to size persistent grids/workspaces */
 int cb200_device_sm_count(void);
 
