@@ -319,15 +319,19 @@ def run_ours(args):
     extra = {}
     full = not args.quick
     if full:
-        # ---- the default mode of the drop-in (COSLAM_B200_NOISE=host): CPU torch.rand(N, S) + upload inside every step ------
+        # ---- the default mode of the drop-in (COSLAM_B200_NOISE=host): the stream of CPU torch.rand(N, S) inside every step ----
+        # (at this size generated on the device from host-walked Mersenne-Twister checkpoints: ops.device_uniform)
         model.noise_mode = 'host'
         e2e_step()
         k = min(3, args.steps)
         ms_host = timed(e2e_step, k)
         model.noise_mode = 'device'
         extra['e2e_host_noise'] = {'value': world * n * k / (ms_host * 1e-3), 'unit': UNIT, 'ms_per_step': ms_host / k, 'steps': k,
-                                   'h2d_bytes_per_step': h2d + n * S * 4, 'd2h_bytes_per_step': 4,
-                                   'note': "the reference's own jitter: torch.rand(z_vals.shape) on the CPU generator + .to(device) every call (scene_rep.py:255)"}
+                                   'h2d_bytes_per_step': h2d + (n * S * 4 if n * S < ops.DEVICE_STREAM_MIN else (n * S // (624 * ops.DEVICE_STREAM_SEGMENT) + 1) * 2496),
+                                   'd2h_bytes_per_step': 4,
+                                   'note': "the reference's own jitter stream, torch.rand(z_vals.shape) of the CPU generator (scene_rep.py:255), bit for bit: "
+                                           "batches of >= 2^20 floats are generated on the device from Mersenne-Twister checkpoints the host walks "
+                                           "(the generator state advances as if torch.rand had run); smaller ones on the host + pinned upload"}
         # ---- BASELINE config 4's ray sweep, device-resident, same step -----------------------------------------------------
         sweep = {}
         for lg in (16, 18, 20, 22):

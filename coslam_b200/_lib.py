@@ -101,7 +101,7 @@ EXPORTS = ['cb200_abi_version', 'cb200_last_error', 'cb200_device_sm_count', 'cb
            'cb200_points_fwd', 'cb200_points_bwd', 'cb200_points_fwd_keep', 'cb200_points_bwd_kept', 'cb200_render_fwd', 'cb200_loss_finish', 'cb200_render_bwd', 'cb200_render_loss_bwd',
            'cb200_debug_positions', 'cb200_debug_gather_peak', 'cb200_points_bwd_noalloc', 'cb200_points_bwd_noalloc_max_points', 'cb200_selftest_mma', 'cb200_set_decoder',
            'cb200_get_decoder', 'cb200_set_forward_pipeline', 'cb200_get_forward_pipeline', 'cb200_cell_table_bytes', 'cb200_cell_table_build',
-           'cb200_cell_table_fold']
+           'cb200_cell_table_fold', 'cb200_torch_rand_device', 'cb200_host_torch_rand_skip', 'cb200_host_torch_rand_segments']
 
 _lib = None
 

@@ -174,6 +174,58 @@ def torch_rand_into(out):
     return out
 
 
+# batches of at least this many uniforms are generated on the device (cb200_torch_rand_device: the same stream, no upload); the host
+# only advances its generator state.  Below it the host loop + pinned upload is quicker than a single-CTA kernel's latency.
+DEVICE_STREAM_MIN = int(os.environ.get('COSLAM_B200_DEVICE_STREAM_MIN', str(1 << 20)))
+
+
+DEVICE_STREAM_SEGMENT = 64      # Mersenne-Twister blocks (of 624 floats) per device CTA
+DEVICE_STREAM_CHUNK = 1 << 24   # floats per host walk + launch: the device generates chunk k while the host walks chunk k + 1
+_STREAM_BUFFERS = {}            # device index -> [pinned checkpoints, device checkpoints, event of the last upload]
+
+
+def device_uniform(n, device):
+    """torch.rand(n).to(device), bit for bit, generated on the device (cb200_host_torch_rand_segments + cb200_torch_rand_device);
+    None if the generator state is not one the routines know."""
+    lib = _lib.load()
+    device = torch.device(device)
+    if n == 0:
+        return torch.empty(0, dtype=torch.float32, device=device)
+    C, words = DEVICE_STREAM_SEGMENT, 624
+    cap_total = n // (words * C) + 2 * ((n + DEVICE_STREAM_CHUNK - 1) // DEVICE_STREAM_CHUNK) + 2
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    buf = _STREAM_BUFFERS.get(key)
+    if buf is None or buf[0].shape[0] < cap_total:
+        buf = _STREAM_BUFFERS[key] = [torch.empty((cap_total, words), dtype=torch.int32).pin_memory(),
+                                      torch.empty((cap_total, words), dtype=torch.int32, device=device), None]
+    if buf[2] is not None:
+        buf[2].synchronize()                       # the previous call's uploads have left the pinned block
+    st = torch.get_rng_state()
+    out = torch.empty(n, dtype=torch.float32, device=device)
+    n_seg, head, head_next = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int32(0)
+    done, used = 0, 0
+    with torch.cuda.device(device):
+        while done < n:
+            take = min(DEVICE_STREAM_CHUNK, n - done)
+            rc = lib.cb200_host_torch_rand_segments(ctypes.c_void_p(st.data_ptr()), ctypes.c_int64(take), ctypes.c_int64(C),
+                                                    ctypes.c_void_p(buf[0].data_ptr() + used * words * 4), ctypes.c_int64(cap_total - used),
+                                                    ctypes.byref(n_seg), ctypes.byref(head), ctypes.byref(head_next))
+            if rc != 0:
+                if done == 0 and rc == -1:
+                    return None                    # nothing consumed yet: the caller falls back to the host loop
+                raise RuntimeError('cb200_host_torch_rand_segments failed (%d) in the middle of a draw' % rc)
+            k = n_seg.value
+            buf[1][used:used + k].copy_(buf[0][used:used + k], non_blocking=True)
+            check(lib.cb200_torch_rand_device(ctypes.c_void_p(buf[1].data_ptr() + used * words * 4), n_seg, ctypes.c_int64(C), head, head_next,
+                                              ctypes.c_int64(take), ctypes.c_void_p(out.data_ptr() + done * 4), stream()), 'torch_rand_device')
+            used += k
+            done += take
+        buf[2] = torch.cuda.Event()
+        buf[2].record()
+    torch.set_rng_state(st)
+    return out
+
+
 _PINNED = {}      # numel -> [[pinned buffer, event of its last upload] x 2, next]
 
 
@@ -182,6 +234,10 @@ def host_uniform(shape, device):
     n = 1
     for d in shape:
         n *= int(d)
+    if n >= DEVICE_STREAM_MIN and torch.device(device).type == 'cuda':
+        out = device_uniform(n, torch.device(device))
+        if out is not None:
+            return out.view(shape)
     slot = _PINNED.get(n)
     if slot is None:
         slot = _PINNED[n] = [[torch.empty(n, dtype=torch.float32).pin_memory(), None], [torch.empty(n, dtype=torch.float32).pin_memory(), None], 0]

@@ -570,6 +570,18 @@ int cb200_points_bwd_noalloc(const cb200_scene* scene, const float* table, const
  * updated in place (write it back with torch.set_rng_state and every later draw is unchanged).  at::mt19937 + the 24-bit
  * uniform_real transformation in a tight loop instead of one virtual call per element.  Returns 0, or -1 for a state it does not understand. */
 int cb200_host_torch_rand(uint8_t* state, int64_t n, float* out);
+/* The same stream produced on the DEVICE for large batches (scene_rep.py:255 then `.to(device)`: here the values never cross PCIe).
+ * The Mersenne-Twister recurrence is sequential, so the HOST still walks it -- cb200_host_torch_rand_segments advances `state` as if n
+ * floats had been drawn (the twist without the outputs, a fifth of the time) and records the 624 state words in front of every
+ * `blocks_per_segment`-th regeneration into `checkpoints` ([capacity][624] uint32, host; -2 if more are needed), returning the number
+ * of segments, the outputs the block current at entry still serves (`head`) and its read index.  cb200_torch_rand_device takes a
+ * DEVICE copy of the checkpoints and writes the n floats with one CTA per segment.  Together: out == torch.rand(n).to(device) bit for
+ * bit, generator state as after that call.  cb200_host_torch_rand_skip: the state advance alone. */
+int cb200_host_torch_rand_segments(uint8_t* state, int64_t n, int64_t blocks_per_segment, uint32_t* checkpoints, int64_t capacity,
+                                   int64_t* n_segments, int64_t* head, int32_t* head_next);
+int cb200_torch_rand_device(const uint32_t* checkpoints, int64_t n_segments, int64_t blocks_per_segment, int64_t head, int32_t head_next,
+                            int64_t n, float* out, void* stream);
+int cb200_host_torch_rand_skip(uint8_t* state, int64_t n);
 
 /* test hook for the bit-exact sample-position gate: pts [P,3] and normalised x [P,3] exactly as the fused
  * kernels compute them (model/scene_rep.py:258 and :186) */

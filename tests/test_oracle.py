@@ -164,3 +164,37 @@ def test_host_torch_rand_is_the_cpu_generators_stream():
     torch.manual_seed(3)
     a2, b2, c2 = torch.randn(5), ops.torch_rand_into(torch.empty(4, 25)), torch.randn(3)
     assert torch.equal(a, a2) and torch.equal(b, b2) and torch.equal(c, c2)
+
+
+def test_host_torch_rand_skip_advances_the_generator_like_a_draw():
+    """cb200_host_torch_rand_skip (the host half of the device-side jitter stream, csrc/host_rng.cu): the generator state after
+    skipping n floats is the state after torch.rand(n), from fresh and mid-block states and across block boundaries."""
+    import ctypes
+    import torch
+    from coslam_b200 import _lib
+    lib = _lib.load()
+    for seed in (0, 7):
+        for warm, n in ((0, 1), (0, 624), (5, 619), (5, 620), (100, 3 * 624 + 17), (623, 1), (300, 1 << 20), (17, 0)):
+            torch.manual_seed(seed)
+            torch.rand(warm)
+            st = torch.get_rng_state()
+            torch.rand(n)
+            want, tail = torch.get_rng_state(), torch.rand(5)
+            assert lib.cb200_host_torch_rand_skip(ctypes.c_void_p(st.data_ptr()), ctypes.c_int64(n)) == 0
+            assert torch.equal(st, want), (seed, warm, n)
+            torch.set_rng_state(st)
+            assert torch.equal(torch.rand(5), tail)
+            # the checkpointing walk (cb200_host_torch_rand_segments) ends in the same state; its first checkpoint is the state at entry
+            torch.manual_seed(seed)
+            torch.rand(warm)
+            st2 = torch.get_rng_state()
+            words_at_entry = st2[24:24 + 8 * 624].clone().view(torch.int64).to(torch.int32)
+            ck = torch.zeros((n // (624 * 4) + 3, 624), dtype=torch.int32)
+            n_seg, head, head_next = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int32(0)
+            assert lib.cb200_host_torch_rand_segments(ctypes.c_void_p(st2.data_ptr()), ctypes.c_int64(n), ctypes.c_int64(4),
+                                                      ctypes.c_void_p(ck.data_ptr()), ctypes.c_int64(ck.shape[0]), ctypes.byref(n_seg),
+                                                      ctypes.byref(head), ctypes.byref(head_next)) == 0
+            assert torch.equal(st2, want) and torch.equal(ck[0], words_at_entry)
+            fresh = warm == 0
+            assert head.value == min(n, 0 if fresh else 624 - warm % 624 if warm % 624 else 0)
+            assert 1 <= n_seg.value <= ck.shape[0]

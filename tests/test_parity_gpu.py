@@ -1381,3 +1381,46 @@ def test_hash_backward_table_only_kernel_matches_general_kernel(order):
     torch.cuda.synchronize()
     assert float(d_b.abs().max()) > 0
     assert float((d_a - d_b).abs().max()) <= 2e-5 * float(d_b.abs().max())
+
+
+def test_device_jitter_stream_is_torch_rand():
+    """cb200_torch_rand_device + cb200_host_torch_rand_skip (csrc/host_rng.cu): the jitter the reference draws with
+    torch.rand(z_vals.shape) on the CPU generator and uploads (model/scene_rep.py:255), generated on the device instead -- the same
+    floats bit for bit and the same generator state afterwards, from fresh and mid-block states, across block boundaries, for a
+    large batch, and through ops.host_uniform (which switches to it at DEVICE_STREAM_MIN floats)."""
+    for seed in (0, 3):
+        for warm, n in ((0, 1), (0, 623), (0, 624), (0, 625), (5, 619), (5, 620), (77, 4 * 624), (623, 1000), (200, 1 << 21)):
+            torch.manual_seed(seed)
+            torch.rand(warm)
+            ref = torch.rand(n)
+            state_ref, tail_ref = torch.get_rng_state(), torch.randn(4)
+            torch.manual_seed(seed)
+            torch.rand(warm)
+            got = ops.device_uniform(n, torch.device(DEV))
+            assert got is not None
+            state, tail = torch.get_rng_state(), torch.randn(4)
+            assert torch.equal(got.cpu(), ref), (seed, warm, n)
+            assert torch.equal(state, state_ref) and torch.equal(tail, tail_ref)
+    chunk = ops.DEVICE_STREAM_CHUNK
+    try:                                                       # several host walks + launches per draw, heads in every chunk
+        ops.DEVICE_STREAM_CHUNK = 100003
+        torch.manual_seed(5)
+        torch.rand(11)
+        ref = torch.rand(1000003)
+        state_ref = torch.get_rng_state()
+        torch.manual_seed(5)
+        torch.rand(11)
+        got = ops.device_uniform(1000003, torch.device(DEV))
+        assert torch.equal(got.cpu(), ref) and torch.equal(torch.get_rng_state(), state_ref)
+    finally:
+        ops.DEVICE_STREAM_CHUNK = chunk
+    saved = ops.DEVICE_STREAM_MIN
+    try:
+        for ops.DEVICE_STREAM_MIN in (1, 1 << 40):             # device stream / host loop + pinned upload: the same tensor
+            torch.manual_seed(11)
+            a = ops.host_uniform((300, 43), DEV)
+            b = ops.host_uniform((1000, 43), DEV)
+            torch.manual_seed(11)
+            assert torch.equal(a.cpu(), torch.rand(300, 43)) and torch.equal(b.cpu(), torch.rand(1000, 43))
+    finally:
+        ops.DEVICE_STREAM_MIN = saved
