@@ -122,11 +122,12 @@ __device__ __forceinline__ void ray_forward(const RenderArgs& a, int64_t ray, in
     if (first == 0xffffffffu) first = 0;                       // argmax of an all-zero mask
     const float z_lim = __fadd_rn(zrow[first], a.trunc_sc);    // scene_rep.py:93-94
     float sum = 0.f;
+    const float inv_trunc = 1.0f / a.trunc;
 #pragma unroll
     for (int k = 0; k < kPerLane; ++k) {
         const int s = lane + 32 * k;
-        const float arg = st.raw[k].w / a.trunc;
-        const float sp = sigmoidf(arg), sn = sigmoidf(-arg);
+        const float arg = st.raw[k].w * inv_trunc;
+        const float sp = sigmoid_fast(arg), sn = sigmoid_fast(-arg);
         st.sa[k] = sp;
         st.bell[k] = sp * sn;
         st.keep[k] = (s < S) && (st.z[k] < z_lim);
@@ -139,9 +140,9 @@ __device__ __forceinline__ void ray_forward(const RenderArgs& a, int64_t ray, in
     for (int k = 0; k < kPerLane; ++k) {
         const float w = st.keep[k] ? st.bell[k] * st.inv_den : 0.f;
         st.wn[k] = w;
-        r += w * sigmoidf(st.raw[k].x);
-        g += w * sigmoidf(st.raw[k].y);
-        b += w * sigmoidf(st.raw[k].z);
+        r += w * sigmoid_fast(st.raw[k].x);
+        g += w * sigmoid_fast(st.raw[k].y);
+        b += w * sigmoid_fast(st.raw[k].z);
         dep += w * st.z[k];
         acc += w;
     }
@@ -254,19 +255,20 @@ __device__ __forceinline__ unsigned ray_backward_from_state(const RenderArgs& a,
     float dot = 0.f;
 #pragma unroll
     for (int k = 0; k < kPerLane; ++k) {
-        const float cr = sigmoidf(st.raw[k].x), cg = sigmoidf(st.raw[k].y), cb = sigmoidf(st.raw[k].z);
+        const float cr = sigmoid_fast(st.raw[k].x), cg = sigmoid_fast(st.raw[k].y), cb = sigmoid_fast(st.raw[k].z);
         gwn[k] = g_map[0] * cr + g_map[1] * cg + g_map[2] * cb + g_dep * st.z[k] + g_acc;
         dot += gwn[k] * st.wn[k];
     }
     dot = warp_sum(dot);
     const float front_edge = __fsub_rn(d, a.trunc_sc), back_edge = __fadd_rn(d, a.trunc_sc);
     float4* out = reinterpret_cast<float4*>(a.d_raw) + ray * S;
+    const float inv_trunc = 1.0f / a.trunc;
     unsigned live = 0;
 #pragma unroll
     for (int k = 0; k < kPerLane; ++k) {
         const int s = lane + 32 * k;
         if (s < S) {
-            const float cr = sigmoidf(st.raw[k].x), cg = sigmoidf(st.raw[k].y), cb = sigmoidf(st.raw[k].z);
+            const float cr = sigmoid_fast(st.raw[k].x), cg = sigmoid_fast(st.raw[k].y), cb = sigmoid_fast(st.raw[k].z);
             float4 o;
             o.x = g_map[0] * st.wn[k] * cr * (1.f - cr);
             o.y = g_map[1] * st.wn[k] * cg * (1.f - cg);
@@ -275,7 +277,7 @@ __device__ __forceinline__ unsigned ray_backward_from_state(const RenderArgs& a,
             float gs = 0.f;
             if (st.keep[k]) {
                 const float g_bell = (gwn[k] - dot) * st.inv_den;
-                gs = g_bell * st.bell[k] * (1.f - 2.f * st.sa[k]) / a.trunc;
+                gs = g_bell * st.bell[k] * (1.f - 2.f * st.sa[k]) * inv_trunc;
             }
             if (a.has_loss) {
                 const float z = st.z[k], sdf = st.raw[k].w;
