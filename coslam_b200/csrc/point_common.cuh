@@ -4,22 +4,46 @@
 
 namespace cb200 {
 
-// position of point p in the unit cube (model/scene_rep.py:258, :186); z_out = its ray parameter (0 for explicit points)
-__device__ __forceinline__ void point_position(const PointsArgs& a, int64_t p, float x[3], float& z_out) {
-    float pt[3];
+// position of point p in the unit cube (model/scene_rep.py:258, :186); z_out = its ray parameter (0 for explicit points).
+// Split into the global loads and the arithmetic so that a tile loop can issue the loads of its NEXT tile's points early (the chain
+// list entry -> ray / sample -> position is three dependent global loads: ~6 % of the forward's warp-stall samples when it sits at
+// the top of a tile, profiles/r2/NOTES.md section 19).
+struct PointLoads {
+    float o[3], d[3], z;      // ray mode: origin, direction, ray parameter; explicit points: o = the point
+};
+
+__device__ __forceinline__ void point_loads(const PointsArgs& a, int64_t p, PointLoads& L) {
     if (a.rays_o) {
         const int64_t ray = p / a.n_samples;
-        const float z = a.z[p];
-        z_out = z;
+        L.z = a.z[p];
 #pragma unroll
-        for (int d = 0; d < 3; ++d) pt[d] = ray_point(a.rays_o[ray * 3 + d], a.rays_d[ray * 3 + d], z);
+        for (int d = 0; d < 3; ++d) {
+            L.o[d] = a.rays_o[ray * 3 + d];
+            L.d[d] = a.rays_d[ray * 3 + d];
+        }
     } else {
-        z_out = 0.f;
+        L.z = 0.f;
 #pragma unroll
-        for (int d = 0; d < 3; ++d) pt[d] = a.pts[p * 3 + d];
+        for (int d = 0; d < 3; ++d) {
+            L.o[d] = a.pts[p * 3 + d];
+            L.d[d] = 0.f;
+        }
     }
+}
+
+__device__ __forceinline__ void point_from_loads(const PointsArgs& a, const PointLoads& L, float x[3], float& z_out) {
+    float pt[3];
+    z_out = L.z;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) pt[d] = a.rays_o ? ray_point(L.o[d], L.d[d], L.z) : L.o[d];
 #pragma unroll
     for (int d = 0; d < 3; ++d) x[d] = a.scene.normalise ? box_normalise(pt[d], a.scene.bb_lo[d], a.scene.bb_ext[d]) : pt[d];
+}
+
+__device__ __forceinline__ void point_position(const PointsArgs& a, int64_t p, float x[3], float& z_out) {
+    PointLoads L;
+    point_loads(a, p, L);
+    point_from_loads(a, L, x, z_out);
 }
 
 struct LevelCorners {

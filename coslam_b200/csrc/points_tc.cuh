@@ -372,19 +372,31 @@ __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char
 #else
 #define PH(i)
 #endif
+    // gather-role point of a tile: list slot -> point -> (ray, sample) -> position is a chain of dependent global loads.  The first
+    // tile's is resolved here; every later one is started while the previous tile sits in its MMA rounds (index after the first MMA
+    // has been issued, ray / sample values after the second) and finished at the end of that tile.
+    auto gather_point_of = [&](int64_t t) -> int64_t {
+        const int64_t raw = t * kTile + row_g;
+        const int64_t slot = raw < n_slots ? raw : n_slots - 1;      // padding slots repeat the last point: same values
+        return list ? (int64_t)list[slot] : slot;
+    };
+    int64_t pg = 0;
+    float x[3] = {0.f, 0.f, 0.f};
+    if (tile_begin < n_tiles) {
+        float zdummy;
+        pg = gather_point_of(tile_begin);
+        point_position(a, pg, x, zdummy);
+    }
     for (int64_t tile = tile_begin; tile < n_tiles; tile += tile_step) {
         const int64_t p_raw = tile * kTile + row;
         const bool valid = p_raw < n_slots;
         const int64_t p_slot = valid ? p_raw : n_slots - 1;
         const int64_t p = list ? (int64_t)list[p_slot] : p_slot;
+        const bool has_next = tile + tile_step < n_tiles;
+        int64_t pg_next = 0;
+        PointLoads next_loads;
         PH(7);
         {
-            const int64_t pg_raw = tile * kTile + row_g;
-            const int64_t pg_slot = pg_raw < n_slots ? pg_raw : n_slots - 1;
-            const int64_t pg = list ? (int64_t)list[pg_slot] : pg_slot;
-            float x[3], zdummy;
-            point_position(a, pg, x, zdummy);
-            // padding slots repeat the last point: same values
             float* const keep = (kJac || a.feat) ? a.feat + pg * a.feat_stride : nullptr;
 #pragma unroll
 #ifdef CB200_PHASE_CLOCKS
@@ -409,6 +421,7 @@ __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char
                         umma_idesc_bf16(128, 32, false, false), false);
             umma_commit(&bar);
         }
+        if (has_next) pg_next = gather_point_of(tile + tile_step);
         TC_WAIT();
         PH(3);
         uint32_t m1;
@@ -425,6 +438,7 @@ __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char
                         umma_idesc_bf16(128, 16, false, false), false);
             umma_commit(&bar);
         }
+        if (has_next) point_loads(a, pg_next, next_loads);
         TC_WAIT();
         float sdf;
         {
@@ -490,6 +504,11 @@ __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char
                 mask16[p * 4 + half] = (uint16_t)m1;
                 mask16[p * 4 + 2 + half] = (uint16_t)m3;
             }
+        }
+        if (has_next) {
+            float zdummy;
+            point_from_loads(a, next_loads, x, zdummy);
+            pg = pg_next;
         }
         tc_fence_before();
         __syncthreads();
@@ -576,11 +595,22 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
 
     // with a compacted list the tiles run over the live points only (slot i -> point live_idx[i])
     const int64_t n_tiles = (n_slots + kTile - 1) / kTile;
+    // The two pointer chases of a tile are taken off its critical path (~5 % of this kernel's warp-stall samples sat on them):
+    // the epilogue-role point of the NEXT tile is read from the list while this tile runs, and this tile's gather-role point is
+    // resolved during the MMA rounds of step (1) -- index at the top, ray / sample values after round b -- instead of in front of step (2).
+    auto point_of = [&](int64_t t, int r) -> int64_t {
+        const int64_t raw = t * kTile + r;
+        const int64_t slot = raw < n_slots ? raw : n_slots - 1;
+        return list ? (int64_t)list[slot] : slot;
+    };
+    int64_t p_ahead = tile_begin < n_tiles ? point_of(tile_begin, row) : 0;
     for (int64_t tile = tile_begin; tile < n_tiles; tile += tile_step) {
         const int64_t p_raw = tile * kTile + row;
         const bool valid = p_raw < n_slots;
-        const int64_t p_slot = valid ? p_raw : n_slots - 1;
-        const int64_t p = list ? (int64_t)list[p_slot] : p_slot;
+        const int64_t p = p_ahead;
+        const int64_t pg_raw = tile * kTile + row_g;
+        const bool valid_g = pg_raw < n_slots;
+        const int64_t pg = point_of(tile, row_g);
 
         // ---- (1) input-gradient chain (epilogue role: 16 columns per thread) --------------------------------------------
         float4 g = reinterpret_cast<const float4*>(a.d_raw)[p];
@@ -609,6 +639,9 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
                         umma_idesc_bf16(128, 64, false, true), false);
             umma_commit(&bar);
         }
+        if (tile + tile_step < n_tiles) p_ahead = point_of(tile + tile_step, row);
+        PointLoads g_loads;
+        point_loads(a, pg, g_loads);
         TC_WAIT();
         {
             uint32_t r[16];
@@ -657,13 +690,9 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
         TC_WAIT();
 
         // ---- (2) one gather pass (gather role: lane pair per point): dL/dx, table scatter, features ---------------------
-        const int64_t pg_raw = tile * kTile + row_g;
-        const bool valid_g = pg_raw < n_slots;
-        const int64_t pg_slot = valid_g ? pg_raw : n_slots - 1;
-        const int64_t pg = list ? (int64_t)list[pg_slot] : pg_slot;
         const bool live = valid_g && !((dead >> src_lane) & 1u);
         float x[3], zray;
-        point_position(a, pg, x, zray);
+        point_from_loads(a, g_loads, x, zray);
         float dx[3] = {0.f, 0.f, 0.f};
 #pragma unroll 1
         for (int c = 0; c < 4; ++c) {
