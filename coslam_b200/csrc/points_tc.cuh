@@ -598,19 +598,19 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
     // The two pointer chases of a tile are taken off its critical path (~5 % of this kernel's warp-stall samples sat on them):
     // the epilogue-role point of the NEXT tile is read from the list while this tile runs, and this tile's gather-role point is
     // resolved during the MMA rounds of step (1) -- index at the top, ray / sample values after round b -- instead of in front of step (2).
-    auto point_of = [&](int64_t t, int r) -> int64_t {
+    auto slot_of = [&](int64_t t, int r) -> int64_t {
         const int64_t raw = t * kTile + r;
-        const int64_t slot = raw < n_slots ? raw : n_slots - 1;
-        return list ? (int64_t)list[slot] : slot;
+        return raw < n_slots ? raw : n_slots - 1;
     };
-    int64_t p_ahead = tile_begin < n_tiles ? point_of(tile_begin, row) : 0;
+    // (one register: list entries are 32-bit; without a list the point is its slot and needs no load)
+    uint32_t p_ahead = (list && tile_begin < n_tiles) ? list[slot_of(tile_begin, row)] : 0u;
     for (int64_t tile = tile_begin; tile < n_tiles; tile += tile_step) {
         const int64_t p_raw = tile * kTile + row;
         const bool valid = p_raw < n_slots;
-        const int64_t p = p_ahead;
+        const int64_t p = list ? (int64_t)p_ahead : slot_of(tile, row);
         const int64_t pg_raw = tile * kTile + row_g;
         const bool valid_g = pg_raw < n_slots;
-        const int64_t pg = point_of(tile, row_g);
+        const uint32_t pg_entry = list ? list[slot_of(tile, row_g)] : 0u;
 
         // ---- (1) input-gradient chain (epilogue role: 16 columns per thread) --------------------------------------------
         float4 g = reinterpret_cast<const float4*>(a.d_raw)[p];
@@ -639,9 +639,7 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
                         umma_idesc_bf16(128, 64, false, true), false);
             umma_commit(&bar);
         }
-        if (tile + tile_step < n_tiles) p_ahead = point_of(tile + tile_step, row);
-        PointLoads g_loads;
-        point_loads(a, pg, g_loads);
+        if (list && tile + tile_step < n_tiles) p_ahead = list[slot_of(tile + tile_step, row)];
         TC_WAIT();
         {
             uint32_t r[16];
@@ -672,6 +670,9 @@ __device__ __forceinline__ void bwd_tile_loop(const PointsArgs& a, unsigned char
                         umma_idesc_bf16(128, 32, false, true), false);
             umma_commit(&bar);
         }
+        const int64_t pg = list ? (int64_t)pg_entry : slot_of(tile, row_g);
+        PointLoads g_loads;
+        point_loads(a, pg, g_loads);                  // consumed behind round d: two MMA rounds of latency cover them
         TC_WAIT();
         {
             uint32_t r[16];
