@@ -199,11 +199,12 @@ __device__ __forceinline__ void pair_combine_keep(const float (&part)[8], int xb
 // [chunk c][feat | d/dx | d/dy | d/dz][thread xb][columns 8c + 4xb .. + 3] -- so that every store (and every load of the backward) of a
 // lane pair is one whole 32-byte sector; they come from the corner values that are in registers anyway.
 // kGS: group stride of the tile the features go to (the warp-specialised forward keeps them in a [128 x 32] tile of its own)
-template <int kDense, bool kJac, uint32_t kGS = kAGS>
-__device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row,
-                                                  float* keep
+// between(): independent work issued while the chunk's 16 gathers are in flight (the forward puts one coordinate's OneBlob there)
+template <int kDense, bool kJac, uint32_t kGS, typename Between>
+__device__ __forceinline__ void encode_grid_chunk_with(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row,
+                                                       float* keep, Between&& between
 #ifdef CB200_PHASE_CLOCKS
-                                                  , long long* sub
+                                                       , long long* sub
 #endif
 ) {
 #ifdef CB200_PHASE_CLOCKS
@@ -213,6 +214,7 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
     float wx[4], w1[4], w2[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) gather_level_x<kDense>(a, 4 * c + q, x, xb, v[q], wx[q], w1[q], w2[q]);
+    between();
 #ifdef CB200_PHASE_CLOCKS
     long long t1 = clock64();
     {
@@ -262,6 +264,20 @@ __device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const flo
 #ifdef CB200_PHASE_CLOCKS
     long long t3 = clock64();
     sub[0] += t1 - t0; sub[1] += t2 - t1; sub[2] += t3 - t2;
+#endif
+}
+
+template <int kDense, bool kJac, uint32_t kGS = kAGS>
+__device__ __forceinline__ void encode_grid_chunk(const PointsArgs& a, const float x[3], int xb, int c, uint32_t a_hi, uint32_t a_lo, int row,
+                                                  float* keep
+#ifdef CB200_PHASE_CLOCKS
+                                                  , long long* sub
+#endif
+) {
+#ifdef CB200_PHASE_CLOCKS
+    encode_grid_chunk_with<kDense, kJac, kGS>(a, x, xb, c, a_hi, a_lo, row, keep, [] {}, sub);
+#else
+    encode_grid_chunk_with<kDense, kJac, kGS>(a, x, xb, c, a_hi, a_lo, row, keep, [] {});
 #endif
 }
 
@@ -398,18 +414,26 @@ __device__ __forceinline__ void fwd_tile_loop(const PointsArgs& a, unsigned char
         PH(7);
         {
             float* const keep = (kJac || a.feat) ? a.feat + pg * a.feat_stride : nullptr;
-#pragma unroll
-#ifdef CB200_PHASE_CLOCKS
-            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense, kJac>(a, x, xb, c, a_hi, a_lo, row_g, keep, sub);
-#else
-            for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense, kJac>(a, x, xb, c, a_hi, a_lo, row_g, keep);
-#endif
-            PH(0);
-#pragma unroll
-            for (int d = 0; d < 3; ++d) {             // OneBlob: thread xb does bins 8 xb .. 8 xb + 7 of every coordinate
+            // OneBlob (thread xb does bins 8 xb .. 8 xb + 7 of every coordinate) is pure arithmetic: one coordinate goes into the shadow of
+            // each of the level chunks 1..3, between the issue of the chunk's 16 gathers and their first use (forward 2.69 -> 2.56 ms at 2^18
+            // rays).  Not when the derivative rows are kept as well: that chunk body has no register to spare (3.41 -> 3.51 ms, a spill).
+            auto blob_coordinate = [&](int d) {
                 float v[8], unused[8];
                 blob_half<false>(x[d], xb, v, unused);
                 tile_store8(a_hi, a_lo, kAGS, row_g, 4 + 2 * d + xb, v);
+            };
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+#ifdef CB200_PHASE_CLOCKS
+                encode_grid_chunk_with<kDense, kJac, kAGS>(a, x, xb, c, a_hi, a_lo, row_g, keep, [&] { if (!kJac && c >= 1) blob_coordinate(c - 1); }, sub);
+#else
+                encode_grid_chunk_with<kDense, kJac, kAGS>(a, x, xb, c, a_hi, a_lo, row_g, keep, [&] { if (!kJac && c >= 1) blob_coordinate(c - 1); });
+#endif
+            }
+            PH(0);
+            if (kJac) {
+#pragma unroll
+                for (int d = 0; d < 3; ++d) blob_coordinate(d);
             }
             PH(1);
         }
