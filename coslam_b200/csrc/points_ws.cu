@@ -72,8 +72,14 @@ __device__ __forceinline__ void ws_gather_role(const PointsArgs& a, uint32_t hba
         WSC(t_grid);
         if (k >= 2) mbar_wait(&B[kBarGFree + b], (uint32_t)(((k >> 1) + 1) & 1));      // layer 1 of tile k - 2 has read G[b]
         WSC(t_wait);
+#ifdef CB200_PHASE_CLOCKS
+        long long sub_unused[3] = {0, 0, 0};      // the one-role kernel's per-chunk clocks (tools/phase_probe.py); this kernel has its own
+#pragma unroll
+        for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense, kJac, kGGS>(a, x, xb, c, g_hi, g_lo, row_g, keep, sub_unused);
+#else
 #pragma unroll
         for (int c = 0; c < 4; ++c) encode_grid_chunk<kDense, kJac, kGGS>(a, x, xb, c, g_hi, g_lo, row_g, keep);
+#endif
         WSC(t_grid);
         if (k >= 1) mbar_wait(&B[kBarBGFree], (uint32_t)((k - 1) & 1));                  // tile k - 1 is done with BG
         WSC(t_wait);
